@@ -1,0 +1,257 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes binding of oracle/_ref/libpgenref.so.
+
+libpgenref.so is the reference's own pgenlib (compiled by oracle/Makefile from the sources
+under /root/reference, never copied) plus oracle/ref_harness.cc.  Only tests/,
+__graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "_ref", "libpgenref.so")
+
+_lib = None
+
+
+def available() -> bool:
+    return os.path.exists(_SO)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not available():
+            raise RuntimeError(f"{_SO} missing: run `make -C oracle ref` where /root/reference exists")
+        L = C.CDLL(_SO)
+        vp, u32, u64, i32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int32
+        L.ref_open.argtypes = [C.c_char_p, C.POINTER(vp), C.c_char_p, C.c_size_t]
+        L.ref_open.restype = C.c_int
+        L.ref_close.argtypes = [vp]
+        L.ref_info.argtypes = [vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]
+        L.ref_vrtype.argtypes = [vp, u32]
+        L.ref_vrtype.restype = u32
+        L.ref_fpos.argtypes = [vp, u32]
+        L.ref_fpos.restype = u64
+        L.ref_set_subset.argtypes = [vp, vp, u32]
+        L.ref_counts.argtypes = [vp, u32, u32, vp]
+        L.ref_dcounts.argtypes = [vp, u32, u32, vp, vp, vp]
+        L.ref_decode_i8.argtypes = [vp, u32, u32, vp]
+        L.ref_missingness.argtypes = [vp, u32, u32, vp, vp]
+        L.ref_dosage.argtypes = [vp, u32, vp, C.POINTER(u32)]
+        L.ref_score.argtypes = [vp, vp, vp, vp, u32, u32, vp, vp, vp]
+        L.ref_sample_counts.argtypes = [vp, u32, u32, u32, vp, vp, vp]
+        L.ref_hwe_lnp.argtypes = [i32, i32, i32, u32]
+        L.ref_hwe_lnp.restype = C.c_double
+        L.ref_hwe_xchr_lnp.argtypes = [i32, i32, i32, i32, i32, u32]
+        L.ref_hwe_xchr_lnp.restype = C.c_double
+        L.ref_hwe_lnp_batch.argtypes = [vp, u32, u32, vp]
+        L.ref_bench_scan.argtypes = [C.c_char_p, u32, u32, u32, u32, C.POINTER(u64)]
+        L.ref_bench_scan.restype = C.c_double
+        L.ref_bench_score.argtypes = [C.c_char_p, u32, vp, vp, vp, u32, u32, vp, vp]
+        L.ref_bench_score.restype = C.c_double
+        L.ref_writer_open.argtypes = [C.c_char_p, u32, u32, u32, C.POINTER(vp)]
+        L.ref_writer_append.argtypes = [vp, vp]
+        L.ref_writer_append_dosage.argtypes = [vp, vp, vp, vp, u32]
+        L.ref_writer_close.argtypes = [vp]
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class RefPgen:
+    """One pgenlib reader (PgenFileInfo + PgenReader), as each DuckDB scan thread owns."""
+
+    def __init__(self, path: str):
+        self._h = C.c_void_p()
+        err = C.create_string_buffer(512)
+        rc = lib().ref_open(os.fsencode(path), C.byref(self._h), err, 512)
+        if rc:
+            raise IOError(f"ref_open({path}) failed rc={rc}: {err.value.decode(errors='replace')}")
+        self._refresh()
+
+    def _refresh(self):
+        V, N, S = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        lib().ref_info(self._h, C.byref(V), C.byref(N), C.byref(S))
+        self.V, self.N, self.sample_ct = V.value, N.value, S.value
+
+    def close(self):
+        if self._h:
+            lib().ref_close(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def vrtypes(self) -> np.ndarray:
+        return np.array([lib().ref_vrtype(self._h, v) for v in range(self.V)], dtype=np.uint8)
+
+    def fpos(self) -> np.ndarray:
+        return np.array([lib().ref_fpos(self._h, v) for v in range(self.V + 1)], dtype=np.uint64)
+
+    def set_subset(self, idx):
+        if idx is None:
+            lib().ref_set_subset(self._h, None, 0)
+        else:
+            a = np.ascontiguousarray(np.sort(np.asarray(idx, dtype=np.uint32)))
+            lib().ref_set_subset(self._h, _p(a), a.size)
+        self._refresh()
+
+    def _rng(self, v0, v1):
+        v1 = self.V if v1 is None else v1
+        return v0, v1
+
+    def counts(self, v0=0, v1=None) -> np.ndarray:
+        v0, v1 = self._rng(v0, v1)
+        out = np.zeros((v1 - v0, 4), dtype=np.uint32)
+        rc = lib().ref_counts(self._h, v0, v1, _p(out))
+        if rc:
+            raise IOError(f"PgrGetCounts rc={rc}")
+        return out
+
+    def dcounts(self, v0=0, v1=None):
+        v0, v1 = self._rng(v0, v1)
+        n = v1 - v0
+        counts = np.zeros((n, 4), dtype=np.uint32)
+        ad = np.zeros((n, 2), dtype=np.uint64)
+        r2 = np.zeros(n, dtype=np.float64)
+        rc = lib().ref_dcounts(self._h, v0, v1, _p(counts), _p(ad), _p(r2))
+        if rc:
+            raise IOError(f"PgrGetDCounts rc={rc}")
+        return counts, ad, r2
+
+    def decode_i8(self, v0=0, v1=None) -> np.ndarray:
+        v0, v1 = self._rng(v0, v1)
+        out = np.zeros((v1 - v0, self.sample_ct), dtype=np.int8)
+        rc = lib().ref_decode_i8(self._h, v0, v1, _p(out))
+        if rc:
+            raise IOError(f"PgrGet rc={rc}")
+        return out
+
+    def missingness(self, v0=0, v1=None):
+        v0, v1 = self._rng(v0, v1)
+        pv = np.zeros(v1 - v0, dtype=np.uint32)
+        ps = np.zeros(self.sample_ct, dtype=np.uint32)
+        rc = lib().ref_missingness(self._h, v0, v1, _p(pv), _p(ps))
+        if rc:
+            raise IOError(f"PgrGetMissingness rc={rc}")
+        return pv, ps
+
+    def dosage(self, vidx: int) -> np.ndarray:
+        out = np.zeros(self.sample_ct, dtype=np.float64)
+        ct = C.c_uint32()
+        rc = lib().ref_dosage(self._h, vidx, _p(out), C.byref(ct))
+        if rc:
+            raise IOError(f"PgrGetD rc={rc}")
+        return out
+
+    def score(self, vidx, flip, weight, mode=0):
+        vidx = np.ascontiguousarray(vidx, dtype=np.uint32)
+        flip = np.ascontiguousarray(flip, dtype=np.uint8)
+        weight = np.ascontiguousarray(weight, dtype=np.float64)
+        s = np.zeros(self.sample_ct, dtype=np.float64)
+        d = np.zeros(self.sample_ct, dtype=np.float64)
+        a = np.zeros(self.sample_ct, dtype=np.uint32)
+        rc = lib().ref_score(self._h, _p(vidx), _p(flip), _p(weight), vidx.size, mode, _p(s), _p(d), _p(a))
+        if rc:
+            raise IOError(f"ref_score rc={rc}")
+        return s, d, a
+
+    def sample_counts(self, v0=0, v1=None, sparse=False):
+        v0, v1 = self._rng(v0, v1)
+        het = np.zeros(self.sample_ct, dtype=np.uint32)
+        hom_alt = np.zeros(self.sample_ct, dtype=np.uint32)
+        missing = np.zeros(self.sample_ct, dtype=np.uint32)
+        rc = lib().ref_sample_counts(self._h, v0, v1, int(sparse), _p(het), _p(hom_alt), _p(missing))
+        if rc:
+            raise IOError(f"ref_sample_counts rc={rc}")
+        return het, hom_alt, missing
+
+
+def hwe_lnp(hets, hom1, hom2, midp=False) -> float:
+    return lib().ref_hwe_lnp(int(hets), int(hom1), int(hom2), int(bool(midp)))
+
+
+def hwe_xchr_lnp(fhets, fhom1, fhom2, male1, male2, midp=False) -> float:
+    return lib().ref_hwe_xchr_lnp(int(fhets), int(fhom1), int(fhom2), int(male1), int(male2), int(bool(midp)))
+
+
+def hwe_lnp_batch(counts: np.ndarray, midp=False) -> np.ndarray:
+    counts = np.ascontiguousarray(counts, dtype=np.uint32)
+    out = np.zeros(counts.shape[0], dtype=np.float64)
+    lib().ref_hwe_lnp_batch(_p(counts), counts.shape[0], int(bool(midp)), _p(out))
+    return out
+
+
+def lnp_to_pvalue(lnp):
+    """LnPToPvalue, src/plink_hardy.cpp:52-64."""
+    lnp = np.asarray(lnp, dtype=np.float64)
+    p = np.exp(lnp)
+    p = np.where(np.isnan(lnp), 1.0, np.clip(p, 0.0, 1.0))
+    return p
+
+
+def bench_scan(path, threads, v0, v1, kind):
+    cs = C.c_uint64()
+    t = lib().ref_bench_scan(os.fsencode(path), threads, v0, v1, kind, C.byref(cs))
+    if t < 0:
+        raise IOError("ref_bench_scan: open failed")
+    return t, cs.value
+
+
+def bench_score(path, threads, vidx, flip, weights):
+    vidx = np.ascontiguousarray(vidx, dtype=np.uint32)
+    flip = np.ascontiguousarray(flip, dtype=np.uint8)
+    weights = np.ascontiguousarray(weights, dtype=np.float64)
+    n, K = weights.shape
+    with RefPgen(path) as r:
+        N = r.N
+    sums = np.zeros((N, K), dtype=np.float64)
+    cts = np.zeros(N, dtype=np.uint32)
+    t = lib().ref_bench_score(os.fsencode(path), threads, _p(vidx), _p(flip), _p(weights), n, K, _p(sums), _p(cts))
+    if t < 0:
+        raise IOError("ref_bench_score: open failed")
+    return t, sums, cts
+
+
+def write_pgen(path: str, genovecs: np.ndarray, N: int, dosage=None):
+    """Write a variable-width (mode 0x10) .pgen with pgenlib's own writer.
+
+    genovecs: (V, ceil(N/32)) uint64, 2-bit codes, trailing bits zero.
+    dosage:   optional list of (present_bits uint64[ceil(N/64)], u16 values) per variant or None.
+    """
+    genovecs = np.ascontiguousarray(genovecs, dtype=np.uint64)
+    V = genovecs.shape[0]
+    h = C.c_void_p()
+    rc = lib().ref_writer_open(os.fsencode(path), V, N, 1 if dosage is not None else 0, C.byref(h))
+    if rc:
+        raise IOError(f"SpgwInitPhase1 rc={rc}")
+    for v in range(V):
+        row = np.ascontiguousarray(genovecs[v])
+        if dosage is not None and dosage[v] is not None:
+            pres, vals = dosage[v]
+            pres = np.ascontiguousarray(pres, dtype=np.uint64)
+            vals = np.ascontiguousarray(vals, dtype=np.uint16)
+            rc = lib().ref_writer_append_dosage(h, _p(row), _p(pres), _p(vals), vals.size)
+        else:
+            rc = lib().ref_writer_append(h, _p(row))
+        if rc:
+            raise IOError(f"SpgwAppend rc={rc} at variant {v}")
+    rc = lib().ref_writer_close(h)
+    if rc:
+        raise IOError(f"SpgwFinish rc={rc}")
