@@ -166,6 +166,10 @@ struct Writer {
   STPgenWriter spgw;
   unsigned char* alloc = nullptr;
   uint32_t N = 0;
+  // vector-aligned, zero-padded copies of the caller's arrays (pgenlib reads whole vectors)
+  uintptr_t* genovec = nullptr;
+  uintptr_t* dosage_present = nullptr;
+  uint16_t* dosage_main = nullptr;
 };
 
 }  // namespace
@@ -571,22 +575,37 @@ int ref_writer_open(const char* path, uint32_t V, uint32_t N, uint32_t dosage, v
   }
   SpgwInitPhase2(max_vrec_len, &w->spgw, w->alloc);
   w->N = N;
+  cachealigned_malloc(RoundUpPow2(NypCtToAlignedWordCt(N) * sizeof(uintptr_t) + 64, kCacheline), &w->genovec);
+  cachealigned_malloc(RoundUpPow2(BitCtToAlignedWordCt(N) * sizeof(uintptr_t) + 64, kCacheline), &w->dosage_present);
+  cachealigned_malloc(RoundUpPow2((static_cast<uintptr_t>(N) + 64) * sizeof(uint16_t), kCacheline), &w->dosage_main);
   *out = w;
   return 0;
+}
+
+static void StageGenovec(Writer* w, const uint64_t* genovec) {
+  const uintptr_t aligned_words = NypCtToAlignedWordCt(w->N);
+  memset(w->genovec, 0, aligned_words * sizeof(uintptr_t));
+  memcpy(w->genovec, genovec, NypCtToWordCt(w->N) * sizeof(uintptr_t));
+  ZeroTrailingNyps(w->N, w->genovec);
 }
 
 // genovec: ceil(N/32) 64-bit words, trailing bits zero.
 int ref_writer_append(void* h, const uint64_t* genovec) {
   Writer* w = static_cast<Writer*>(h);
-  return static_cast<int>(SpgwAppendBiallelicGenovec(reinterpret_cast<const uintptr_t*>(genovec), &w->spgw));
+  StageGenovec(w, genovec);
+  return static_cast<int>(SpgwAppendBiallelicGenovec(w->genovec, &w->spgw));
 }
 
 int ref_writer_append_dosage(void* h, const uint64_t* genovec, const uint64_t* dosage_present,
                              const uint16_t* dosage_main, uint32_t dosage_ct) {
   Writer* w = static_cast<Writer*>(h);
-  return static_cast<int>(SpgwAppendBiallelicGenovecDosage16(reinterpret_cast<const uintptr_t*>(genovec),
-                                                             reinterpret_cast<const uintptr_t*>(dosage_present),
-                                                             dosage_main, dosage_ct, &w->spgw));
+  StageGenovec(w, genovec);
+  const uintptr_t aligned_words = BitCtToAlignedWordCt(w->N);
+  memset(w->dosage_present, 0, aligned_words * sizeof(uintptr_t));
+  memcpy(w->dosage_present, dosage_present, BitCtToWordCt(w->N) * sizeof(uintptr_t));
+  memcpy(w->dosage_main, dosage_main, static_cast<size_t>(dosage_ct) * sizeof(uint16_t));
+  return static_cast<int>(SpgwAppendBiallelicGenovecDosage16(w->genovec, w->dosage_present, w->dosage_main, dosage_ct,
+                                                             &w->spgw));
 }
 
 int ref_writer_close(void* h) {
@@ -595,6 +614,9 @@ int ref_writer_close(void* h) {
   PglErr ce = kPglRetSuccess;
   CleanupSpgw(&w->spgw, &ce);
   aligned_free_cond(w->alloc);
+  aligned_free_cond(w->genovec);
+  aligned_free_cond(w->dosage_present);
+  aligned_free_cond(w->dosage_main);
   delete w;
   return static_cast<int>(e);
 }

@@ -1,0 +1,99 @@
+"""ctypes binding of libplinkgpu.so (include/plinkgpu.h).
+
+This is the same binding a reference maintainer would write against the C ABI; there is no
+Python or CPU fallback behind it: a missing library or a missing GPU raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libplinkgpu.so")
+
+PD_OK = 0
+PD_ERR_OPEN, PD_ERR_READ, PD_ERR_MALFORMED, PD_ERR_NOT_SUPPORTED = 1, 2, 3, 4
+PD_ERR_NOMEM, PD_ERR_INVALID_ARG, PD_ERR_CUDA = 5, 6, 7
+ERR_NAMES = {
+    1: "PD_ERR_OPEN", 2: "PD_ERR_READ", 3: "PD_ERR_MALFORMED", 4: "PD_ERR_NOT_SUPPORTED",
+    5: "PD_ERR_NOMEM", 6: "PD_ERR_INVALID_ARG", 7: "PD_ERR_CUDA",
+}
+
+
+class OpenOpts(C.Structure):
+    _fields_ = [("device", C.c_int32), ("tile_bytes", C.c_uint64), ("n_staging", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class Info(C.Structure):
+    _fields_ = [
+        ("variant_ct", C.c_uint32), ("sample_ct", C.c_uint32), ("mode", C.c_uint32), ("fixed_width", C.c_uint32),
+        ("has_ld", C.c_uint32), ("has_difflist", C.c_uint32), ("has_dosage", C.c_uint32), ("has_phase", C.c_uint32),
+        ("has_multiallelic", C.c_uint32), ("resident", C.c_uint32), ("data_bytes", C.c_uint64),
+        ("resident_bytes", C.c_uint64),
+    ]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("launches", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("record_bytes", C.c_uint64),
+        ("kernel_ms", C.c_double), ("aux_kernel_ms", C.c_double), ("total_ms", C.c_double),
+        ("scan_launches", C.c_uint64),
+    ]
+
+
+# Every symbol include/plinkgpu.h declares: (name, restype, argtypes)
+_vp, _u32, _u64 = C.c_void_p, C.c_uint32, C.c_uint64
+SYMBOLS = {
+    "pd_open": (C.c_int, [C.c_char_p, C.POINTER(OpenOpts), C.POINTER(_vp), C.c_char_p, C.c_size_t]),
+    "pd_open_mem": (C.c_int, [_vp, _u64, _vp, _u64, C.POINTER(OpenOpts), C.POINTER(_vp), C.c_char_p, C.c_size_t]),
+    "pd_probe": (C.c_int, [C.c_char_p, C.POINTER(Info), _vp, _vp, _u32, C.c_char_p, C.c_size_t]),
+    "pd_close": (None, [_vp]),
+    "pd_last_error": (C.c_char_p, [_vp]),
+    "pd_info": (C.c_int, [_vp, C.POINTER(Info)]),
+    "pd_index": (C.c_int, [_vp, _vp, _vp]),
+    "pd_load_resident": (C.c_int, [_vp, _u32, _u32]),
+    "pd_unload": (C.c_int, [_vp]),
+    "pd_set_sample_subset": (C.c_int, [_vp, _vp, _u32]),
+    "pd_counts": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "pd_counts_masked": (C.c_int, [_vp, _u32, _u32, _vp, _vp]),
+    "pd_counts_start": (C.c_int, [_vp, _u32, _u32, C.POINTER(_vp)]),
+    "pd_counts_fetch": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "pd_job_free": (None, [_vp]),
+    "pd_hardy": (C.c_int, [_vp, _u32, _u32, _u32, _vp, _vp]),
+    "pd_hwe_from_counts": (C.c_int, [_vp, _vp, _u32, _u32, _vp]),
+    "pd_missing_by_sample": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "pd_sample_counts": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),
+    "pd_decode_i8": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "pd_dosage_f64": (C.c_int, [_vp, _vp, _u32, _vp]),
+    "pd_dosage_counts": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),
+    "pd_score": (C.c_int, [_vp, _vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
+    "pd_get_stats": (C.c_int, [_vp, C.POINTER(Stats)]),
+    "pd_reset_stats": (C.c_int, [_vp]),
+    "pd_version": (C.c_char_p, []),
+}
+
+_lib = None
+
+
+def load():
+    """Load libplinkgpu.so; raises if it has not been built (python __graft_entry__.py build)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} not found: the CUDA extension is required (no CPU fallback). "
+                "Build it with `make -C plinking_duck_b200/csrc`."
+            )
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(lib, name)  # AttributeError if the library does not export it
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+class PlinkGpuError(IOError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"{ERR_NAMES.get(code, code)}: {msg}")
+        self.code = code

@@ -1,0 +1,304 @@
+// Context management, HBM residency and the pinned double-buffered staging pipeline.
+//
+// What the reference does per scan thread -- fopen + fseeko + fread_unlocked per variant record
+// into a private buffer (InitReadPtrs, pgenlib_read.cc:2763-2802) -- becomes: contiguous record
+// ranges ("tiles", cut where no LD dependency crosses) read into page-locked buffers and pushed
+// with cudaMemcpyAsync on a copy stream while the previous tile's kernels run.
+#include "ctx.h"
+
+#include <algorithm>
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+
+namespace pdx {
+
+cudaError_t DevBuf::Reserve(size_t bytes) {
+  if (bytes <= cap && p) return cudaSuccess;
+  if (p) cudaFree(p);
+  p = nullptr;
+  cap = 0;
+  cudaError_t e = cudaMalloc(&p, bytes);
+  if (e == cudaSuccess) cap = bytes;
+  return e;
+}
+void DevBuf::Free() {
+  if (p) cudaFree(p);
+  p = nullptr;
+  cap = 0;
+}
+cudaError_t PinnedBuf::Reserve(size_t bytes) {
+  if (bytes <= cap && p) return cudaSuccess;
+  if (p) cudaFreeHost(p);
+  p = nullptr;
+  cap = 0;
+  cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocDefault);
+  if (e == cudaSuccess) cap = bytes;
+  return e;
+}
+void PinnedBuf::Free() {
+  if (p) cudaFreeHost(p);
+  p = nullptr;
+  cap = 0;
+}
+
+pdk::SubsetDev SubsetState::Dev() const {
+  pdk::SubsetDev d{};
+  if (!active) return d;
+  d.mask2_shifts = d_mask2.as<uint8_t>();
+  d.mask2_stride = stride2;
+  d.mask1_shifts = d_mask1.as<uint8_t>();
+  d.mask1_stride = stride1;
+  d.include_words = d_words.as<uint32_t>();
+  d.cum_popcount = d_cum.as<uint32_t>();
+  d.subset_ct = count;
+  return d;
+}
+void SubsetState::Free() {
+  d_words.Free();
+  d_cum.Free();
+  d_mask2.Free();
+  d_mask1.Free();
+  active = false;
+}
+
+int CheckCuda(pd_ctx_impl* c, cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return PD_OK;
+  char buf[256];
+  snprintf(buf, sizeof(buf), "CUDA failure in %s: %s", what, cudaGetErrorString(e));
+  return c->SetError(PD_ERR_CUDA, buf);
+}
+
+int* DevErr(pd_ctx_impl* c) { return c->d_misc.as<int>(); }
+uint32_t* DevWorkCounter(pd_ctx_impl* c) { return reinterpret_cast<uint32_t*>(c->d_misc.as<int>() + 4); }
+
+int CheckDeviceError(pd_ctx_impl* c) {
+  int* h = c->h_misc.as<int>();
+  cudaError_t e = cudaMemcpyAsync(h, DevErr(c), 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  if (e != cudaSuccess) return CheckCuda(c, e, "error readback");
+  if (h[0]) {
+    const int code = h[0];
+    char buf[128];
+    snprintf(buf, sizeof(buf), "malformed or unsupported variant record at variant %d", h[1]);
+    cudaMemsetAsync(DevErr(c), 0, 2 * sizeof(int), c->stream);
+    return c->SetError(code, buf);
+  }
+  return PD_OK;
+}
+
+uint32_t ExtendToBase(const pd_ctx_impl* c, uint32_t v) { return c->idx.Ldbase(v); }
+
+// Subset mask upload + derived layouts (replaces BuildSampleSubset's interleaved vec and
+// cumulative popcounts, src/plink_common.cpp:1222-1250).
+int BuildSubset(pd_ctx_impl* c, const uint64_t* include, const SubsetState* and_with, SubsetState* out) {
+  const uint32_t N = c->idx.sample_ct;
+  const uint32_t nwords = (N + 31) / 32;
+  const uint32_t padded = ((nwords + 3) & ~3u) + 8;  // 16-byte multiple plus slack
+  out->words.assign(padded, 0u);
+  const uint32_t* src32 = reinterpret_cast<const uint32_t*>(include);
+  for (uint32_t w = 0; w < nwords; ++w) {
+    uint32_t x = src32[w];
+    if (and_with && and_with->active) x &= and_with->words[w];
+    out->words[w] = x;
+  }
+  if (N & 31) out->words[nwords - 1] &= (1u << (N & 31)) - 1u;
+  uint32_t cnt = 0;
+  for (uint32_t w = 0; w < nwords; ++w) cnt += static_cast<uint32_t>(__builtin_popcount(out->words[w]));
+  out->count = cnt;
+  out->stride2 = ((N + 3) / 4 + 16 + 15) / 16 * 16 + 16;
+  out->stride1 = ((N + 7) / 8 + 16 + 15) / 16 * 16 + 16;
+  cudaError_t e = out->d_words.Reserve(padded * 4);
+  if (e == cudaSuccess) e = out->d_cum.Reserve(padded * 4);
+  if (e == cudaSuccess) e = out->d_mask2.Reserve(16ull * out->stride2);
+  if (e == cudaSuccess) e = out->d_mask1.Reserve(16ull * out->stride1);
+  if (e != cudaSuccess) return CheckCuda(c, e, "subset allocation");
+  e = cudaMemcpyAsync(out->d_words.p, out->words.data(), padded * 4, cudaMemcpyHostToDevice, c->stream);
+  if (e != cudaSuccess) return CheckCuda(c, e, "subset upload");
+  c->stats.h2d_bytes += padded * 4;
+  pdk::launch_build_masks(out->d_words.as<uint32_t>(), N, out->d_mask2.as<uint8_t>(), out->stride2,
+                          out->d_mask1.as<uint8_t>(), out->stride1, c->stream, &c->launch_stats);
+  pdk::launch_cum_popcount(out->d_words.as<uint32_t>(), padded, out->d_cum.as<uint32_t>(), c->stream,
+                           &c->launch_stats);
+  e = cudaStreamSynchronize(c->stream);  // out->words must stay valid until the copy is done
+  if (e != cudaSuccess) return CheckCuda(c, e, "subset build");
+  out->active = true;
+  return PD_OK;
+}
+
+namespace {
+
+// Parallel read of [off, off+len) into dst: page-cache pread (or memcpy from a pageable image)
+// is a few GB/s per thread, PCIe Gen5 wants ~50 GB/s.
+bool ParallelRead(const ByteSource& src, uint64_t off, uint8_t* dst, uint64_t len) {
+  const uint64_t kChunk = 8ull << 20;
+  const uint32_t nthreads = static_cast<uint32_t>(std::min<uint64_t>(8, (len + kChunk - 1) / kChunk));
+  if (nthreads <= 1) return src.ReadAt(off, dst, len);
+  std::atomic<uint64_t> next(0);
+  std::atomic<bool> ok(true);
+  auto worker = [&]() {
+    for (;;) {
+      const uint64_t o = next.fetch_add(kChunk);
+      if (o >= len) break;
+      const uint64_t n = std::min(kChunk, len - o);
+      if (!src.ReadAt(off + o, dst + o, n)) ok.store(false);
+    }
+  };
+  std::vector<std::thread> pool;
+  for (uint32_t t = 1; t < nthreads; ++t) pool.emplace_back(worker);
+  worker();
+  for (auto& th : pool) th.join();
+  return ok.load();
+}
+
+void PlanTiles(const pd_ctx_impl* c, uint32_t v0, uint32_t v1, std::vector<Tile>* tiles) {
+  const PgenIndex& ix = c->idx;
+  if (ix.fixed) {
+    uint64_t per = c->tile_bytes / ix.fixed_width;
+    if (per == 0) per = 1;
+    for (uint64_t a = v0; a < v1; a += per) {
+      const uint32_t b = static_cast<uint32_t>(std::min<uint64_t>(v1, a + per));
+      tiles->push_back(Tile{static_cast<uint32_t>(a), b, ix.RecOff(static_cast<uint32_t>(a)),
+                            ix.data_start + static_cast<uint64_t>(b) * ix.fixed_width});
+    }
+    return;
+  }
+  uint32_t a = v0;
+  while (a < v1) {
+    uint32_t b = a + 1;
+    // extend while under budget; never cut in front of an LD-compressed record
+    while (b < v1 && ((ix.fpos[b + 1] - ix.fpos[a] <= c->tile_bytes) || ix.ldbase[b] != b)) ++b;
+    tiles->push_back(Tile{a, b, ix.fpos[a], ix.fpos[b]});
+    a = b;
+  }
+}
+
+cudaEvent_t PoolEvent(pd_ctx_impl* c, size_t i) {
+  while (c->ev_pool.size() <= i) {
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    c->ev_pool.push_back(e);
+  }
+  return c->ev_pool[i];
+}
+
+}  // namespace
+
+int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, const TileFn& fn,
+            const std::function<void(const Tile&, cudaEvent_t)>& after_tile) {
+  const PgenIndex& ixh = c->idx;
+  if (v_begin > v_end || v_end > ixh.variant_ct) return c->SetError(PD_ERR_INVALID_ARG, "variant range out of bounds");
+  const uint32_t v0 = (v_begin < v_end) ? ExtendToBase(c, v_begin) : v_begin;
+  if (v_ext) *v_ext = v0;
+  c->stats.record_bytes = 0;
+  c->stats.kernel_ms = 0;
+  c->stats.aux_kernel_ms = 0;
+  c->stats.total_ms = 0;
+  c->stats.scan_launches = 0;
+  if (v_begin == v_end) return PD_OK;
+
+  pdk::RecIndex ix{};
+  ix.fpos = c->d_fpos.as<uint64_t>();
+  ix.vrtypes = c->d_vrtypes.as<uint8_t>();
+  ix.ldbase = c->d_ldbase.as<uint32_t>();
+  ix.base_slot = c->d_base_slot.as<uint32_t>();
+  ix.fixed_start = ixh.data_start;
+  ix.fixed_width = ixh.fixed_width;
+  ix.const_vrtype = ixh.const_vrtype;
+  ix.N = ixh.sample_ct;
+  c->stats.record_bytes = ixh.RecOff(v_end - 1) + (ixh.fixed ? ixh.fixed_width : ixh.fpos[v_end] - ixh.fpos[v_end - 1]) -
+                          ixh.RecOff(v_begin);
+
+  cudaEventRecord(c->ev_t0, c->stream);
+  int rc = PD_OK;
+  if (c->resident && v0 >= c->res_v0 && v_end <= c->res_v1) {
+    Tile t{v0, v_end, ixh.RecOff(v0), ixh.fixed ? ixh.data_start + static_cast<uint64_t>(v_end) * ixh.fixed_width
+                                               : ixh.fpos[v_end]};
+    ix.data = c->d_resident.as<uint8_t>() + kSlack;
+    ix.data_fpos = c->res_f0;
+    cudaEvent_t k0 = PoolEvent(c, 0), k1 = PoolEvent(c, 1);
+    cudaEventRecord(k0, c->stream);
+    rc = fn(t, ix, c->stream);
+    cudaEventRecord(k1, c->stream);
+    if (after_tile) after_tile(t, k1);
+    cudaError_t e = cudaEventSynchronize(k1);
+    if (rc == PD_OK && e != cudaSuccess) rc = CheckCuda(c, e, "scan kernels");
+    if (rc == PD_OK) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, k0, k1);
+      c->stats.kernel_ms = ms;
+    }
+  } else {
+    std::vector<Tile> tiles;
+    PlanTiles(c, v0, v_end, &tiles);
+    uint64_t max_len = 0;
+    for (auto& t : tiles) max_len = std::max(max_len, t.f1 - t.f0);
+    const uint32_t nbuf = c->n_staging;
+    for (uint32_t b = 0; b < nbuf && rc == PD_OK; ++b) {
+      cudaError_t e = c->d_stage[b].Reserve(max_len + 2 * kSlack);
+      if (e == cudaSuccess && !c->src_pinned) e = c->h_stage[b].Reserve(max_len);
+      if (e != cudaSuccess) rc = CheckCuda(c, e, "staging allocation");
+    }
+    for (size_t i = 0; i < tiles.size() && rc == PD_OK; ++i) {
+      const Tile& t = tiles[i];
+      const uint32_t b = static_cast<uint32_t>(i % nbuf);
+      const uint64_t len = t.f1 - t.f0;
+      if (i >= nbuf) {
+        cudaError_t e = cudaEventSynchronize(c->ev_done[b]);  // buffer b's previous tile fully consumed
+        if (e != cudaSuccess) {
+          rc = CheckCuda(c, e, "tile completion");
+          break;
+        }
+      }
+      const uint8_t* hsrc;
+      if (c->src_pinned) {
+        hsrc = c->pgen.mem() + t.f0;
+      } else {
+        if (!ParallelRead(c->pgen, t.f0, c->h_stage[b].as<uint8_t>(), len)) {
+          rc = c->SetError(PD_ERR_READ, ".pgen read failure");
+          break;
+        }
+        hsrc = c->h_stage[b].as<uint8_t>();
+      }
+      cudaError_t e = cudaMemcpyAsync(c->d_stage[b].as<uint8_t>() + kSlack, hsrc, len, cudaMemcpyHostToDevice,
+                                      c->copy_stream);
+      if (e != cudaSuccess) {
+        rc = CheckCuda(c, e, "H2D staging copy");
+        break;
+      }
+      c->stats.h2d_bytes += len;
+      cudaEventRecord(c->ev_copied[b], c->copy_stream);
+      cudaStreamWaitEvent(c->stream, c->ev_copied[b], 0);
+      ix.data = c->d_stage[b].as<uint8_t>() + kSlack;
+      ix.data_fpos = t.f0;
+      cudaEvent_t k0 = PoolEvent(c, 2 * i), k1 = PoolEvent(c, 2 * i + 1);
+      cudaEventRecord(k0, c->stream);
+      rc = fn(t, ix, c->stream);
+      cudaEventRecord(k1, c->stream);
+      cudaEventRecord(c->ev_done[b], c->stream);
+      if (after_tile) after_tile(t, k1);
+    }
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (rc == PD_OK && e != cudaSuccess) rc = CheckCuda(c, e, "scan kernels");
+    if (rc == PD_OK) {
+      double tot = 0;
+      for (size_t i = 0; i < tiles.size(); ++i) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, PoolEvent(c, 2 * i), PoolEvent(c, 2 * i + 1));
+        tot += ms;
+      }
+      c->stats.kernel_ms = tot;
+    }
+  }
+  cudaEventRecord(c->ev_t1, c->stream);
+  cudaEventSynchronize(c->ev_t1);
+  if (rc == PD_OK) {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev_t0, c->ev_t1);
+    c->stats.total_ms = ms;
+    rc = CheckDeviceError(c);
+  }
+  return rc;
+}
+
+}  // namespace pdx

@@ -1,0 +1,123 @@
+// Host-side context of libplinkgpu: index, device buffers, staging ring, scan executor.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <condition_variable>
+#include <functional>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/plinkgpu.h"
+#include "kernels.cuh"
+#include "pgen_index.h"
+
+namespace pdx {
+
+constexpr uint32_t kSlack = 64;  // readable bytes before/after every record buffer (aligned 16 B loads)
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  // Grow-only device allocation.
+  cudaError_t Reserve(size_t bytes);
+  void Free();
+  template <class T>
+  T* as() const { return static_cast<T*>(p); }
+};
+
+struct PinnedBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t Reserve(size_t bytes);
+  void Free();
+  template <class T>
+  T* as() const { return static_cast<T*>(p); }
+};
+
+// Device-side form of one sample mask (the context subset, or subset AND stratum).
+struct SubsetState {
+  bool active = false;
+  uint32_t count = 0;
+  std::vector<uint32_t> words;  // N bits as 32-bit words, padded
+  DevBuf d_words, d_cum, d_mask2, d_mask1;
+  uint32_t stride2 = 0, stride1 = 0;
+  pdk::SubsetDev Dev() const;
+  void Free();
+};
+
+struct Tile {
+  uint32_t v0, v1;      // variants staged (v0 is never LD-compressed)
+  uint64_t f0, f1;      // file byte range
+};
+
+struct pd_ctx_impl {
+  ByteSource pgen, pgi;
+  bool have_pgi = false;
+  PgenIndex idx;
+  int device = 0;
+  uint64_t tile_bytes = 64ull << 20;
+  uint32_t n_staging = 3;
+  bool src_pinned = false;  // memory image is page-locked: DMA straight from it
+
+  cudaStream_t stream = nullptr;       // compute
+  cudaStream_t copy_stream = nullptr;  // H2D staging
+  std::mutex mu;
+  std::string last_error;
+
+  // device copies of the index (variable-width files)
+  DevBuf d_fpos, d_vrtypes, d_ldbase, d_base_slot, d_slot_vidx;
+  std::vector<uint32_t> base_slot;  // [V]: scratch slot of the LD base (non-type-0 bases), else ~0u
+  std::vector<uint32_t> slot_vidx;  // slot -> base variant
+
+  // residency
+  DevBuf d_resident;
+  bool resident = false;
+  uint32_t res_v0 = 0, res_v1 = 0;
+  uint64_t res_f0 = 0, res_f1 = 0;
+
+  // staging ring
+  std::vector<PinnedBuf> h_stage;
+  std::vector<DevBuf> d_stage;
+  std::vector<cudaEvent_t> ev_copied, ev_done;
+
+  // work buffers
+  DevBuf d_counts, d_scratch, d_misc, d_pvals, d_acc;
+  PinnedBuf h_misc;   // int err[2] + small readbacks
+  PinnedBuf h_out;    // pinned bounce buffer for results
+  cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
+  std::vector<cudaEvent_t> ev_pool;
+
+  SubsetState subset;
+
+  pdk::LaunchStats launch_stats;
+  pd_stats_t stats{};
+
+  int SetError(int code, const std::string& msg) {
+    last_error = msg;
+    return code;
+  }
+};
+
+// Per-tile callback: records of [t.v0, t.v1) are reachable through ix; enqueue kernels on s.
+using TileFn = std::function<int(const Tile& t, const pdk::RecIndex& ix, cudaStream_t s)>;
+
+// Plans tiles for [v_begin, v_end) (extended back to the LD base of v_begin), stages each one
+// (or points at the resident copy) and calls fn.  *v_ext receives the first staged variant.
+// after_tile (optional) runs on the host after tile i's kernels are enqueued, with the event that
+// marks their completion.
+int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, const TileFn& fn,
+            const std::function<void(const Tile&, cudaEvent_t)>& after_tile = nullptr);
+
+int CheckCuda(pd_ctx_impl* c, cudaError_t e, const char* what);
+int CheckDeviceError(pd_ctx_impl* c);  // reads the device error word after a synchronize
+int* DevErr(pd_ctx_impl* c);
+uint32_t* DevWorkCounter(pd_ctx_impl* c);
+uint32_t ExtendToBase(const pd_ctx_impl* c, uint32_t v);
+int BuildSubset(pd_ctx_impl* c, const uint64_t* include, const SubsetState* and_with, SubsetState* out);
+
+}  // namespace pdx
+
+struct pd_ctx : pdx::pd_ctx_impl {};

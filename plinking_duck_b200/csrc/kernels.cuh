@@ -1,0 +1,69 @@
+// Launch wrappers of the sm_100a scan kernels (definitions in kernels_*.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace pdk {
+
+// Where record v lives in device memory.
+struct RecIndex {
+  const uint8_t* data;      // device byte holding file offset data_fpos (>= 16 B slack both sides)
+  uint64_t data_fpos;
+  const uint64_t* fpos;     // [V+1] file offsets, nullptr for fixed-width files
+  const uint8_t* vrtypes;   // [V], nullptr for fixed-width files
+  const uint32_t* ldbase;   // [V], nullptr for fixed-width files
+  const uint32_t* base_slot;// [V] scratch slot of the LD base when it is not a type-0 record, else ~0u
+  uint64_t fixed_start;     // file offset of record 0 (fixed-width)
+  uint32_t fixed_width;
+  uint32_t const_vrtype;
+  uint32_t N;               // raw sample count
+};
+
+// Sample subset (and strata) in the layouts the kernels consume.
+struct SubsetDev {
+  const uint8_t* mask2_shifts;  // 16 shifted copies of the 2-bit-expanded include mask; nullptr = all samples
+  uint32_t mask2_stride;
+  const uint8_t* mask1_shifts;  // 16 shifted copies of the 1-bit include mask
+  uint32_t mask1_stride;
+  const uint32_t* include_words;// unshifted 1-bit mask as 32-bit words, padded
+  const uint32_t* cum_popcount; // exclusive prefix popcount per 32-bit word (RawToSubsettedPos)
+  uint32_t subset_ct;
+};
+
+// Scratch for dense copies of non-type-0 LD bases.
+struct LdScratch {
+  uint8_t* dense;          // slot s at dense + (s - slot_lo) * stride
+  uint32_t stride;         // bytes per slot, multiple of 16
+  uint32_t slot_lo;
+};
+
+struct LaunchStats {
+  uint64_t launches = 0;
+};
+
+// ---- subset mask construction ----
+void launch_build_masks(const uint32_t* include_words, uint32_t N, uint8_t* mask2_shifts, uint32_t mask2_stride,
+                        uint8_t* mask1_shifts, uint32_t mask1_stride, cudaStream_t s, LaunchStats* st);
+void launch_cum_popcount(const uint32_t* include_words, uint32_t nwords, uint32_t* cum, cudaStream_t s, LaunchStats* st);
+
+// ---- K1/K2: genotype counts over fixed-width 2-bit records ----
+// out[v - v_begin] = (hom_ref, het, hom_alt, missing).  main_bytes_only: records may carry
+// trailing dosage tracks (modes 0x03/0x04); only the leading ceil(N/4) bytes are counted.
+void launch_count_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_begin, uint32_t v_end, uint4* out,
+                        cudaStream_t s, LaunchStats* st);
+
+// ---- K3: genotype counts over variable-width records (vrtype 0-7, LD resolved) ----
+// Scans [v_begin, v_end); v_begin must not be LD-compressed.  out[v - v_begin].
+// work_counter: device uint32 (zeroed by the wrapper).  err: device int[2] = {code, vidx}.
+void launch_count_var(const RecIndex& ix, const SubsetDev& sub, const LdScratch& scratch, uint32_t v_begin,
+                      uint32_t v_end, uint4* out, uint32_t* work_counter, int* err, cudaStream_t s, LaunchStats* st);
+
+// Dense 2-bit copies of the LD bases slot_lo..slot_hi (inclusive) listed in slot_vidx.
+void launch_decode_bases(const RecIndex& ix, const uint32_t* slot_vidx, const LdScratch& scratch, uint32_t slot_hi,
+                         int* err, cudaStream_t s, LaunchStats* st);
+
+// ---- K8: exact Hardy-Weinberg test on the device ----
+// counts[n] as produced by the count kernels; out_p[n] = p-value clamped to [0,1].
+void launch_hwe(const uint4* counts, uint32_t n, uint32_t midp, double* out_p, cudaStream_t s, LaunchStats* st);
+
+}  // namespace pdk

@@ -1,0 +1,246 @@
+"""PgenContext: one opened .pgen on one B200, a thin object over the C ABI."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+from . import _native as nat
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def include_bits(indices, n: int) -> np.ndarray:
+    """sample_include bitmask (uint64 words, LSB first) from sample indices."""
+    words = np.zeros((n + 63) // 64 + 1, dtype=np.uint64)
+    idx = np.unique(np.asarray(indices, dtype=np.int64))
+    if idx.size and (idx[0] < 0 or idx[-1] >= n):
+        raise ValueError("sample index out of range")
+    np.bitwise_or.at(words, idx >> 6, np.uint64(1) << (idx & 63).astype(np.uint64))
+    return words
+
+
+def probe(path: str):
+    """Header-only parse (no GPU): (Info, vrtypes, fpos)."""
+    lib = nat.load()
+    info = nat.Info()
+    err = C.create_string_buffer(512)
+    rc = lib.pd_probe(os.fsencode(path), C.byref(info), None, None, 0, err, 512)
+    if rc:
+        raise nat.PlinkGpuError(rc, err.value.decode(errors="replace"))
+    vt = np.zeros(info.variant_ct, dtype=np.uint8)
+    fpos = np.zeros(info.variant_ct + 1, dtype=np.uint64)
+    rc = lib.pd_probe(os.fsencode(path), C.byref(info), _p(vt), _p(fpos), info.variant_ct, err, 512)
+    if rc:
+        raise nat.PlinkGpuError(rc, err.value.decode(errors="replace"))
+    return info, vt, fpos
+
+
+class PgenContext:
+    """Owns a pd_ctx.  All heavy lifting happens in libplinkgpu.so on the GPU."""
+
+    def __init__(self, path: Optional[str] = None, *, image: Optional[np.ndarray] = None, pgi: Optional[np.ndarray] = None,
+                 device: int = -1, tile_bytes: int = 0, n_staging: int = 0):
+        self._lib = nat.load()
+        self._h = C.c_void_p()
+        self._keep = (image, pgi)
+        opts = nat.OpenOpts(device, tile_bytes, n_staging, 0)
+        err = C.create_string_buffer(512)
+        if image is not None:
+            pg = pgi.ctypes.data_as(C.c_void_p) if pgi is not None else None
+            rc = self._lib.pd_open_mem(image.ctypes.data_as(C.c_void_p), image.nbytes, pg,
+                                       pgi.nbytes if pgi is not None else 0, C.byref(opts), C.byref(self._h), err, 512)
+        else:
+            rc = self._lib.pd_open(os.fsencode(path), C.byref(opts), C.byref(self._h), err, 512)
+        if rc:
+            raise nat.PlinkGpuError(rc, err.value.decode(errors="replace"))
+        info = self.info()
+        self.variant_ct = info.variant_ct
+        self.raw_sample_ct = info.sample_ct
+        self.sample_ct = info.sample_ct  # effective (after subset)
+
+    @classmethod
+    def from_pointer(cls, ptr: int, nbytes: int, **kw):
+        """Open a .pgen image living at a raw host address (e.g. a pinned torch tensor)."""
+        arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(nbytes,))
+        return cls(image=arr, **kw)
+
+    # -- lifetime --
+    def close(self):
+        if self._h:
+            self._lib.pd_close(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc: int):
+        if rc:
+            raise nat.PlinkGpuError(rc, self._lib.pd_last_error(self._h).decode(errors="replace"))
+
+    def _range(self, v0, v1):
+        v1 = self.variant_ct if v1 is None else v1
+        return int(v0), int(v1)
+
+    # -- metadata --
+    def info(self) -> nat.Info:
+        out = nat.Info()
+        self._check(self._lib.pd_info(self._h, C.byref(out)))
+        return out
+
+    def index(self):
+        vt = np.zeros(self.variant_ct, dtype=np.uint8)
+        fpos = np.zeros(self.variant_ct + 1, dtype=np.uint64)
+        self._check(self._lib.pd_index(self._h, _p(vt), _p(fpos)))
+        return vt, fpos
+
+    def stats(self) -> nat.Stats:
+        out = nat.Stats()
+        self._check(self._lib.pd_get_stats(self._h, C.byref(out)))
+        return out
+
+    def reset_stats(self):
+        self._check(self._lib.pd_reset_stats(self._h))
+
+    # -- residency / subset --
+    def load_resident(self, v0=0, v1=None):
+        v0, v1 = self._range(v0, v1)
+        self._check(self._lib.pd_load_resident(self._h, v0, v1))
+
+    def unload(self):
+        self._check(self._lib.pd_unload(self._h))
+
+    def set_subset(self, indices):
+        if indices is None:
+            self._check(self._lib.pd_set_sample_subset(self._h, None, 0))
+            self.sample_ct = self.raw_sample_ct
+            return
+        bits = include_bits(indices, self.raw_sample_ct)
+        cnt = int(np.unique(np.asarray(indices)).size)
+        self._check(self._lib.pd_set_sample_subset(self._h, _p(bits), cnt))
+        self.sample_ct = cnt
+
+    # -- per-variant reductions --
+    def counts(self, v0=0, v1=None) -> np.ndarray:
+        v0, v1 = self._range(v0, v1)
+        out = np.zeros((max(v1 - v0, 0), 4), dtype=np.uint32)
+        self._check(self._lib.pd_counts(self._h, v0, v1, _p(out)))
+        return out
+
+    def counts_masked(self, stratum_indices, v0=0, v1=None) -> np.ndarray:
+        v0, v1 = self._range(v0, v1)
+        bits = include_bits(stratum_indices, self.raw_sample_ct)
+        out = np.zeros((max(v1 - v0, 0), 4), dtype=np.uint32)
+        self._check(self._lib.pd_counts_masked(self._h, v0, v1, _p(bits), _p(out)))
+        return out
+
+    def counts_async(self, v0=0, v1=None) -> "CountsJob":
+        v0, v1 = self._range(v0, v1)
+        return CountsJob(self, v0, v1)
+
+    def hardy(self, v0=0, v1=None, midp=False):
+        v0, v1 = self._range(v0, v1)
+        n = max(v1 - v0, 0)
+        counts = np.zeros((n, 4), dtype=np.uint32)
+        p = np.zeros(n, dtype=np.float64)
+        self._check(self._lib.pd_hardy(self._h, v0, v1, int(bool(midp)), _p(counts), _p(p)))
+        return counts, p
+
+    def hwe_from_counts(self, counts, midp=False) -> np.ndarray:
+        counts = np.ascontiguousarray(counts, dtype=np.uint32).reshape(-1, 4)
+        p = np.zeros(counts.shape[0], dtype=np.float64)
+        self._check(self._lib.pd_hwe_from_counts(self._h, _p(counts), counts.shape[0], int(bool(midp)), _p(p)))
+        return p
+
+    # -- per-sample accumulations --
+    def missing_by_sample(self, v0=0, v1=None) -> np.ndarray:
+        v0, v1 = self._range(v0, v1)
+        out = np.zeros(self.sample_ct, dtype=np.uint32)
+        self._check(self._lib.pd_missing_by_sample(self._h, v0, v1, _p(out)))
+        return out
+
+    def sample_counts(self, v0=0, v1=None):
+        v0, v1 = self._range(v0, v1)
+        het = np.zeros(self.sample_ct, dtype=np.uint32)
+        hom_alt = np.zeros(self.sample_ct, dtype=np.uint32)
+        missing = np.zeros(self.sample_ct, dtype=np.uint32)
+        self._check(self._lib.pd_sample_counts(self._h, v0, v1, _p(het), _p(hom_alt), _p(missing)))
+        return het, hom_alt, missing
+
+    # -- decode --
+    def decode_i8(self, v0=0, v1=None) -> np.ndarray:
+        v0, v1 = self._range(v0, v1)
+        out = np.zeros((max(v1 - v0, 0), self.sample_ct), dtype=np.int8)
+        self._check(self._lib.pd_decode_i8(self._h, v0, v1, _p(out)))
+        return out
+
+    def dosage_f64(self, vidx) -> np.ndarray:
+        vidx = np.ascontiguousarray(vidx, dtype=np.uint32)
+        out = np.zeros((vidx.size, self.sample_ct), dtype=np.float64)
+        self._check(self._lib.pd_dosage_f64(self._h, _p(vidx), vidx.size, _p(out)))
+        return out
+
+    def dosage_counts(self, v0=0, v1=None):
+        v0, v1 = self._range(v0, v1)
+        n = max(v1 - v0, 0)
+        counts = np.zeros((n, 4), dtype=np.uint32)
+        ad = np.zeros((n, 2), dtype=np.uint64)
+        r2 = np.zeros(n, dtype=np.float64)
+        self._check(self._lib.pd_dosage_counts(self._h, v0, v1, _p(counts), _p(ad), _p(r2)))
+        return counts, ad, r2
+
+    def score(self, vidx, flip, weights, mode=0):
+        vidx = np.ascontiguousarray(vidx, dtype=np.uint32)
+        weights = np.ascontiguousarray(weights, dtype=np.float64)
+        if weights.ndim == 1:
+            weights = weights.reshape(-1, 1)
+        n, K = weights.shape
+        if n != vidx.size:
+            raise ValueError("weights rows must match vidx")
+        fl = None if flip is None else np.ascontiguousarray(flip, dtype=np.uint8)
+        sums = np.zeros((self.sample_ct, K), dtype=np.float64)
+        dsum = np.zeros(self.sample_ct, dtype=np.float64)
+        act = np.zeros(self.sample_ct, dtype=np.uint32)
+        self._check(self._lib.pd_score(self._h, _p(vidx), _p(fl), _p(weights), n, K, int(mode), _p(sums), _p(dsum), _p(act)))
+        return sums, dsum, act
+
+
+class CountsJob:
+    """pd_counts_start / pd_counts_fetch: what a DuckDB scan's claim loop would hold."""
+
+    def __init__(self, ctx: PgenContext, v0: int, v1: int):
+        self._ctx = ctx
+        self._j = C.c_void_p()
+        self.v0, self.v1 = v0, v1
+        ctx._check(ctx._lib.pd_counts_start(ctx._h, v0, v1, C.byref(self._j)))
+
+    def fetch(self, a: int, b: int) -> np.ndarray:
+        out = np.zeros((max(b - a, 0), 4), dtype=np.uint32)
+        rc = self._ctx._lib.pd_counts_fetch(self._j, a, b, _p(out))
+        if rc:
+            raise nat.PlinkGpuError(rc, self._ctx._lib.pd_last_error(self._ctx._h).decode(errors="replace"))
+        return out
+
+    def close(self):
+        if self._j:
+            self._ctx._lib.pd_job_free(self._j)
+            self._j = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,165 @@
+"""Seeded synthetic genotype data and .pgen writers used by tests and bench (test infrastructure).
+
+Genotype codes follow the .pgen 2-bit encoding: 0 hom-ref, 1 het, 2 hom-alt, 3 missing.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def gen_hwe_genotypes(V: int, N: int, seed: int, missing: float = 0.01, maf_lo=0.05, maf_hi=0.5) -> np.ndarray:
+    """SURVEY 8d model: p_v ~ U(maf_lo, maf_hi), g ~ Binomial(2, p_v), `missing` fraction set to 3."""
+    rng = np.random.default_rng(seed)
+    p = rng.uniform(maf_lo, maf_hi, size=(V, 1))
+    u = rng.random((V, N))
+    g = (u < p * p).astype(np.int8) * 2
+    g[(u >= p * p) & (u < p * p + 2 * p * (1 - p))] = 1
+    if missing > 0:
+        g[rng.random((V, N)) < missing] = 3
+    return g
+
+
+def gen_mixed_genotypes(V: int, N: int, seed: int) -> np.ndarray:
+    """A mixture that makes pgenlib's writer emit every main-track record type:
+    dense (0), two-category dominated (1-bit), near-copies of the previous variant (LD, 2),
+    inverted near-copies (3), rare variants (4), ALT-major (6), mostly-missing (7), monomorphic."""
+    rng = np.random.default_rng(seed)
+    g = np.zeros((V, N), dtype=np.int8)
+    prev = None
+    for v in range(V):
+        kind = rng.integers(0, 10)
+        if kind <= 1 or prev is None:
+            p = rng.uniform(0.1, 0.5)
+            u = rng.random(N)
+            row = np.where(u < p * p, 2, np.where(u < p * p + 2 * p * (1 - p), 1, 0)).astype(np.int8)
+            row[rng.random(N) < 0.02] = 3
+        elif kind == 2:  # two dominant categories + a few others -> 1-bit
+            a, b = rng.choice(4, size=2, replace=False)
+            row = np.where(rng.random(N) < rng.uniform(0.2, 0.5), a, b).astype(np.int8)
+            k = rng.integers(0, max(1, N // 40) + 1)
+            if k:
+                idx = rng.choice(N, size=k, replace=False)
+                row[idx] = rng.integers(0, 4, size=k)
+        elif kind == 3 or kind == 4:  # LD: previous variant with a few changes
+            row = prev.copy()
+            k = rng.integers(0, max(1, N // 30) + 1)
+            if k:
+                idx = rng.choice(N, size=k, replace=False)
+                row[idx] = rng.integers(0, 4, size=k)
+        elif kind == 5:  # inverted LD
+            row = prev.copy()
+            swap0, swap2 = row == 0, row == 2
+            row[swap0] = 2
+            row[swap2] = 0
+            k = rng.integers(0, max(1, N // 50) + 1)
+            if k:
+                idx = rng.choice(N, size=k, replace=False)
+                row[idx] = rng.integers(0, 4, size=k)
+        elif kind == 6 or kind == 7:  # rare variant
+            row = np.zeros(N, dtype=np.int8)
+            k = rng.integers(0, max(1, N // 20) + 1)
+            if k:
+                idx = rng.choice(N, size=k, replace=False)
+                row[idx] = rng.choice([1, 1, 1, 2, 3], size=k)
+        elif kind == 8:  # ALT-major
+            row = np.full(N, 2, dtype=np.int8)
+            k = rng.integers(0, max(1, N // 20) + 1)
+            if k:
+                idx = rng.choice(N, size=k, replace=False)
+                row[idx] = rng.choice([0, 1, 3], size=k)
+        else:  # mostly missing
+            row = np.full(N, 3, dtype=np.int8)
+            k = rng.integers(0, max(1, N // 20) + 1)
+            if k:
+                idx = rng.choice(N, size=k, replace=False)
+                row[idx] = rng.choice([0, 1, 2], size=k)
+        g[v] = row
+        prev = row
+    return g
+
+
+def gen_rare_genotypes(V: int, N: int, seed: int) -> np.ndarray:
+    """MAF model of the reference's rare-variant fixture (test/data/generate_rare_test_data.sh:32-46):
+    95 % log-uniform [1/2N, 1 %], 5 % log-uniform [1 %, 50 %], 1 % missing."""
+    rng = np.random.default_rng(seed)
+    g = np.zeros((V, N), dtype=np.int8)
+    for v in range(V):
+        if rng.random() < 0.95:
+            maf = np.exp(rng.uniform(np.log(1.0 / (2 * N)), np.log(0.01)))
+        else:
+            maf = np.exp(rng.uniform(np.log(0.01), np.log(0.5)))
+        u = rng.random(N)
+        row = np.where(u < maf * maf, 2, np.where(u < maf * maf + 2 * maf * (1 - maf), 1, 0)).astype(np.int8)
+        row[rng.random(N) < 0.01] = 3
+        g[v] = row
+    return g
+
+
+def pack_2bit_bytes(g: np.ndarray) -> np.ndarray:
+    """(V, N) codes -> (V, ceil(N/4)) uint8, sample 0 in the low bits, trailing bits zero."""
+    V, N = g.shape
+    nb = (N + 3) // 4
+    pad = np.zeros((V, nb * 4), dtype=np.uint8)
+    pad[:, :N] = g.astype(np.uint8) & 3
+    q = pad.reshape(V, nb, 4)
+    return (q[:, :, 0] | (q[:, :, 1] << 2) | (q[:, :, 2] << 4) | (q[:, :, 3] << 6)).astype(np.uint8)
+
+
+def to_genovec_words(g: np.ndarray) -> np.ndarray:
+    """(V, N) codes -> (V, ceil(N/32)) uint64 genovecs."""
+    V, N = g.shape
+    b = pack_2bit_bytes(g)
+    nw = (N + 31) // 32
+    buf = np.zeros((V, nw * 8), dtype=np.uint8)
+    buf[:, : b.shape[1]] = b
+    return buf.view(np.uint64).reshape(V, nw)
+
+
+def fixed_header(V: int, N: int) -> bytes:
+    """Mode 0x02 header: magic, mode, V, N (u32 LE), header_ctrl 0x40 (pgenlib_read.cc:877-911)."""
+    return bytes([0x6C, 0x1B, 0x02]) + int(V).to_bytes(4, "little") + int(N).to_bytes(4, "little") + bytes([0x40])
+
+
+def fixed_pgen_image(g: np.ndarray) -> np.ndarray:
+    V, N = g.shape
+    body = pack_2bit_bytes(g).reshape(-1)
+    return np.concatenate([np.frombuffer(fixed_header(V, N), dtype=np.uint8), body])
+
+
+def write_fixed_pgen(path: str, g: np.ndarray):
+    fixed_pgen_image(g).tofile(path)
+
+
+def counts_numpy(g: np.ndarray) -> np.ndarray:
+    return np.stack([(g == k).sum(axis=1) for k in range(4)], axis=1).astype(np.uint32)
+
+
+def gen_dosage_variants(V: int, N: int, seed: int):
+    """Hardcalls + per-variant dosage lists in the form oracle.ref.write_pgen takes.
+    Dosages are consistent with the hardcalls (|dosage - hardcall| < 0.5)."""
+    rng = np.random.default_rng(seed)
+    g = np.zeros((V, N), dtype=np.int8)
+    dos = []
+    for v in range(V):
+        frac = [0.0, 0.02, 0.5, 1.0][v % 4]
+        has = rng.random(N) < frac if frac < 1.0 else np.ones(N, dtype=bool)
+        d16 = rng.integers(0, 32769, size=N)
+        # keep away from the rounding boundaries 8192 / 24576
+        d16 = np.where(np.abs(d16 - 8192) < 40, 8000, d16)
+        d16 = np.where(np.abs(d16 - 24576) < 40, 24700, d16)
+        hard = np.where(d16 < 8192, 0, np.where(d16 < 24576, 1, 2)).astype(np.int8)
+        p = rng.uniform(0.1, 0.5)
+        u = rng.random(N)
+        plain = np.where(u < p * p, 2, np.where(u < p * p + 2 * p * (1 - p), 1, 0)).astype(np.int8)
+        row = np.where(has, hard, plain)
+        miss = (rng.random(N) < 0.03) & ~has
+        row[miss] = 3
+        g[v] = row
+        if has.any():
+            words = np.zeros((N + 63) // 64, dtype=np.uint64)
+            idx = np.nonzero(has)[0]
+            np.bitwise_or.at(words, idx >> 6, np.uint64(1) << (idx & 63).astype(np.uint64))
+            dos.append((words, d16[has].astype(np.uint16)))
+        else:
+            dos.append(None)
+    return g, dos
