@@ -70,6 +70,7 @@ typedef struct pd_stats_t {
   double aux_kernel_ms;     /* CUDA-event time of follow-up kernels (LD fix-up, HWE, ...)       */
   double total_ms;          /* CUDA-event time of the last call's whole device section          */
   uint64_t scan_launches;   /* launches of the dominant scan kernel in the last call            */
+  double call_ms;           /* CUDA-event time of the last call, first enqueue to last result copy */
 } pd_stats_t;
 
 /* ---- open / close : replaces PgfiInitPhase1 + PgfiInitPhase2 + PgrInit per scan thread

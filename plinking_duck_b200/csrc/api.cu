@@ -34,6 +34,8 @@ void DestroyCtx(pd_ctx* c) {
   if (c->ev_b) cudaEventDestroy(c->ev_b);
   if (c->ev_t0) cudaEventDestroy(c->ev_t0);
   if (c->ev_t1) cudaEventDestroy(c->ev_t1);
+  if (c->ev_c0) cudaEventDestroy(c->ev_c0);
+  if (c->ev_c1) cudaEventDestroy(c->ev_c1);
   if (c->stream) cudaStreamDestroy(c->stream);
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   delete c;
@@ -60,6 +62,7 @@ int InitDevice(pd_ctx* c, const pd_open_opts* opts) {
   if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return CheckCuda(c, e, "stream");
   if ((e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return CheckCuda(c, e, "stream");
   cudaEventCreate(&c->ev_a); cudaEventCreate(&c->ev_b); cudaEventCreate(&c->ev_t0); cudaEventCreate(&c->ev_t1);
+  cudaEventCreate(&c->ev_c0); cudaEventCreate(&c->ev_c1);
   c->h_stage.resize(c->n_staging);
   c->d_stage.resize(c->n_staging);
   c->ev_copied.resize(c->n_staging);

@@ -89,11 +89,22 @@ int pd_counts(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* out_counts)
   if (!c || (!out_counts && v_end > v_begin)) return PD_ERR_INVALID_ARG;
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
+  cudaEventRecord(c->ev_c0, c->stream);
   uint32_t v_ext = 0;
   int rc = CountsToDevice(c, c->subset, v_begin, v_end, &v_ext);
   if (rc != PD_OK) return rc;
-  return DownloadRows(c, c->d_counts.as<uint4>() + (v_begin - v_ext), static_cast<size_t>(v_end - v_begin) * 16,
-                      out_counts);
+  if (v_end > v_begin) {
+    cudaError_t e = cudaMemcpyAsync(out_counts, c->d_counts.as<uint4>() + (v_begin - v_ext),
+                                    static_cast<size_t>(v_end - v_begin) * 16, cudaMemcpyDeviceToHost, c->stream);
+    cudaEventRecord(c->ev_c1, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) return CheckCuda(c, e, "result download");
+    c->stats.d2h_bytes += static_cast<size_t>(v_end - v_begin) * 16;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev_c0, c->ev_c1);
+    c->stats.call_ms = ms;
+  }
+  return PD_OK;
 }
 
 int pd_counts_masked(pd_ctx* c, uint32_t v_begin, uint32_t v_end, const uint64_t* stratum_include,
@@ -201,6 +212,7 @@ int pd_hardy(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_
   if (!c || (!out_p && v_end > v_begin)) return PD_ERR_INVALID_ARG;
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
+  cudaEventRecord(c->ev_c0, c->stream);
   uint32_t v_ext = 0;
   int rc = CountsToDevice(c, c->subset, v_begin, v_end, &v_ext);
   if (rc != PD_OK) return rc;
@@ -212,14 +224,20 @@ int pd_hardy(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_
   cudaEventRecord(c->ev_a, c->stream);
   pdk::launch_hwe(counts, n, midp, c->d_pvals.as<double>(), c->stream, &c->launch_stats);
   cudaEventRecord(c->ev_b, c->stream);
-  rc = DownloadRows(c, c->d_pvals.p, static_cast<size_t>(n) * 8, out_p);
-  if (rc == PD_OK && out_counts) rc = DownloadRows(c, counts, static_cast<size_t>(n) * 16, out_counts);
-  if (rc == PD_OK) {
-    float ms = 0;
-    cudaEventElapsedTime(&ms, c->ev_a, c->ev_b);
-    c->stats.aux_kernel_ms = ms;
+  e = cudaMemcpyAsync(out_p, c->d_pvals.p, static_cast<size_t>(n) * 8, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess && out_counts) {
+    e = cudaMemcpyAsync(out_counts, counts, static_cast<size_t>(n) * 16, cudaMemcpyDeviceToHost, c->stream);
   }
-  return rc;
+  cudaEventRecord(c->ev_c1, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  if (e != cudaSuccess) return CheckCuda(c, e, "result download");
+  c->stats.d2h_bytes += static_cast<size_t>(n) * (out_counts ? 24 : 8);
+  float ms = 0;
+  cudaEventElapsedTime(&ms, c->ev_a, c->ev_b);
+  c->stats.aux_kernel_ms = ms;
+  cudaEventElapsedTime(&ms, c->ev_c0, c->ev_c1);
+  c->stats.call_ms = ms;
+  return PD_OK;
 }
 
 int pd_hwe_from_counts(pd_ctx* c, const uint32_t* counts, uint32_t n, uint32_t midp, double* out_p) {

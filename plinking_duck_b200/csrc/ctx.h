@@ -87,7 +87,7 @@ struct pd_ctx_impl {
   DevBuf d_counts, d_scratch, d_misc, d_pvals, d_acc;
   PinnedBuf h_misc;   // int err[2] + small readbacks
   PinnedBuf h_out;    // pinned bounce buffer for results
-  cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
+  cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_t0 = nullptr, ev_t1 = nullptr, ev_c0 = nullptr, ev_c1 = nullptr;
   std::vector<cudaEvent_t> ev_pool;
 
   SubsetState subset;

@@ -134,9 +134,9 @@ class PgenContext:
         self.sample_ct = cnt
 
     # -- per-variant reductions --
-    def counts(self, v0=0, v1=None) -> np.ndarray:
+    def counts(self, v0=0, v1=None, out=None) -> np.ndarray:
         v0, v1 = self._range(v0, v1)
-        out = np.zeros((max(v1 - v0, 0), 4), dtype=np.uint32)
+        out = np.zeros((max(v1 - v0, 0), 4), dtype=np.uint32) if out is None else out
         self._check(self._lib.pd_counts(self._h, v0, v1, _p(out)))
         return out
 
@@ -151,11 +151,13 @@ class PgenContext:
         v0, v1 = self._range(v0, v1)
         return CountsJob(self, v0, v1)
 
-    def hardy(self, v0=0, v1=None, midp=False):
+    def hardy(self, v0=0, v1=None, midp=False, out_counts=None, out_p=None):
+        """out_counts / out_p: optional preallocated (e.g. page-locked) result arrays."""
         v0, v1 = self._range(v0, v1)
         n = max(v1 - v0, 0)
-        counts = np.zeros((n, 4), dtype=np.uint32)
-        p = np.zeros(n, dtype=np.float64)
+        counts = np.zeros((n, 4), dtype=np.uint32) if out_counts is None else out_counts
+        p = np.zeros(n, dtype=np.float64) if out_p is None else out_p
+        assert counts.size >= 4 * n and p.size >= n
         self._check(self._lib.pd_hardy(self._h, v0, v1, int(bool(midp)), _p(counts), _p(p)))
         return counts, p
 
