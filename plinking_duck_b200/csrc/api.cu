@@ -20,6 +20,7 @@ void DestroyCtx(pd_ctx* c) {
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
+  if (c->d2h_stream) cudaStreamSynchronize(c->d2h_stream);
   c->d_fpos.Free(); c->d_vrtypes.Free(); c->d_ldbase.Free(); c->d_base_slot.Free(); c->d_slot_vidx.Free();
   c->d_resident.Free();
   for (auto& b : c->h_stage) b.Free();
@@ -28,6 +29,14 @@ void DestroyCtx(pd_ctx* c) {
   for (auto e : c->ev_done) cudaEventDestroy(e);
   for (auto e : c->ev_pool) cudaEventDestroy(e);
   c->d_counts.Free(); c->d_scratch.Free(); c->d_misc.Free(); c->d_pvals.Free(); c->d_acc.Free();
+  c->d_dense.Free(); c->d_rowptrs.Free(); c->d_vlist.Free(); c->d_aux.Free(); c->d_aux2.Free();
+  for (int b = 0; b < 2; ++b) {
+    c->d_out[b].Free();
+    c->h_bounce[b].Free();
+    if (c->ev_out_ready[b]) cudaEventDestroy(c->ev_out_ready[b]);
+    if (c->ev_out_free[b]) cudaEventDestroy(c->ev_out_free[b]);
+  }
+  if (c->d2h_stream) cudaStreamDestroy(c->d2h_stream);
   c->h_misc.Free(); c->h_out.Free();
   c->subset.Free();
   if (c->ev_a) cudaEventDestroy(c->ev_a);
@@ -63,6 +72,11 @@ int InitDevice(pd_ctx* c, const pd_open_opts* opts) {
   if ((e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return CheckCuda(c, e, "stream");
   cudaEventCreate(&c->ev_a); cudaEventCreate(&c->ev_b); cudaEventCreate(&c->ev_t0); cudaEventCreate(&c->ev_t1);
   cudaEventCreate(&c->ev_c0); cudaEventCreate(&c->ev_c1);
+  if ((e = cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking)) != cudaSuccess) return CheckCuda(c, e, "stream");
+  for (int b = 0; b < 2; ++b) {
+    cudaEventCreateWithFlags(&c->ev_out_ready[b], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&c->ev_out_free[b], cudaEventDisableTiming);
+  }
   c->h_stage.resize(c->n_staging);
   c->d_stage.resize(c->n_staging);
   c->ev_copied.resize(c->n_staging);

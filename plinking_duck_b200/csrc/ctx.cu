@@ -51,6 +51,7 @@ pdk::SubsetDev SubsetState::Dev() const {
   d.mask1_stride = stride1;
   d.include_words = d_words.as<uint32_t>();
   d.cum_popcount = d_cum.as<uint32_t>();
+  d.subset_idx = d_idx.as<uint32_t>();
   d.subset_ct = count;
   return d;
 }
@@ -59,6 +60,7 @@ void SubsetState::Free() {
   d_cum.Free();
   d_mask2.Free();
   d_mask1.Free();
+  d_idx.Free();
   active = false;
 }
 
@@ -112,6 +114,7 @@ int BuildSubset(pd_ctx_impl* c, const uint64_t* include, const SubsetState* and_
   if (e == cudaSuccess) e = out->d_cum.Reserve(padded * 4);
   if (e == cudaSuccess) e = out->d_mask2.Reserve(16ull * out->stride2);
   if (e == cudaSuccess) e = out->d_mask1.Reserve(16ull * out->stride1);
+  if (e == cudaSuccess) e = out->d_idx.Reserve(std::max<size_t>(16, static_cast<size_t>(cnt) * 4));
   if (e != cudaSuccess) return CheckCuda(c, e, "subset allocation");
   e = cudaMemcpyAsync(out->d_words.p, out->words.data(), padded * 4, cudaMemcpyHostToDevice, c->stream);
   if (e != cudaSuccess) return CheckCuda(c, e, "subset upload");
@@ -120,6 +123,8 @@ int BuildSubset(pd_ctx_impl* c, const uint64_t* include, const SubsetState* and_
                           out->d_mask1.as<uint8_t>(), out->stride1, c->stream, &c->launch_stats);
   pdk::launch_cum_popcount(out->d_words.as<uint32_t>(), padded, out->d_cum.as<uint32_t>(), c->stream,
                            &c->launch_stats);
+  pdk::launch_subset_indices(out->d_words.as<uint32_t>(), out->d_cum.as<uint32_t>(), nwords, out->d_idx.as<uint32_t>(),
+                             c->stream, &c->launch_stats);
   e = cudaStreamSynchronize(c->stream);  // out->words must stay valid until the copy is done
   if (e != cudaSuccess) return CheckCuda(c, e, "subset build");
   out->active = true;
@@ -299,6 +304,135 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
     rc = CheckDeviceError(c);
   }
   return rc;
+}
+
+
+// ---- dense-row batches ---------------------------------------------------------------------------
+
+uint32_t DenseSlotStride(const pd_ctx_impl* c) { return ((c->idx.sample_ct + 3) / 4 + 15) / 16 * 16 + 16; }
+
+namespace {
+
+constexpr uint64_t kDenseScratchBytes = 64ull << 20;  // decoded rows of one batch: stays L2-resident
+constexpr uint32_t kMaxBatchRows = 65536;
+
+uint32_t ClampBatchRows(const pd_ctx_impl* c, uint32_t max_rows) {
+  uint64_t r = max_rows ? max_rows : kMaxBatchRows;
+  if (r > kMaxBatchRows) r = kMaxBatchRows;
+  if (!c->idx.fixed) r = std::min<uint64_t>(r, std::max<uint64_t>(1, kDenseScratchBytes / DenseSlotStride(c)));
+  return static_cast<uint32_t>(std::max<uint64_t>(1, r));
+}
+
+int ReserveDense(pd_ctx_impl* c, uint32_t rows, bool need_ptrs) {
+  cudaError_t e = cudaSuccess;
+  if (!c->idx.fixed) e = c->d_dense.Reserve(static_cast<size_t>(rows) * DenseSlotStride(c) + 64);
+  if (e == cudaSuccess && need_ptrs) e = c->d_rowptrs.Reserve(static_cast<size_t>(rows) * sizeof(void*));
+  return e == cudaSuccess ? PD_OK : CheckCuda(c, e, "dense row scratch allocation");
+}
+
+struct TileBytesGuard {
+  pd_ctx_impl* c;
+  uint64_t saved;
+  TileBytesGuard(pd_ctx_impl* ctx, uint64_t min_bytes) : c(ctx), saved(ctx->tile_bytes) {
+    if (min_bytes > c->tile_bytes) c->tile_bytes = min_bytes;
+  }
+  ~TileBytesGuard() { c->tile_bytes = saved; }
+};
+
+}  // namespace
+
+int RunRows(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t max_rows, uint64_t min_tile_bytes,
+            const RowFn& fn) {
+  const uint32_t cap = ClampBatchRows(c, max_rows);
+  const bool fixed = c->idx.fixed;
+  int rc = ReserveDense(c, cap, !fixed);
+  if (rc != PD_OK) return rc;
+  TileBytesGuard guard(c, min_tile_bytes);
+  const uint32_t slot_stride = DenseSlotStride(c);
+  return RunScan(c, v_begin, v_end, nullptr, [&](const Tile& t, const pdk::RecIndex& ix, cudaStream_t s) {
+    const uint32_t a = std::max(t.v0, v_begin);
+    for (uint32_t v = a; v < t.v1; v += cap) {
+      RowBatch b{};
+      b.row0 = v - v_begin;
+      b.n = std::min(cap, t.v1 - v);
+      b.v_first = v;
+      b.rows.nrows = b.n;
+      b.rows.N = ix.N;
+      if (fixed) {
+        b.rows.base = ix.data + (ix.fixed_start + static_cast<uint64_t>(v) * ix.fixed_width - ix.data_fpos);
+        b.rows.stride = ix.fixed_width;
+      } else {
+        pdk::launch_densify(ix, nullptr, v, b.n, c->d_dense.as<uint8_t>(), slot_stride,
+                            c->d_rowptrs.as<const uint8_t*>(), DevWorkCounter(c), DevErr(c), s, &c->launch_stats);
+        b.rows.ptrs = c->d_rowptrs.as<const uint8_t*>();
+      }
+      const int r = fn(b, ix, s);
+      if (r != PD_OK) return r;
+    }
+    return PD_OK;
+  });
+}
+
+int RunRowsList(pd_ctx_impl* c, const uint32_t* vlist, uint32_t n, uint32_t max_rows, const RowFn& fn) {
+  if (!n) return PD_OK;
+  const PgenIndex& ixh = c->idx;
+  for (uint32_t i = 0; i < n; ++i) {
+    if (vlist[i] >= ixh.variant_ct || (i && vlist[i] <= vlist[i - 1])) {
+      return c->SetError(PD_ERR_INVALID_ARG, "variant list must be strictly ascending and inside the file");
+    }
+  }
+  const uint32_t cap = ClampBatchRows(c, max_rows);
+  int rc = ReserveDense(c, cap, true);
+  if (rc != PD_OK) return rc;
+  cudaError_t e = c->d_vlist.Reserve(static_cast<size_t>(n) * 4);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(c->d_vlist.p, vlist, static_cast<size_t>(n) * 4, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);  // vlist may be pageable caller memory
+  if (e != cudaSuccess) return CheckCuda(c, e, "variant list upload");
+  c->stats.h2d_bytes += static_cast<size_t>(n) * 4;
+  const uint32_t slot_stride = DenseSlotStride(c);
+  // Segments: maximal runs of listed variants whose gaps are small enough that staging the gap
+  // is cheaper than another pipeline start (always one segment when the range is resident).
+  const uint64_t kGapBytes = 4ull << 20;
+  uint32_t i0 = 0;
+  double kernel_ms = 0, total_ms = 0;
+  uint64_t rec_bytes = 0;
+  while (i0 < n) {
+    uint32_t i1 = i0 + 1;
+    while (i1 < n) {
+      const uint64_t gap = ixh.RecOff(ixh.Ldbase(vlist[i1])) - ixh.RecOff(vlist[i1 - 1]);
+      const bool res = c->resident && vlist[i0] >= c->res_v0 && vlist[i1] < c->res_v1;
+      if (!res && gap > kGapBytes) break;
+      ++i1;
+    }
+    rc = RunScan(c, vlist[i0], vlist[i1 - 1] + 1, nullptr, [&](const Tile& t, const pdk::RecIndex& ix, cudaStream_t s) {
+      const uint32_t* lo = std::lower_bound(vlist + i0, vlist + i1, t.v0);
+      const uint32_t* hi = std::lower_bound(vlist + i0, vlist + i1, t.v1);
+      for (uint32_t j = static_cast<uint32_t>(lo - vlist); j < static_cast<uint32_t>(hi - vlist); j += cap) {
+        RowBatch b{};
+        b.row0 = j;
+        b.n = std::min<uint32_t>(cap, static_cast<uint32_t>(hi - vlist) - j);
+        b.v_first = vlist[j];
+        b.d_vlist = c->d_vlist.as<uint32_t>() + j;
+        b.rows.nrows = b.n;
+        b.rows.N = ix.N;
+        pdk::launch_densify(ix, b.d_vlist, 0, b.n, c->d_dense.as<uint8_t>(), slot_stride,
+                            c->d_rowptrs.as<const uint8_t*>(), DevWorkCounter(c), DevErr(c), s, &c->launch_stats);
+        b.rows.ptrs = c->d_rowptrs.as<const uint8_t*>();
+        const int r = fn(b, ix, s);
+        if (r != PD_OK) return r;
+      }
+      return PD_OK;
+    });
+    if (rc != PD_OK) return rc;
+    kernel_ms += c->stats.kernel_ms;
+    total_ms += c->stats.total_ms;
+    rec_bytes += c->stats.record_bytes;
+    i0 = i1;
+  }
+  c->stats.kernel_ms = kernel_ms;
+  c->stats.total_ms = total_ms;
+  c->stats.record_bytes = rec_bytes;
+  return PD_OK;
 }
 
 }  // namespace pdx

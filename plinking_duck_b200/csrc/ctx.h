@@ -42,7 +42,7 @@ struct SubsetState {
   bool active = false;
   uint32_t count = 0;
   std::vector<uint32_t> words;  // N bits as 32-bit words, padded
-  DevBuf d_words, d_cum, d_mask2, d_mask1;
+  DevBuf d_words, d_cum, d_mask2, d_mask1, d_idx;  // d_idx: raw index of every subset sample, ascending
   uint32_t stride2 = 0, stride1 = 0;
   pdk::SubsetDev Dev() const;
   void Free();
@@ -85,6 +85,10 @@ struct pd_ctx_impl {
 
   // work buffers
   DevBuf d_counts, d_scratch, d_misc, d_pvals, d_acc;
+  DevBuf d_dense, d_rowptrs, d_vlist, d_out[2], d_aux, d_aux2;  // dense-row batches and their outputs
+  PinnedBuf h_bounce[2];
+  cudaStream_t d2h_stream = nullptr;
+  cudaEvent_t ev_out_ready[2] = {nullptr, nullptr}, ev_out_free[2] = {nullptr, nullptr};
   PinnedBuf h_misc;   // int err[2] + small readbacks
   PinnedBuf h_out;    // pinned bounce buffer for results
   cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_t0 = nullptr, ev_t1 = nullptr, ev_c0 = nullptr, ev_c1 = nullptr;
@@ -117,6 +121,26 @@ int* DevErr(pd_ctx_impl* c);
 uint32_t* DevWorkCounter(pd_ctx_impl* c);
 uint32_t ExtendToBase(const pd_ctx_impl* c, uint32_t v);
 int BuildSubset(pd_ctx_impl* c, const uint64_t* include, const SubsetState* and_with, SubsetState* out);
+
+// One batch of dense 2-bit rows handed to a sample-wise consumer.
+struct RowBatch {
+  uint32_t row0;           // index of the batch's first row in the operation's row space
+  uint32_t n;              // rows in this batch
+  uint32_t v_first;        // variant of row 0 when the batch is a contiguous range
+  const uint32_t* d_vlist; // device list of the batch's variants (list mode), else nullptr
+  pdk::DenseRows rows;
+};
+using RowFn = std::function<int(const RowBatch&, const pdk::RecIndex&, cudaStream_t)>;
+
+// Streams [v_begin, v_end) through the staging pipeline (or the resident copy) and hands it to fn
+// in batches of at most max_rows dense rows.  min_tile_bytes raises the staging tile size for
+// consumers that amortise per-launch work over many rows.
+int RunRows(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t max_rows, uint64_t min_tile_bytes,
+            const RowFn& fn);
+// Same for an ascending list of distinct variants (host array); rows follow the list order.
+int RunRowsList(pd_ctx_impl* c, const uint32_t* vlist, uint32_t n, uint32_t max_rows, const RowFn& fn);
+uint32_t DenseSlotStride(const pd_ctx_impl* c);
+int DownloadRows(pd_ctx_impl* c, const void* dev, size_t bytes, void* host);
 
 }  // namespace pdx
 

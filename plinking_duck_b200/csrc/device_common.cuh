@@ -266,13 +266,15 @@ __device__ __forceinline__ bool parse_difflist(const uint8_t*& p, const uint8_t*
 }
 
 // Warp-cooperative walk: lane g of each batch of 32 groups decodes group g serially and calls
-// f(sample_id, geno2bit) for every entry.  Group start offsets come from a warp prefix sum of
+// f(sample_id, geno2bit, entry_ordinal) for every entry.  Group start offsets come from a warp prefix sum of
 // the stored group byte lengths, which is what makes the varint stream parallel at group
 // granularity.  Returns false (on all lanes) if any lane saw malformed input.
 template <class F>
-__device__ __forceinline__ bool difflist_walk(const Difflist& d, uint32_t N, int lane, F f) {
+__device__ __forceinline__ bool difflist_walk(const Difflist& d, uint32_t N, int lane, F f,
+                                              const uint8_t** track_end = nullptr) {
   bool ok = true;
   uint64_t batch_off = 0;
+  const uint8_t* my_end = d.deltas;  // meaningful on the lane that walked the last group
   for (uint32_t g0 = 0; g0 < d.ngroups; g0 += 32) {
     const uint32_t g = g0 + lane;
     uint32_t sz = 0;
@@ -303,7 +305,7 @@ __device__ __forceinline__ bool difflist_walk(const Difflist& d, uint32_t N, int
             break;
           }
           if (d.raregeno && !(k & 3)) gb = d.raregeno[(g << 4) + (k >> 2)];
-          f(id, (gb >> (2 * (k & 3))) & 3u);
+          f(id, (gb >> (2 * (k & 3))) & 3u, (g << 6) + k);
           if (k + 1 < cnt) {
             uint32_t delta;
             if (!get_vint31(ptr, gend, delta)) {
@@ -313,9 +315,17 @@ __device__ __forceinline__ bool difflist_walk(const Difflist& d, uint32_t N, int
             id += delta;
           }
         }
+        my_end = ptr;
       }
     }
     batch_off += total;
+  }
+  if (track_end) {
+    // byte after the last group's deltas = end of the whole difflist
+    const uint32_t last_lane = d.ngroups ? ((d.ngroups - 1) & 31u) : 0u;
+    const unsigned long long e =
+        __shfl_sync(0xffffffffu, static_cast<unsigned long long>(reinterpret_cast<uintptr_t>(my_end)), last_lane);
+    *track_end = reinterpret_cast<const uint8_t*>(static_cast<uintptr_t>(e));
   }
   return __all_sync(0xffffffffu, ok);
 }
@@ -327,8 +337,31 @@ __device__ __forceinline__ uint32_t geno_at(const uint8_t* dense, uint32_t id) {
 __device__ __forceinline__ bool bit_at(const uint8_t* bits, uint32_t id) { return (bits[id >> 3] >> (id & 7)) & 1u; }
 
 
-// ---- full decode of one non-LD record into a dense, word-aligned 2-bit genovec ----------------
-// dst: ceil(N/16) 32-bit words (global or shared), warp-cooperative.  Types 0, 1, 4, 5, 6, 7
+// ---- unaligned bit-window loads ------------------------------------------------------------------
+// 32 bits starting `bitoff` bits after byte pointer `row` (any alignment); reads the two aligned
+// 32-bit words that cover the window, so up to 7 bytes past the window may be touched (every
+// record buffer carries >= 16 B of slack).
+__device__ __forceinline__ uint32_t load_bits32(const uint8_t* row, uint64_t bitoff) {
+  const uintptr_t a = reinterpret_cast<uintptr_t>(row) + (bitoff >> 3);
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~static_cast<uintptr_t>(3));
+  const uint32_t sh = (static_cast<uint32_t>(a & 3) << 3) + static_cast<uint32_t>(bitoff & 7);
+  const uint32_t lo = __ldg(w);
+  if (sh == 0) return lo;
+  return __funnelshift_r(lo, __ldg(w + 1), sh);
+}
+
+// Word k (16 genotypes) of a packed 2-bit row at any byte alignment.
+__device__ __forceinline__ uint32_t row_word(const uint8_t* row, uint32_t k) {
+  return load_bits32(row, static_cast<uint64_t>(k) << 5);
+}
+
+// Same through L2 only (rows that other lanes patched with atomics moments ago).
+__device__ __forceinline__ uint32_t geno_at_cg(const uint32_t* dense_words, uint32_t id) {
+  return (__ldcg(dense_words + (id >> 4)) >> (2 * (id & 15))) & 3u;
+}
+
+// ---- full decode of one record into a dense, word-aligned 2-bit genovec --------------------------
+// dst: ceil(N/16) 32-bit words (global), warp-cooperative.  Types 0, 1, 4, 5, 6, 7
 // (ParseNonLdGenovecSubsetUnsafe, pgenlib_read.cc:2711-2741, without the subsetting).  Difflist
 // entries are patched with atomicXor of (background ^ new) so that lanes touching the same word
 // cannot lose updates.  Returns false on malformed input (uniform across the warp).
@@ -346,15 +379,7 @@ __device__ __forceinline__ bool decode_nonld_dense(uint32_t main, const uint8_t*
   const uint32_t geno_bytes = (N + 3) >> 2;
   if (main == 0) {
     if (static_cast<uint64_t>(end - p) < geno_bytes) return false;
-    for (uint32_t w = lane; w < nwords; w += 32) {
-      const uint32_t b0 = w << 2;
-      uint32_t x = 0;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        if (b0 + j < geno_bytes) x |= static_cast<uint32_t>(p[b0 + j]) << (8 * j);
-      }
-      dst[w] = x;
-    }
+    for (uint32_t w = lane; w < nwords; w += 32) dst[w] = row_word(p, w);
     __syncwarp();
     return true;
   }
@@ -372,8 +397,7 @@ __device__ __forceinline__ bool decode_nonld_dense(uint32_t main, const uint8_t*
     if (low + delta > 3u) return false;
     const uint8_t* bits = p + 1;
     for (uint32_t w = lane; w < nwords; w += 32) {
-      uint32_t b16 = bits[2 * w];
-      if (2 * w + 1 < bit_bytes) b16 |= static_cast<uint32_t>(bits[2 * w + 1]) << 8;
+      const uint32_t b16 = load_bits32(bits, static_cast<uint64_t>(w) << 4) & 0xffffu;
       dst[w] = low * kM5 + spread16(b16) * delta;
     }
     __syncwarp();
@@ -382,7 +406,7 @@ __device__ __forceinline__ bool decode_nonld_dense(uint32_t main, const uint8_t*
     if (!parse_difflist(q, end, N, true, d)) return false;
     bool ok = true;
     if (d.len) {
-      ok = difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g) {
+      ok = difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g, uint32_t) {
         const uint32_t orig = low + (bit_at(bits, id) ? delta : 0u);
         atomicXor(&dst[id >> 4], (orig ^ g) << (2 * (id & 15)));
       });
@@ -399,7 +423,7 @@ __device__ __forceinline__ bool decode_nonld_dense(uint32_t main, const uint8_t*
     if (!parse_difflist(q, end, N, true, d)) return false;
     bool ok = true;
     if (d.len) {
-      ok = difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g) {
+      ok = difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g, uint32_t) {
         atomicXor(&dst[id >> 4], (common ^ g) << (2 * (id & 15)));
       });
     }
@@ -407,6 +431,34 @@ __device__ __forceinline__ bool decode_nonld_dense(uint32_t main, const uint8_t*
     return ok;
   }
   return false;
+}
+
+// LD-compressed record (type 2 / 3) on top of an already decoded copy of its base in dst:
+// patch the difflist entries in, then swap categories 0 and 2 for type 3
+// (ReadGenovecSubsetUnsafe, pgenlib_read.cc:2863-2869; GenovecInvertUnsafe, pgenlib_misc.h:303).
+__device__ __forceinline__ bool apply_ld_record(uint32_t main, const uint8_t* p, const uint8_t* end, uint32_t N,
+                                                uint32_t* dst, int lane) {
+  const uint32_t nwords = (N + 15) >> 4;
+  const uint8_t* q = p;
+  Difflist d;
+  if (!parse_difflist(q, end, N, true, d)) return false;
+  bool ok = true;
+  if (d.len) {
+    __threadfence_block();
+    ok = difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g, uint32_t) {
+      const uint32_t old = geno_at_cg(dst, id);  // each sample id occurs once per difflist
+      atomicXor(&dst[id >> 4], (old ^ g) << (2 * (id & 15)));
+    });
+  }
+  __syncwarp();
+  if (main == 3) {
+    for (uint32_t w = lane; w < nwords; w += 32) {
+      const uint32_t x = __ldcg(dst + w);
+      dst[w] = x ^ ((~x & kM5) << 1);
+    }
+    __syncwarp();
+  }
+  return ok;
 }
 
 }  // namespace pdk

@@ -27,6 +27,7 @@ struct SubsetDev {
   uint32_t mask1_stride;
   const uint32_t* include_words;// unshifted 1-bit mask as 32-bit words, padded
   const uint32_t* cum_popcount; // exclusive prefix popcount per 32-bit word (RawToSubsettedPos)
+  const uint32_t* subset_idx;   // [subset_ct] raw sample index of every subset sample, ascending
   uint32_t subset_ct;
 };
 
@@ -61,6 +62,32 @@ void launch_count_var(const RecIndex& ix, const SubsetDev& sub, const LdScratch&
 // Dense 2-bit copies of the LD bases slot_lo..slot_hi (inclusive) listed in slot_vidx.
 void launch_decode_bases(const RecIndex& ix, const uint32_t* slot_vidx, const LdScratch& scratch, uint32_t slot_hi,
                          int* err, cudaStream_t s, LaunchStats* st);
+
+// ---- dense 2-bit rows of a batch of variants (K3b) and their sample-wise consumers (K4, K5) ----
+struct DenseRows {
+  const uint8_t* const* ptrs;  // [nrows] byte pointers (any alignment), or nullptr:
+  const uint8_t* base;         //   row r at base + r * stride (fixed-width records, used in place)
+  uint64_t stride;
+  uint32_t nrows;
+  uint32_t N;                  // raw sample count; bits past N in a row are undefined
+};
+
+// Row r = variant vlist[r] (vlist != nullptr) or v0 + r.  Type-0 records are pointed at in place,
+// everything else (difflist, 1-bit, LD with its base resolved) is decoded into scratch slot r.
+void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint32_t nrows, uint8_t* scratch,
+                    uint32_t slot_stride, const uint8_t** ptrs, uint32_t* work_counter, int* err, cudaStream_t s,
+                    LaunchStats* st);
+// out[r * n_out + j] = {0,1,2,-9} of sample subset_idx[j] (or j) -- PgrGet + GenoarrToBytesMinus9.
+void launch_expand_i8(const DenseRows& rows, const uint32_t* subset_idx, uint32_t n_out, int8_t* out, cudaStream_t s,
+                      LaunchStats* st);
+// acc_*[raw sample] += number of rows where the sample is het / hom-alt / missing.
+// kinds: bit 0 het, bit 1 hom-alt, bit 2 missing (4 = missing only, 7 = all three).
+void launch_sample_acc(const DenseRows& rows, uint32_t kinds, uint32_t* acc_het, uint32_t* acc_hom, uint32_t* acc_mis,
+                       cudaStream_t s, LaunchStats* st);
+void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t n, uint32_t* dst, cudaStream_t s,
+                       LaunchStats* st);
+void launch_subset_indices(const uint32_t* include_words, const uint32_t* cum, uint32_t nwords, uint32_t* out,
+                           cudaStream_t s, LaunchStats* st);
 
 // ---- K8: exact Hardy-Weinberg test on the device ----
 // counts[n] as produced by the count kernels; out_p[n] = p-value clamped to [0,1].

@@ -123,7 +123,7 @@ k_count_var(RecIndex ix, SubsetDev sub, LdScratch scratch, uint32_t v_begin, uin
               cnt[code_high] = high_ct;
             } else {
               uint32_t t0 = 0, t1 = 0, t2 = 0, t3 = 0, hdec = 0;
-              ok = difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g) {
+              ok = difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g, uint32_t) {
                 if (included(sub, id)) {
                   t0 += (g == 0); t1 += (g == 1); t2 += (g == 2); t3 += (g == 3);
                   hdec += bit_at(bits, id);
@@ -162,7 +162,7 @@ k_count_var(RecIndex ix, SubsetDev sub, LdScratch scratch, uint32_t v_begin, uin
             cnt[common] = n_eff - d.len;
           } else {
             uint32_t t0 = 0, t1 = 0, t2 = 0, t3 = 0;
-            ok = difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g) {
+            ok = difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g, uint32_t) {
               if (included(sub, id)) {
                 t0 += (g == 0); t1 += (g == 1); t2 += (g == 2); t3 += (g == 3);
               }
@@ -192,7 +192,7 @@ k_count_var(RecIndex ix, SubsetDev sub, LdScratch scratch, uint32_t v_begin, uin
       ok = parse_difflist(q, end, N, true, d);
       if (ok && d.len) {
         int32_t i0 = 0, i1 = 0, i2 = 0, i3 = 0;
-        ok = difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g) {
+        ok = difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g, uint32_t) {
           if (!MASKED || included(sub, id)) {
             const uint32_t old = geno_at(dense, id);
             i0 += static_cast<int32_t>(g == 0) - static_cast<int32_t>(old == 0);

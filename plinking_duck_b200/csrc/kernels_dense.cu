@@ -1,0 +1,332 @@
+// K3b/K4/K5: dense 2-bit rows for a batch of variants, and the consumers that read them
+// sample-wise: int8 expansion (read_pgen / read_pfile) and per-sample het / hom-alt / missing
+// accumulators (plink_missing sample mode, read_pfile orient := 'sample').
+//
+// Reference code these replace:
+//   * PgrGet -> ReadGenovecSubsetUnsafe (pgenlib_read.cc:2847-2912) for every vrtype, incl. the
+//     LD cache (LdLoadAndCopyGenovecSubset :2808-2838): k_densify
+//   * GenoarrToBytesMinus9 (pgenlib_ffi_support.cc:25-43) + CopyNyparrNonemptySubset: k_expand_i8
+//   * PgrGetMissingness + the ctz walk (src/plink_missing.cpp:593-609) and the dense Phase-1
+//     loop of src/pfile_reader.cpp:3322-3428: k_sample_acc
+#include "device_common.cuh"
+#include "kernels.cuh"
+
+namespace pdk {
+
+namespace {
+
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ void report_error(int* err, int code, uint32_t vidx) {
+  if (atomicCAS(&err[0], 0, code) == 0) err[1] = static_cast<int>(vidx);
+}
+
+__device__ __forceinline__ const uint8_t* row_ptr(const DenseRows& rows, uint32_t r) {
+  return rows.ptrs ? rows.ptrs[r] : rows.base + static_cast<uint64_t>(r) * rows.stride;
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_densify: one warp per row (claimed from a counter: records differ in size by 1000x).
+// Row r is variant vlist[r] (or v0 + r).  Type-0 records are used in place; every other type is
+// decoded into scratch slot r.  LD records decode their base into their own slot first, so rows
+// are independent of each other and of batch boundaries.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+k_densify(RecIndex ix, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t nrows, uint8_t* __restrict__ scratch,
+          uint32_t slot_stride, const uint8_t** __restrict__ ptrs, uint32_t* __restrict__ work_counter,
+          int* __restrict__ err) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t N = ix.N;
+  for (;;) {
+    uint32_t r = 0;
+    if (lane == 0) r = atomicAdd(work_counter, 1u);
+    r = __shfl_sync(0xffffffffu, r, 0);
+    if (r >= nrows) return;
+    const uint32_t v = vlist ? vlist[r] : v0 + r;
+    if (!ix.fpos) {  // fixed-width file: every main track is a raw 2-bit array, used in place
+      if (lane == 0) ptrs[r] = ix.data + (ix.fixed_start + static_cast<uint64_t>(v) * ix.fixed_width - ix.data_fpos);
+      continue;
+    }
+    const uint32_t main = ix.vrtypes[v] & 7u;
+    const uint8_t* p = ix.data + (ix.fpos[v] - ix.data_fpos);
+    const uint8_t* end = ix.data + (ix.fpos[v + 1] - ix.data_fpos);
+    uint32_t* slot = reinterpret_cast<uint32_t*>(scratch + static_cast<uint64_t>(r) * slot_stride);
+    bool ok = true;
+    const uint8_t* out = reinterpret_cast<const uint8_t*>(slot);
+    if (main == 0) {
+      ok = static_cast<uint64_t>(end - p) >= ((N + 3) >> 2);
+      out = p;
+    } else if (main == 2 || main == 3) {
+      const uint32_t b = ix.ldbase[v];
+      const uint32_t bmain = ix.vrtypes[b] & 7u;
+      const uint8_t* bp = ix.data + (ix.fpos[b] - ix.data_fpos);
+      const uint8_t* bend = ix.data + (ix.fpos[b + 1] - ix.data_fpos);
+      ok = (b < v) && bmain != 2 && bmain != 3 && decode_nonld_dense(bmain, bp, bend, N, slot, lane);
+      if (ok) ok = apply_ld_record(main, p, end, N, slot, lane);
+    } else {
+      ok = decode_nonld_dense(main, p, end, N, slot, lane);
+    }
+    if (lane == 0) {
+      if (!ok) report_error(err, kErrMalformed, v);
+      ptrs[r] = out;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_expand_i8: the whole (nrows x n_out) int8 matrix as one flat byte array; each thread owns 16
+// consecutive output bytes (one 128-bit store).  Fast path: the 16 bytes sit inside one row and
+// no subset is active -> one 32-bit window load + bit tricks.  Otherwise per-byte gather.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t expand4(uint32_t b) {
+  // 4 genotypes (8 bits) -> 4 bytes {0,1,2,-9}
+  const uint32_t t = (b | (b << 6) | (b << 12) | (b << 18)) & 0x03030303u;
+  const uint32_t m = t & (t >> 1) & 0x01010101u;
+  return t ^ (m * 0xF4u);
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_expand_i8(DenseRows rows, const uint32_t* __restrict__ subset_idx, uint32_t n_out, uint64_t total_bytes,
+            int8_t* __restrict__ out) {
+  const uint64_t nchunks = (total_bytes + 15) >> 4;
+  for (uint64_t c = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; c < nchunks;
+       c += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
+    const uint64_t f0 = c << 4;
+    uint32_t r = static_cast<uint32_t>(f0 / n_out);
+    uint32_t col = static_cast<uint32_t>(f0 - static_cast<uint64_t>(r) * n_out);
+    if (!subset_idx && col + 16 <= n_out && f0 + 16 <= total_bytes) {
+      const uint32_t x = load_bits32(row_ptr(rows, r), static_cast<uint64_t>(col) << 1);
+      uint4 o;
+      o.x = expand4(x & 0xffu);
+      o.y = expand4((x >> 8) & 0xffu);
+      o.z = expand4((x >> 16) & 0xffu);
+      o.w = expand4(x >> 24);
+      *reinterpret_cast<uint4*>(out + f0) = o;
+    } else {
+      const uint8_t* row = row_ptr(rows, r);
+      const uint32_t n = static_cast<uint32_t>(min(static_cast<uint64_t>(16), total_bytes - f0));
+      for (uint32_t k = 0; k < n; ++k) {
+        const uint32_t raw = subset_idx ? subset_idx[col] : col;
+        const uint32_t g = geno_at(row, raw);
+        out[f0 + k] = static_cast<int8_t>(g == 3 ? -9 : static_cast<int>(g));
+        if (++col == n_out) {
+          col = 0;
+          ++r;
+          if (f0 + k + 1 < total_bytes) row = row_ptr(rows, r);
+        }
+      }
+    }
+  }
+}
+
+}  // namespace
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------
+// k_sample_acc: transposed pass.  A thread owns one 32-bit word column (16 samples) and walks
+// the rows of its chunk; loads of a warp are 128 contiguous bytes of one record.  Per-sample
+// counters are kept bit-sliced in registers and widened 2 -> 4 -> 8 bits (3 / 15 / 255 rows of
+// headroom), so the steady state costs ~5 integer ops per flag kind per word; only every 255
+// rows (or at chunk end) the 8-bit lanes are flushed to the global uint32 accumulators.
+// ---------------------------------------------------------------------------------------------
+struct Widen {
+  uint32_t b0, b1;  // 4-bit fields: samples 2j / 2j+1
+  uint32_t c[4];    // 8-bit fields: samples 4k, 4k+2, 4k+1, 4k+3
+  __device__ __forceinline__ void clear() {
+    b0 = b1 = 0;
+    c[0] = c[1] = c[2] = c[3] = 0;
+  }
+  __device__ __forceinline__ void add_a(uint32_t a) {  // a: 2-bit fields, each <= 3
+    b0 += a & 0x33333333u;
+    b1 += (a >> 2) & 0x33333333u;
+  }
+  __device__ __forceinline__ void b_to_c() {
+    c[0] += b0 & 0x0F0F0F0Fu;
+    c[1] += (b0 >> 4) & 0x0F0F0F0Fu;
+    c[2] += b1 & 0x0F0F0F0Fu;
+    c[3] += (b1 >> 4) & 0x0F0F0F0Fu;
+    b0 = b1 = 0;
+  }
+  __device__ __forceinline__ void flush(uint32_t* __restrict__ acc, uint32_t s0, uint32_t N) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t x = c[q];
+      if (x) {
+        const uint32_t off = (q == 0) ? 0u : (q == 1) ? 2u : (q == 2) ? 1u : 3u;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint32_t val = (x >> (8 * k)) & 0xffu;
+          const uint32_t s = s0 + 4u * k + off;
+          if (val && s < N) atomicAdd(acc + s, val);
+        }
+      }
+      c[q] = 0;
+    }
+  }
+};
+
+template <int KINDS>
+__device__ __forceinline__ void acc_flags(uint32_t x, uint32_t& het, uint32_t& hom, uint32_t& mis) {
+  const uint32_t e = x & kM5, o = (x >> 1) & kM5;
+  if (KINDS & 1) het += e & ~o;
+  if (KINDS & 2) hom += o & ~e;
+  if (KINDS & 4) mis += e & o;
+}
+
+template <int KINDS>
+__global__ void __launch_bounds__(128)
+k_sample_acc(DenseRows rows, uint32_t rows_per_chunk, uint32_t* __restrict__ acc_het, uint32_t* __restrict__ acc_hom,
+             uint32_t* __restrict__ acc_mis) {
+  const uint32_t N = rows.N;
+  const uint32_t ncols = (N + 15) >> 4;
+  const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= ncols) return;
+  const uint32_t r0 = blockIdx.y * rows_per_chunk;
+  const uint32_t r1 = min(rows.nrows, r0 + rows_per_chunk);
+  const uint32_t valid = min(16u, N - 16u * w);
+  const uint32_t colmask = valid == 16 ? 0xffffffffu : ((1u << (2 * valid)) - 1u);
+  Widen het, hom, mis;
+  het.clear();
+  hom.clear();
+  mis.clear();
+  uint32_t nb = 0, nc = 0;
+  auto step_b = [&]() {
+    if (++nb == 5) {
+      nb = 0;
+      if (KINDS & 1) het.b_to_c();
+      if (KINDS & 2) hom.b_to_c();
+      if (KINDS & 4) mis.b_to_c();
+      if (++nc == 17) {
+        nc = 0;
+        if (KINDS & 1) het.flush(acc_het, 16u * w, N);
+        if (KINDS & 2) hom.flush(acc_hom, 16u * w, N);
+        if (KINDS & 4) mis.flush(acc_mis, 16u * w, N);
+      }
+    }
+  };
+  uint32_t r = r0;
+  for (; r + 6 <= r1; r += 6) {
+    uint32_t x[6];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) x[j] = row_word(row_ptr(rows, r + j), w) & colmask;
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+      uint32_t a_het = 0, a_hom = 0, a_mis = 0;
+#pragma unroll
+      for (int j = 0; j < 3; ++j) acc_flags<KINDS>(x[3 * t + j], a_het, a_hom, a_mis);
+      if (KINDS & 1) het.add_a(a_het);
+      if (KINDS & 2) hom.add_a(a_hom);
+      if (KINDS & 4) mis.add_a(a_mis);
+      step_b();
+    }
+  }
+  while (r < r1) {
+    uint32_t a_het = 0, a_hom = 0, a_mis = 0;
+    for (int j = 0; j < 3 && r < r1; ++j, ++r) {
+      acc_flags<KINDS>(row_word(row_ptr(rows, r), w) & colmask, a_het, a_hom, a_mis);
+    }
+    if (KINDS & 1) het.add_a(a_het);
+    if (KINDS & 2) hom.add_a(a_hom);
+    if (KINDS & 4) mis.add_a(a_mis);
+    step_b();
+  }
+  if (KINDS & 1) { het.b_to_c(); het.flush(acc_het, 16u * w, N); }
+  if (KINDS & 2) { hom.b_to_c(); hom.flush(acc_hom, 16u * w, N); }
+  if (KINDS & 4) { mis.b_to_c(); mis.flush(acc_mis, 16u * w, N); }
+}
+
+__global__ void k_gather_u32(const uint32_t* __restrict__ src, const uint32_t* __restrict__ idx, uint32_t n,
+                             uint32_t* __restrict__ dst) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = src[idx ? idx[i] : i];
+}
+
+// Raw index of every subset sample, ascending (the subset order of PgrSampleSubsetIndex).
+__global__ void k_subset_indices(const uint32_t* __restrict__ include_words, const uint32_t* __restrict__ cum,
+                                 uint32_t nwords, uint32_t* __restrict__ out) {
+  const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= nwords) return;
+  uint32_t bits = include_words[w];
+  uint32_t pos = cum[w];
+  while (bits) {
+    out[pos++] = 32u * w + (__ffs(bits) - 1);
+    bits &= bits - 1;
+  }
+}
+
+int g_sm = 0;
+int sm_count() {
+  if (!g_sm) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_sm, cudaDevAttrMultiProcessorCount, dev);
+    if (g_sm <= 0) g_sm = 148;
+  }
+  return g_sm;
+}
+
+}  // namespace
+
+void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint32_t nrows, uint8_t* scratch,
+                    uint32_t slot_stride, const uint8_t** ptrs, uint32_t* work_counter, int* err, cudaStream_t s,
+                    LaunchStats* st) {
+  if (!nrows) return;
+  cudaMemsetAsync(work_counter, 0, sizeof(uint32_t), s);
+  uint64_t blocks = (static_cast<uint64_t>(nrows) * 32 + kThreads - 1) / kThreads;
+  const uint64_t max_blocks = static_cast<uint64_t>(sm_count()) * 8;
+  if (blocks > max_blocks) blocks = max_blocks;
+  k_densify<<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, vlist, v0, nrows, scratch, slot_stride, ptrs,
+                                                              work_counter, err);
+  if (st) st->launches++;
+}
+
+void launch_expand_i8(const DenseRows& rows, const uint32_t* subset_idx, uint32_t n_out, int8_t* out, cudaStream_t s,
+                      LaunchStats* st) {
+  const uint64_t total = static_cast<uint64_t>(rows.nrows) * n_out;
+  if (!total) return;
+  const uint64_t nchunks = (total + 15) >> 4;
+  uint64_t blocks = (nchunks + kThreads - 1) / kThreads;
+  const uint64_t max_blocks = static_cast<uint64_t>(sm_count()) * 32;
+  if (blocks > max_blocks) blocks = max_blocks;
+  k_expand_i8<<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(rows, subset_idx, n_out, total, out);
+  if (st) st->launches++;
+}
+
+void launch_sample_acc(const DenseRows& rows, uint32_t kinds, uint32_t* acc_het, uint32_t* acc_hom, uint32_t* acc_mis,
+                       cudaStream_t s, LaunchStats* st) {
+  if (!rows.nrows || !rows.N) return;
+  const uint32_t ncols = (rows.N + 15) >> 4;
+  const uint32_t bx = (ncols + 127) / 128;
+  // aim at ~16 CTAs of 128 threads per SM, but keep >= 510 rows per chunk when rows allow so
+  // that the 8-bit -> 32-bit flushes stay rare
+  uint32_t want_y = (static_cast<uint32_t>(sm_count()) * 16 + bx - 1) / bx;
+  if (want_y < 1) want_y = 1;
+  uint32_t rpc = (rows.nrows + want_y - 1) / want_y;
+  if (rpc < 255) rpc = 255;
+  rpc = (rpc + 5) / 6 * 6;
+  const uint32_t by = (rows.nrows + rpc - 1) / rpc;
+  dim3 grid(bx, by);
+  switch (kinds) {
+    case 4: k_sample_acc<4><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis); break;
+    case 7: k_sample_acc<7><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis); break;
+    default: k_sample_acc<7><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis); break;
+  }
+  if (st) st->launches++;
+}
+
+void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t n, uint32_t* dst, cudaStream_t s,
+                       LaunchStats* st) {
+  if (!n) return;
+  k_gather_u32<<<(n + 255) / 256, 256, 0, s>>>(src, idx, n, dst);
+  if (st) st->launches++;
+}
+
+void launch_subset_indices(const uint32_t* include_words, const uint32_t* cum, uint32_t nwords, uint32_t* out,
+                           cudaStream_t s, LaunchStats* st) {
+  if (!nwords) return;
+  k_subset_indices<<<(nwords + 255) / 256, 256, 0, s>>>(include_words, cum, nwords, out);
+  if (st) st->launches++;
+}
+
+}  // namespace pdk

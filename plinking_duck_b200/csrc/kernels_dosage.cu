@@ -1,0 +1,344 @@
+// K6: dosage tracks.  Replaces PgrGetD -> ReadGenovecHphaseSubsetUnsafe + ParseDosage16
+// (pgenlib_read.cc:7484-7505, 7210-7482) + Dosage16ToDoublesMinus9 (pgenlib_ffi_support.cc:268-279)
+// and the dosage half of PgrGetDCounts -> GetBasicGenotypeCountsAndDosage16s (:7921-8172).
+//
+// Record layout after the main genotype track (pgen_spec.tex:469-610): [aux1 multiallelic patches,
+// bit 3] [aux2 hardcall phase, bit 4] [aux3 dosage-present list / bitarray] [aux4 u16 dosages]
+// [aux7/8 dosage phase, bit 7].  The dosage track can only be found by walking what precedes it:
+// the main track's difflist ends where its last varint group ends, and the phase track's length
+// depends on the number of heterozygous hardcalls (SkipAux2, pgenlib_read.cc:6844-6865).
+#include "device_common.cuh"
+#include "kernels.cuh"
+
+namespace pdk {
+
+namespace {
+
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ void report_error(int* err, int code, uint32_t vidx) {
+  if (atomicCAS(&err[0], 0, code) == 0) err[1] = static_cast<int>(vidx);
+}
+
+__device__ __forceinline__ const uint8_t* row_ptr(const DenseRows& rows, uint32_t r) {
+  return rows.ptrs ? rows.ptrs[r] : rows.base + static_cast<uint64_t>(r) * rows.stride;
+}
+
+__device__ __forceinline__ uint32_t ld_u16(const uint8_t* p, uint32_t i) {
+  return static_cast<uint32_t>(p[2ull * i]) | (static_cast<uint32_t>(p[2ull * i + 1]) << 8);
+}
+
+// End of a difflist that starts at q (warp-uniform result).  has_geno: 2-bit values present.
+__device__ __forceinline__ bool difflist_end(const uint8_t* q, const uint8_t* end, uint32_t N, bool has_geno, int lane,
+                                             const uint8_t** out_end, Difflist* out_d) {
+  Difflist d;
+  if (!parse_difflist(q, end, N, has_geno, d)) return false;
+  if (out_d) *out_d = d;
+  if (!d.len) {
+    *out_end = q;
+    return true;
+  }
+  return difflist_walk(d, N, lane, [](uint32_t, uint32_t, uint32_t) {}, out_end);
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_dosage_locate: one warp per row.  Finds aux3 / aux4, validates their extent, and for the
+// bitarray form writes the exclusive prefix popcount per 32-bit word (rank table) used to map a
+// sample to its slot in the u16 value array.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+k_dosage_locate(RecIndex ix, DenseRows rows, const uint32_t* __restrict__ vlist, uint32_t v0,
+                DosageLoc* __restrict__ loc, uint32_t* __restrict__ rank, uint32_t rank_stride,
+                int* __restrict__ err) {
+  const uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (r >= rows.nrows) return;
+  const uint32_t N = ix.N;
+  const uint32_t v = vlist ? vlist[r] : v0 + r;
+  uint32_t vrtype;
+  const uint8_t *p, *end;
+  if (ix.fpos) {
+    vrtype = ix.vrtypes[v];
+    p = ix.data + (ix.fpos[v] - ix.data_fpos);
+    end = ix.data + (ix.fpos[v + 1] - ix.data_fpos);
+  } else {
+    vrtype = ix.const_vrtype;
+    p = ix.data + (ix.fixed_start + static_cast<uint64_t>(v) * ix.fixed_width - ix.data_fpos);
+    end = p + ix.fixed_width;
+  }
+  DosageLoc out;
+  out.track3 = nullptr;
+  out.values = nullptr;
+  out.kind = 0;
+  out.raw_ct = 0;
+  const uint32_t dos = (vrtype >> 5) & 3u;
+  int bad = 0;
+  if (dos) {
+    if (vrtype & 0x08u) {
+      bad = kErrNotSupported;  // multiallelic dosage: pgenlib_read.cc:7350-7356 refuses it too
+    } else {
+      const uint32_t main = vrtype & 7u;
+      const uint8_t* q = p;
+      bool ok = true;
+      if (main == 0) {
+        q = p + ((N + 3) >> 2);
+      } else if (main == 1) {
+        q = p + 1 + ((N + 7) >> 3);
+        ok = q <= end && difflist_end(q, end, N, true, lane, &q, nullptr);
+      } else if (main != 5) {
+        ok = difflist_end(q, end, N, true, lane, &q, nullptr);
+      }
+      ok = ok && q <= end;
+      if (ok && (vrtype & 0x10u)) {
+        // aux2: 1 + het_ct/8 bytes; if bit 0 is set they are an explicit phasepresent array and
+        // ceil(popcount - 1, 8) bytes of phaseinfo follow.
+        Planes c = {0u, 0u, 0u};
+        planes_2bit<32, 2, false>(row_ptr(rows, r), N, lane, c);
+        const uint32_t het = group_sum<32>(c.e) - group_sum<32>(c.b);
+        const uint32_t first = 1 + (het >> 3);
+        ok = static_cast<uint64_t>(end - q) >= first;
+        if (ok) {
+          const bool explicit_pp = q[0] & 1u;
+          uint32_t pc = popcount_bits<32>(q, first * 8, nullptr, 0, lane);
+          pc = group_sum<32>(pc);
+          q += first;
+          if (explicit_pp) {
+            const uint32_t second = (pc - 1 + 7) >> 3;
+            ok = static_cast<uint64_t>(end - q) >= second;
+            q += second;
+          }
+        }
+      }
+      if (ok) {
+        if (dos == 1) {
+          Difflist d;
+          const uint8_t* vals = q;
+          ok = difflist_end(q, end, N, false, lane, &vals, &d);
+          out.track3 = q;
+          out.values = vals;
+          out.raw_ct = ok ? d.len : 0;
+          out.kind = 1;
+          // a dosage list may list up to N samples (ParseAndSaveDeltalistAsBitarr), unlike
+          // genotype difflists which are capped at N/8: parse_difflist enforces the tighter cap.
+        } else if (dos == 2) {
+          out.values = q;
+          out.raw_ct = N;
+          out.kind = 2;
+        } else {
+          const uint32_t bit_bytes = (N + 7) >> 3;
+          ok = static_cast<uint64_t>(end - q) >= bit_bytes;
+          if (ok) {
+            out.track3 = q;
+            out.values = q + bit_bytes;
+            out.kind = 3;
+            // rank table + total
+            const uint32_t nw = (N + 31) >> 5;
+            uint32_t running = 0;
+            uint32_t* rk = rank + static_cast<uint64_t>(r) * rank_stride;
+            for (uint32_t w0 = 0; w0 < nw; w0 += 32) {
+              const uint32_t w = w0 + lane;
+              uint32_t bits = 0;
+              if (w < nw) {
+                bits = load_bits32(q, static_cast<uint64_t>(w) << 5);
+                const uint32_t valid = min(32u, N - 32u * w);
+                if (valid < 32) bits &= (1u << valid) - 1u;
+              }
+              const uint32_t pc = __popc(bits);
+              uint32_t incl = pc;
+#pragma unroll
+              for (int off = 1; off < 32; off <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
+                if (lane >= off) incl += t;
+              }
+              if (w < nw) rk[w] = running + incl - pc;
+              running += __shfl_sync(0xffffffffu, incl, 31);
+            }
+            out.raw_ct = running;
+          }
+        }
+      }
+      if (ok) ok = static_cast<uint64_t>(end - out.values) >= 2ull * out.raw_ct;
+      if (!ok) bad = kErrMalformed;
+    }
+  }
+  if (lane == 0) {
+    if (bad) {
+      report_error(err, bad, v);
+      out.kind = 0;
+    }
+    loc[r] = out;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_dosage_fill: out[r][j] = hardcall {0,1,2,-9} of subset sample j, overridden by its dosage
+// (u16 * 2^-14) for the unconditional and bitarray forms.  List-form rows are patched afterwards
+// by k_dosage_scatter.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+k_dosage_fill(DenseRows rows, const DosageLoc* __restrict__ loc, const uint32_t* __restrict__ rank,
+              uint32_t rank_stride, const uint32_t* __restrict__ subset_idx, uint32_t n_out, double* __restrict__ out) {
+  const uint32_t r = blockIdx.y;
+  const uint8_t* row = row_ptr(rows, r);
+  const DosageLoc L = loc[r];
+  const uint32_t* rk = rank + static_cast<uint64_t>(r) * rank_stride;
+  double* o = out + static_cast<uint64_t>(r) * n_out;
+  for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n_out; j += gridDim.x * blockDim.x) {
+    const uint32_t raw = subset_idx ? subset_idx[j] : j;
+    const uint32_t g = geno_at(row, raw);
+    double val = (g == 3) ? -9.0 : static_cast<double>(g);
+    if (L.kind == 2) {
+      const uint32_t u = ld_u16(L.values, raw);
+      if (u != 65535u) val = static_cast<double>(u) * 0.00006103515625;
+    } else if (L.kind == 3) {
+      const uint32_t bits = load_bits32(L.track3, static_cast<uint64_t>(raw >> 5) << 5);
+      if ((bits >> (raw & 31)) & 1u) {
+        const uint32_t k = rk[raw >> 5] + __popc(bits & ((1u << (raw & 31)) - 1u));
+        val = static_cast<double>(ld_u16(L.values, k)) * 0.00006103515625;
+      }
+    }
+    o[j] = val;
+  }
+}
+
+__device__ __forceinline__ bool subset_pos(const SubsetDev& sub, uint32_t id, uint32_t& pos) {
+  if (!sub.include_words) {
+    pos = id;
+    return true;
+  }
+  const uint32_t w = sub.include_words[id >> 5];
+  if (!((w >> (id & 31)) & 1u)) return false;
+  pos = sub.cum_popcount[id >> 5] + __popc(w & ((1u << (id & 31)) - 1u));
+  return true;
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_dosage_scatter(DenseRows rows, const DosageLoc* __restrict__ loc, SubsetDev sub, uint32_t n_out,
+                 double* __restrict__ out, int* __restrict__ err) {
+  const uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (r >= rows.nrows) return;
+  const DosageLoc L = loc[r];
+  if (L.kind != 1 || !L.raw_ct) return;
+  const uint8_t* q = L.track3;
+  Difflist d;
+  if (!parse_difflist(q, L.values, rows.N, false, d)) return;  // validated by k_dosage_locate
+  double* o = out + static_cast<uint64_t>(r) * n_out;
+  difflist_walk(d, rows.N, lane, [&](uint32_t id, uint32_t, uint32_t k) {
+    uint32_t pos;
+    if (subset_pos(sub, id, pos)) o[pos] = static_cast<double>(ld_u16(L.values, k)) * 0.00006103515625;
+  });
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_dosage_stats: one warp per row -> integer sums over the (subset) samples that carry a
+// dosage: count, sum u16, sum u16^2 and the hardcall categories they replace.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+k_dosage_stats(DenseRows rows, const DosageLoc* __restrict__ loc, const uint32_t* __restrict__ rank,
+               uint32_t rank_stride, SubsetDev sub, uint32_t n_out, DosageStats* __restrict__ stats) {
+  const uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (r >= rows.nrows) return;
+  const DosageLoc L = loc[r];
+  const uint8_t* row = row_ptr(rows, r);
+  const uint32_t N = rows.N;
+  unsigned long long sum = 0, sumsq = 0;
+  uint32_t ct = 0, r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+  auto take = [&](uint32_t id, uint32_t u) {
+    sum += u;
+    sumsq += static_cast<unsigned long long>(u) * u;
+    ++ct;
+    const uint32_t g = geno_at(row, id);
+    r0 += (g == 0);
+    r1 += (g == 1);
+    r2 += (g == 2);
+    r3 += (g == 3);
+  };
+  if (L.kind == 1 && L.raw_ct) {
+    const uint8_t* q = L.track3;
+    Difflist d;
+    if (parse_difflist(q, L.values, N, false, d)) {
+      difflist_walk(d, N, lane, [&](uint32_t id, uint32_t, uint32_t k) {
+        uint32_t pos;
+        if (subset_pos(sub, id, pos)) take(id, ld_u16(L.values, k));
+      });
+    }
+  } else if (L.kind == 2) {
+    for (uint32_t j = lane; j < n_out; j += 32) {
+      const uint32_t raw = sub.subset_idx ? sub.subset_idx[j] : j;
+      const uint32_t u = ld_u16(L.values, raw);
+      if (u != 65535u) take(raw, u);
+    }
+  } else if (L.kind == 3) {
+    const uint32_t nw = (N + 31) >> 5;
+    const uint32_t* rk = rank + static_cast<uint64_t>(r) * rank_stride;
+    for (uint32_t w = lane; w < nw; w += 32) {
+      uint32_t all = load_bits32(L.track3, static_cast<uint64_t>(w) << 5);
+      const uint32_t valid = min(32u, N - 32u * w);
+      if (valid < 32) all &= (1u << valid) - 1u;
+      uint32_t bits = sub.include_words ? (all & sub.include_words[w]) : all;
+      const uint32_t base = rk[w];
+      while (bits) {
+        const uint32_t b = __ffs(bits) - 1;
+        take(32u * w + b, ld_u16(L.values, base + __popc(all & ((1u << b) - 1u))));
+        bits &= bits - 1;
+      }
+    }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    sum += __shfl_xor_sync(0xffffffffu, sum, off);
+    sumsq += __shfl_xor_sync(0xffffffffu, sumsq, off);
+  }
+  ct = group_sum<32>(ct);
+  r0 = group_sum<32>(r0);
+  r1 = group_sum<32>(r1);
+  r2 = group_sum<32>(r2);
+  r3 = group_sum<32>(r3);
+  if (lane == 0) {
+    DosageStats s;
+    s.sum = sum;
+    s.sumsq = sumsq;
+    s.ct = ct;
+    s.replaced[0] = r0;
+    s.replaced[1] = r1;
+    s.replaced[2] = r2;
+    s.replaced[3] = r3;
+    s.kind = L.kind;
+    s.pad = 0;
+    stats[r] = s;
+  }
+}
+
+}  // namespace
+
+void launch_dosage_locate(const RecIndex& ix, const DenseRows& rows, const uint32_t* vlist, uint32_t v0, DosageLoc* loc,
+                          uint32_t* rank, uint32_t rank_stride, int* err, cudaStream_t s, LaunchStats* st) {
+  if (!rows.nrows) return;
+  const uint32_t blocks = (rows.nrows * 32 + kThreads - 1) / kThreads;
+  k_dosage_locate<<<blocks, kThreads, 0, s>>>(ix, rows, vlist, v0, loc, rank, rank_stride, err);
+  if (st) st->launches++;
+}
+
+void launch_dosage_fill(const DenseRows& rows, const DosageLoc* loc, const uint32_t* rank, uint32_t rank_stride,
+                        const SubsetDev& sub, uint32_t n_out, double* out, int* err, cudaStream_t s, LaunchStats* st) {
+  if (!rows.nrows || !n_out) return;
+  uint32_t bx = (n_out + kThreads * 4 - 1) / (kThreads * 4);
+  if (bx < 1) bx = 1;
+  dim3 grid(bx, rows.nrows);
+  k_dosage_fill<<<grid, kThreads, 0, s>>>(rows, loc, rank, rank_stride, sub.subset_idx, n_out, out);
+  const uint32_t blocks = (rows.nrows * 32 + kThreads - 1) / kThreads;
+  k_dosage_scatter<<<blocks, kThreads, 0, s>>>(rows, loc, sub, n_out, out, err);
+  if (st) st->launches += 2;
+}
+
+void launch_dosage_stats(const DenseRows& rows, const DosageLoc* loc, const uint32_t* rank, uint32_t rank_stride,
+                         const SubsetDev& sub, uint32_t n_out, DosageStats* stats, cudaStream_t s, LaunchStats* st) {
+  if (!rows.nrows) return;
+  const uint32_t blocks = (rows.nrows * 32 + kThreads - 1) / kThreads;
+  k_dosage_stats<<<blocks, kThreads, 0, s>>>(rows, loc, rank, rank_stride, sub, n_out, stats);
+  if (st) st->launches++;
+}
+
+}  // namespace pdk

@@ -1,0 +1,133 @@
+"""GPU parity: sample-wise consumers of decoded genotype rows through the C ABI --
+pd_decode_i8 (PgrGet + GenoarrToBytesMinus9), pd_missing_by_sample (plink_missing sample mode),
+pd_sample_counts (read_pfile orient := 'sample') -- vs pgenlib goldens, bit-exact."""
+import numpy as np
+import pytest
+
+from conftest import fixture_names, fixture_path
+
+pytestmark = pytest.mark.gpu
+
+
+def _ctx(name, **kw):
+    from plinking_duck_b200.pgen import PgenContext
+
+    return PgenContext(fixture_path(name), **kw)
+
+
+@pytest.mark.parametrize("name", fixture_names())
+@pytest.mark.parametrize("mode", ["stream", "stream_small_tiles", "resident"])
+def test_decode_i8_bit_exact(name, mode, golden):
+    key = name + "/i8"
+    if key not in golden:
+        pytest.skip("no int8 golden (matrix too large)")
+    kw = dict(tile_bytes=700, n_staging=2) if mode == "stream_small_tiles" else {}
+    with _ctx(name, **kw) as c:
+        if mode == "resident":
+            c.load_resident()
+        got = c.decode_i8()
+        assert c.stats().launches > 0
+    assert np.array_equal(got, golden[key])
+
+
+@pytest.mark.parametrize("name", fixture_names())
+def test_decode_i8_subranges_and_subset(name, golden):
+    key = name + "/i8"
+    if key not in golden:
+        pytest.skip("no int8 golden")
+    exp = golden[key]
+    V = exp.shape[0]
+    rng = np.random.default_rng(9)
+    with _ctx(name, tile_bytes=4096) as c:
+        for _ in range(4):
+            a = int(rng.integers(0, V))
+            b = int(rng.integers(a, V + 1))
+            assert np.array_equal(c.decode_i8(a, b), exp[a:b]), (a, b)
+        if name + "/subset_i8" in golden:
+            c.set_subset(golden[name + "/subset"])
+            assert np.array_equal(c.decode_i8(), golden[name + "/subset_i8"])
+            c.set_subset(None)
+            assert np.array_equal(c.decode_i8(0, min(V, 7)), exp[: min(V, 7)])
+
+
+def test_decode_i8_large_n_against_counts(golden):
+    """syn_n70000 has no int8 golden: check the decoded matrix through its per-variant counts."""
+    name = "syn_n70000"
+    with _ctx(name) as c:
+        g = c.decode_i8()
+    exp = golden[name + "/counts"]
+    got = np.stack([(g == 0).sum(1), (g == 1).sum(1), (g == 2).sum(1), (g == -9).sum(1)], axis=1)
+    assert np.array_equal(got.astype(np.uint32), exp)
+
+
+@pytest.mark.parametrize("name", fixture_names())
+@pytest.mark.parametrize("mode", ["stream", "stream_small_tiles", "resident"])
+def test_missing_by_sample_bit_exact(name, mode, golden):
+    kw = dict(tile_bytes=900, n_staging=2) if mode == "stream_small_tiles" else {}
+    with _ctx(name, **kw) as c:
+        if mode == "resident":
+            c.load_resident()
+        got = c.missing_by_sample()
+    assert np.array_equal(got, golden[name + "/missing_by_sample"])
+
+
+@pytest.mark.parametrize("name", fixture_names())
+def test_missing_by_sample_subset_and_range(name, golden):
+    with _ctx(name) as c:
+        if name + "/subset" in golden:
+            c.set_subset(golden[name + "/subset"])
+            assert np.array_equal(c.missing_by_sample(), golden[name + "/subset_missing_by_sample"])
+            c.set_subset(None)
+        if name + "/i8" in golden:
+            i8 = golden[name + "/i8"]
+            V = i8.shape[0]
+            a, b = V // 3, max(V // 3, (2 * V) // 3)
+            assert np.array_equal(c.missing_by_sample(a, b), (i8[a:b] == -9).sum(0).astype(np.uint32))
+        # variant-mode and sample-mode totals agree (test/sql/streaming_threading.test:165-171)
+        assert int(c.missing_by_sample().sum()) == int(c.counts()[:, 3].sum())
+
+
+@pytest.mark.parametrize("name", fixture_names())
+@pytest.mark.parametrize("mode", ["stream", "resident"])
+def test_sample_counts_bit_exact(name, mode, golden):
+    with _ctx(name) as c:
+        if mode == "resident":
+            c.load_resident()
+        het, hom_alt, missing = c.sample_counts()
+    exp = golden[name + "/sample_counts"]
+    assert np.array_equal(het, exp[0])
+    assert np.array_equal(hom_alt, exp[1])
+    assert np.array_equal(missing, exp[2])
+
+
+def test_rare_small_sparse_golden_sums():
+    """test/sql/read_pfile_sample_counts_sparse.test:13 -- sums 99217 / 1947 / 224 / 1012."""
+    with _ctx("rare_small") as c:
+        het, hom_alt, missing = c.sample_counts()
+        V, N = c.variant_ct, c.raw_sample_ct
+    assert (int(het.sum()), int(hom_alt.sum()), int(missing.sum())) == (1947, 224, 1012)
+    assert V * N - 1947 - 224 - 1012 == 99217
+
+
+def test_fixed_width_sample_paths(tmp_path):
+    import synth
+    from plinking_duck_b200.pgen import PgenContext
+
+    for (V, N) in [(700, 1), (300, 37), (1000, 1000), (2100, 4099), (40, 100003)]:
+        g = synth.gen_hwe_genotypes(V, N, seed=3 * V + N, missing=0.05)
+        img = synth.fixed_pgen_image(g)
+        exp_i8 = np.where(g == 3, -9, g).astype(np.int8)
+        with PgenContext(image=img, tile_bytes=1 << 16) as c:
+            for resident in (False, True):
+                if resident:
+                    c.load_resident()
+                assert np.array_equal(c.decode_i8(), exp_i8), (V, N, resident)
+                het, hom, mis = c.sample_counts()
+                assert np.array_equal(het, (g == 1).sum(0).astype(np.uint32)), (V, N, resident)
+                assert np.array_equal(hom, (g == 2).sum(0).astype(np.uint32)), (V, N, resident)
+                assert np.array_equal(mis, (g == 3).sum(0).astype(np.uint32)), (V, N, resident)
+                assert np.array_equal(c.missing_by_sample(), mis)
+            sub = np.arange(0, N, 3)
+            c.set_subset(sub)
+            assert np.array_equal(c.decode_i8(5, min(V, 50)), exp_i8[5:min(V, 50)][:, sub])
+            assert np.array_equal(c.missing_by_sample(), (g[:, sub] == 3).sum(0).astype(np.uint32))
