@@ -29,7 +29,9 @@ void DestroyCtx(pd_ctx* c) {
   for (auto e : c->ev_done) cudaEventDestroy(e);
   for (auto e : c->ev_pool) cudaEventDestroy(e);
   c->d_counts.Free(); c->d_scratch.Free(); c->d_misc.Free(); c->d_pvals.Free(); c->d_acc.Free();
-  c->d_dense.Free(); c->d_rowptrs.Free(); c->d_vlist.Free(); c->d_aux.Free(); c->d_aux2.Free();
+  c->d_dense.Free(); c->d_rowptrs.Free(); c->d_vlist.Free();
+  c->d_loc.Free(); c->d_rank.Free(); c->d_dstats.Free(); c->d_srow.Free(); c->d_weights.Free(); c->d_flip.Free();
+  c->d_score.Free(); c->d_dsum.Free(); c->d_act.Free();
   for (int b = 0; b < 2; ++b) {
     c->d_out[b].Free();
     c->h_bounce[b].Free();

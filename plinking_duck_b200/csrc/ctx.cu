@@ -314,7 +314,7 @@ uint32_t DenseSlotStride(const pd_ctx_impl* c) { return ((c->idx.sample_ct + 3) 
 namespace {
 
 constexpr uint64_t kDenseScratchBytes = 64ull << 20;  // decoded rows of one batch: stays L2-resident
-constexpr uint32_t kMaxBatchRows = 65536;
+constexpr uint32_t kMaxBatchRows = 65535;  // also the gridDim.y limit
 
 uint32_t ClampBatchRows(const pd_ctx_impl* c, uint32_t max_rows) {
   uint64_t r = max_rows ? max_rows : kMaxBatchRows;

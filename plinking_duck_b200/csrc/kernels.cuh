@@ -89,6 +89,54 @@ void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t n, uin
 void launch_subset_indices(const uint32_t* include_words, const uint32_t* cum, uint32_t nwords, uint32_t* out,
                            cudaStream_t s, LaunchStats* st);
 
+// ---- K6: dosage tracks ----
+struct DosageLoc {            // where a row's dosage tracks are (written by launch_dosage_locate)
+  const uint8_t* track3;      // sample-id list (kind 1) or N-bit array (kind 3)
+  const uint8_t* values;      // little-endian u16 dosages, any alignment
+  uint32_t kind;              // 0 none, 1 list, 2 unconditional (65535 = missing), 3 bitarray
+  uint32_t raw_ct;            // stored values
+};
+struct DosageStats {          // over the subset samples that carry a dosage
+  unsigned long long sum;     // sum of u16 dosages
+  unsigned long long sumsq;   // sum of squares
+  uint32_t ct;
+  uint32_t replaced[4];       // hardcall categories of those samples
+  uint32_t kind;
+  uint32_t pad;
+};
+// rank: [nrows x rank_stride] scratch for the bitarray form (exclusive prefix popcounts per 32 bits).
+void launch_dosage_locate(const RecIndex& ix, const DenseRows& rows, const uint32_t* vlist, uint32_t v0, DosageLoc* loc,
+                          uint32_t* rank, uint32_t rank_stride, int* err, cudaStream_t s, LaunchStats* st);
+// out[r * n_out + j] = ALT dosage of subset sample j (hardcall where none is stored, -9 = missing).
+void launch_dosage_fill(const DenseRows& rows, const DosageLoc* loc, const uint32_t* rank, uint32_t rank_stride,
+                        const SubsetDev& sub, uint32_t n_out, double* out, int* err, cudaStream_t s, LaunchStats* st);
+void launch_dosage_stats(const DenseRows& rows, const DosageLoc* loc, const uint32_t* rank, uint32_t rank_stride,
+                         const SubsetDev& sub, uint32_t n_out, DosageStats* stats, cudaStream_t s, LaunchStats* st);
+// Genotype counts of dense rows (any alignment), optionally under the subset mask.
+void launch_count_rows(const DenseRows& rows, const SubsetDev& sub, uint4* out, cudaStream_t s, LaunchStats* st);
+
+// ---- K7: plink_score ----
+constexpr uint32_t kScoreActive = 1u;   // row contributes (non_missing_ct > 0, sd > 0)
+constexpr uint32_t kScoreFlip = 2u;     // scored allele is REF: dosage -> 2 - dosage
+constexpr uint32_t kScoreCenter = 4u;   // (scored - mean) / sd
+constexpr uint32_t kScoreImpute = 8u;   // missing calls count with the mean dosage
+struct ScoreRow {
+  double T[4];          // contribution of hardcall 0 / 1 / 2 / missing
+  double mean_scored;
+  double sd;
+  uint32_t flags;
+  uint32_t kind;        // dosage storage kind of the row (DosageLoc::kind)
+};
+// counts: (subset) hardcall counts per row; stats: dosage sums per row or nullptr; flip: per row or nullptr.
+void launch_score_prep(const uint4* counts, const DosageStats* stats, const uint8_t* flip, uint32_t nrows, uint32_t mode,
+                       ScoreRow* out, cudaStream_t s, LaunchStats* st);
+// weights: nrows x K (row-major) for the rows of this batch.  score: n_out x K, dosage_sums / allele_cts: n_out;
+// all three are accumulated into.  loc / rank may be nullptr when the file stores no dosages.
+void launch_score_acc(const DenseRows& rows, const ScoreRow* srow, const DosageLoc* loc, const uint32_t* rank,
+                      uint32_t rank_stride, const double* weights, uint32_t K, const SubsetDev& sub, uint32_t n_out,
+                      uint32_t mode, double* score, double* dosage_sums, uint32_t* allele_cts, cudaStream_t s,
+                      LaunchStats* st);
+
 // ---- K8: exact Hardy-Weinberg test on the device ----
 // counts[n] as produced by the count kernels; out_p[n] = p-value clamped to [0,1].
 void launch_hwe(const uint4* counts, uint32_t n, uint32_t midp, double* out_p, cudaStream_t s, LaunchStats* st);

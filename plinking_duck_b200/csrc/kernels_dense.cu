@@ -255,6 +255,28 @@ __global__ void k_subset_indices(const uint32_t* __restrict__ include_words, con
   }
 }
 
+// Genotype counts of dense rows: one warp per row, rows may sit at any byte alignment.
+template <bool MASKED>
+__global__ void __launch_bounds__(kThreads)
+k_count_rows(DenseRows rows, SubsetDev sub, uint4* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+  const uint32_t n_eff = MASKED ? sub.subset_ct : rows.N;
+  for (uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < rows.nrows; r += nwarps) {
+    const uint8_t* p = row_ptr(rows, r);
+    Planes c = {0u, 0u, 0u};
+    if (MASKED) {
+      planes_2bit_masked<32, 4, false>(p, rows.N, sub.mask2_shifts, sub.mask2_stride, lane, c);
+    } else {
+      planes_2bit<32, 4, false>(p, rows.N, lane, c);
+    }
+    c.e = group_sum<32>(c.e);
+    c.o = group_sum<32>(c.o);
+    c.b = group_sum<32>(c.b);
+    if (lane == 0) out[r] = planes_to_counts(c, n_eff);
+  }
+}
+
 int g_sm = 0;
 int sm_count() {
   if (!g_sm) {
@@ -311,6 +333,19 @@ void launch_sample_acc(const DenseRows& rows, uint32_t kinds, uint32_t* acc_het,
     case 4: k_sample_acc<4><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis); break;
     case 7: k_sample_acc<7><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis); break;
     default: k_sample_acc<7><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis); break;
+  }
+  if (st) st->launches++;
+}
+
+void launch_count_rows(const DenseRows& rows, const SubsetDev& sub, uint4* out, cudaStream_t s, LaunchStats* st) {
+  if (!rows.nrows) return;
+  uint64_t blocks = (static_cast<uint64_t>(rows.nrows) * 32 + kThreads - 1) / kThreads;
+  const uint64_t max_blocks = static_cast<uint64_t>(sm_count()) * 8;
+  if (blocks > max_blocks) blocks = max_blocks;
+  if (sub.mask2_shifts) {
+    k_count_rows<true><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(rows, sub, out);
+  } else {
+    k_count_rows<false><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(rows, sub, out);
   }
   if (st) st->launches++;
 }

@@ -118,8 +118,8 @@ k_dosage_locate(RecIndex ix, DenseRows rows, const uint32_t* __restrict__ vlist,
           out.values = vals;
           out.raw_ct = ok ? d.len : 0;
           out.kind = 1;
-          // a dosage list may list up to N samples (ParseAndSaveDeltalistAsBitarr), unlike
-          // genotype difflists which are capped at N/8: parse_difflist enforces the tighter cap.
+          // same header rules as a genotype difflist, incl. the N/8 length cap
+          // (ParseAndSaveDeltalistAsBitarr -> ParseDifflistHeader, pgenlib_read.cc:6136-6138)
         } else if (dos == 2) {
           out.values = q;
           out.raw_ct = N;

@@ -1,0 +1,75 @@
+// Device -> host result streaming shared by the decode entry points.
+#pragma once
+#include "ctx.h"
+
+namespace pdx {
+
+bool IsPinnedHost(const void* p);
+void ParallelMemcpy(void* dst, const void* src, size_t n);
+
+// Double-buffered device -> host streaming of per-batch outputs.  Batch i is produced into
+// d_out[i & 1] on the compute stream and copied out on the D2H stream while batch i + 1 is being
+// produced.  Pageable destinations go through a pinned bounce buffer.
+struct OutPipe {
+  pd_ctx_impl* c;
+  bool direct;          // destination is page-locked: DMA straight into it
+  size_t buf_bytes;
+  struct Pending {
+    void* dst = nullptr;
+    size_t bytes = 0;
+    bool live = false;
+  } pend[2];
+  uint32_t next = 0;
+
+  int Init(pd_ctx_impl* ctx, const void* user_dst, size_t bytes_per_batch) {
+    c = ctx;
+    direct = IsPinnedHost(user_dst);
+    buf_bytes = bytes_per_batch;
+    for (int b = 0; b < 2; ++b) {
+      cudaError_t e = c->d_out[b].Reserve(bytes_per_batch + 64);
+      if (e == cudaSuccess && !direct) e = c->h_bounce[b].Reserve(bytes_per_batch);
+      if (e != cudaSuccess) return CheckCuda(c, e, "output buffer allocation");
+      pend[b] = Pending{};
+    }
+    return PD_OK;
+  }
+  // Finishes the host side of whatever was last sent from buffer b.
+  int Retire(int b) {
+    if (!pend[b].live) return PD_OK;
+    cudaError_t e = cudaEventSynchronize(c->ev_out_free[b]);
+    if (e != cudaSuccess) return CheckCuda(c, e, "result download");
+    if (!direct) ParallelMemcpy(pend[b].dst, c->h_bounce[b].p, pend[b].bytes);
+    pend[b].live = false;
+    return PD_OK;
+  }
+  // Buffer the next batch should be produced into (its previous contents are safely out).
+  int Acquire(void** dev, int* slot) {
+    const int b = static_cast<int>(next++ & 1);
+    const int rc = Retire(b);
+    if (rc != PD_OK) return rc;
+    *dev = c->d_out[b].p;
+    *slot = b;
+    return PD_OK;
+  }
+  // Call after the producing kernels of slot b were enqueued on stream s.
+  int Send(int b, cudaStream_t s, void* host_dst, size_t bytes) {
+    cudaEventRecord(c->ev_out_ready[b], s);
+    cudaStreamWaitEvent(c->d2h_stream, c->ev_out_ready[b], 0);
+    void* dst = direct ? host_dst : c->h_bounce[b].p;
+    cudaError_t e = cudaMemcpyAsync(dst, c->d_out[b].p, bytes, cudaMemcpyDeviceToHost, c->d2h_stream);
+    if (e != cudaSuccess) return CheckCuda(c, e, "result download");
+    cudaEventRecord(c->ev_out_free[b], c->d2h_stream);  // Acquire() waits on it before slot b is reused
+    pend[b].dst = host_dst;
+    pend[b].bytes = bytes;
+    pend[b].live = true;
+    c->stats.d2h_bytes += bytes;
+    return PD_OK;
+  }
+  int Finish() {
+    int rc = Retire(0);
+    const int rc2 = Retire(1);
+    return rc != PD_OK ? rc : rc2;
+  }
+};
+
+}  // namespace pdx

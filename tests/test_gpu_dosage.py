@@ -1,0 +1,151 @@
+"""GPU parity: dosage decode (PgrGetD + Dosage16ToDoublesMinus9), dosage-aware counts (PgrGetDCounts)
+and plink_score through the C ABI vs pgenlib goldens.
+
+Integer outputs (counts, all_dosages numerators, allele counts) are bit-exact.  Decoded dosages and
+IMP_R2 are computed with the reference's own fp64 operation order and must be bit-identical too.
+Score sums: relative tolerance 1e-12 of the sum's natural scale (sum of |w| x max dosage 2), the
+north_star's fp64 bound -- the reference's own sums depend on thread arrival order
+(src/plink_score.cpp:657-664), so tolerance parity is the only meaningful kind."""
+import numpy as np
+import pytest
+
+from conftest import fixture_names, fixture_path
+
+pytestmark = pytest.mark.gpu
+
+SCORE_RTOL = 1e-12
+
+
+def _ctx(name, **kw):
+    from plinking_duck_b200.pgen import PgenContext
+
+    return PgenContext(fixture_path(name), **kw)
+
+
+def _dosage_fixtures(golden):
+    return [n for n in fixture_names() if n + "/dcounts" in golden]
+
+
+def pytest_generate_tests(metafunc):
+    if "dname" in metafunc.fixturenames:
+        import os
+
+        g = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden.npz"))
+        metafunc.parametrize("dname", [n for n in fixture_names() if n + "/dcounts" in g])
+
+
+@pytest.mark.parametrize("mode", ["stream", "stream_small_tiles", "resident"])
+def test_dosage_counts(dname, mode, golden):
+    kw = dict(tile_bytes=600, n_staging=2) if mode == "stream_small_tiles" else {}
+    with _ctx(dname, **kw) as c:
+        if mode == "resident":
+            c.load_resident()
+        counts, ad, r2 = c.dosage_counts()
+    assert np.array_equal(counts, golden[dname + "/dcounts"])
+    assert np.array_equal(ad, golden[dname + "/all_dosages"])
+    exp = golden[dname + "/imp_r2"]
+    assert np.array_equal(np.isnan(r2), np.isnan(exp))
+    ok = ~np.isnan(exp)
+    assert np.array_equal(r2[ok], exp[ok])
+
+
+def test_dosage_example_known_answers():
+    """test/sql/plink_freq_dosage.test:103-118: ALT_FREQ / OBS_CT / IMP_R2 of dosage_example."""
+    with _ctx("dosage_example") as c:
+        counts, ad, r2 = c.dosage_counts()
+    ad = ad.astype(np.float64)
+    alt_freq = ad[:, 1] / (ad[:, 0] + ad[:, 1])
+    obs_ct = (ad[:, 0] + ad[:, 1]) / 16384.0
+    assert np.allclose(alt_freq, [0.4583333333333333, 0.4499969482421875, 0.5, 0.20833333333333334], rtol=1e-15)
+    assert np.array_equal(obs_ct, [6, 8, 8, 6])
+    assert np.allclose(r2, [1.2900887786091624, 0.7374153374407626, 1.0, 0.3857199844561125], rtol=1e-15)
+
+
+def test_dosage_f64(dname, golden):
+    exp = golden[dname + "/dosage_first"]
+    nd = exp.shape[0]
+    with _ctx(dname) as c:
+        got = c.dosage_f64(np.arange(nd))
+        assert np.array_equal(got, exp)
+        # sparse list + resident
+        pick = np.arange(0, nd, 3)
+        c.load_resident()
+        assert np.array_equal(c.dosage_f64(pick), exp[pick])
+
+
+def test_dosage_subset(golden):
+    from oracle import ref
+
+    if not ref.available():
+        pytest.skip("oracle/_ref not built")
+    for name in ("syn_dosage", "dosage_example", "syn_n257"):
+        with ref.RefPgen(fixture_path(name)) as r, _ctx(name) as c:
+            N = r.N
+            sub = np.arange(0, N, 2) if N > 4 else np.array([1, 3])
+            r.set_subset(sub)
+            c.set_subset(sub)
+            exp = np.stack([r.dosage(v) for v in range(r.V)])
+            assert np.array_equal(c.dosage_f64(np.arange(r.V)), exp), name
+            ec, ead, er2 = r.dcounts()
+            gc, gad, gr2 = c.dosage_counts()
+            assert np.array_equal(gc, ec) and np.array_equal(gad, ead), name
+            ok = ~np.isnan(er2)
+            assert np.array_equal(gr2[ok], er2[ok]) and np.array_equal(np.isnan(gr2), np.isnan(er2)), name
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_score_matches_oracle(dname, mode, golden):
+    w = golden[dname + "/score_w"]
+    fl = golden[dname + "/score_flip"]
+    V = w.size
+    with _ctx(dname) as c:
+        s, d, a = c.score(np.arange(V), fl, w, mode)
+    scale = 2.0 * np.abs(w).sum() + 1.0
+    es, ed, ea = (golden[dname + f"/score_m{mode}_{k}"] for k in ("sum", "dsum", "ct"))
+    assert np.array_equal(a, ea)
+    assert np.max(np.abs(s[:, 0] - es)) <= SCORE_RTOL * scale * (50.0 if mode == 2 else 1.0)
+    assert np.max(np.abs(d - ed)) <= SCORE_RTOL * (2.0 * V + 1.0)
+
+
+def test_score_known_answers():
+    """test/sql/plink_score.test:48-75: weights [1.0, 0.5, -0.5, 2.0] on pgen_example ->
+    SCORE_SUM -0.5 / 1.0 / 3.5 / 6.0, NAMED_ALLELE_DOSAGE_SUM 3 / 3 / 4 / 5."""
+    w = np.array([1.0, 0.5, -0.5, 2.0])
+    with _ctx("pgen_example") as c:
+        s, d, a = c.score(np.arange(4), None, w, 0)
+    assert np.allclose(s[:, 0], [-0.5, 1.0, 3.5, 6.0], rtol=1e-15, atol=1e-15)
+    assert np.allclose(d, [3, 3, 4, 5])
+    assert np.array_equal(a, [8, 8, 8, 8])
+    assert np.allclose(s[:, 0] / a, [-0.0625, 0.125, 0.4375, 0.75])
+
+
+def test_score_multi_column_and_subset(golden):
+    """K = 16 columns equal 16 single-column runs; all-ones weights give SCORE_SUM == NAMED_ALLELE_DOSAGE_SUM
+    (test/sql/streaming_threading.test:226-233)."""
+    name = "syn_n1000"
+    rng = np.random.default_rng(3)
+    with _ctx(name) as c:
+        V = c.variant_ct
+        vid = np.sort(rng.choice(V, size=V // 2, replace=False)).astype(np.uint32)
+        W = rng.standard_normal((vid.size, 16))
+        fl = (rng.random(vid.size) < 0.2).astype(np.uint8)
+        S, D, A = c.score(vid, fl, W, 0)
+        for k in (0, 7, 15):
+            s1, d1, a1 = c.score(vid, fl, W[:, k], 0)
+            assert np.allclose(S[:, k], s1[:, 0], rtol=1e-13, atol=1e-10)
+            assert np.array_equal(a1, A) and np.allclose(d1, D)
+        ones, dn, _ = c.score(vid, None, np.ones(vid.size), 0)
+        assert np.allclose(ones[:, 0], dn, rtol=1e-13)
+        sub = np.arange(0, c.raw_sample_ct, 3)
+        c.set_subset(sub)
+        Ss, Ds, As = c.score(vid, fl, W[:, :3], 1)
+        assert Ss.shape == (sub.size, 3)
+    from oracle import ref
+
+    if ref.available():
+        with ref.RefPgen(fixture_path(name)) as r:
+            r.set_subset(sub)
+            for k in range(3):
+                es, ed, ea = r.score(vid, fl, W[:, k], 1)
+                assert np.allclose(Ss[:, k], es, rtol=1e-12, atol=1e-9)
+                assert np.array_equal(As, ea)
