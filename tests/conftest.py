@@ -35,3 +35,34 @@ def fixture_names():
 
 def fixture_path(name):
     return os.path.join(FIX_DIR, name + ".pgen")
+
+
+def ensure_built():
+    """Build libplinkgpu.so (and, where the reference tree exists, oracle/_ref) if absent.
+    nvcc cross-compiles for sm_100a without a GPU, so this also works on the CPU-only box."""
+    import subprocess
+
+    lib = os.path.join(ROOT, "plinking_duck_b200", "libplinkgpu.so")
+    if not os.path.exists(lib):
+        subprocess.run(["make", "-j8"], cwd=os.path.join(ROOT, "plinking_duck_b200", "csrc"), check=True,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.STDOUT)
+    ref_so = os.path.join(ROOT, "oracle", "_ref", "libpgenref.so")
+    if not os.path.exists(ref_so) and os.path.isdir("/root/reference/third_party/plink-ng/2.0/include"):
+        subprocess.run(["make", "-j8", "ref"], cwd=os.path.join(ROOT, "oracle"), check=True,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.STDOUT)
+
+
+@pytest.fixture(scope="session")
+def built():
+    ensure_built()
+    return True
+
+
+@pytest.fixture(scope="session")
+def refmod(built):
+    """oracle.ref, or skip when oracle/_ref/libpgenref.so could not be built (no reference tree)."""
+    from oracle import ref
+
+    if not ref.available():
+        pytest.skip("oracle/_ref/libpgenref.so not available")
+    return ref

@@ -1,0 +1,86 @@
+"""CPU: the C-ABI library loads, exports every symbol include/plinkgpu.h declares, and its host-only
+entry points (pd_probe: header / index parse) agree with pgenlib.  No compute calls are made."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, fixture_names, fixture_path
+
+
+def _declared_symbols():
+    out = []
+    for h in sorted(os.listdir(os.path.join(ROOT, "include"))):
+        if h.endswith(".h"):
+            src = open(os.path.join(ROOT, "include", h)).read()
+            src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+            out += re.findall(r"\b(pd[a-z]*_[a-z0-9_]+)\s*\(", src)
+    return sorted(set(out))
+
+
+def test_header_symbols_are_bound_and_exported(built):
+    from plinking_duck_b200 import _native as nat
+
+    declared = _declared_symbols()
+    assert len(declared) >= 25
+    lib = C.CDLL(nat.LIB_PATH)
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/*.h but not exported"
+        assert name in nat.SYMBOLS, f"{name} has no ctypes binding"
+    assert set(nat.SYMBOLS) <= set(declared)
+    assert nat.load().pd_version().decode().endswith("sm_100a")
+
+
+def test_no_cpu_fallback(built):
+    """Without a CUDA device pd_open must fail loudly (PD_ERR_CUDA), never compute on the host."""
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from plinking_duck_b200 import _native as nat
+    from plinking_duck_b200.pgen import PgenContext
+
+    with pytest.raises(nat.PlinkGpuError) as e:
+        PgenContext(fixture_path("pgen_example"))
+    assert e.value.code == nat.PD_ERR_CUDA
+    assert "no CPU fallback" in str(e.value)
+
+
+@pytest.mark.parametrize("name", fixture_names())
+def test_probe_index_matches_pgenlib(name, golden, built, fixture_meta):
+    from plinking_duck_b200.pgen import probe
+
+    info, vt, fpos = probe(fixture_path(name))
+    assert info.variant_ct == fixture_meta[name]["V"] and info.sample_ct == fixture_meta[name]["N"]
+    assert np.array_equal(vt, golden[name + "/vrtypes"])
+    assert np.array_equal(fpos, golden[name + "/fpos"])
+    assert bool(info.has_ld) == bool(((vt & 6) == 2).any())
+    assert bool(info.has_dosage) == bool((vt & 0x60).any())
+
+
+def test_probe_rejects_bad_files(tmp_path, built):
+    import synth
+    from plinking_duck_b200 import _native as nat
+    from plinking_duck_b200.pgen import probe
+
+    with pytest.raises(nat.PlinkGpuError) as e:
+        probe(str(tmp_path / "nope.pgen"))
+    assert e.value.code == nat.PD_ERR_OPEN
+    bad = tmp_path / "bad.pgen"
+    bad.write_bytes(bytes(range(13)))
+    with pytest.raises(nat.PlinkGpuError) as e:
+        probe(str(bad))
+    assert e.value.code == nat.PD_ERR_MALFORMED
+    g = synth.gen_hwe_genotypes(10, 10, 1)
+    trunc = tmp_path / "trunc.pgen"
+    synth.fixed_pgen_image(g)[:-1].tofile(str(trunc))
+    with pytest.raises(nat.PlinkGpuError) as e:
+        probe(str(trunc))
+    assert e.value.code == nat.PD_ERR_MALFORMED
+    ok = tmp_path / "ok.pgen"
+    synth.write_fixed_pgen(str(ok), g)
+    info, vt, fpos = probe(str(ok))
+    assert (info.variant_ct, info.sample_ct, info.mode, info.fixed_width) == (10, 10, 2, 3)
+    assert np.array_equal(fpos, 12 + 3 * np.arange(11))
