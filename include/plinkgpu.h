@@ -78,7 +78,10 @@ typedef struct pd_stats_t {
  *      per-variant index are parsed ONCE. ---- */
 int pd_open(const char* pgen_path, const pd_open_opts* opts, pd_ctx** out, char* errbuf, size_t errbuf_len);
 /* Same, over a .pgen image already in host memory (not copied; must outlive the context).
- * pgi/pgi_len: the external index for modes 0x20/0x21, else NULL/0. */
+ * pgi/pgi_len: the external index for modes 0x20/0x21, else NULL/0.
+ * pgen_bytes may also be DEVICE memory on the context's device (an image produced by an upstream
+ * GPU stage): it is then used in place, permanently resident; the allocation must extend at least
+ * 64 readable bytes past len. */
 int pd_open_mem(const void* pgen_bytes, uint64_t len, const void* pgi_bytes, uint64_t pgi_len,
                 const pd_open_opts* opts, pd_ctx** out, char* errbuf, size_t errbuf_len);
 /* Header-only probe, no device needed: what the bind phase does with PgfiInitPhase1/2 to read V, N
@@ -158,6 +161,19 @@ int pd_dosage_counts(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t* ou
 #define PD_SCORE_CENTER 2
 int pd_score(pd_ctx* ctx, const uint32_t* vidx, const uint8_t* flip, const double* weights, uint32_t n_var,
              uint32_t K, uint32_t mode, double* score_sums, double* dosage_sums, uint32_t* allele_cts);
+
+/* ---- device-side results for multi-GPU reductions.  After pd_score / pd_missing_by_sample /
+ *      pd_sample_counts (whose host output pointers may then be NULL), the accumulators of the last
+ *      call stay in HBM; the caller all-reduces them in place over NVLink (NCCL) and reads them back
+ *      once, instead of bouncing every rank's partial sums through host memory.
+ *      which: PD_RESULT_SCORE (double[sample_ct x K]), PD_RESULT_DOSAGE_SUM (double[sample_ct]),
+ *      PD_RESULT_ALLELE_CT (uint32[sample_ct]), PD_RESULT_SAMPLE_COUNTS (uint32[3 x sample_ct]:
+ *      het, hom_alt, missing).  The pointers are valid until the next call on the context. ---- */
+#define PD_RESULT_SCORE 0
+#define PD_RESULT_DOSAGE_SUM 1
+#define PD_RESULT_ALLELE_CT 2
+#define PD_RESULT_SAMPLE_COUNTS 3
+int pd_device_result(pd_ctx* ctx, uint32_t which, void** dev_ptr, uint64_t* bytes);
 
 /* ---- instrumentation (the reference has only BindPhaseTimer, src/include/plink_profile.hpp) ---- */
 int pd_get_stats(const pd_ctx* ctx, pd_stats_t* out);

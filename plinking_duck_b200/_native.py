@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libplinkgpu.so")
 PD_OK = 0
 PD_ERR_OPEN, PD_ERR_READ, PD_ERR_MALFORMED, PD_ERR_NOT_SUPPORTED = 1, 2, 3, 4
 PD_ERR_NOMEM, PD_ERR_INVALID_ARG, PD_ERR_CUDA = 5, 6, 7
+PD_RESULT_SCORE, PD_RESULT_DOSAGE_SUM, PD_RESULT_ALLELE_CT, PD_RESULT_SAMPLE_COUNTS = 0, 1, 2, 3
 ERR_NAMES = {
     1: "PD_ERR_OPEN", 2: "PD_ERR_READ", 3: "PD_ERR_MALFORMED", 4: "PD_ERR_NOT_SUPPORTED",
     5: "PD_ERR_NOMEM", 6: "PD_ERR_INVALID_ARG", 7: "PD_ERR_CUDA",
@@ -67,6 +68,7 @@ SYMBOLS = {
     "pd_dosage_f64": (C.c_int, [_vp, _vp, _u32, _vp]),
     "pd_dosage_counts": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),
     "pd_score": (C.c_int, [_vp, _vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
+    "pd_device_result": (C.c_int, [_vp, _u32, C.POINTER(_vp), C.POINTER(_u64)]),
     "pd_get_stats": (C.c_int, [_vp, C.POINTER(Stats)]),
     "pd_reset_stats": (C.c_int, [_vp]),
     "pd_version": (C.c_char_p, []),

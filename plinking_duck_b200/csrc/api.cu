@@ -194,10 +194,30 @@ int pd_open_mem(const void* pgen_bytes, uint64_t len, const void* pgi_bytes, uin
   cudaPointerAttributes attr{};
   if (cudaPointerGetAttributes(&attr, pgen_bytes) == cudaSuccess && attr.type == cudaMemoryTypeHost) {
     c->src_pinned = true;
+  } else if (attr.type == cudaMemoryTypeDevice) {
+    // Image already in HBM (produced by an upstream GPU stage): used in place.  The allocation
+    // must extend >= 64 readable bytes past `len` (aligned 16-byte loads on the last record).
+    c->pgen.OpenDevice(pgen_bytes, len);
+    c->dev_image = true;
   } else {
     cudaGetLastError();  // unregistered host memory reports an error on some drivers
   }
-  return FinishOpen(c, opts, out, errbuf, errbuf_len);
+  int rc = FinishOpen(c, opts, out, errbuf, errbuf_len);
+  if (rc == PD_OK && c->dev_image) {
+    if (c->device != attr.device) {
+      CopyErr(errbuf, errbuf_len, "device image lives on a different device than the context");
+      DestroyCtx(c);
+      *out = nullptr;
+      return PD_ERR_INVALID_ARG;
+    }
+    c->resident = true;
+    c->res_ptr = static_cast<const uint8_t*>(pgen_bytes);
+    c->res_v0 = 0;
+    c->res_v1 = c->idx.variant_ct;
+    c->res_f0 = 0;
+    c->res_f1 = len;
+  }
+  return rc;
 }
 
 void pd_close(pd_ctx* ctx) { DestroyCtx(ctx); }
@@ -329,6 +349,7 @@ int pd_load_resident(pd_ctx* c, uint32_t v_begin, uint32_t v_end) {
   const uint64_t f0 = ix.RecOff(v0);
   const uint64_t f1 = ix.fixed ? ix.data_start + static_cast<uint64_t>(v_end) * ix.fixed_width : ix.fpos[v_end];
   const uint64_t len = f1 - f0;
+  if (c->dev_image) return PD_OK;  // already in HBM
   c->resident = false;
   cudaError_t e = c->d_resident.Reserve(len + 2 * kSlack);
   if (e != cudaSuccess) {
@@ -365,6 +386,7 @@ int pd_load_resident(pd_ctx* c, uint32_t v_begin, uint32_t v_end) {
   if (e != cudaSuccess) return CheckCuda(c, e, "resident copy");
   c->stats.h2d_bytes += len;
   c->resident = true;
+  c->res_ptr = dst;
   c->res_v0 = v0;
   c->res_v1 = v_end;
   c->res_f0 = f0;
@@ -376,6 +398,7 @@ int pd_unload(pd_ctx* c) {
   if (!c) return PD_ERR_INVALID_ARG;
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
+  if (c->dev_image) return PD_OK;
   c->resident = false;
   c->d_resident.Free();
   return PD_OK;

@@ -211,7 +211,7 @@ int pd_dosage_counts(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* out_
 
 int pd_score(pd_ctx* c, const uint32_t* vidx, const uint8_t* flip, const double* weights, uint32_t n_var, uint32_t K,
              uint32_t mode, double* score_sums, double* dosage_sums, uint32_t* allele_cts) {
-  if (!c || !score_sums || !K || mode > 2 || (n_var && (!vidx || !weights))) return PD_ERR_INVALID_ARG;
+  if (!c || !K || mode > 2 || (n_var && (!vidx || !weights))) return PD_ERR_INVALID_ARG;
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   const uint32_t n_out = c->subset.active ? c->subset.count : c->idx.sample_ct;
@@ -260,7 +260,12 @@ int pd_score(pd_ctx* c, const uint32_t* vidx, const uint8_t* flip, const double*
     });
     if (rc != PD_OK) return rc;
   }
-  e = cudaMemcpyAsync(score_sums, c->d_score.p, static_cast<size_t>(n_out) * K * 8, cudaMemcpyDeviceToHost, c->stream);
+  c->last_score_n = n_out;
+  c->last_score_k = K;
+  e = cudaSuccess;
+  if (score_sums) {
+    e = cudaMemcpyAsync(score_sums, c->d_score.p, static_cast<size_t>(n_out) * K * 8, cudaMemcpyDeviceToHost, c->stream);
+  }
   if (e == cudaSuccess && dosage_sums) {
     e = cudaMemcpyAsync(dosage_sums, c->d_dsum.p, static_cast<size_t>(n_out) * 8, cudaMemcpyDeviceToHost, c->stream);
   }

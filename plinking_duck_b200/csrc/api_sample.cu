@@ -62,6 +62,7 @@ int SampleAccumulate(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t 
   if (rc != PD_OK) return rc;
   const uint32_t* idx = c->subset.active ? c->subset.d_idx.as<uint32_t>() : nullptr;
   uint32_t* out = c->d_out[0].as<uint32_t>();
+  cudaMemsetAsync(out, 0, 3 * static_cast<size_t>(n_out) * 4, c->stream);
   for (uint32_t k = 0; k < 3; ++k) {
     if (kinds & (1u << k)) {
       pdk::launch_gather_u32(acc + k * npad, idx, n_out, out + static_cast<size_t>(k) * n_out, c->stream, &c->launch_stats);
@@ -75,15 +76,19 @@ int SampleAccumulate(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t 
 extern "C" {
 
 int pd_missing_by_sample(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* out_missing) {
-  if (!c || !out_missing) return PD_ERR_INVALID_ARG;
+  if (!c) return PD_ERR_INVALID_ARG;
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   cudaEventRecord(c->ev_c0, c->stream);
   uint32_t n_out = 0;
   int rc = SampleAccumulate(c, v_begin, v_end, 4, &n_out);
   if (rc != PD_OK) return rc;
-  cudaError_t e = cudaMemcpyAsync(out_missing, c->d_out[0].as<uint32_t>() + 2 * static_cast<size_t>(n_out),
-                                  static_cast<size_t>(n_out) * 4, cudaMemcpyDeviceToHost, c->stream);
+  c->last_sample_n = n_out;
+  cudaError_t e = cudaSuccess;
+  if (out_missing) {
+    e = cudaMemcpyAsync(out_missing, c->d_out[0].as<uint32_t>() + 2 * static_cast<size_t>(n_out),
+                        static_cast<size_t>(n_out) * 4, cudaMemcpyDeviceToHost, c->stream);
+  }
   cudaEventRecord(c->ev_c1, c->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
   if (e != cudaSuccess) return CheckCuda(c, e, "result download");
@@ -96,7 +101,9 @@ int pd_missing_by_sample(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* 
 
 int pd_sample_counts(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* out_het, uint32_t* out_hom_alt,
                      uint32_t* out_missing) {
-  if (!c || !out_het || !out_hom_alt || !out_missing) return PD_ERR_INVALID_ARG;
+  if (!c) return PD_ERR_INVALID_ARG;
+  const bool want = out_het || out_hom_alt || out_missing;
+  if (want && !(out_het && out_hom_alt && out_missing)) return PD_ERR_INVALID_ARG;
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   cudaEventRecord(c->ev_c0, c->stream);
@@ -105,9 +112,13 @@ int pd_sample_counts(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* out_
   if (rc != PD_OK) return rc;
   const uint32_t* d = c->d_out[0].as<uint32_t>();
   const size_t bytes = static_cast<size_t>(n_out) * 4;
-  cudaError_t e = cudaMemcpyAsync(out_het, d, bytes, cudaMemcpyDeviceToHost, c->stream);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(out_hom_alt, d + n_out, bytes, cudaMemcpyDeviceToHost, c->stream);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(out_missing, d + 2 * static_cast<size_t>(n_out), bytes, cudaMemcpyDeviceToHost, c->stream);
+  c->last_sample_n = n_out;
+  cudaError_t e = cudaSuccess;
+  if (want) {
+    e = cudaMemcpyAsync(out_het, d, bytes, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_hom_alt, d + n_out, bytes, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_missing, d + 2 * static_cast<size_t>(n_out), bytes, cudaMemcpyDeviceToHost, c->stream);
+  }
   cudaEventRecord(c->ev_c1, c->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
   if (e != cudaSuccess) return CheckCuda(c, e, "result download");
@@ -153,6 +164,33 @@ int pd_decode_i8(pd_ctx* c, uint32_t v_begin, uint32_t v_end, int8_t* out) {
     c->stats.call_ms = ms;
   }
   return rc != PD_OK ? rc : rc2;
+}
+
+int pd_device_result(pd_ctx* c, uint32_t which, void** dev_ptr, uint64_t* bytes) {
+  if (!c || !dev_ptr || !bytes) return PD_ERR_INVALID_ARG;
+  std::lock_guard<std::mutex> lock(c->mu);
+  switch (which) {
+    case PD_RESULT_SCORE:
+      *dev_ptr = c->d_score.p;
+      *bytes = static_cast<uint64_t>(c->last_score_n) * c->last_score_k * 8;
+      break;
+    case PD_RESULT_DOSAGE_SUM:
+      *dev_ptr = c->d_dsum.p;
+      *bytes = static_cast<uint64_t>(c->last_score_n) * 8;
+      break;
+    case PD_RESULT_ALLELE_CT:
+      *dev_ptr = c->d_act.p;
+      *bytes = static_cast<uint64_t>(c->last_score_n) * 4;
+      break;
+    case PD_RESULT_SAMPLE_COUNTS:
+      *dev_ptr = c->d_out[0].p;
+      *bytes = static_cast<uint64_t>(c->last_sample_n) * 12;
+      break;
+    default:
+      return c->SetError(PD_ERR_INVALID_ARG, "unknown result id");
+  }
+  if (!*dev_ptr || !*bytes) return c->SetError(PD_ERR_INVALID_ARG, "no such result is held on the device");
+  return PD_OK;
 }
 
 }  // extern "C"

@@ -219,7 +219,7 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
   if (c->resident && v0 >= c->res_v0 && v_end <= c->res_v1) {
     Tile t{v0, v_end, ixh.RecOff(v0), ixh.fixed ? ixh.data_start + static_cast<uint64_t>(v_end) * ixh.fixed_width
                                                : ixh.fpos[v_end]};
-    ix.data = c->d_resident.as<uint8_t>() + kSlack;
+    ix.data = c->res_ptr;
     ix.data_fpos = c->res_f0;
     cudaEvent_t k0 = PoolEvent(c, 0), k1 = PoolEvent(c, 1);
     cudaEventRecord(k0, c->stream);

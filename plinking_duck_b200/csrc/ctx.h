@@ -74,6 +74,8 @@ struct pd_ctx_impl {
 
   // residency
   DevBuf d_resident;
+  const uint8_t* res_ptr = nullptr;  // device byte holding file offset res_f0
+  bool dev_image = false;            // the caller's image is device memory: always resident, never copied
   bool resident = false;
   uint32_t res_v0 = 0, res_v1 = 0;
   uint64_t res_f0 = 0, res_f1 = 0;
@@ -96,6 +98,7 @@ struct pd_ctx_impl {
   std::vector<cudaEvent_t> ev_pool;
 
   SubsetState subset;
+  uint32_t last_score_n = 0, last_score_k = 0, last_sample_n = 0;  // extents of the results left on the device
 
   pdk::LaunchStats launch_stats;
   pd_stats_t stats{};

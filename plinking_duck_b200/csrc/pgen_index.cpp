@@ -2,6 +2,7 @@
 // pgenlib is stricter or differs from the spec text, pgenlib_read.cc.
 #include "pgen_index.h"
 
+#include <cuda_runtime.h>
 #include <fcntl.h>
 #include <sys/stat.h>
 #include <unistd.h>
@@ -38,8 +39,15 @@ void ByteSource::OpenMem(const void* p, uint64_t len) {
   size_ = len;
 }
 
+void ByteSource::OpenDevice(const void* p, uint64_t len) {
+  dev_ = static_cast<const uint8_t*>(p);
+  mem_ = nullptr;
+  size_ = len;
+}
+
 bool ByteSource::ReadAt(uint64_t off, void* dst, uint64_t len) const {
   if (off > size_ || len > size_ - off) return false;
+  if (dev_) return cudaMemcpy(dst, dev_ + off, len, cudaMemcpyDeviceToHost) == cudaSuccess;
   if (mem_) {
     memcpy(dst, mem_ + off, len);
     return true;

@@ -20,6 +20,9 @@ class ByteSource {
   ByteSource& operator=(const ByteSource&) = delete;
   bool OpenFile(const char* path, std::string* err);
   void OpenMem(const void* p, uint64_t len);
+  // A .pgen image that already lives in device memory (reads go through cudaMemcpy).
+  void OpenDevice(const void* p, uint64_t len);
+  const uint8_t* dev() const { return dev_; }
   uint64_t size() const { return size_; }
   bool is_mem() const { return mem_ != nullptr; }
   const uint8_t* mem() const { return mem_; }
@@ -29,6 +32,7 @@ class ByteSource {
  private:
   int fd_ = -1;
   const uint8_t* mem_ = nullptr;
+  const uint8_t* dev_ = nullptr;
   uint64_t size_ = 0;
 };
 

@@ -69,6 +69,25 @@ class PgenContext:
         arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(nbytes,))
         return cls(image=arr, **kw)
 
+    @classmethod
+    def from_device_pointer(cls, ptr: int, nbytes: int, device: int = -1, **kw):
+        """Open a .pgen image that already lives in this GPU's memory (used in place, always resident).
+        The allocation must extend >= 64 bytes past nbytes."""
+        self = cls.__new__(cls)
+        self._lib = nat.load()
+        self._h = C.c_void_p()
+        self._keep = None
+        opts = nat.OpenOpts(device, kw.get("tile_bytes", 0), kw.get("n_staging", 0), 0)
+        err = C.create_string_buffer(512)
+        rc = self._lib.pd_open_mem(C.c_void_p(ptr), nbytes, None, 0, C.byref(opts), C.byref(self._h), err, 512)
+        if rc:
+            raise nat.PlinkGpuError(rc, err.value.decode(errors="replace"))
+        info = self.info()
+        self.variant_ct = info.variant_ct
+        self.raw_sample_ct = info.sample_ct
+        self.sample_ct = info.sample_ct
+        return self
+
     # -- lifetime --
     def close(self):
         if self._h:
