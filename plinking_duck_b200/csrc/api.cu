@@ -37,6 +37,8 @@ void DestroyCtx(pd_ctx* c) {
     c->h_bounce[b].Free();
     if (c->ev_out_ready[b]) cudaEventDestroy(c->ev_out_ready[b]);
     if (c->ev_out_free[b]) cudaEventDestroy(c->ev_out_free[b]);
+    if (c->ev_prod0[b]) cudaEventDestroy(c->ev_prod0[b]);
+    if (c->ev_prod1[b]) cudaEventDestroy(c->ev_prod1[b]);
   }
   if (c->d2h_stream) cudaStreamDestroy(c->d2h_stream);
   c->h_misc.Free(); c->h_out.Free();
@@ -78,6 +80,8 @@ int InitDevice(pd_ctx* c, const pd_open_opts* opts) {
   for (int b = 0; b < 2; ++b) {
     cudaEventCreateWithFlags(&c->ev_out_ready[b], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&c->ev_out_free[b], cudaEventDisableTiming);
+    cudaEventCreate(&c->ev_prod0[b]);
+    cudaEventCreate(&c->ev_prod1[b]);
   }
   c->h_stage.resize(c->n_staging);
   c->d_stage.resize(c->n_staging);

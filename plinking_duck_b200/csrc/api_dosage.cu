@@ -149,6 +149,7 @@ int pd_dosage_f64(pd_ctx* c, const uint32_t* vidx, uint32_t n_var, double* out) 
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev_c0, c->ev_c1);
     c->stats.call_ms = ms;
+    c->stats.kernel_ms = pipe.produce_ms;  // the decode kernels alone; call_ms includes the D2H stream
   }
   return rc != PD_OK ? rc : rc2;
 }

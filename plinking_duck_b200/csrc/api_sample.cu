@@ -63,10 +63,10 @@ int SampleAccumulate(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t 
   const uint32_t* idx = c->subset.active ? c->subset.d_idx.as<uint32_t>() : nullptr;
   uint32_t* out = c->d_out[0].as<uint32_t>();
   cudaMemsetAsync(out, 0, 3 * static_cast<size_t>(n_out) * 4, c->stream);
-  for (uint32_t k = 0; k < 3; ++k) {
-    if (kinds & (1u << k)) {
-      pdk::launch_gather_u32(acc + k * npad, idx, n_out, out + static_cast<size_t>(k) * n_out, c->stream, &c->launch_stats);
-    }
+  if (kinds == 7) {
+    pdk::launch_planes_to_counts(acc, acc + npad, acc + 2 * npad, idx, n_out, out, c->stream, &c->launch_stats);
+  } else {
+    pdk::launch_gather_u32(acc + 2 * npad, idx, n_out, out + 2 * static_cast<size_t>(n_out), c->stream, &c->launch_stats);
   }
   return PD_OK;
 }
@@ -162,6 +162,7 @@ int pd_decode_i8(pd_ctx* c, uint32_t v_begin, uint32_t v_end, int8_t* out) {
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev_c0, c->ev_c1);
     c->stats.call_ms = ms;
+    c->stats.kernel_ms = pipe.produce_ms;  // the decode kernels alone; call_ms includes the D2H stream
   }
   return rc != PD_OK ? rc : rc2;
 }

@@ -92,6 +92,7 @@ struct pd_ctx_impl {
   PinnedBuf h_bounce[2];
   cudaStream_t d2h_stream = nullptr;
   cudaEvent_t ev_out_ready[2] = {nullptr, nullptr}, ev_out_free[2] = {nullptr, nullptr};
+  cudaEvent_t ev_prod0[2] = {nullptr, nullptr}, ev_prod1[2] = {nullptr, nullptr};  // producer kernel timing
   PinnedBuf h_misc;   // int err[2] + small readbacks
   PinnedBuf h_out;    // pinned bounce buffer for results
   cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_t0 = nullptr, ev_t1 = nullptr, ev_c0 = nullptr, ev_c1 = nullptr;

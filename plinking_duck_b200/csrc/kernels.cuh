@@ -80,10 +80,13 @@ void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint
 // out[r * n_out + j] = {0,1,2,-9} of sample subset_idx[j] (or j) -- PgrGet + GenoarrToBytesMinus9.
 void launch_expand_i8(const DenseRows& rows, const uint32_t* subset_idx, uint32_t n_out, int8_t* out, cudaStream_t s,
                       LaunchStats* st);
-// acc_*[raw sample] += number of rows where the sample is het / hom-alt / missing.
-// kinds: bit 0 het, bit 1 hom-alt, bit 2 missing (4 = missing only, 7 = all three).
+// Per raw sample, number of rows whose E (low) bit / O (high) bit / both bits are set:
+// acc_het += |E|, acc_hom += |O|, acc_mis += |E & O|; het = E - B, hom_alt = O - B, missing = B
+// (launch_planes_to_counts).  kinds: 4 = missing (B) only, 7 = all three planes.
 void launch_sample_acc(const DenseRows& rows, uint32_t kinds, uint32_t* acc_het, uint32_t* acc_hom, uint32_t* acc_mis,
                        cudaStream_t s, LaunchStats* st);
+void launch_planes_to_counts(const uint32_t* pe, const uint32_t* po, const uint32_t* pb, const uint32_t* idx, uint32_t n,
+                             uint32_t* out, cudaStream_t s, LaunchStats* st);
 void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t n, uint32_t* dst, cudaStream_t s,
                        LaunchStats* st);
 void launch_subset_indices(const uint32_t* include_words, const uint32_t* cum, uint32_t nwords, uint32_t* out,
@@ -126,6 +129,8 @@ struct ScoreRow {
   double sd;
   uint32_t flags;
   uint32_t kind;        // dosage storage kind of the row (DosageLoc::kind)
+  uint32_t cmask;       // bit g set: hardcall g counts towards ALLELE_CT (0 for skipped rows)
+  uint32_t pad;
 };
 // counts: (subset) hardcall counts per row; stats: dosage sums per row or nullptr; flip: per row or nullptr.
 void launch_score_prep(const uint4* counts, const DosageStats* stats, const uint8_t* flip, uint32_t nrows, uint32_t mode,

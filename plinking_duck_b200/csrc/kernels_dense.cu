@@ -166,74 +166,174 @@ struct Widen {
   }
 };
 
+// Bit planes of one word: E (low bits), O (high bits), B = E & O.  The accumulators count planes,
+// not categories: het = E - B, hom_alt = O - B, missing = B are formed once per sample at the end
+// (k_planes_to_counts), which saves two logic ops per word in the streaming loop.
 template <int KINDS>
-__device__ __forceinline__ void acc_flags(uint32_t x, uint32_t& het, uint32_t& hom, uint32_t& mis) {
+__device__ __forceinline__ void acc_flags(uint32_t x, uint32_t& pe, uint32_t& po, uint32_t& pb) {
   const uint32_t e = x & kM5, o = (x >> 1) & kM5;
-  if (KINDS & 1) het += e & ~o;
-  if (KINDS & 2) hom += o & ~e;
-  if (KINDS & 4) mis += e & o;
+  if (KINDS & 1) pe += e;
+  if (KINDS & 2) po += o;
+  if (KINDS & 4) pb += e & o;
 }
 
-template <int KINDS>
+// VEC consecutive 32-bit words (16 samples each) of a row starting at word w0.  ALIGNED (decided
+// on the host for the whole launch): one vector load.  Otherwise VEC + 1 aligned words
+// funnel-shifted into place.  Either way straight-line code, so the loads of several rows can be
+// in flight together.
+template <int VEC, bool ALIGNED>
+__device__ __forceinline__ void load_words(const uint8_t* row, uint32_t w0, uint32_t (&x)[VEC]) {
+  const uintptr_t a = reinterpret_cast<uintptr_t>(row) + 4ull * w0;
+  if (ALIGNED) {
+    if (VEC == 4) {
+      const uint4 v = ldg_stream(reinterpret_cast<const uint4*>(a));
+      x[0] = v.x; x[1 % VEC] = v.y; x[2 % VEC] = v.z; x[3 % VEC] = v.w;
+    } else if (VEC == 2) {
+      const uint2 v = __ldg(reinterpret_cast<const uint2*>(a));
+      x[0] = v.x; x[1 % VEC] = v.y;
+    } else {
+      x[0] = __ldg(reinterpret_cast<const uint32_t*>(a));
+    }
+  } else {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~static_cast<uintptr_t>(3));
+    const uint32_t sh = static_cast<uint32_t>(a & 3) << 3;
+    uint32_t t[VEC + 1];
+#pragma unroll
+    for (int k = 0; k <= VEC; ++k) t[k] = __ldg(w + k);
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) x[k] = __funnelshift_r(t[k], t[k + 1], sh);  // sh == 0 -> t[k]
+  }
+}
+
+// MODE 0: rows at base + r * stride, vector-aligned; 1: same, any alignment; 2: row pointer table.
+template <int KINDS, int VEC, int MODE>
 __global__ void __launch_bounds__(128)
 k_sample_acc(DenseRows rows, uint32_t rows_per_chunk, uint32_t* __restrict__ acc_het, uint32_t* __restrict__ acc_hom,
              uint32_t* __restrict__ acc_mis) {
+  constexpr int UNROLL = 6;  // two groups of three rows: the 2-bit stage holds three rows
   const uint32_t N = rows.N;
   const uint32_t ncols = (N + 15) >> 4;
-  const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
-  if (w >= ncols) return;
+  const uint32_t w0 = (blockIdx.x * blockDim.x + threadIdx.x) * VEC;
+  if (w0 >= ncols) return;
   const uint32_t r0 = blockIdx.y * rows_per_chunk;
   const uint32_t r1 = min(rows.nrows, r0 + rows_per_chunk);
-  const uint32_t valid = min(16u, N - 16u * w);
-  const uint32_t colmask = valid == 16 ? 0xffffffffu : ((1u << (2 * valid)) - 1u);
-  Widen het, hom, mis;
-  het.clear();
-  hom.clear();
-  mis.clear();
+  Widen het[VEC], hom[VEC], mis[VEC];
+#pragma unroll
+  for (int k = 0; k < VEC; ++k) {
+    het[k].clear();
+    hom[k].clear();
+    mis[k].clear();
+  }
   uint32_t nb = 0, nc = 0;
+  auto flush_all = [&]() {
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+      if (KINDS & 1) het[k].flush(acc_het, 16u * (w0 + k), N);
+      if (KINDS & 2) hom[k].flush(acc_hom, 16u * (w0 + k), N);
+      if (KINDS & 4) mis[k].flush(acc_mis, 16u * (w0 + k), N);
+    }
+  };
+  auto b_to_c_all = [&]() {
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+      if (KINDS & 1) het[k].b_to_c();
+      if (KINDS & 2) hom[k].b_to_c();
+      if (KINDS & 4) mis[k].b_to_c();
+    }
+  };
   auto step_b = [&]() {
     if (++nb == 5) {
       nb = 0;
-      if (KINDS & 1) het.b_to_c();
-      if (KINDS & 2) hom.b_to_c();
-      if (KINDS & 4) mis.b_to_c();
+      b_to_c_all();
       if (++nc == 17) {
         nc = 0;
-        if (KINDS & 1) het.flush(acc_het, 16u * w, N);
-        if (KINDS & 2) hom.flush(acc_hom, 16u * w, N);
-        if (KINDS & 4) mis.flush(acc_mis, 16u * w, N);
+        flush_all();
       }
     }
   };
-  uint32_t r = r0;
-  for (; r + 6 <= r1; r += 6) {
-    uint32_t x[6];
+  // Software pipeline: the loads of the next UNROLL rows are issued before the current rows are
+  // consumed, so every warp always has a batch in flight.
+  auto load_batch = [&](uint32_t rr, uint32_t (&x)[UNROLL][VEC]) {
+    const uint8_t* rp[UNROLL];
 #pragma unroll
-    for (int j = 0; j < 6; ++j) x[j] = row_word(row_ptr(rows, r + j), w) & colmask;
+    for (int j = 0; j < UNROLL; ++j) {
+      rp[j] = (MODE == 2) ? rows.ptrs[rr + j] : rows.base + static_cast<uint64_t>(rr + j) * rows.stride;
+    }
 #pragma unroll
-    for (int t = 0; t < 2; ++t) {
-      uint32_t a_het = 0, a_hom = 0, a_mis = 0;
+    for (int j = 0; j < UNROLL; ++j) load_words<VEC, MODE == 0>(rp[j], w0, x[j]);
+  };
+  auto consume = [&](uint32_t (&x)[UNROLL][VEC]) {
 #pragma unroll
-      for (int j = 0; j < 3; ++j) acc_flags<KINDS>(x[3 * t + j], a_het, a_hom, a_mis);
-      if (KINDS & 1) het.add_a(a_het);
-      if (KINDS & 2) hom.add_a(a_hom);
-      if (KINDS & 4) mis.add_a(a_mis);
+    for (int t = 0; t < UNROLL / 3; ++t) {
+#pragma unroll
+      for (int k = 0; k < VEC; ++k) {
+        uint32_t a_het = 0, a_hom = 0, a_mis = 0;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) acc_flags<KINDS>(x[3 * t + j][k], a_het, a_hom, a_mis);
+        if (KINDS & 1) het[k].add_a(a_het);
+        if (KINDS & 2) hom[k].add_a(a_hom);
+        if (KINDS & 4) mis[k].add_a(a_mis);
+      }
       step_b();
+    }
+  };
+  uint32_t r = r0;
+  if (r + UNROLL <= r1) {
+    uint32_t xa[UNROLL][VEC], xb[UNROLL][VEC];
+    load_batch(r, xa);
+    for (;;) {
+      if (r + 2 * UNROLL > r1) {
+        consume(xa);
+        r += UNROLL;
+        break;
+      }
+      load_batch(r + UNROLL, xb);
+      consume(xa);
+      r += UNROLL;
+      if (r + 2 * UNROLL > r1) {
+        consume(xb);
+        r += UNROLL;
+        break;
+      }
+      load_batch(r + UNROLL, xa);
+      consume(xb);
+      r += UNROLL;
     }
   }
   while (r < r1) {
-    uint32_t a_het = 0, a_hom = 0, a_mis = 0;
+    uint32_t a_het[VEC], a_hom[VEC], a_mis[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) a_het[k] = a_hom[k] = a_mis[k] = 0;
     for (int j = 0; j < 3 && r < r1; ++j, ++r) {
-      acc_flags<KINDS>(row_word(row_ptr(rows, r), w) & colmask, a_het, a_hom, a_mis);
+      uint32_t x[VEC];
+      load_words<VEC, MODE == 0>(row_ptr(rows, r), w0, x);
+#pragma unroll
+      for (int k = 0; k < VEC; ++k) acc_flags<KINDS>(x[k], a_het[k], a_hom[k], a_mis[k]);
     }
-    if (KINDS & 1) het.add_a(a_het);
-    if (KINDS & 2) hom.add_a(a_hom);
-    if (KINDS & 4) mis.add_a(a_mis);
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+      if (KINDS & 1) het[k].add_a(a_het[k]);
+      if (KINDS & 2) hom[k].add_a(a_hom[k]);
+      if (KINDS & 4) mis[k].add_a(a_mis[k]);
+    }
     step_b();
   }
-  if (KINDS & 1) { het.b_to_c(); het.flush(acc_het, 16u * w, N); }
-  if (KINDS & 2) { hom.b_to_c(); hom.flush(acc_hom, 16u * w, N); }
-  if (KINDS & 4) { mis.b_to_c(); mis.flush(acc_mis, 16u * w, N); }
+  b_to_c_all();
+  flush_all();
+}
+
+// acc arrays hold plane counts (E, O, B) per raw sample; out gets het / hom_alt / missing of the
+// subset samples, three arrays of n each.
+__global__ void k_planes_to_counts(const uint32_t* __restrict__ pe, const uint32_t* __restrict__ po,
+                                   const uint32_t* __restrict__ pb, const uint32_t* __restrict__ idx, uint32_t n,
+                                   uint32_t* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t s = idx ? idx[i] : i;
+  const uint32_t b = pb[s];
+  out[i] = pe[s] - b;
+  out[n + i] = po[s] - b;
+  out[2ull * n + i] = b;
 }
 
 __global__ void k_gather_u32(const uint32_t* __restrict__ src, const uint32_t* __restrict__ idx, uint32_t n,
@@ -319,20 +419,29 @@ void launch_sample_acc(const DenseRows& rows, uint32_t kinds, uint32_t* acc_het,
                        cudaStream_t s, LaunchStats* st) {
   if (!rows.nrows || !rows.N) return;
   const uint32_t ncols = (rows.N + 15) >> 4;
-  const uint32_t bx = (ncols + 127) / 128;
-  // aim at ~16 CTAs of 128 threads per SM, but keep >= 510 rows per chunk when rows allow so
+  const uint32_t vec = (kinds == 4) ? 4 : 2;  // words per thread: 64 B / 32 B of a record per warp-row... x32 lanes
+  const uint32_t nthreads = (ncols + vec - 1) / vec;
+  const uint32_t bx = (nthreads + 127) / 128;
+  // aim at ~12 CTAs of 128 threads per SM, but keep >= 255 rows per chunk when rows allow so
   // that the 8-bit -> 32-bit flushes stay rare
-  uint32_t want_y = (static_cast<uint32_t>(sm_count()) * 16 + bx - 1) / bx;
+  uint32_t want_y = (static_cast<uint32_t>(sm_count()) * 12 + bx - 1) / bx;
   if (want_y < 1) want_y = 1;
   uint32_t rpc = (rows.nrows + want_y - 1) / want_y;
   if (rpc < 255) rpc = 255;
   rpc = (rpc + 5) / 6 * 6;
   const uint32_t by = (rows.nrows + rpc - 1) / rpc;
   dim3 grid(bx, by);
-  switch (kinds) {
-    case 4: k_sample_acc<4><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis); break;
-    case 7: k_sample_acc<7><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis); break;
-    default: k_sample_acc<7><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis); break;
+  const uint32_t align = 4 * vec;
+  const bool aligned = !rows.ptrs && (reinterpret_cast<uintptr_t>(rows.base) % align == 0) && (rows.stride % align == 0);
+  const int mode = rows.ptrs ? 2 : (aligned ? 0 : 1);
+  if (kinds == 4) {
+    if (mode == 0) k_sample_acc<4, 4, 0><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
+    else if (mode == 1) k_sample_acc<4, 4, 1><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
+    else k_sample_acc<4, 4, 2><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
+  } else {
+    if (mode == 0) k_sample_acc<7, 2, 0><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
+    else if (mode == 1) k_sample_acc<7, 2, 1><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
+    else k_sample_acc<7, 2, 2><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
   }
   if (st) st->launches++;
 }
@@ -347,6 +456,13 @@ void launch_count_rows(const DenseRows& rows, const SubsetDev& sub, uint4* out, 
   } else {
     k_count_rows<false><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(rows, sub, out);
   }
+  if (st) st->launches++;
+}
+
+void launch_planes_to_counts(const uint32_t* pe, const uint32_t* po, const uint32_t* pb, const uint32_t* idx, uint32_t n,
+                             uint32_t* out, cudaStream_t s, LaunchStats* st) {
+  if (!n) return;
+  k_planes_to_counts<<<(n + 255) / 256, 256, 0, s>>>(pe, po, pb, idx, n, out);
   if (st) st->launches++;
 }
 

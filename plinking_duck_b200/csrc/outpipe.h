@@ -20,6 +20,7 @@ struct OutPipe {
     bool live = false;
   } pend[2];
   uint32_t next = 0;
+  double produce_ms = 0;  // CUDA-event time of the producing kernels, summed over batches
 
   int Init(pd_ctx_impl* ctx, const void* user_dst, size_t bytes_per_batch) {
     c = ctx;
@@ -39,6 +40,8 @@ struct OutPipe {
     cudaError_t e = cudaEventSynchronize(c->ev_out_free[b]);
     if (e != cudaSuccess) return CheckCuda(c, e, "result download");
     if (!direct) ParallelMemcpy(pend[b].dst, c->h_bounce[b].p, pend[b].bytes);
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, c->ev_prod0[b], c->ev_prod1[b]) == cudaSuccess) produce_ms += ms;
     pend[b].live = false;
     return PD_OK;
   }
@@ -49,10 +52,12 @@ struct OutPipe {
     if (rc != PD_OK) return rc;
     *dev = c->d_out[b].p;
     *slot = b;
+    cudaEventRecord(c->ev_prod0[b], c->stream);
     return PD_OK;
   }
   // Call after the producing kernels of slot b were enqueued on stream s.
   int Send(int b, cudaStream_t s, void* host_dst, size_t bytes) {
+    cudaEventRecord(c->ev_prod1[b], s);
     cudaEventRecord(c->ev_out_ready[b], s);
     cudaStreamWaitEvent(c->d2h_stream, c->ev_out_ready[b], 0);
     void* dst = direct ? host_dst : c->h_bounce[b].p;

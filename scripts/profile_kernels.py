@@ -1,0 +1,96 @@
+#!/usr/bin/env python
+"""Per-kernel throughput on device-resident records (development tool; bench.py is the contract).
+
+Generates a fixed-width .pgen image straight into HBM and times every entry point with the library's
+own CUDA-event stats: kernel_ms (scan kernels only) and call_ms (whole call incl. result copies).
+Prints one JSON line per operation with achieved GB/s of algorithmic bytes against MEASURED_PEAKS.json.
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--variants", type=int, default=200_000)
+    ap.add_argument("--samples", type=int, default=100_000)
+    ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--ops", default="counts,counts_subset,hardy,missing_by_sample,sample_counts,decode_i8,score1,score16")
+    ap.add_argument("--score-variants", type=int, default=20_000)
+    ap.add_argument("--decode-variants", type=int, default=20_000)
+    args = ap.parse_args()
+
+    import torch
+
+    import bench
+    from plinking_duck_b200.pgen import PgenContext
+
+    dev = torch.device("cuda", 0)
+    V, N = args.variants, args.samples
+    W = (N + 3) // 4
+    nbytes = 12 + V * W
+    img = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
+    bench.generate_image_gpu(V, N, 1234, dev, img)
+    peak, _ = bench.peaks()
+    ctx = PgenContext.from_device_pointer(img.data_ptr(), nbytes, device=0)
+    ops = args.ops.split(",")
+    rng = np.random.default_rng(5)
+
+    def report(name, fn, alg_bytes, calls, extra=None):
+        fn()  # warm-up
+        ks, cs = [], []
+        for _ in range(args.reps):
+            fn()
+            st = ctx.stats()
+            ks.append(st.kernel_ms)
+            cs.append(st.call_ms)
+        k, c = float(np.median(ks)), float(np.median(cs))
+        line = {"op": name, "kernel_ms": k, "call_ms": c, "alg_GBps_kernel": alg_bytes / (k * 1e-3) / 1e9 if k else None,
+                "frac_of_peak": alg_bytes / (k * 1e-3) / 1e9 / peak if k else None,
+                "Tcalls_per_s_kernel": calls / (k * 1e-3) / 1e12 if k else None,
+                "Tcalls_per_s_call": calls / (c * 1e-3) / 1e12 if c else None}
+        if extra:
+            line.update(extra)
+        print(json.dumps(line), flush=True)
+
+    if "counts" in ops:
+        report("counts", lambda: ctx.counts(), V * W, V * N)
+    if "counts_subset" in ops:
+        ctx.set_subset(np.arange(0, N, 2))
+        report("counts_subset50", lambda: ctx.counts(), V * W, V * N)
+        ctx.set_subset(None)
+    if "hardy" in ops:
+        report("hardy", lambda: ctx.hardy(), V * W, V * N)
+    if "missing_by_sample" in ops:
+        report("missing_by_sample", lambda: ctx.missing_by_sample(), V * W, V * N)
+    if "sample_counts" in ops:
+        report("sample_counts", lambda: ctx.sample_counts(), V * W, V * N)
+    if "decode_i8" in ops:
+        Vd = min(V, args.decode_variants)
+        out = torch.empty((Vd, N), dtype=torch.int8, pin_memory=True).numpy()
+        import ctypes as C
+
+        def dec():
+            ctx._check(ctx._lib.pd_decode_i8(ctx._h, 0, Vd, out.ctypes.data_as(C.c_void_p)))
+
+        report("decode_i8", dec, Vd * (W + N), Vd * N, {"note": "kernel_ms = expand kernels; call_ms includes D2H of N bytes/variant"})
+    for K in (1, 16):
+        if f"score{K}" in ops:
+            Vs = min(V, args.score_variants)
+            vid = np.arange(Vs, dtype=np.uint32)
+            Wt = rng.standard_normal((Vs, K))
+            fl = (rng.random(Vs) < 0.1).astype(np.uint8)
+            report(f"score_K{K}", lambda: ctx.score(vid, fl, Wt, 0), Vs * W, Vs * N,
+                   {"flops": 2.0 * Vs * N * K, "note": "TFLOP/s = flops / kernel_ms"})
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()
