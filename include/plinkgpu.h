@@ -127,6 +127,11 @@ int pd_hardy(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint3
 /* Exact-test p-values for caller-supplied counts (n x 4, as pd_counts), computed on the device. */
 int pd_hwe_from_counts(pd_ctx* ctx, const uint32_t* counts, uint32_t n, uint32_t midp, double* out_p);
 
+/* chrX non-PAR exact test on the device: replaces HweExactTestXchr -> plink2::HweXchrLnP
+ * (src/plink_hardy.cpp:83-95).  c5[5*i + {0..4}] = female hom_ref, female het, female hom_alt,
+ * male REF-hemizygous, male ALT-hemizygous. */
+int pd_hwe_xchr_from_counts(pd_ctx* ctx, const uint32_t* c5, uint32_t n, uint32_t midp, double* out_p);
+
 /* ---- plink_missing sample mode: replaces PgrGetMissingness + the ctz bit walk + mutex merge
  *      (src/plink_missing.cpp:585-619).  out_missing[effective sample_ct]. ---- */
 int pd_missing_by_sample(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t* out_missing);

@@ -263,4 +263,27 @@ int pd_hwe_from_counts(pd_ctx* c, const uint32_t* counts, uint32_t n, uint32_t m
   return rc;
 }
 
+int pd_hwe_xchr_from_counts(pd_ctx* c, const uint32_t* c5, uint32_t n, uint32_t midp, double* out_p) {
+  if (!c || (n && (!c5 || !out_p))) return PD_ERR_INVALID_ARG;
+  if (!n) return PD_OK;
+  std::lock_guard<std::mutex> lock(c->mu);
+  cudaSetDevice(c->device);
+  cudaError_t e = c->d_counts.Reserve(static_cast<size_t>(n) * 20);
+  if (e == cudaSuccess) e = c->d_pvals.Reserve(static_cast<size_t>(n) * 8);
+  if (e != cudaSuccess) return CheckCuda(c, e, "allocation");
+  e = cudaMemcpyAsync(c->d_counts.p, c5, static_cast<size_t>(n) * 20, cudaMemcpyHostToDevice, c->stream);
+  if (e != cudaSuccess) return CheckCuda(c, e, "counts upload");
+  c->stats.h2d_bytes += static_cast<size_t>(n) * 20;
+  cudaEventRecord(c->ev_a, c->stream);
+  pdk::launch_hwe_xchr(c->d_counts.as<uint32_t>(), n, midp, c->d_pvals.as<double>(), c->stream, &c->launch_stats);
+  cudaEventRecord(c->ev_b, c->stream);
+  int rc = DownloadRows(c, c->d_pvals.p, static_cast<size_t>(n) * 8, out_p);
+  if (rc == PD_OK) {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev_a, c->ev_b);
+    c->stats.aux_kernel_ms = ms;
+  }
+  return rc;
+}
+
 }  // extern "C"

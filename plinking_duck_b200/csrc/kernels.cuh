@@ -145,5 +145,7 @@ void launch_score_acc(const DenseRows& rows, const ScoreRow* srow, const DosageL
 // ---- K8: exact Hardy-Weinberg test on the device ----
 // counts[n] as produced by the count kernels; out_p[n] = p-value clamped to [0,1].
 void launch_hwe(const uint4* counts, uint32_t n, uint32_t midp, double* out_p, cudaStream_t s, LaunchStats* st);
+// chrX exact test: c5[n][5] = female hom_ref, het, hom_alt, male ref, male alt.
+void launch_hwe_xchr(const uint32_t* c5, uint32_t n, uint32_t midp, double* out_p, cudaStream_t s, LaunchStats* st);
 
 }  // namespace pdk

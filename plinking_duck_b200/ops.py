@@ -1,0 +1,114 @@
+"""ctypes binding of the operator layer (include/plinkgpu_ops.h): the reference's table functions
+as numpy record arrays.  Argument names follow the SQL surface (midp, dosage, samples, region is a
+variant range here because .pvar parsing stays in the extension)."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _native as nat
+from .pgen import PgenContext, _p
+
+PLOIDY_AUTOSOMAL, PLOIDY_CHR_X, PLOIDY_CHR_Y, PLOIDY_CHR_MT = 0, 1, 2, 3
+
+FREQ_DTYPE = np.dtype([("ALT_FREQ", "<f8"), ("IMP_R2", "<f8"), ("OBS_CT", "<u4"), ("HOM_REF_CT", "<i4"), ("HET_CT", "<i4"),
+                       ("HOM_ALT_CT", "<i4"), ("MISSING_CT", "<i4"), ("freq_is_null", "u1"), ("counts_are_null", "u1"),
+                       ("pad", "u1", (2,))], align=True)
+HARDY_DTYPE = np.dtype([("O_HET", "<f8"), ("E_HET", "<f8"), ("P_HWE", "<f8"), ("HOM_REF_CT", "<i4"), ("HET_CT", "<i4"),
+                        ("HOM_ALT_CT", "<i4"), ("stats_are_null", "u1"), ("counts_are_null", "u1"), ("pad", "u1", (2,))],
+                       align=True)
+MISSING_DTYPE = np.dtype([("MISSING_CT", "<u4"), ("OBS_CT", "<u4"), ("F_MISS", "<f8")], align=True)
+SCORE_DTYPE = np.dtype([("ALLELE_CT", "<u4"), ("DENOM", "<u4"), ("NAMED_ALLELE_DOSAGE_SUM", "<f8"), ("SCORE_SUM", "<f8"),
+                        ("SCORE_AVG", "<f8")], align=True)
+
+_vp, _u32 = C.c_void_p, C.c_uint32
+_OPS = {
+    "pdop_classify_ploidy": (C.c_int, [C.c_char_p, C.c_int32, C.c_char_p]),
+    "pdop_freq": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _u32, _vp]),
+    "pdop_hardy": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _u32, _vp]),
+    "pdop_missing_variant": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "pdop_missing_sample": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "pdop_score": (C.c_int, [_vp, _vp, _vp, _vp, _u32, _u32, _vp]),
+    "pdop_counts_pass": (C.c_int, [_vp, C.c_double, C.c_double, C.c_int64, C.c_int64]),
+}
+_bound = False
+
+
+def _lib():
+    global _bound
+    lib = nat.load()
+    if not _bound:
+        for name, (res, args) in _OPS.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        _bound = True
+    return lib
+
+
+def classify_ploidy(chrom: str, pos: int, build: str = "GRCh38") -> int:
+    r = _lib().pdop_classify_ploidy(chrom.encode(), int(pos), build.encode())
+    if r < 0:
+        raise ValueError(f"unrecognized build '{build}' (expected 'GRCh38'/'hg38', 'GRCh37'/'hg19', or 'none')")
+    return r
+
+
+def _u8(a, n, what):
+    if a is None:
+        return None
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    if a.size != n:
+        raise ValueError(f"{what} must have {n} entries")
+    return a
+
+
+def _range(ctx, v0, v1):
+    return int(v0), int(ctx.variant_ct if v1 is None else v1)
+
+
+def plink_freq(ctx: PgenContext, v0=0, v1=None, *, ploidy=None, sex=None, dosage=False) -> np.ndarray:
+    v0, v1 = _range(ctx, v0, v1)
+    out = np.zeros(max(v1 - v0, 0), dtype=FREQ_DTYPE)
+    pl, sx = _u8(ploidy, ctx.variant_ct, "ploidy"), _u8(sex, ctx.raw_sample_ct, "sex")
+    ctx._check(_lib().pdop_freq(ctx._h, v0, v1, _p(pl), _p(sx), int(bool(dosage)), _p(out)))
+    return out
+
+
+def plink_hardy(ctx: PgenContext, v0=0, v1=None, *, ploidy=None, sex=None, midp=False) -> np.ndarray:
+    v0, v1 = _range(ctx, v0, v1)
+    out = np.zeros(max(v1 - v0, 0), dtype=HARDY_DTYPE)
+    pl, sx = _u8(ploidy, ctx.variant_ct, "ploidy"), _u8(sex, ctx.raw_sample_ct, "sex")
+    ctx._check(_lib().pdop_hardy(ctx._h, v0, v1, _p(pl), _p(sx), int(bool(midp)), _p(out)))
+    return out
+
+
+def plink_missing(ctx: PgenContext, v0=0, v1=None, *, mode="variant") -> np.ndarray:
+    v0, v1 = _range(ctx, v0, v1)
+    if mode == "variant":
+        out = np.zeros(max(v1 - v0, 0), dtype=MISSING_DTYPE)
+        ctx._check(_lib().pdop_missing_variant(ctx._h, v0, v1, _p(out)))
+    elif mode == "sample":
+        out = np.zeros(ctx.sample_ct, dtype=MISSING_DTYPE)
+        ctx._check(_lib().pdop_missing_sample(ctx._h, v0, v1, _p(out)))
+    else:
+        raise ValueError("plink_missing: mode must be 'variant' or 'sample'")
+    return out
+
+
+def plink_score(ctx: PgenContext, vidx: Sequence[int], weights, *, flip=None, no_mean_imputation=False,
+                center=False) -> np.ndarray:
+    vidx = np.ascontiguousarray(vidx, dtype=np.uint32)
+    w = np.ascontiguousarray(weights, dtype=np.float64)
+    if w.shape != vidx.shape:
+        raise ValueError("plink_score: weights list length must match the number of variants")
+    fl = None if flip is None else np.ascontiguousarray(flip, dtype=np.uint8)
+    mode = 2 if center else (1 if no_mean_imputation else 0)
+    out = np.zeros(ctx.sample_ct, dtype=SCORE_DTYPE)
+    ctx._check(_lib().pdop_score(ctx._h, _p(vidx), _p(fl), _p(w), vidx.size, mode, _p(out)))
+    return out
+
+
+def counts_pass(counts, af_min=-1.0, af_max=-1.0, ac_min=-1, ac_max=-1) -> bool:
+    c = np.ascontiguousarray(counts, dtype=np.uint32)
+    return bool(_lib().pdop_counts_pass(_p(c), float(af_min), float(af_max), int(ac_min), int(ac_max)))

@@ -186,6 +186,13 @@ class PgenContext:
         self._check(self._lib.pd_hwe_from_counts(self._h, _p(counts), counts.shape[0], int(bool(midp)), _p(p)))
         return p
 
+    def hwe_xchr_from_counts(self, c5, midp=False) -> np.ndarray:
+        """c5: (n, 5) female hom_ref / het / hom_alt, male ref / alt."""
+        c5 = np.ascontiguousarray(c5, dtype=np.uint32).reshape(-1, 5)
+        p = np.zeros(c5.shape[0], dtype=np.float64)
+        self._check(self._lib.pd_hwe_xchr_from_counts(self._h, _p(c5), c5.shape[0], int(bool(midp)), _p(p)))
+        return p
+
     # -- per-sample accumulations --
     def missing_by_sample(self, v0=0, v1=None) -> np.ndarray:
         v0, v1 = self._range(v0, v1)

@@ -22,14 +22,16 @@ def _declared_symbols():
 
 def test_header_symbols_are_bound_and_exported(built):
     from plinking_duck_b200 import _native as nat
+    from plinking_duck_b200 import ops
 
     declared = _declared_symbols()
-    assert len(declared) >= 25
+    assert len(declared) >= 30
     lib = C.CDLL(nat.LIB_PATH)
+    bound = set(nat.SYMBOLS) | set(ops._OPS)
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/*.h but not exported"
-        assert name in nat.SYMBOLS, f"{name} has no ctypes binding"
-    assert set(nat.SYMBOLS) <= set(declared)
+        assert name in bound, f"{name} has no ctypes binding"
+    assert bound <= set(declared)
     assert nat.load().pd_version().decode().endswith("sm_100a")
 
 
@@ -84,3 +86,24 @@ def test_probe_rejects_bad_files(tmp_path, built):
     info, vt, fpos = probe(str(ok))
     assert (info.variant_ct, info.sample_ct, info.mode, info.fixed_width) == (10, 10, 2, 3)
     assert np.array_equal(fpos, 12 + 3 * np.arange(11))
+
+
+def test_ploidy_classification_matches_reference_rules(built):
+    """ClassifyChromPloidy / ResolveParBounds (src/plink_common.cpp:1926-1979)."""
+    from plinking_duck_b200 import ops
+
+    assert ops.classify_ploidy("1", 100) == ops.PLOIDY_AUTOSOMAL
+    assert ops.classify_ploidy("chrX", 50_000_000) == ops.PLOIDY_CHR_X
+    assert ops.classify_ploidy("23", 50_000_000) == ops.PLOIDY_CHR_X
+    assert ops.classify_ploidy("X", 1_000_000) == ops.PLOIDY_AUTOSOMAL          # GRCh38 PAR1
+    assert ops.classify_ploidy("X", 2_781_480) == ops.PLOIDY_CHR_X
+    assert ops.classify_ploidy("X", 2_700_000, "hg19") == ops.PLOIDY_CHR_X     # outside GRCh37 PAR1
+    assert ops.classify_ploidy("X", 1_000_000, "none") == ops.PLOIDY_CHR_X
+    assert ops.classify_ploidy("PAR1", 5) == ops.PLOIDY_AUTOSOMAL
+    assert ops.classify_ploidy("chrY", 5) == ops.PLOIDY_CHR_Y and ops.classify_ploidy("24", 5) == ops.PLOIDY_CHR_Y
+    for mt in ("MT", "chrM", "M", "26"):
+        assert ops.classify_ploidy(mt, 5) == ops.PLOIDY_CHR_MT
+    with pytest.raises(ValueError):
+        ops.classify_ploidy("X", 5, "GRCh99")
+    assert ops.counts_pass([1, 1, 1, 1], af_min=0.4, af_max=0.6) and not ops.counts_pass([1, 1, 1, 1], af_min=0.6)
+    assert not ops.counts_pass([0, 0, 0, 4]) and ops.counts_pass([2, 1, 1, 0], ac_min=3, ac_max=3)
