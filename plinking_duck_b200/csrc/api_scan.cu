@@ -213,16 +213,44 @@ int pd_hardy(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   cudaEventRecord(c->ev_c0, c->stream);
-  uint32_t v_ext = 0;
-  int rc = CountsToDevice(c, c->subset, v_begin, v_end, &v_ext);
-  if (rc != PD_OK) return rc;
+  if (v_begin > v_end || v_end > c->idx.variant_ct) return c->SetError(PD_ERR_INVALID_ARG, "variant range out of bounds");
   const uint32_t n = v_end - v_begin;
-  if (!n) return PD_OK;
-  cudaError_t e = c->d_pvals.Reserve(static_cast<size_t>(n) * 8);
+  cudaError_t e = c->d_pvals.Reserve(std::max<size_t>(8, static_cast<size_t>(n) * 8));
   if (e != cudaSuccess) return CheckCuda(c, e, "p-value allocation");
+  uint32_t v_ext = v_begin;
+  bool fused = false;
+  int rc = PD_OK;
+  if (c->idx.fixed && n) {
+    // K1h: counts and exact tests of a tile in one kernel (fixed-width records have no LD bases,
+    // so rows start at v_begin).
+    e = c->d_counts.Reserve(static_cast<size_t>(n) * 16);
+    if (e == cudaSuccess) e = c->d_ready.Reserve(static_cast<size_t>(n) * 4);
+    if (e != cudaSuccess) return CheckCuda(c, e, "counts allocation");
+    const pdk::SubsetDev sd = c->subset.Dev();
+    uint4* out_dev = c->d_counts.as<uint4>();
+    double* p_dev = c->d_pvals.as<double>();
+    uint32_t* ready = c->d_ready.as<uint32_t>();
+    bool all_fused = true;
+    rc = RunScan(c, v_begin, v_end, &v_ext, [&](const Tile& t, const pdk::RecIndex& ix, cudaStream_t s) {
+      const uint32_t off = t.v0 - v_begin;
+      if (!pdk::launch_hardy_fixed(ix, sd, t.v0, t.v1, out_dev + off, p_dev + off, midp, DevWorkCounter(c),
+                                   ready + off, s, &c->launch_stats)) {
+        all_fused = false;
+        pdk::launch_count_fixed(ix, sd, t.v0, t.v1, out_dev + off, s, &c->launch_stats);
+      }
+      c->stats.scan_launches += 1;
+      return PD_OK;
+    });
+    if (rc != PD_OK) return rc;
+    fused = all_fused;
+  } else {
+    rc = CountsToDevice(c, c->subset, v_begin, v_end, &v_ext);
+    if (rc != PD_OK) return rc;
+  }
+  if (!n) return PD_OK;
   const uint4* counts = c->d_counts.as<uint4>() + (v_begin - v_ext);
   cudaEventRecord(c->ev_a, c->stream);
-  pdk::launch_hwe(counts, n, midp, c->d_pvals.as<double>(), c->stream, &c->launch_stats);
+  if (!fused) pdk::launch_hwe(counts, n, midp, c->d_pvals.as<double>(), DevWorkCounter(c), c->stream, &c->launch_stats);
   cudaEventRecord(c->ev_b, c->stream);
   e = cudaMemcpyAsync(out_p, c->d_pvals.p, static_cast<size_t>(n) * 8, cudaMemcpyDeviceToHost, c->stream);
   if (e == cudaSuccess && out_counts) {
@@ -234,7 +262,7 @@ int pd_hardy(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_
   c->stats.d2h_bytes += static_cast<size_t>(n) * (out_counts ? 24 : 8);
   float ms = 0;
   cudaEventElapsedTime(&ms, c->ev_a, c->ev_b);
-  c->stats.aux_kernel_ms = ms;
+  c->stats.aux_kernel_ms = fused ? 0.0 : ms;  // fused: the exact tests ran inside the scan kernel
   cudaEventElapsedTime(&ms, c->ev_c0, c->ev_c1);
   c->stats.call_ms = ms;
   return PD_OK;
@@ -252,7 +280,7 @@ int pd_hwe_from_counts(pd_ctx* c, const uint32_t* counts, uint32_t n, uint32_t m
   if (e != cudaSuccess) return CheckCuda(c, e, "counts upload");
   c->stats.h2d_bytes += static_cast<size_t>(n) * 16;
   cudaEventRecord(c->ev_a, c->stream);
-  pdk::launch_hwe(c->d_counts.as<uint4>(), n, midp, c->d_pvals.as<double>(), c->stream, &c->launch_stats);
+  pdk::launch_hwe(c->d_counts.as<uint4>(), n, midp, c->d_pvals.as<double>(), DevWorkCounter(c), c->stream, &c->launch_stats);
   cudaEventRecord(c->ev_b, c->stream);
   int rc = DownloadRows(c, c->d_pvals.p, static_cast<size_t>(n) * 8, out_p);
   if (rc == PD_OK) {

@@ -112,6 +112,40 @@ __device__ __forceinline__ void planes_2bit(const uint8_t* p, uint32_t nsamp, in
   }
 }
 
+// Software-pipelined form for warps that share their SM with compute-heavy warps (K1h): the loads
+// of block i+1 are issued before block i is reduced, so a warp always has 32 x UNROLL x 16 bytes
+// in flight instead of alternating between waiting and counting.  Whole warp (LANES = 32).
+template <int UNROLL>
+__device__ __forceinline__ void planes_2bit_pipelined(const uint8_t* p, uint32_t nsamp, int lane, Planes& c) {
+  const uintptr_t addr = reinterpret_cast<uintptr_t>(p);
+  const uint32_t shift = static_cast<uint32_t>(addr & 15);
+  const uint4* base = reinterpret_cast<const uint4*>(addr - shift);
+  const int64_t lo = 8ll * shift;
+  const int64_t hi = lo + 2ll * nsamp;
+  const uint32_t nchunks = static_cast<uint32_t>((hi + 127) >> 7);
+  constexpr uint32_t kStep = 32 * UNROLL;
+  uint4 cur[UNROLL], nxt[UNROLL];
+  auto load = [&](uint4 (&v)[UNROLL], uint32_t c0) {
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) {
+      const uint32_t cc = c0 + j * 32;
+      v[j] = cc < nchunks ? ldg_stream(base + cc) : make_uint4(0, 0, 0, 0);
+    }
+  };
+  load(cur, lane);
+  for (uint32_t c0 = lane; c0 < nchunks; c0 += kStep) {
+    load(nxt, c0 + kStep);  // past the end: zeros, no loads
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) {
+      const uint32_t cc = c0 + j * 32;
+      if (cc == 0 || cc + 1 >= nchunks) clip_chunk(cur[j], 128ll * cc, lo, hi);
+      acc_chunk(cur[j], c);
+    }
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) cur[j] = nxt[j];
+  }
+}
+
 // Same with a 2-bit-expanded include mask.  `mask` is the shifted copy whose byte 0 lines up
 // with the aligned-down record address (see build_shifted_masks), so clipping is implicit.
 template <int LANES, int UNROLL, bool STREAM>

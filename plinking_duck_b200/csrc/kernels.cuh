@@ -53,6 +53,13 @@ void launch_cum_popcount(const uint32_t* include_words, uint32_t nwords, uint32_
 void launch_count_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_begin, uint32_t v_end, uint4* out,
                         cudaStream_t s, LaunchStats* st);
 
+// ---- K1h: plink_hardy over fixed-width records, counts and exact test in one kernel ----
+// Returns false (nothing launched) when the records are too short for the fused form; the caller
+// then runs launch_count_fixed + launch_hwe.  queue: device uint32[2]; ready: device uint32[nrec].
+bool launch_hardy_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_begin, uint32_t v_end, uint4* out,
+                        double* out_p, uint32_t midp, uint32_t* queue, uint32_t* ready, cudaStream_t s,
+                        LaunchStats* st);
+
 // ---- K3: genotype counts over variable-width records (vrtype 0-7, LD resolved) ----
 // Scans [v_begin, v_end); v_begin must not be LD-compressed.  out[v - v_begin].
 // work_counter: device uint32 (zeroed by the wrapper).  err: device int[2] = {code, vidx}.
@@ -144,7 +151,9 @@ void launch_score_acc(const DenseRows& rows, const ScoreRow* srow, const DosageL
 
 // ---- K8: exact Hardy-Weinberg test on the device ----
 // counts[n] as produced by the count kernels; out_p[n] = p-value clamped to [0,1].
-void launch_hwe(const uint4* counts, uint32_t n, uint32_t midp, double* out_p, cudaStream_t s, LaunchStats* st);
+// queue: device uint32 work counter (zeroed by the wrapper).
+void launch_hwe(const uint4* counts, uint32_t n, uint32_t midp, double* out_p, uint32_t* queue, cudaStream_t s,
+                LaunchStats* st);
 // chrX exact test: c5[n][5] = female hom_ref, het, hom_alt, male ref, male alt.
 void launch_hwe_xchr(const uint32_t* c5, uint32_t n, uint32_t midp, double* out_p, cudaStream_t s, LaunchStats* st);
 

@@ -6,6 +6,7 @@
 // CountparseDifflistSubset :3453-3511, CountparseOnebitSubset :3516-3593,
 // LdSubsetAdjustGenocounts :3294-3384).  HBM-bound: 0.25 B per genotype call.
 #include "device_common.cuh"
+#include "hwe_device.cuh"
 #include "kernels.cuh"
 
 namespace pdk {
@@ -31,18 +32,76 @@ k_count_fixed(const uint8_t* __restrict__ data, uint64_t first_off, uint32_t wid
   const uint32_t ngroups = (gridDim.x * blockDim.x) / LANES;
   const int lane = threadIdx.x & (LANES - 1);
   const uint32_t n_eff = MASKED ? sub.subset_ct : N;
-  for (uint32_t r = tid / LANES; r < nrec; r += ngroups) {
-    const uint8_t* p = data + first_off + static_cast<uint64_t>(r) * width;
+  // The loop condition is warp-uniform (first group of the warp) so that the shuffles always see
+  // all 32 lanes; a group past the end in the last iteration just skips its record.
+  for (uint64_t r_warp = (tid & ~31u) / LANES, r = tid / LANES; r_warp < nrec; r_warp += ngroups, r += ngroups) {
     Planes c = {0u, 0u, 0u};
-    if (MASKED) {
-      planes_2bit_masked<LANES, 4, true>(p, N, sub.mask2_shifts, sub.mask2_stride, lane, c);
-    } else {
-      planes_2bit<LANES, 4, true>(p, N, lane, c);
+    if (r < nrec) {
+      const uint8_t* p = data + first_off + r * width;
+      if (MASKED) {
+        planes_2bit_masked<LANES, 4, true>(p, N, sub.mask2_shifts, sub.mask2_stride, lane, c);
+      } else {
+        planes_2bit<LANES, 4, true>(p, N, lane, c);
+      }
     }
     c.e = group_sum<LANES>(c.e);
     c.o = group_sum<LANES>(c.o);
     c.b = group_sum<LANES>(c.b);
-    if (lane == 0) out[r] = planes_to_counts(c, n_eff);
+    if (lane == 0 && r < nrec) out[r] = planes_to_counts(c, n_eff);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1h: plink_hardy over fixed-width records in ONE kernel -- counts (HBM-bound) and the exact test
+// (fp64-bound) run side by side on every SM instead of back to back.  Warps 0..CW-1 of a CTA claim
+// chunks of records from a counter and count them exactly like K1 (a whole warp per record); each
+// finished record is published with a release store to ready[r].  The other warps walk exact-test
+// tables: they claim windows of 32 variants, and every lane that finishes a table takes the next
+// variant of the window (hwe_warp_queue's scheme), waiting only for that variant's ready flag.
+// Counting warps never wait for anything, so the kernel cannot deadlock whatever the residency.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t kHardyChunk = 8;   // records per claim of a counting warp
+constexpr int kHardyCountWarps = 6;   // of the 8 warps of a CTA; measured best split on B200 (profiles/r01_hardy_split.txt)
+
+__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+template <bool MASKED, int CW>
+__global__ void __launch_bounds__(kThreads, 4)
+k_hardy_fixed(const uint8_t* __restrict__ data, uint64_t first_off, uint32_t width, uint32_t N, uint32_t nrec,
+              SubsetDev sub, uint4* out, double* __restrict__ out_p, uint32_t midp, uint32_t* __restrict__ queue,
+              uint32_t* ready) {
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t warp = threadIdx.x >> 5;
+  if (warp >= CW) {
+    hwe_consume(queue + 1, nrec, ready, out, out_p, midp != 0);
+    return;
+  }
+  const uint32_t n_eff = MASKED ? sub.subset_ct : N;
+  for (;;) {
+    uint32_t chunk = 0;
+    if (lane == 0) chunk = atomicAdd(queue, 1u);
+    chunk = __shfl_sync(0xffffffffu, chunk, 0);
+    const uint64_t r0 = static_cast<uint64_t>(chunk) * kHardyChunk;
+    if (r0 >= nrec) return;
+    const uint32_t r1 = static_cast<uint32_t>(r0 + kHardyChunk < nrec ? r0 + kHardyChunk : nrec);
+    for (uint32_t r = static_cast<uint32_t>(r0); r < r1; ++r) {
+      const uint8_t* p = data + first_off + static_cast<uint64_t>(r) * width;
+      Planes c = {0u, 0u, 0u};
+      if (MASKED) {
+        planes_2bit_masked<32, 4, true>(p, N, sub.mask2_shifts, sub.mask2_stride, lane, c);
+      } else {
+        planes_2bit_pipelined<4>(p, N, lane, c);
+      }
+      c.e = group_sum<32>(c.e);
+      c.o = group_sum<32>(c.o);
+      c.b = group_sum<32>(c.b);
+      if (lane == 0) {
+        out[r] = planes_to_counts(c, n_eff);
+        st_release_u32(ready + r, 1u);
+      }
+    }
   }
 }
 
@@ -345,6 +404,10 @@ void launch_fixed_t(const RecIndex& ix, const SubsetDev& sub, uint32_t v_begin, 
   }
 }
 
+
+// Enough record bytes per variant that counting, not the exact test, is the long pole.
+bool hardy_fused_applicable(uint32_t N) { return pick_lanes(N) == 32; }
+
 }  // namespace
 
 void launch_build_masks(const uint32_t* include_words, uint32_t N, uint8_t* mask2_shifts, uint32_t mask2_stride,
@@ -372,6 +435,30 @@ void launch_count_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_beg
     default: launch_fixed_t<4>(ix, sub, v_begin, nrec, out, s); break;
   }
   if (st) st->launches++;
+}
+
+bool launch_hardy_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_begin, uint32_t v_end, uint4* out,
+                        double* out_p, uint32_t midp, uint32_t* queue, uint32_t* ready, cudaStream_t s,
+                        LaunchStats* st) {
+  const uint32_t nrec = v_end - v_begin;
+  if (!nrec) return true;
+  if (!hardy_fused_applicable(ix.N)) return false;
+  const uint64_t first_off = ix.fixed_start + static_cast<uint64_t>(v_begin) * ix.fixed_width - ix.data_fpos;
+  cudaMemsetAsync(queue, 0, 2 * sizeof(uint32_t), s);
+  cudaMemsetAsync(ready, 0, static_cast<size_t>(nrec) * sizeof(uint32_t), s);
+  // One resident wave: 4 CTAs per SM (launch bounds); 6 warps of a CTA count, 2 test.
+  uint64_t blocks = (static_cast<uint64_t>(nrec) + kHardyChunk * kHardyCountWarps - 1) / (kHardyChunk * kHardyCountWarps);
+  const uint64_t max_blocks = static_cast<uint64_t>(sm_count()) * 4;
+  if (blocks > max_blocks) blocks = max_blocks;
+  if (sub.mask2_shifts) {
+    k_hardy_fixed<true, kHardyCountWarps><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(
+        ix.data, first_off, ix.fixed_width, ix.N, nrec, sub, out, out_p, midp, queue, ready);
+  } else {
+    k_hardy_fixed<false, kHardyCountWarps><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(
+        ix.data, first_off, ix.fixed_width, ix.N, nrec, sub, out, out_p, midp, queue, ready);
+  }
+  if (st) st->launches++;
+  return true;
 }
 
 void launch_decode_bases(const RecIndex& ix, const uint32_t* slot_vidx, const LdScratch& scratch, uint32_t slot_hi,

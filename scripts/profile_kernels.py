@@ -68,6 +68,16 @@ def main():
         ctx.set_subset(None)
     if "hardy" in ops:
         report("hardy", lambda: ctx.hardy(), V * W, V * N)
+    if "hwe_only" in ops:
+        cnts = ctx.counts()
+        def hw():
+            ctx.hwe_from_counts(cnts)
+        hw()
+        a = []
+        for _ in range(args.reps):
+            hw()
+            a.append(ctx.stats().aux_kernel_ms)
+        print(json.dumps({"op": "hwe_only", "variants": V, "samples": N, "kernel_ms": float(np.median(a))}), flush=True)
     if "missing_by_sample" in ops:
         report("missing_by_sample", lambda: ctx.missing_by_sample(), V * W, V * N)
     if "sample_counts" in ops:
