@@ -31,7 +31,7 @@ void DestroyCtx(pd_ctx* c) {
   c->d_counts.Free(); c->d_scratch.Free(); c->d_misc.Free(); c->d_pvals.Free(); c->d_acc.Free(); c->d_ready.Free();
   c->d_dense.Free(); c->d_rowptrs.Free(); c->d_vlist.Free();
   c->d_loc.Free(); c->d_rank.Free(); c->d_dstats.Free(); c->d_srow.Free(); c->d_weights.Free(); c->d_flip.Free();
-  c->d_score.Free(); c->d_dsum.Free(); c->d_act.Free();
+  c->d_score.Free(); c->d_dsum.Free(); c->d_act.Free(); c->d_tc.Free();
   for (int b = 0; b < 2; ++b) {
     c->d_out[b].Free();
     c->h_bounce[b].Free();

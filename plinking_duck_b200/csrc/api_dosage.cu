@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 
@@ -234,14 +235,23 @@ int pd_score(pd_ctx* c, const uint32_t* vidx, const uint8_t* flip, const double*
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     if (e != cudaSuccess) return CheckCuda(c, e, "weights upload");
     c->stats.h2d_bytes += static_cast<size_t>(n_var) * (K * 8 + (flip ? 1 : 0));
-    const uint32_t max_rows = DosageBatchRows(c, 4096);
+    const pdk::SubsetDev sd = c->subset.Dev();
+    const bool dos = c->idx.has_dosage;
+    // K7t (tensor cores) takes hardcall-only files scanned over all samples; explicit dosages and sample
+    // subsets stay on the fp64 CUDA-core kernel.  PD_SCORE_PATH=fp64 forces the latter (A/B timing).
+    static const bool force_fp64 = [] {
+      const char* v = getenv("PD_SCORE_PATH");
+      return v && !strcmp(v, "fp64");
+    }();
+    const bool tc = !dos && !c->subset.active && pdk::score_tc_applicable(K) && !force_fp64;
+    const uint32_t max_rows = DosageBatchRows(c, tc ? 65535 : 4096);
     rc = ReserveDosage(c, max_rows);
     if (rc != PD_OK) return rc;
     e = c->d_counts.Reserve(static_cast<size_t>(max_rows) * 16);
     if (e == cudaSuccess) e = c->d_srow.Reserve(static_cast<size_t>(max_rows) * sizeof(pdk::ScoreRow));
+    if (e == cudaSuccess && tc) e = c->d_tc.Reserve(pdk::score_tc_workspace_bytes(max_rows, n_out));
     if (e != cudaSuccess) return CheckCuda(c, e, "score allocation");
-    const pdk::SubsetDev sd = c->subset.Dev();
-    const bool dos = c->idx.has_dosage;
+    bool first = true;
     rc = RunRowsList(c, vidx, n_var, max_rows, [&](const RowBatch& b, const pdk::RecIndex& ix, cudaStream_t s) {
       pdk::launch_count_rows(b.rows, sd, c->d_counts.as<uint4>(), s, &c->launch_stats);
       if (dos) {
@@ -252,10 +262,17 @@ int pd_score(pd_ctx* c, const uint32_t* vidx, const uint8_t* flip, const double*
       pdk::launch_score_prep(c->d_counts.as<uint4>(), dos ? c->d_dstats.as<pdk::DosageStats>() : nullptr,
                              flip ? c->d_flip.as<uint8_t>() + b.row0 : nullptr, b.n, mode, c->d_srow.as<pdk::ScoreRow>(),
                              s, &c->launch_stats);
-      pdk::launch_score_acc(b.rows, c->d_srow.as<pdk::ScoreRow>(), dos ? c->d_loc.as<pdk::DosageLoc>() : nullptr,
-                            c->d_rank.as<uint32_t>(), RankStride(c), c->d_weights.as<double>() + static_cast<size_t>(b.row0) * K,
-                            K, sd, n_out, mode, c->d_score.as<double>(), c->d_dsum.as<double>(), c->d_act.as<uint32_t>(), s,
-                            &c->launch_stats);
+      const double* w = c->d_weights.as<double>() + static_cast<size_t>(b.row0) * K;
+      if (tc) {
+        pdk::launch_score_tc(b.rows, c->d_counts.as<uint4>(), c->d_srow.as<pdk::ScoreRow>(), w, K, mode, n_out, max_rows,
+                             c->d_tc.p, first, c->d_score.as<double>(), c->d_dsum.as<double>(), c->d_act.as<uint32_t>(),
+                             s, &c->launch_stats);
+        first = false;
+      } else {
+        pdk::launch_score_acc(b.rows, c->d_srow.as<pdk::ScoreRow>(), dos ? c->d_loc.as<pdk::DosageLoc>() : nullptr,
+                              c->d_rank.as<uint32_t>(), RankStride(c), w, K, sd, n_out, mode, c->d_score.as<double>(),
+                              c->d_dsum.as<double>(), c->d_act.as<uint32_t>(), s, &c->launch_stats);
+      }
       c->stats.scan_launches += 1;
       return PD_OK;
     });

@@ -88,7 +88,7 @@ struct pd_ctx_impl {
   // work buffers
   DevBuf d_counts, d_scratch, d_misc, d_pvals, d_acc, d_ready;
   DevBuf d_dense, d_rowptrs, d_vlist, d_out[2];  // dense-row batches and their outputs
-  DevBuf d_loc, d_rank, d_dstats, d_srow, d_weights, d_flip, d_score, d_dsum, d_act;  // dosage / score
+  DevBuf d_loc, d_rank, d_dstats, d_srow, d_weights, d_flip, d_score, d_dsum, d_act, d_tc;  // dosage / score
   PinnedBuf h_bounce[2];
   cudaStream_t d2h_stream = nullptr;
   cudaEvent_t ev_out_ready[2] = {nullptr, nullptr}, ev_out_free[2] = {nullptr, nullptr};

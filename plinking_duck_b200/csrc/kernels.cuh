@@ -149,6 +149,15 @@ void launch_score_acc(const DenseRows& rows, const ScoreRow* srow, const DosageL
                       uint32_t mode, double* score, double* dosage_sums, uint32_t* allele_cts, cudaStream_t s,
                       LaunchStats* st);
 
+// ---- K7t: the same accumulation on the tensor cores (tcgen05 int8 limbs, exact integer sums) for
+// hardcall rows without a sample subset.  workspace: score_tc_workspace_bytes(max_rows, n_samples)
+// bytes of device memory kept across the batches of one call; first_batch clears its accumulators.
+size_t score_tc_workspace_bytes(uint32_t max_rows, uint32_t n_samples);
+bool score_tc_applicable(uint32_t K);
+void launch_score_tc(const DenseRows& rows, const uint4* counts, const ScoreRow* srow, const double* weights, uint32_t K,
+                     uint32_t mode, uint32_t n_samples, uint32_t max_rows, void* workspace, bool first_batch,
+                     double* score, double* dosage_sums, uint32_t* allele_cts, cudaStream_t s, LaunchStats* st);
+
 // ---- K8: exact Hardy-Weinberg test on the device ----
 // counts[n] as produced by the count kernels; out_p[n] = p-value clamped to [0,1].
 // queue: device uint32 work counter (zeroed by the wrapper).
