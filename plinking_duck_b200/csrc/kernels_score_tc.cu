@@ -35,14 +35,14 @@ constexpr uint32_t kSlabK = 32;     // k-rows per MMA (K of kind::i8)
 constexpr uint32_t kRowsM = 128;    // MMA M: weight-limb rows
 constexpr uint32_t kLimbs = 7;
 constexpr uint32_t kStages = 4;     // B slabs (8 KB each) between the unpackers and the MMA
-constexpr uint32_t kAStages = 12;   // A slabs (4 KB bulk copies): deep enough to cover their global latency
+constexpr uint32_t kAStages = 6;    // A slabs (4 KB bulk copies): deep enough to cover their L2 latency
 constexpr uint32_t kBBytes = kTileN * kSlabK;  // 8 KB
 constexpr uint32_t kABytes = kRowsM * kSlabK;  // 4 KB
 constexpr uint32_t kProducers = 128;  // threads that unpack one slab
 constexpr uint32_t kGroups = 2;       // producer groups; group g unpacks slabs g, g + kGroups, ... of the CTA
 constexpr uint32_t kProdWarps = kGroups * kProducers / 32;
 constexpr uint32_t kMmaThreads = kGroups * kProducers + 64;  // + one warp (MMA issue, TMEM) + one warp (A copies)
-constexpr uint32_t kPrefetch = 4;   // slabs of packed bytes a producer keeps in flight in registers
+constexpr uint32_t kPrefetch = 3;   // steps of packed bytes a producer group keeps in flight (cp.async ring)
 constexpr uint32_t kPlaneM = 0x80000000u;
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -76,6 +76,15 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                    smem_u32(dst)),
                "l"(src), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
+}
+// 16-byte asynchronous copy global -> shared (LDGSTS); src_bytes = 0 zero-fills without reading.
+__device__ __forceinline__ void cp_async16(void* dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
@@ -302,6 +311,8 @@ k_tc_quant(DenseRows rows, const ScoreRow* __restrict__ srow, const double* __re
 struct MmaSmem {
   alignas(128) uint8_t b[kStages][kBBytes];
   alignas(128) uint8_t a[kAStages][kABytes];
+  // packed 2-bit bytes in flight: per group and step, two 16-byte chunks per producer thread
+  alignas(128) uint4 p[kGroups][kPrefetch][2][kProducers];
   alignas(8) uint64_t full[kStages];
   uint64_t empty[kStages];
   uint64_t a_full[kAStages];
@@ -310,28 +321,20 @@ struct MmaSmem {
   uint32_t tmem_base;
 };
 
-// 8 codes (16 bits) -> one code per nibble.
-__device__ __forceinline__ uint32_t spread_nibbles(uint32_t x) {
-  x = (x | (x << 8)) & 0x00FF00FFu;
-  x = (x | (x << 4)) & 0x0F0F0F0Fu;
-  x = (x | (x << 2)) & 0x33333333u;
-  return x;
-}
-// 16 packed 2-bit codes -> 16 bytes through the 4-entry byte table `tab` (PRMT selects by nibble).
+// 16 packed 2-bit codes -> 16 bytes through the 4-entry byte table `tab`.  A code sitting in the low
+// bits of a nibble IS a PRMT selector, so the even codes (w & 0x3333..) and the odd codes
+// ((w >> 2) & 0x3333..) are looked up four at a time and the two byte streams interleaved by PRMT.
 __device__ __forceinline__ uint4 unpack16(uint32_t w, uint32_t tab) {
-  const uint32_t lo = spread_nibbles(w & 0xffffu), hi = spread_nibbles(w >> 16);
+  const uint32_t ev = w & 0x33333333u, od = (w >> 2) & 0x33333333u;
+  const uint32_t e0 = __byte_perm(tab, 0u, ev), o0 = __byte_perm(tab, 0u, od);              // codes 0,2,4,6 / 1,3,5,7
+  const uint32_t e1 = __byte_perm(tab, 0u, ev >> 16), o1 = __byte_perm(tab, 0u, od >> 16);  // codes 8,10,.. / 9,11,..
   uint4 o;
-  o.x = __byte_perm(tab, 0u, lo);
-  o.y = __byte_perm(tab, 0u, lo >> 16);
-  o.z = __byte_perm(tab, 0u, hi);
-  o.w = __byte_perm(tab, 0u, hi >> 16);
+  o.x = __byte_perm(e0, o0, 0x5140u);
+  o.y = __byte_perm(e0, o0, 0x7362u);
+  o.z = __byte_perm(e1, o1, 0x5140u);
+  o.w = __byte_perm(e1, o1, 0x7362u);
   return o;
 }
-
-struct PackedQuarter {  // 16 bytes (64 samples) of one k-row, fetched as 5 aligned words + the k-row's plane
-  uint32_t w[5];
-  uint32_t sh_plane;    // bit shift (0, 8, 16, 24) | plane flag
-};
 
 __global__ void __launch_bounds__(kMmaThreads, 2)
 k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, const int8_t* __restrict__ a_tiles,
@@ -349,7 +352,7 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
   if (warp == kProdWarps) {
     if (lane == 0) {
       for (uint32_t i = 0; i < kStages; ++i) {
-        mbar_init(&sm.full[i], kProducers);
+        mbar_init(&sm.full[i], kProducers / 32);
         mbar_init(&sm.empty[i], 1);
       }
       for (uint32_t i = 0; i < kAStages; ++i) {
@@ -375,59 +378,82 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
     const uint32_t row_bytes = (n_raw + 3) >> 2;
     const uint32_t off = tile * (kTileN / 4) + gq * 16;  // byte offset of this quarter inside a row
     const uint32_t nit = s1 - s0;
-    // Two-level register pipeline: the k-row's pointer is requested 2 x kPrefetch steps ahead, its
-    // packed bytes kPrefetch steps ahead, so neither dependent load is waited for when it is used.
+    const uint32_t tg = threadIdx.x & (kProducers - 1);
+    // Pipeline: the k-row's pointer is requested 2 x kPrefetch steps ahead (one register load), its
+    // packed bytes kPrefetch steps ahead with cp.async into this thread's own ring slots -- rows start
+    // at any byte, so the 32 aligned bytes around the 16 wanted ones are copied.  Asynchronous copies
+    // hold no registers and no scoreboard, which is what lets ~20 KB per SM stay in flight.
     // Step j of group grp is the CTA's slab it = grp + j * kGroups.
-    auto fetch_ptr = [&](uint32_t slab) { return __ldg(krow_ptr + static_cast<uint64_t>(slab) * kSlabK + kk); };
-    auto fetch = [&](PackedQuarter& q, unsigned long long kp) {
-      const uintptr_t row = static_cast<uintptr_t>(kp & ~(1ull << 63));
-      const uintptr_t p = row + off;
-      const uint32_t* a = reinterpret_cast<const uint32_t*>(p & ~uintptr_t(3));
-      const uintptr_t end = row + row_bytes;  // words starting at or past it are not read
-#pragma unroll
-      for (int j = 0; j < 5; ++j) q.w[j] = (reinterpret_cast<uintptr_t>(a + j) < end) ? __ldg(a + j) : 0u;
-      q.sh_plane = (static_cast<uint32_t>(p & 3) << 3) | ((kp >> 63) ? kPlaneM : 0u);
+    auto it_of = [&](uint32_t j) { return grp + j * kGroups; };
+    auto fetch_ptr = [&](uint32_t j) {
+      return it_of(j) < nit ? __ldg(krow_ptr + static_cast<uint64_t>(s0 + it_of(j)) * kSlabK + kk) : 0ull;
     };
-    auto emit = [&](const PackedQuarter& q, uint32_t it) {
+    auto issue = [&](uint32_t j, unsigned long long kp) -> uint32_t {
+      uint32_t sp = 0;
+      if (it_of(j) < nit) {
+        const uintptr_t p = static_cast<uintptr_t>(kp & ~(1ull << 63)) + off;
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(p & ~uintptr_t(15));
+        const uint32_t nb = off < row_bytes ? 16u : 0u;  // quarters past the end of the row: zeros
+        cp_async16(&sm.p[grp][j % kPrefetch][0][tg], src, nb);
+        cp_async16(&sm.p[grp][j % kPrefetch][1][tg], src + 16, nb);
+        sp = (static_cast<uint32_t>(p & 15) << 3) | ((kp >> 63) ? kPlaneM : 0u);
+      }
+      cp_async_commit();  // one group per step, empty past the end, so that wait_group counts stay aligned
+      return sp;
+    };
+    auto emit = [&](uint32_t j, uint32_t sp) {
+      const uint32_t it = it_of(j);
       const uint32_t stage = it % kStages;
+      const uint4 x0 = sm.p[grp][j % kPrefetch][0][tg], x1 = sm.p[grp][j % kPrefetch][1][tg];
+      // the 16 wanted bytes start (sp >> 3) & 15 bytes into the 32: whole words first, then a funnel shift
+      uint32_t w[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+      if (sp & 64u) {
+#pragma unroll
+        for (int i = 0; i < 6; ++i) w[i] = w[i + 2];
+      }
+      if (sp & 32u) {
+#pragma unroll
+        for (int i = 0; i < 5; ++i) w[i] = w[i + 1];
+      }
+      const uint32_t sh = sp & 31u;
+      const uint32_t tab = (sp & kPlaneM) ? 0x01000000u : 0x00020100u;  // M: [3] -> 1;  G: 0, 1, 2, missing -> 0
       mbar_wait(&sm.empty[stage], ((it / kStages) & 1u) ^ 1u);
-      const uint32_t sh = q.sh_plane & 31u;
-      const uint32_t tab = (q.sh_plane & kPlaneM) ? 0x01000000u : 0x00020100u;  // M: [3] -> 1;  G: 0, 1, 2, missing -> 0
       uint8_t* dst = sm.b[stage] + (kk & 7u) * 16u + (kk >> 3) * kBLbo + (gq * 4u) * kBSbo;
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const uint32_t w = __funnelshift_r(q.w[u], q.w[u + 1], sh);
-        *reinterpret_cast<uint4*>(dst + u * kBSbo) = unpack16(w, tab);
+        *reinterpret_cast<uint4*>(dst + u * kBSbo) = unpack16(__funnelshift_r(w[u], w[u + 1], sh), tab);
       }
       fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
-      mbar_arrive(&sm.full[stage]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.full[stage]);  // one arrival per warp: 32 would serialise on the barrier word
     };
-    PackedQuarter buf[kPrefetch];
+    uint32_t sps[kPrefetch];
     unsigned long long ptrs[kPrefetch];
-    auto it_of = [&](uint32_t j) { return grp + j * kGroups; };
 #pragma unroll
-    for (uint32_t d = 0; d < kPrefetch; ++d) ptrs[d] = (it_of(d) < nit) ? fetch_ptr(s0 + it_of(d)) : 0ull;
+    for (uint32_t d = 0; d < kPrefetch; ++d) ptrs[d] = fetch_ptr(d);
 #pragma unroll
     for (uint32_t d = 0; d < kPrefetch; ++d) {
-      if (it_of(d) < nit) fetch(buf[d], ptrs[d]);
-      ptrs[d] = (it_of(kPrefetch + d) < nit) ? fetch_ptr(s0 + it_of(kPrefetch + d)) : 0ull;
+      sps[d] = issue(d, ptrs[d]);
+      ptrs[d] = fetch_ptr(kPrefetch + d);
     }
     for (uint32_t jb = 0; it_of(jb) < nit; jb += kPrefetch) {
 #pragma unroll
       for (uint32_t d = 0; d < kPrefetch; ++d) {
         const uint32_t j = jb + d;
-        if (it_of(j) < nit) {
-          emit(buf[d], it_of(j));
-          if (it_of(j + kPrefetch) < nit) fetch(buf[d], ptrs[d]);
-          ptrs[d] = (it_of(j + 2 * kPrefetch) < nit) ? fetch_ptr(s0 + it_of(j + 2 * kPrefetch)) : 0ull;
+        if (it_of(j) < nit) {  // uniform for the group
+          cp_async_wait<kPrefetch - 1>();  // step j's copies have landed (this thread reads only its own)
+          emit(j, sps[d]);
+          sps[d] = issue(j + kPrefetch, ptrs[d]);
+          ptrs[d] = fetch_ptr(j + 2 * kPrefetch);
         }
       }
     }
+    cp_async_wait<0>();
     // ================= epilogue: TMEM -> acc32 =================
     mbar_wait(&sm.acc_ready, 0);
     tc_fence_after();
     const uint32_t r = wq * 32 + lane;  // limb row = TMEM lane (a warp reaches lanes 32 * (warp % 4) ..)
-    for (uint32_t c0 = grp * (kTileN / kGroups); c0 < (grp + 1) * (kTileN / kGroups); c0 += 16) {
+    for (uint32_t c0 = grp * 16; c0 < kTileN; c0 += 16 * kGroups) {
       uint32_t v[16];
       tmem_ld16(tmem + ((wq * 32u) << 16) + c0, v);
 #pragma unroll
