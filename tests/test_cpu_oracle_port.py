@@ -1,0 +1,74 @@
+"""CPU: pins oracle/pgen_oracle.c (the plain-C restatement of the reference path) against
+(a) the reference's sqllogictest known answers (tests/kat.py) and (b) golden.npz, i.e. the outputs of the
+reference's OWN pgenlib over every fixture: index, counts (all / subset), int8 decode, missingness, the
+exact HWE test (vs HweLnP, within the restatement's stated fp64 noise) and plink_score in all three modes."""
+import subprocess
+import os
+
+import numpy as np
+import pytest
+
+import kat
+from conftest import ROOT, fixture_names, fixture_path
+
+
+@pytest.fixture(scope="module")
+def port():
+    subprocess.run(["make", "-s", "port"], cwd=os.path.join(ROOT, "oracle"), check=True)
+    from oracle import port as p
+
+    return p
+
+
+def test_port_kat(port):
+    with port.PortPgen(fixture_path("pgen_example")) as r:
+        c = r.counts()
+        assert np.array_equal(c, kat.PGEN_EXAMPLE_COUNTS)
+        assert list(r.missing_by_sample()) == kat.PGEN_EXAMPLE_MISSING_BY_SAMPLE
+        s, d, a = r.score(np.arange(4), None, kat.SCORE_W, 0)
+        assert np.allclose(s, kat.SCORE_SUM) and np.allclose(d, kat.SCORE_DOSAGE_SUM) and (a == 8).all()
+        s, d, a = r.score(np.arange(4), None, kat.SCORE_W, 1)
+        for i, (act, ss, ds) in kat.SCORE_NOIMPUTE.items():
+            assert (int(a[i]), float(s[i]), float(d[i])) == (act, ss, ds)
+        s, d, a = r.score(np.array([1]), None, np.array([1.0]), 2)
+        for i, v in kat.SCORE_CENTER_RS2.items():
+            assert abs(s[i] - v) < 1e-15
+    p = [port.hwe_exact(int(x[1]), int(x[0]), int(x[2])) for x in kat.PGEN_EXAMPLE_COUNTS]
+    pm = [port.hwe_exact(int(x[1]), int(x[0]), int(x[2]), True) for x in kat.PGEN_EXAMPLE_COUNTS]
+    assert np.allclose(p, kat.PGEN_EXAMPLE_P_HWE, atol=5e-7)
+    assert np.allclose(pm, kat.PGEN_EXAMPLE_P_HWE_MIDP, atol=5e-7)
+    with port.PortPgen(fixture_path("all_missing")) as r:
+        assert np.array_equal(r.counts(), kat.ALL_MISSING_COUNTS)
+    with port.PortPgen(fixture_path("rare_small")) as r:
+        assert tuple(int(x) for x in r.counts().sum(0)) == kat.RARE_SMALL_SUMS
+
+
+@pytest.mark.parametrize("name", fixture_names())
+def test_port_matches_reference_goldens(name, golden, port):
+    with port.PortPgen(fixture_path(name)) as r:
+        vt, fp = r.index()
+        assert np.array_equal(vt, golden[name + "/vrtypes"])
+        assert np.array_equal(fp, golden[name + "/fpos"])
+        c = r.counts()
+        assert np.array_equal(c, golden[name + "/counts"])
+        assert np.array_equal(r.missing_by_sample(), golden[name + "/missing_by_sample"])
+        assert np.array_equal(c[:, 3], golden[name + "/missing_by_variant"])
+        if name + "/i8" in golden:
+            assert np.array_equal(r.decode_i8(), golden[name + "/i8"])
+        if name + "/subset" in golden:
+            sub = golden[name + "/subset"]
+            assert np.array_equal(r.counts(subset=sub), golden[name + "/subset_counts"])
+        # exact test vs HweLnP: |p - exp(lnp)| within the noise of HweLnP's log-factorials
+        lnp = golden[name + "/hwe_lnp"]
+        n2 = 2.0 * c[:, :3].sum(1).astype(float)
+        tol = 1e-13 + 16 * 2.2e-16 * n2 * np.log(n2 + 2.0)
+        p = np.array([port.hwe_exact(int(x[1]), int(x[0]), int(x[2])) for x in c])
+        assert np.all(np.abs(p - np.clip(np.exp(lnp), 0, 1)) <= tol)
+        if name + "/score_m0_sum" in golden and not (vt & 0x60).any():
+            w, fl = golden[name + "/score_w"], golden[name + "/score_flip"]
+            for mode in (0, 1, 2):
+                s, d, a = r.score(np.arange(r.variant_ct), fl, w, mode)
+                es, ed, ea = (golden[name + f"/score_m{mode}_{k}"] for k in ("sum", "dsum", "ct"))
+                assert np.array_equal(a, ea.reshape(-1))
+                assert np.allclose(s, es.reshape(-1), rtol=1e-12, atol=1e-9)
+                assert np.allclose(d, ed.reshape(-1), rtol=1e-12, atol=1e-9)

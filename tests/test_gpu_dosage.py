@@ -9,6 +9,7 @@ north_star's fp64 bound -- the reference's own sums depend on thread arrival ord
 import numpy as np
 import pytest
 
+import synth
 from conftest import fixture_names, fixture_path
 
 pytestmark = pytest.mark.gpu
@@ -149,3 +150,81 @@ def test_score_multi_column_and_subset(golden):
                 es, ed, ea = r.score(vid, fl, W[:, k], 1)
                 assert np.allclose(Ss[:, k], es, rtol=1e-12, atol=1e-9)
                 assert np.array_equal(As, ea)
+
+
+def _score_numpy(g, w, flip, mode):
+    """src/plink_score.cpp:598-653 restated with numpy in fp64 (hardcalls only): per scored variant
+    mean = sum_alt / non_missing; skip if non_missing == 0; mode 0 missing -> mean, mode 1 missing skipped,
+    mode 2 (d' - mean') / sqrt(2 f (1 - f)) with missing contributing nothing."""
+    V, N = g.shape
+    K = w.shape[1]
+    score = np.zeros((N, K))
+    dsum = np.zeros(N)
+    act = np.zeros(N, dtype=np.uint32)
+    for v in range(V):
+        row = g[v]
+        nm = row != 3
+        n = int(nm.sum())
+        if n == 0:
+            continue
+        mean = float(row[nm].sum()) / n
+        d = row.astype(np.float64)
+        if mode == 2:
+            f = mean / 2.0
+            sd = np.sqrt(2.0 * f * (1.0 - f))
+            if sd == 0.0:
+                continue
+            dd = (2.0 - d) if flip[v] else d
+            mm = (2.0 - mean) if flip[v] else mean
+            val = np.where(nm, (dd - mm) / sd, 0.0)
+            act += 2 * nm.astype(np.uint32)
+        else:
+            if mode == 0:
+                d = np.where(nm, d, mean)
+                cnt = np.ones(N, dtype=bool)
+            else:
+                cnt = nm
+            dd = (2.0 - d) if flip[v] else d
+            val = np.where(cnt, dd, 0.0)
+            dsum += val
+            act += 2 * cnt.astype(np.uint32)
+        score += val[:, None] * w[v][None, :]
+    return score, dsum, act
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+@pytest.mark.parametrize("N,K", [(1000, 16), (257, 1), (2049, 5)])
+def test_score_tensor_core_path_vs_fp64_loop(N, K, mode, tmp_path):
+    """K7t (tcgen05 int8 limbs) on a fixed-width hardcall file: sample tiles that end inside a tile, k-row
+    splits, variants without missing calls, an all-missing variant and a monomorphic one (sd = 0 in mode 2).
+    Tolerance: the stated fp64 bound 1e-12 relative to the magnitude of the sum of |terms|."""
+    V = 700
+    g = synth.gen_hwe_genotypes(V, N, seed=11 + N, missing=0.02)
+    g[5] = 3            # all missing: skipped
+    g[6] = 0            # monomorphic
+    g[7][g[7] == 3] = 1  # no missing calls: no M row
+    rng = np.random.default_rng(N + K)
+    w = rng.standard_normal((V, K)) * np.exp(rng.uniform(-6, 6, size=(1, K)))  # columns of very different scale
+    fl = (rng.random(V) < 0.3).astype(np.uint8)
+    from plinking_duck_b200.pgen import PgenContext
+
+    with PgenContext(image=synth.fixed_pgen_image(g), device=0) as c:
+        c.load_resident()
+        S, D, A = c.score(np.arange(V, dtype=np.uint32), fl, w, mode)
+        st = c.stats()
+    es, ed, ea = _score_numpy(g, w, fl, mode)
+    assert np.array_equal(A, ea)
+    bound = 1e-12 * (np.abs(w).sum(axis=0) * 2.0 + 1.0)
+    assert np.all(np.abs(S - es) <= bound[None, :]), float(np.max(np.abs(S - es) / bound[None, :]))
+    if mode != 2:
+        assert np.allclose(D, ed, rtol=1e-13, atol=1e-9)
+    assert st.launches > 0
+    from oracle import ref
+
+    if ref.available():
+        path = str(tmp_path / "tc.pgen")
+        synth.write_fixed_pgen(path, g)
+        with ref.RefPgen(path) as r:
+            rs, rd, ra = r.score(np.arange(V, dtype=np.uint32), fl, w[:, 0], mode)
+        assert np.array_equal(A, ra)
+        assert np.all(np.abs(S[:, 0] - np.asarray(rs).reshape(-1)) <= bound[0])
