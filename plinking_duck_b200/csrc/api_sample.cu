@@ -54,6 +54,17 @@ int SampleAccumulate(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t 
   if (e != cudaSuccess) return CheckCuda(c, e, "accumulator allocation");
   uint32_t* acc = c->d_acc.as<uint32_t>();
   cudaMemsetAsync(acc, 0, 3 * npad * 4, c->stream);
+  // Variable-width files: difflist records are walked sparsely inside the densify launch and only
+  // the raw / 1-bit / LD records reach launch_sample_acc (pdk::SparseAcc).
+  uint32_t* sw = DevSparseWords(c);
+  cudaMemsetAsync(sw, 0, 4 * sizeof(uint32_t), c->stream);
+  const pdk::SparseAcc sparse{kinds, acc, acc + npad, acc + 2 * npad, sw + 1, sw};
+  struct Scope {
+    pd_ctx_impl* c;
+    ~Scope() { c->sparse_acc = nullptr; }
+  } scope{c};
+  c->sparse_acc = c->idx.fixed ? nullptr : &sparse;
+  const uint32_t* base = c->idx.fixed ? nullptr : sw + 1;
   int rc = RunRows(c, v_begin, v_end, 0, 256ull << 20, [&](const RowBatch& b, const pdk::RecIndex&, cudaStream_t s) {
     pdk::launch_sample_acc(b.rows, kinds, acc, acc + npad, acc + 2 * npad, s, &c->launch_stats);
     c->stats.scan_launches += 1;
@@ -64,9 +75,10 @@ int SampleAccumulate(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t 
   uint32_t* out = c->d_out[0].as<uint32_t>();
   cudaMemsetAsync(out, 0, 3 * static_cast<size_t>(n_out) * 4, c->stream);
   if (kinds == 7) {
-    pdk::launch_planes_to_counts(acc, acc + npad, acc + 2 * npad, idx, n_out, out, c->stream, &c->launch_stats);
+    pdk::launch_planes_to_counts(acc, acc + npad, acc + 2 * npad, idx, n_out, out, c->stream, &c->launch_stats, base);
   } else {
-    pdk::launch_gather_u32(acc + 2 * npad, idx, n_out, out + 2 * static_cast<size_t>(n_out), c->stream, &c->launch_stats);
+    pdk::launch_gather_u32(acc + 2 * npad, idx, n_out, out + 2 * static_cast<size_t>(n_out), c->stream, &c->launch_stats,
+                           base ? base + 2 : nullptr);
   }
   return PD_OK;
 }

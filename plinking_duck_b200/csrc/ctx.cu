@@ -73,6 +73,7 @@ int CheckCuda(pd_ctx_impl* c, cudaError_t e, const char* what) {
 
 int* DevErr(pd_ctx_impl* c) { return c->d_misc.as<int>(); }
 uint32_t* DevWorkCounter(pd_ctx_impl* c) { return reinterpret_cast<uint32_t*>(c->d_misc.as<int>() + 4); }
+uint32_t* DevSparseWords(pd_ctx_impl* c) { return reinterpret_cast<uint32_t*>(c->d_misc.as<int>() + 8); }
 
 int CheckDeviceError(pd_ctx_impl* c) {
   int* h = c->h_misc.as<int>();
@@ -349,12 +350,25 @@ int RunRows(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t max_rows,
   if (rc != PD_OK) return rc;
   TileBytesGuard guard(c, min_tile_bytes);
   const uint32_t slot_stride = DenseSlotStride(c);
+  const pdk::SparseAcc* sparse = fixed ? nullptr : c->sparse_acc;
   return RunScan(c, v_begin, v_end, nullptr, [&](const Tile& t, const pdk::RecIndex& ix, cudaStream_t s) {
     const uint32_t a = std::max(t.v0, v_begin);
-    for (uint32_t v = a; v < t.v1; v += cap) {
+    uint32_t n = 0;
+    for (uint32_t v = a; v < t.v1; v += n) {
+      n = std::min(cap, t.v1 - v);
+      if (sparse) {
+        // Difflist records need no scratch slot: a batch ends when cap records that do are in it.
+        uint32_t dense = 0;
+        n = 0;
+        while (v + n < t.v1 && n < kMaxBatchRows) {
+          const uint32_t main = c->idx.vrtypes[v + n] & 7u;
+          if (main < 4 && ++dense > cap) break;
+          ++n;
+        }
+      }
       RowBatch b{};
       b.row0 = v - v_begin;
-      b.n = std::min(cap, t.v1 - v);
+      b.n = n;
       b.v_first = v;
       b.rows.nrows = b.n;
       b.rows.N = ix.N;
@@ -363,8 +377,13 @@ int RunRows(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t max_rows,
         b.rows.stride = ix.fixed_width;
       } else {
         pdk::launch_densify(ix, nullptr, v, b.n, c->d_dense.as<uint8_t>(), slot_stride,
-                            c->d_rowptrs.as<const uint8_t*>(), DevWorkCounter(c), DevErr(c), s, &c->launch_stats);
+                            c->d_rowptrs.as<const uint8_t*>(), DevWorkCounter(c), DevErr(c), s, &c->launch_stats,
+                            sparse);
         b.rows.ptrs = c->d_rowptrs.as<const uint8_t*>();
+        if (sparse) {
+          b.rows.nrows = std::min(b.n, cap);
+          b.rows.nrows_dev = sparse->dense_count;
+        }
       }
       const int r = fn(b, ix, s);
       if (r != PD_OK) return r;

@@ -87,6 +87,7 @@ struct pd_ctx_impl {
 
   // work buffers
   DevBuf d_counts, d_scratch, d_misc, d_pvals, d_acc, d_ready;
+  const pdk::SparseAcc* sparse_acc = nullptr;  // set by SampleAccumulate around RunRows: difflist records skip densify
   DevBuf d_dense, d_rowptrs, d_vlist, d_out[2];  // dense-row batches and their outputs
   DevBuf d_loc, d_rank, d_dstats, d_srow, d_weights, d_flip, d_score, d_dsum, d_act, d_tc;  // dosage / score
   PinnedBuf h_bounce[2];
@@ -124,6 +125,7 @@ int CheckCuda(pd_ctx_impl* c, cudaError_t e, const char* what);
 int CheckDeviceError(pd_ctx_impl* c);  // reads the device error word after a synchronize
 int* DevErr(pd_ctx_impl* c);
 uint32_t* DevWorkCounter(pd_ctx_impl* c);
+uint32_t* DevSparseWords(pd_ctx_impl* c);  // [0] dense row count of the current batch, [1..3] base planes
 uint32_t ExtendToBase(const pd_ctx_impl* c, uint32_t v);
 int BuildSubset(pd_ctx_impl* c, const uint64_t* include, const SubsetState* and_with, SubsetState* out);
 

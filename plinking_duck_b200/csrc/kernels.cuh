@@ -77,13 +77,30 @@ struct DenseRows {
   uint64_t stride;
   uint32_t nrows;
   uint32_t N;                  // raw sample count; bits past N in a row are undefined
+  const uint32_t* nrows_dev;   // when set: the row count lives on the device (<= nrows), see SparseAcc
+};
+
+// Sparse per-sample accumulation (plink_missing sample mode / read_pfile orient := 'sample' on
+// difflist records): with this passed to launch_densify, records of type 4/5/6/7 are never expanded.
+// Their difflist entries go straight into the per-sample plane counters as (entry - common) deltas,
+// the common genotype's planes are added once per record to base[0..2], and only the remaining
+// records (raw, 1-bit, LD) are decoded; their row pointers are appended to ptrs in arrival order
+// and counted in *dense_count.  The sparse walk is the GPU form of the reference's Phase 1
+// "sparse" branch (src/pfile_reader.cpp:3322-3428, PgrGetDifflistOrGenovec).
+struct SparseAcc {
+  uint32_t kinds;        // as launch_sample_acc
+  uint32_t* acc_e;       // [N] plane counters, the same arrays launch_sample_acc adds to
+  uint32_t* acc_o;
+  uint32_t* acc_b;
+  uint32_t* base;        // [3] E / O / B counts owed to every sample (zeroed by the caller per operation)
+  uint32_t* dense_count; // [1] rows appended to ptrs by this launch (zeroed by launch_densify)
 };
 
 // Row r = variant vlist[r] (vlist != nullptr) or v0 + r.  Type-0 records are pointed at in place,
 // everything else (difflist, 1-bit, LD with its base resolved) is decoded into scratch slot r.
 void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint32_t nrows, uint8_t* scratch,
                     uint32_t slot_stride, const uint8_t** ptrs, uint32_t* work_counter, int* err, cudaStream_t s,
-                    LaunchStats* st);
+                    LaunchStats* st, const SparseAcc* sparse = nullptr);
 // out[r * n_out + j] = {0,1,2,-9} of sample subset_idx[j] (or j) -- PgrGet + GenoarrToBytesMinus9.
 void launch_expand_i8(const DenseRows& rows, const uint32_t* subset_idx, uint32_t n_out, int8_t* out, cudaStream_t s,
                       LaunchStats* st);
@@ -93,9 +110,10 @@ void launch_expand_i8(const DenseRows& rows, const uint32_t* subset_idx, uint32_
 void launch_sample_acc(const DenseRows& rows, uint32_t kinds, uint32_t* acc_het, uint32_t* acc_hom, uint32_t* acc_mis,
                        cudaStream_t s, LaunchStats* st);
 void launch_planes_to_counts(const uint32_t* pe, const uint32_t* po, const uint32_t* pb, const uint32_t* idx, uint32_t n,
-                             uint32_t* out, cudaStream_t s, LaunchStats* st);
+                             uint32_t* out, cudaStream_t s, LaunchStats* st, const uint32_t* base = nullptr);
+// dst[i] = src[idx[i]] (+ *add when given)
 void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t n, uint32_t* dst, cudaStream_t s,
-                       LaunchStats* st);
+                       LaunchStats* st, const uint32_t* add = nullptr);
 void launch_subset_indices(const uint32_t* include_words, const uint32_t* cum, uint32_t nwords, uint32_t* out,
                            cudaStream_t s, LaunchStats* st);
 

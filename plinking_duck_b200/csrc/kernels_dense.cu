@@ -25,18 +25,46 @@ __device__ __forceinline__ const uint8_t* row_ptr(const DenseRows& rows, uint32_
   return rows.ptrs ? rows.ptrs[r] : rows.base + static_cast<uint64_t>(r) * rows.stride;
 }
 
+// One difflist record (type 4 / 6 / 7, or the all-common type 5) added to the per-sample plane counters
+// without expanding it: every listed sample gets planes(entry) - planes(common), the common planes
+// go to base[] once.  Unsigned wrap-around makes the negative deltas exact: the final per-sample
+// value base + acc is a true count >= 0.
+__device__ __forceinline__ bool sparse_accumulate(uint32_t common, bool all_common, const uint8_t* p, const uint8_t* end,
+                                                  uint32_t N, int lane, const SparseAcc& sa) {
+  const uint32_t ce = common & 1u, co = common >> 1, cb = ce & co;
+  if (lane == 0) {
+    if ((sa.kinds & 1u) && ce) atomicAdd(sa.base + 0, 1u);
+    if ((sa.kinds & 2u) && co) atomicAdd(sa.base + 1, 1u);
+    if ((sa.kinds & 4u) && cb) atomicAdd(sa.base + 2, 1u);
+  }
+  if (all_common) return true;
+  const uint8_t* q = p;
+  Difflist d;
+  if (!parse_difflist(q, end, N, true, d)) return false;
+  if (!d.len) return true;
+  const uint32_t kinds = sa.kinds;
+  return difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g, uint32_t) {
+    const uint32_t ge = g & 1u, go = g >> 1, gb = ge & go;
+    if ((kinds & 1u) && ge != ce) atomicAdd(sa.acc_e + id, ge - ce);
+    if ((kinds & 2u) && go != co) atomicAdd(sa.acc_o + id, go - co);
+    if ((kinds & 4u) && gb != cb) atomicAdd(sa.acc_b + id, gb - cb);
+  });
+}
+
 // ---------------------------------------------------------------------------------------------
 // k_densify: one warp per row (claimed from a counter: records differ in size by 1000x).
 // Row r is variant vlist[r] (or v0 + r).  Type-0 records are used in place; every other type is
 // decoded into scratch slot r.  LD records decode their base into their own slot first, so rows
 // are independent of each other and of batch boundaries.
 // ---------------------------------------------------------------------------------------------
+template <bool SPARSE>
 __global__ void __launch_bounds__(kThreads)
 k_densify(RecIndex ix, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t nrows, uint8_t* __restrict__ scratch,
           uint32_t slot_stride, const uint8_t** __restrict__ ptrs, uint32_t* __restrict__ work_counter,
-          int* __restrict__ err) {
+          int* __restrict__ err, SparseAcc sa) {
   const int lane = threadIdx.x & 31;
   const uint32_t N = ix.N;
+  const bool sparse = SPARSE && sa.dense_count != nullptr;
   for (;;) {
     uint32_t r = 0;
     if (lane == 0) r = atomicAdd(work_counter, 1u);
@@ -50,7 +78,17 @@ k_densify(RecIndex ix, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t
     const uint32_t main = ix.vrtypes[v] & 7u;
     const uint8_t* p = ix.data + (ix.fpos[v] - ix.data_fpos);
     const uint8_t* end = ix.data + (ix.fpos[v + 1] - ix.data_fpos);
-    uint32_t* slot = reinterpret_cast<uint32_t*>(scratch + static_cast<uint64_t>(r) * slot_stride);
+    if (SPARSE && sparse && main >= 4) {
+      const bool ok = sparse_accumulate(main == 5 ? 0u : (main & 3u), main == 5, p, end, N, lane, sa);
+      if (!ok && lane == 0) report_error(err, kErrMalformed, v);
+      continue;
+    }
+    uint32_t slot_idx = r;
+    if (SPARSE && sparse) {  // decoded rows are packed: slot and pointer index come from the counter
+      if (lane == 0) slot_idx = atomicAdd(sa.dense_count, 1u);
+      slot_idx = __shfl_sync(0xffffffffu, slot_idx, 0);
+    }
+    uint32_t* slot = reinterpret_cast<uint32_t*>(scratch + static_cast<uint64_t>(slot_idx) * slot_stride);
     bool ok = true;
     const uint8_t* out = reinterpret_cast<const uint8_t*>(slot);
     if (main == 0) {
@@ -68,7 +106,7 @@ k_densify(RecIndex ix, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t
     }
     if (lane == 0) {
       if (!ok) report_error(err, kErrMalformed, v);
-      ptrs[r] = out;
+      ptrs[slot_idx] = out;
     }
   }
 }
@@ -215,8 +253,15 @@ k_sample_acc(DenseRows rows, uint32_t rows_per_chunk, uint32_t* __restrict__ acc
   const uint32_t ncols = (N + 15) >> 4;
   const uint32_t w0 = (blockIdx.x * blockDim.x + threadIdx.x) * VEC;
   if (w0 >= ncols) return;
+  uint32_t nrows = rows.nrows;
+  if (rows.nrows_dev) {  // packed rows of a sparse batch: spread what there is over the chunks of the grid
+    nrows = min(nrows, __ldg(rows.nrows_dev));
+    rows_per_chunk = ((nrows + gridDim.y - 1) / gridDim.y + UNROLL - 1) / UNROLL * UNROLL;
+    if (rows_per_chunk < 4 * UNROLL) rows_per_chunk = 4 * UNROLL;
+  }
   const uint32_t r0 = blockIdx.y * rows_per_chunk;
-  const uint32_t r1 = min(rows.nrows, r0 + rows_per_chunk);
+  if (r0 >= nrows) return;
+  const uint32_t r1 = min(nrows, r0 + rows_per_chunk);
   Widen het[VEC], hom[VEC], mis[VEC];
 #pragma unroll
   for (int k = 0; k < VEC; ++k) {
@@ -326,20 +371,20 @@ k_sample_acc(DenseRows rows, uint32_t rows_per_chunk, uint32_t* __restrict__ acc
 // subset samples, three arrays of n each.
 __global__ void k_planes_to_counts(const uint32_t* __restrict__ pe, const uint32_t* __restrict__ po,
                                    const uint32_t* __restrict__ pb, const uint32_t* __restrict__ idx, uint32_t n,
-                                   uint32_t* __restrict__ out) {
+                                   uint32_t* __restrict__ out, const uint32_t* __restrict__ base) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint32_t s = idx ? idx[i] : i;
-  const uint32_t b = pb[s];
-  out[i] = pe[s] - b;
-  out[n + i] = po[s] - b;
+  const uint32_t b = pb[s] + (base ? base[2] : 0u);
+  out[i] = pe[s] + (base ? base[0] : 0u) - b;
+  out[n + i] = po[s] + (base ? base[1] : 0u) - b;
   out[2ull * n + i] = b;
 }
 
 __global__ void k_gather_u32(const uint32_t* __restrict__ src, const uint32_t* __restrict__ idx, uint32_t n,
-                             uint32_t* __restrict__ dst) {
+                             uint32_t* __restrict__ dst, const uint32_t* __restrict__ add) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) dst[i] = src[idx ? idx[i] : i];
+  if (i < n) dst[i] = src[idx ? idx[i] : i] + (add ? *add : 0u);
 }
 
 // Raw index of every subset sample, ascending (the subset order of PgrSampleSubsetIndex).
@@ -392,14 +437,20 @@ int sm_count() {
 
 void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint32_t nrows, uint8_t* scratch,
                     uint32_t slot_stride, const uint8_t** ptrs, uint32_t* work_counter, int* err, cudaStream_t s,
-                    LaunchStats* st) {
+                    LaunchStats* st, const SparseAcc* sparse) {
+  if (sparse) cudaMemsetAsync(sparse->dense_count, 0, sizeof(uint32_t), s);
   if (!nrows) return;
   cudaMemsetAsync(work_counter, 0, sizeof(uint32_t), s);
   uint64_t blocks = (static_cast<uint64_t>(nrows) * 32 + kThreads - 1) / kThreads;
   const uint64_t max_blocks = static_cast<uint64_t>(sm_count()) * 8;
   if (blocks > max_blocks) blocks = max_blocks;
-  k_densify<<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, vlist, v0, nrows, scratch, slot_stride, ptrs,
-                                                              work_counter, err);
+  if (sparse) {
+    k_densify<true><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, vlist, v0, nrows, scratch, slot_stride, ptrs,
+                                                                      work_counter, err, *sparse);
+  } else {
+    k_densify<false><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, vlist, v0, nrows, scratch, slot_stride,
+                                                                       ptrs, work_counter, err, SparseAcc{});
+  }
   if (st) st->launches++;
 }
 
@@ -460,16 +511,16 @@ void launch_count_rows(const DenseRows& rows, const SubsetDev& sub, uint4* out, 
 }
 
 void launch_planes_to_counts(const uint32_t* pe, const uint32_t* po, const uint32_t* pb, const uint32_t* idx, uint32_t n,
-                             uint32_t* out, cudaStream_t s, LaunchStats* st) {
+                             uint32_t* out, cudaStream_t s, LaunchStats* st, const uint32_t* base) {
   if (!n) return;
-  k_planes_to_counts<<<(n + 255) / 256, 256, 0, s>>>(pe, po, pb, idx, n, out);
+  k_planes_to_counts<<<(n + 255) / 256, 256, 0, s>>>(pe, po, pb, idx, n, out, base);
   if (st) st->launches++;
 }
 
 void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t n, uint32_t* dst, cudaStream_t s,
-                       LaunchStats* st) {
+                       LaunchStats* st, const uint32_t* add) {
   if (!n) return;
-  k_gather_u32<<<(n + 255) / 256, 256, 0, s>>>(src, idx, n, dst);
+  k_gather_u32<<<(n + 255) / 256, 256, 0, s>>>(src, idx, n, dst, add);
   if (st) st->launches++;
 }
 

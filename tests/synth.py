@@ -4,6 +4,8 @@ Genotype codes follow the .pgen 2-bit encoding: 0 hom-ref, 1 het, 2 hom-alt, 3 m
 """
 from __future__ import annotations
 
+import struct
+
 import numpy as np
 
 
@@ -163,3 +165,46 @@ def gen_dosage_variants(V: int, N: int, seed: int):
         else:
             dos.append(None)
     return g, dos
+
+
+def rewrite_with_all_ref_records(src: str, dst: str) -> int:
+    """Re-emit a variable-width .pgen (mode 0x10) so that every all-ref record -- which pgenlib's writer
+    stores as a type-4 record holding an empty difflist -- becomes a zero-length vrtype-5 record (the writer
+    only emits those under FUTURE_ENCODER, pgenlib_write.cc:1009-1014, but every reader accepts them).
+    Records that serve as an LD base are left alone.  Index layout: 8-bit vrtypes, 4-byte record lengths
+    (header_ctrl 0x47).  Returns the number of records converted."""
+    from oracle.port import PortPgen
+
+    with PortPgen(src) as p:
+        vt, fpos = p.index()
+        V, N = p.variant_ct, p.sample_ct
+    vt = np.asarray(vt).astype(np.uint8)
+    fpos = np.asarray(fpos).astype(np.int64)
+    raw = np.fromfile(src, dtype=np.uint8)
+    recs, types, converted = [], [], 0
+    for v in range(V):
+        rec = raw[fpos[v]:fpos[v + 1]].tobytes()
+        t = int(vt[v])
+        next_is_ld = v + 1 < V and (int(vt[v + 1]) & 7) in (2, 3)
+        if (t & 7) == 4 and t == 4 and rec == b"\x00" and not next_is_ld:
+            rec, t = b"", 5
+            converted += 1
+        recs.append(rec)
+        types.append(t)
+    nblocks = (V + 65535) // 65536
+    hdr_len = 12 + 8 * nblocks + V * 5
+    out = bytearray(b"\x6c\x1b\x10" + struct.pack("<II", V, N) + b"\x47")
+    lens = np.array([len(r) for r in recs], dtype=np.int64)
+    starts = hdr_len + np.concatenate([[0], np.cumsum(lens)])
+    for b in range(nblocks):
+        out += struct.pack("<Q", int(starts[b * 65536]))
+    for b in range(nblocks):
+        lo, hi = b * 65536, min(V, (b + 1) * 65536)
+        out += bytes(types[lo:hi])
+        out += lens[lo:hi].astype("<u4").tobytes()
+    assert len(out) == hdr_len
+    for r in recs:
+        out += r
+    with open(dst, "wb") as f:
+        f.write(bytes(out))
+    return converted

@@ -72,3 +72,30 @@ def test_port_matches_reference_goldens(name, golden, port):
                 assert np.array_equal(a, ea.reshape(-1))
                 assert np.allclose(s, es.reshape(-1), rtol=1e-12, atol=1e-9)
                 assert np.allclose(d, ed.reshape(-1), rtol=1e-12, atol=1e-9)
+
+
+def test_all_ref_vrtype5_records(port, tmp_path):
+    """vrtype 5 (all-ref, zero-length record) never leaves pgenlib's stock writer, so the fixtures lack it:
+    rewrite a pgenlib-written file with those records (synth.rewrite_with_all_ref_records) and require the
+    reference's reader and the port to agree with the genotype matrix on it."""
+    import synth
+    from oracle import ref
+
+    if not ref.available():
+        pytest.skip("oracle/_ref not built: no pgenlib writer")
+    V, N = 300, 257
+    g = synth.gen_rare_genotypes(V, N, 1)
+    g[0] = 0
+    g[1] = 2
+    g[2] = 3
+    g[10:14] = 0
+    a, b = str(tmp_path / "a.pgen"), str(tmp_path / "b.pgen")
+    ref.write_pgen(a, synth.to_genovec_words(g), N)
+    assert synth.rewrite_with_all_ref_records(a, b) >= 5
+    with ref.RefPgen(b) as r:
+        assert 5 in set(int(x) & 7 for x in r.vrtypes())
+        assert np.array_equal(r.counts(), synth.counts_numpy(g))
+    with port.PortPgen(b) as p:
+        assert np.array_equal(p.counts(), synth.counts_numpy(g))
+        assert np.array_equal(p.missing_by_sample(), (g == 3).sum(0))
+        assert np.array_equal(p.decode_i8(), np.where(g == 3, -9, g))

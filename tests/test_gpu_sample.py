@@ -131,3 +131,55 @@ def test_fixed_width_sample_paths(tmp_path):
             c.set_subset(sub)
             assert np.array_equal(c.decode_i8(5, min(V, 50)), exp_i8[5:min(V, 50)][:, sub])
             assert np.array_equal(c.missing_by_sample(), (g[:, sub] == 3).sum(0).astype(np.uint32))
+
+
+def test_sparse_sample_accumulation_on_pgenlib_written_records(tmp_path):
+    """Difflist records (vrtype 4/5/6/7) are accumulated per sample without being expanded
+    (pdk::SparseAcc, the GPU form of src/pfile_reader.cpp:3322-3428's sparse branch): a file written by
+    pgenlib's own writer with all-ref (type 5), all-hom-alt (type 6, empty difflist), all-missing (type 7),
+    rare-variant and common rows interleaved, so every batch mixes sparse and decoded rows."""
+    import synth
+    from oracle import ref
+    from plinking_duck_b200.pgen import PgenContext
+
+    if not ref.available():
+        pytest.skip("oracle/_ref not built: no pgenlib writer")
+    for (V, N) in [(900, 300), (260, 70001)]:
+        g = synth.gen_rare_genotypes(V, N, seed=V + N)
+        common = synth.gen_hwe_genotypes(V, N, seed=V, missing=0.03)
+        pick = np.arange(V) % 7 == 3
+        g[pick] = common[pick]
+        g[0] = 0
+        g[1] = 2
+        g[2] = 3
+        g[3] = 0
+        g[3, N // 2] = 1
+        g[V - 1] = 0
+        g[V - 2] = 2
+        g[V - 2, ::5] = 3
+        g[10:14] = 0
+        path = str(tmp_path / f"sparse_{V}_{N}.pgen")
+        ref.write_pgen(path + ".tmp", synth.to_genovec_words(g), N)
+        assert synth.rewrite_with_all_ref_records(path + ".tmp", path) >= 3
+        with ref.RefPgen(path) as r:
+            vt = set(int(x) & 7 for x in r.vrtypes())
+            assert np.array_equal(r.counts(), synth.counts_numpy(g))
+        assert {4, 5, 6, 7} <= vt, vt
+        exp = [(g == k).sum(0).astype(np.uint32) for k in (1, 2, 3)]
+        for kw in (dict(), dict(tile_bytes=3000, n_staging=2)):
+            with PgenContext(path, **kw) as c:
+                for resident in (False, True):
+                    if resident:
+                        c.load_resident()
+                    het, hom, mis = c.sample_counts()
+                    assert np.array_equal(het, exp[0]) and np.array_equal(hom, exp[1]) and np.array_equal(mis, exp[2])
+                    assert np.array_equal(c.missing_by_sample(), exp[2])
+                    assert np.array_equal(c.counts(), synth.counts_numpy(g))
+                    a, b = V // 3, V - 1
+                    assert np.array_equal(c.missing_by_sample(a, b), (g[a:b] == 3).sum(0).astype(np.uint32))
+                sub = np.arange(1, N, 3)
+                c.set_subset(sub)
+                het, hom, mis = c.sample_counts()
+                assert np.array_equal(het, exp[0][sub]) and np.array_equal(hom, exp[1][sub])
+                assert np.array_equal(mis, exp[2][sub])
+                assert np.array_equal(c.missing_by_sample(), exp[2][sub])
