@@ -293,6 +293,10 @@ def run_ours(args):
     two = np.stack([(body >> s) & 3 for s in (0, 2, 4, 6)], axis=2).reshape(64, W * 4)[:, :N]
     exp = np.stack([(two == k).sum(1) for k in range(4)], axis=1).astype(np.uint32)
     assert np.array_equal(out_counts[:64], exp), "GPU counts disagree with the host image"
+    # size-independent properties over the whole range: the four counts of every variant add up to N,
+    # every p-value is a probability
+    assert np.all(out_counts[:V].reshape(V, 4).sum(axis=1, dtype=np.uint64) == N), "counts do not add up to N"
+    assert np.all(np.isfinite(out_p[:V])) and float(out_p[:V].min()) >= 0.0 and float(out_p[:V].max()) <= 1.0
 
     peak, peak_kind = peaks()
     k_ms = float(np.mean(kern_ms))
