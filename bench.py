@@ -299,6 +299,7 @@ def run_ours(args):
     assert np.all(np.isfinite(out_p[:V])) and float(out_p[:V].min()) >= 0.0 and float(out_p[:V].max()) <= 1.0
 
     peak, peak_kind = peaks()
+    traffic, traffic_src = measured_traffic(float(V) * W, fused=float(np.mean(hwe_ms)) == 0.0)
     k_ms = float(np.mean(kern_ms))
     alg_bytes = float(V) * W
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
@@ -344,7 +345,8 @@ def run_ours(args):
                     "source": "page-locked host image of the .pgen, staged per step through the C ABI"},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": f"MEASURED_PEAKS.json ({peak_kind})",
+                         "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": f"MEASURED_PEAKS.json ({peak_kind})",
                          "kernel": "k_hardy_fixed (counts + exact test fused)" if float(np.mean(hwe_ms)) == 0.0 else "k_count_fixed",
                          "kernel_ms": k_ms, "hwe_kernel_ms": float(np.mean(hwe_ms))},
             "wall_ms_per_step": wall_ms,
