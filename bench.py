@@ -189,6 +189,19 @@ def peaks():
     return 6650.0, "fallback"
 
 
+def measured_traffic(alg_bytes, fused):
+    """DRAM bytes of one launch of the dominant kernel: the ratio dram bytes / algorithmic bytes of the
+    committed `ncu --set full` capture (profiles/traffic.json), scaled to this launch's algorithmic bytes."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)["k_hardy_fixed"]
+    except (OSError, KeyError, ValueError):
+        return None, None
+    if not fused:
+        return None, None
+    return alg_bytes * t["dram_bytes_per_algorithmic_byte"], f"{t['capture']} ratio x this launch's algorithmic bytes"
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
