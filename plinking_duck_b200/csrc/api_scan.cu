@@ -219,6 +219,7 @@ int pd_hardy(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_
   if (e != cudaSuccess) return CheckCuda(c, e, "p-value allocation");
   uint32_t v_ext = v_begin;
   bool fused = false;
+  bool direct = false;  // results already stored to the caller's arrays by the kernel
   int rc = PD_OK;
   if (c->idx.fixed && n) {
     // K1h: counts and exact tests of a tile in one kernel (fixed-width records have no LD bases,
@@ -230,11 +231,25 @@ int pd_hardy(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_
     uint4* out_dev = c->d_counts.as<uint4>();
     double* p_dev = c->d_pvals.as<double>();
     uint32_t* ready = c->d_ready.as<uint32_t>();
+    // Page-locked caller arrays are written by the kernel itself (mapped stores over PCIe while the scan
+    // runs) instead of by two copies after it: 24 B per variant that no longer trail the last tile.
+    uint4* host_counts = nullptr;
+    if (pdk::hardy_fused_applicable(c->idx.sample_ct) && IsPinnedHost(out_p) && (!out_counts || IsPinnedHost(out_counts))) {
+      void *dp = nullptr, *dc = nullptr;
+      if (cudaHostGetDevicePointer(&dp, out_p, 0) == cudaSuccess &&
+          (!out_counts || cudaHostGetDevicePointer(&dc, out_counts, 0) == cudaSuccess)) {
+        p_dev = static_cast<double*>(dp);
+        host_counts = static_cast<uint4*>(dc);
+        direct = true;
+      } else {
+        cudaGetLastError();
+      }
+    }
     bool all_fused = true;
     rc = RunScan(c, v_begin, v_end, &v_ext, [&](const Tile& t, const pdk::RecIndex& ix, cudaStream_t s) {
       const uint32_t off = t.v0 - v_begin;
       if (!pdk::launch_hardy_fixed(ix, sd, t.v0, t.v1, out_dev + off, p_dev + off, midp, DevWorkCounter(c),
-                                   ready + off, s, &c->launch_stats)) {
+                                   ready + off, s, &c->launch_stats, host_counts ? host_counts + off : nullptr)) {
         all_fused = false;
         pdk::launch_count_fixed(ix, sd, t.v0, t.v1, out_dev + off, s, &c->launch_stats);
       }
@@ -252,9 +267,12 @@ int pd_hardy(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_
   cudaEventRecord(c->ev_a, c->stream);
   if (!fused) pdk::launch_hwe(counts, n, midp, c->d_pvals.as<double>(), DevWorkCounter(c), c->stream, &c->launch_stats);
   cudaEventRecord(c->ev_b, c->stream);
-  e = cudaMemcpyAsync(out_p, c->d_pvals.p, static_cast<size_t>(n) * 8, cudaMemcpyDeviceToHost, c->stream);
-  if (e == cudaSuccess && out_counts) {
-    e = cudaMemcpyAsync(out_counts, counts, static_cast<size_t>(n) * 16, cudaMemcpyDeviceToHost, c->stream);
+  e = cudaSuccess;
+  if (!(direct && fused)) {
+    e = cudaMemcpyAsync(out_p, c->d_pvals.p, static_cast<size_t>(n) * 8, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess && out_counts) {
+      e = cudaMemcpyAsync(out_counts, counts, static_cast<size_t>(n) * 16, cudaMemcpyDeviceToHost, c->stream);
+    }
   }
   cudaEventRecord(c->ev_c1, c->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);

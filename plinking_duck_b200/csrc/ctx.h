@@ -125,6 +125,7 @@ int CheckCuda(pd_ctx_impl* c, cudaError_t e, const char* what);
 int CheckDeviceError(pd_ctx_impl* c);  // reads the device error word after a synchronize
 int* DevErr(pd_ctx_impl* c);
 uint32_t* DevWorkCounter(pd_ctx_impl* c);
+bool IsPinnedHost(const void* p);  // api_sample.cu
 uint32_t* DevSparseWords(pd_ctx_impl* c);  // [0] dense row count of the current batch, [1..3] base planes
 uint32_t ExtendToBase(const pd_ctx_impl* c, uint32_t v);
 int BuildSubset(pd_ctx_impl* c, const uint64_t* include, const SubsetState* and_with, SubsetState* out);

@@ -56,9 +56,12 @@ void launch_count_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_beg
 // ---- K1h: plink_hardy over fixed-width records, counts and exact test in one kernel ----
 // Returns false (nothing launched) when the records are too short for the fused form; the caller
 // then runs launch_count_fixed + launch_hwe.  queue: device uint32[2]; ready: device uint32[nrec].
+// out_p may be the device view of page-locked host memory (p-values are write-only for the kernel);
+// host_out, when given, is such a view for the counts, written in addition to out.
+bool hardy_fused_applicable(uint32_t N);
 bool launch_hardy_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_begin, uint32_t v_end, uint4* out,
                         double* out_p, uint32_t midp, uint32_t* queue, uint32_t* ready, cudaStream_t s,
-                        LaunchStats* st);
+                        LaunchStats* st, uint4* host_out = nullptr);
 
 // ---- K3: genotype counts over variable-width records (vrtype 0-7, LD resolved) ----
 // Scans [v_begin, v_end); v_begin must not be LD-compressed.  out[v - v_begin].

@@ -71,7 +71,7 @@ template <bool MASKED, int CW>
 __global__ void __launch_bounds__(kThreads, 4)
 k_hardy_fixed(const uint8_t* __restrict__ data, uint64_t first_off, uint32_t width, uint32_t N, uint32_t nrec,
               SubsetDev sub, uint4* out, double* __restrict__ out_p, uint32_t midp, uint32_t* __restrict__ queue,
-              uint32_t* ready) {
+              uint32_t* ready, uint4* __restrict__ host_out) {
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t warp = threadIdx.x >> 5;
   if (warp >= CW) {
@@ -98,8 +98,10 @@ k_hardy_fixed(const uint8_t* __restrict__ data, uint64_t first_off, uint32_t wid
       c.o = group_sum<32>(c.o);
       c.b = group_sum<32>(c.b);
       if (lane == 0) {
-        out[r] = planes_to_counts(c, n_eff);
+        const uint4 cnt = planes_to_counts(c, n_eff);
+        out[r] = cnt;
         st_release_u32(ready + r, 1u);
+        if (host_out) host_out[r] = cnt;  // caller's page-locked array, written over PCIe as results appear
       }
     }
   }
@@ -405,10 +407,10 @@ void launch_fixed_t(const RecIndex& ix, const SubsetDev& sub, uint32_t v_begin, 
 }
 
 
+}  // namespace
+
 // Enough record bytes per variant that counting, not the exact test, is the long pole.
 bool hardy_fused_applicable(uint32_t N) { return pick_lanes(N) == 32; }
-
-}  // namespace
 
 void launch_build_masks(const uint32_t* include_words, uint32_t N, uint8_t* mask2_shifts, uint32_t mask2_stride,
                         uint8_t* mask1_shifts, uint32_t mask1_stride, cudaStream_t s, LaunchStats* st) {
@@ -439,7 +441,7 @@ void launch_count_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_beg
 
 bool launch_hardy_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_begin, uint32_t v_end, uint4* out,
                         double* out_p, uint32_t midp, uint32_t* queue, uint32_t* ready, cudaStream_t s,
-                        LaunchStats* st) {
+                        LaunchStats* st, uint4* host_out) {
   const uint32_t nrec = v_end - v_begin;
   if (!nrec) return true;
   if (!hardy_fused_applicable(ix.N)) return false;
@@ -452,10 +454,10 @@ bool launch_hardy_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_beg
   if (blocks > max_blocks) blocks = max_blocks;
   if (sub.mask2_shifts) {
     k_hardy_fixed<true, kHardyCountWarps><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(
-        ix.data, first_off, ix.fixed_width, ix.N, nrec, sub, out, out_p, midp, queue, ready);
+        ix.data, first_off, ix.fixed_width, ix.N, nrec, sub, out, out_p, midp, queue, ready, host_out);
   } else {
     k_hardy_fixed<false, kHardyCountWarps><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(
-        ix.data, first_off, ix.fixed_width, ix.N, nrec, sub, out, out_p, midp, queue, ready);
+        ix.data, first_off, ix.fixed_width, ix.N, nrec, sub, out, out_p, midp, queue, ready, host_out);
   }
   if (st) st->launches++;
   return true;
