@@ -8,6 +8,10 @@
 //   * GenoarrToBytesMinus9 (pgenlib_ffi_support.cc:25-43) + CopyNyparrNonemptySubset: k_expand_i8
 //   * PgrGetMissingness + the ctz walk (src/plink_missing.cpp:593-609) and the dense Phase-1
 //     loop of src/pfile_reader.cpp:3322-3428: k_sample_acc
+#include <cstdlib>
+#include <cstring>
+#include <type_traits>
+
 #include "device_common.cuh"
 #include "kernels.cuh"
 
@@ -367,6 +371,228 @@ k_sample_acc(DenseRows rows, uint32_t rows_per_chunk, uint32_t* __restrict__ acc
   flush_all();
 }
 
+// ---------------------------------------------------------------------------------------------
+// k_sample_acc_v: the same transposed pass with VERTICAL counters and no global atomics in the
+// steady state.  A thread owns 2 consecutive 32-bit words of a record (32 samples).  The E / O / B
+// planes of the two words are interleaved into full 32-bit words (bit 2j = sample j of word 0,
+// bit 2j+1 = sample j of word 1), so every bit of a register is a sample, and rows are added with
+// carry-save adders (Harley-Seal, 16 rows per block): 15 CSAs (two LOP3 each: majority and 3-input
+// xor) produce a weight-16 carry that ripples into four more bit planes -- 2.4 logic ops per row
+// and plane.  Eight bit planes hold up to 255 rows; every 240 rows they are turned into per-sample
+// bytes (nibble * 0x00204081 spreads 4 bits into 4 bytes) and added to thread-private 16-bit
+// counters in shared memory; only at the end of the chunk (<= 65535 rows) each sample costs one
+// atomicAdd.  (The byte-counter kernel above flushes to global memory every 255 rows: at 100k samples
+// that is 0.4 atomics per record byte, which -- not the arithmetic -- is what bounded it.)
+// The row pointer is carried, not recomputed, and full 16-row blocks run without bounds checks:
+// the loop is bound by the integer pipe, so every instruction per row counts.
+// MODE 0: rows 8-byte aligned (one 64-bit load); 1: 4-byte aligned (fixed-width files: records start
+// 12 bytes into the file; two 32-bit loads); 3: any alignment (three loads + funnel shifts);
+// 2: row pointer table, any alignment.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t lop3_maj(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+__device__ __forceinline__ uint32_t lop3_xor(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+__device__ __forceinline__ void csa(uint32_t& hi, uint32_t& lo, uint32_t a, uint32_t b, uint32_t c) {
+  hi = lop3_maj(a, b, c);
+  lo = lop3_xor(a, b, c);
+}
+
+struct VPlane {
+  uint32_t ones, twos, fours, eights;
+  uint32_t hi[4];  // weights 16 .. 128
+  __device__ __forceinline__ void clear() {
+    ones = twos = fours = eights = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) hi[i] = 0;
+  }
+  // 8 rows in, carry of weight 8 out
+  __device__ __forceinline__ uint32_t add8(const uint32_t (&r)[8]) {
+    uint32_t ta, tb, fa, fb, carry;
+    csa(ta, ones, ones, r[0], r[1]);
+    csa(tb, ones, ones, r[2], r[3]);
+    csa(fa, twos, twos, ta, tb);
+    csa(ta, ones, ones, r[4], r[5]);
+    csa(tb, ones, ones, r[6], r[7]);
+    csa(fb, twos, twos, ta, tb);
+    csa(carry, fours, fours, fa, fb);
+    return carry;
+  }
+  __device__ __forceinline__ void add_carries(uint32_t ea, uint32_t eb) {
+    uint32_t carry;
+    csa(carry, eights, eights, ea, eb);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t t = hi[i] & carry;
+      hi[i] ^= carry;
+      carry = t;
+    }
+  }
+  // slot m of this thread (stride 128 words) holds bits 2m (low half) and 2m+1 (high half)
+  __device__ __forceinline__ void to_shared(uint32_t* __restrict__ mine) {
+    if ((ones | twos | fours | eights | hi[0] | hi[1] | hi[2] | hi[3]) != 0u) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        uint32_t v = (((ones >> (4 * k)) & 0xFu) * 0x00204081u) & 0x01010101u;
+        v |= ((((twos >> (4 * k)) & 0xFu) * 0x00204081u) & 0x01010101u) << 1;
+        v |= ((((fours >> (4 * k)) & 0xFu) * 0x00204081u) & 0x01010101u) << 2;
+        v |= ((((eights >> (4 * k)) & 0xFu) * 0x00204081u) & 0x01010101u) << 3;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v |= ((((hi[i] >> (4 * k)) & 0xFu) * 0x00204081u) & 0x01010101u) << (4 + i);
+        mine[(2 * k) * 128] += __byte_perm(v, 0u, 0x4140);
+        mine[(2 * k + 1) * 128] += __byte_perm(v, 0u, 0x4342);
+      }
+    }
+    clear();
+  }
+};
+
+template <int MODE>
+__device__ __forceinline__ void load_pair(const uint8_t* p, uint32_t (&x)[2]) {
+  if (MODE == 0) {
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+    x[0] = v.x;
+    x[1] = v.y;
+  } else if (MODE == 1) {
+    x[0] = __ldg(reinterpret_cast<const uint32_t*>(p));
+    x[1] = __ldg(reinterpret_cast<const uint32_t*>(p) + 1);
+  } else {
+    load_words<2, false>(p, 0, x);
+  }
+}
+
+template <int KINDS, int MODE>
+__global__ void __launch_bounds__(128, 6)
+k_sample_acc_v(DenseRows rows, uint32_t rows_per_chunk, uint32_t* __restrict__ acc_het, uint32_t* __restrict__ acc_hom,
+               uint32_t* __restrict__ acc_mis) {
+  constexpr int NP = ((KINDS & 1) ? 1 : 0) + ((KINDS & 2) ? 1 : 0) + ((KINDS & 4) ? 1 : 0);
+  __shared__ uint32_t sm[NP * 16 * 128];
+  const uint32_t N = rows.N;
+  const uint32_t ncols = (N + 15) >> 4;
+  const uint32_t w0 = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
+  uint32_t nrows = rows.nrows;
+  if (rows.nrows_dev) {  // packed rows of a sparse batch: spread what there is over the chunks of the grid
+    nrows = min(nrows, __ldg(rows.nrows_dev));
+    rows_per_chunk = ((nrows + gridDim.y - 1) / gridDim.y + 15) / 16 * 16;
+    if (rows_per_chunk < 32) rows_per_chunk = 32;
+  }
+  const uint32_t r0 = blockIdx.y * rows_per_chunk;
+  if (w0 >= ncols || r0 >= nrows) return;
+  const uint32_t r1 = min(nrows, r0 + rows_per_chunk);
+#pragma unroll
+  for (int i = 0; i < NP * 16; ++i) sm[i * 128 + threadIdx.x] = 0u;
+  VPlane vc[NP];
+#pragma unroll
+  for (int q = 0; q < NP; ++q) vc[q].clear();
+  const uint64_t stride = rows.stride;
+  // 8 rows starting at row rr; GUARD: rows >= r1 read as zero
+  auto load8 = [&](uint32_t rr, uint32_t (&x)[8][2], auto guard) {
+    constexpr bool GUARD = decltype(guard)::value;
+    if (MODE == 2) {
+      const uint8_t* rp[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) rp[j] = rows.ptrs[GUARD ? min(rr + j, r1 - 1) : rr + j] + 4ull * w0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (!GUARD || rr + j < r1) load_pair<MODE>(rp[j], x[j]);
+        else x[j][0] = x[j][1] = 0u;
+      }
+    } else {
+      const uint8_t* p = rows.base + static_cast<uint64_t>(rr) * stride + 4ull * w0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (!GUARD || rr + j < r1) load_pair<MODE>(p, x[j]);
+        else x[j][0] = x[j][1] = 0u;
+        p += stride;
+      }
+    }
+  };
+  auto process = [&](const uint32_t (&x)[8][2], uint32_t (&carry)[NP]) {
+    uint32_t pl[NP][8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const uint32_t a = x[j][0], b = x[j][1];
+      const uint32_t e = bitselect(kM5, a, b << 1);
+      const uint32_t o = bitselect(kM5, a >> 1, b);
+      int q = 0;
+      if (KINDS & 1) pl[q++][j] = e;
+      if (KINDS & 2) pl[q++][j] = o;
+      if (KINDS & 4) pl[q++][j] = e & o;
+    }
+#pragma unroll
+    for (int q = 0; q < NP; ++q) carry[q] = vc[q].add8(pl[q]);
+  };
+  auto to_shared_all = [&]() {
+#pragma unroll
+    for (int q = 0; q < NP; ++q) vc[q].to_shared(sm + q * 16 * 128 + threadIdx.x);
+  };
+  uint32_t xa[8][2], xb[8][2];
+  uint32_t ca[NP], cb[NP];
+  uint32_t blocks = 0;
+  uint32_t r = r0;
+  using No = std::integral_constant<bool, false>;
+  using Yes = std::integral_constant<bool, true>;
+  if (r + 16 <= r1) {
+    load8(r, xa, No());
+    for (; r + 32 <= r1; r += 16) {  // the 16 rows after this block are all there: no guards
+      load8(r + 8, xb, No());
+      process(xa, ca);
+      load8(r + 16, xa, No());
+      process(xb, cb);
+#pragma unroll
+      for (int q = 0; q < NP; ++q) vc[q].add_carries(ca[q], cb[q]);
+      if (++blocks == 15) {
+        blocks = 0;
+        to_shared_all();
+      }
+    }
+    // r + 16 <= r1 < r + 32: xa holds rows r .. r+7
+    load8(r + 8, xb, No());
+    process(xa, ca);
+    process(xb, cb);
+#pragma unroll
+    for (int q = 0; q < NP; ++q) vc[q].add_carries(ca[q], cb[q]);
+    r += 16;
+    to_shared_all();
+  }
+  if (r < r1) {  // fewer than 16 rows left
+    load8(r, xa, Yes());
+    load8(r + 8, xb, Yes());
+    process(xa, ca);
+    process(xb, cb);
+#pragma unroll
+    for (int q = 0; q < NP; ++q) vc[q].add_carries(ca[q], cb[q]);
+    to_shared_all();
+  }
+  // one atomicAdd per sample and plane for the whole chunk
+  const uint32_t s0 = 16u * w0;
+#pragma unroll
+  for (int q = 0; q < NP; ++q) {
+    int kind = 0, seen = 0;
+#pragma unroll
+    for (int b = 0; b < 3; ++b) {
+      if (KINDS & (1 << b)) {
+        if (seen == q) kind = b;
+        ++seen;
+      }
+    }
+    uint32_t* __restrict__ acc = kind == 0 ? acc_het : (kind == 1 ? acc_hom : acc_mis);
+#pragma unroll
+    for (int m = 0; m < 16; ++m) {
+      const uint32_t v = sm[(q * 16 + m) * 128 + threadIdx.x];
+      const uint32_t lo = v & 0xffffu, hi = v >> 16;
+      if (lo && s0 + m < N) atomicAdd(acc + s0 + m, lo);
+      if (hi && s0 + 16 + m < N) atomicAdd(acc + s0 + 16 + m, hi);
+    }
+  }
+}
+
 // acc arrays hold plane counts (E, O, B) per raw sample; out gets het / hom_alt / missing of the
 // subset samples, three arrays of n each.
 __global__ void k_planes_to_counts(const uint32_t* __restrict__ pe, const uint32_t* __restrict__ po,
@@ -469,22 +695,47 @@ void launch_expand_i8(const DenseRows& rows, const uint32_t* subset_idx, uint32_
 void launch_sample_acc(const DenseRows& rows, uint32_t kinds, uint32_t* acc_het, uint32_t* acc_hom, uint32_t* acc_mis,
                        cudaStream_t s, LaunchStats* st) {
   if (!rows.nrows || !rows.N) return;
+  static const bool byte_counters = [] {
+    const char* e = getenv("PD_SAMPLE_ACC");  // "bytes": the widening byte-counter kernel, for A/B runs
+    return e && !strcmp(e, "bytes");
+  }();
   const uint32_t ncols = (rows.N + 15) >> 4;
-  const uint32_t vec = (kinds == 4) ? 4 : 2;  // words per thread: 64 B / 32 B of a record per warp-row... x32 lanes
+  const uint32_t vec = byte_counters ? ((kinds == 4) ? 4 : 2) : 2;  // 32-bit words of a record per thread
   const uint32_t nthreads = (ncols + vec - 1) / vec;
   const uint32_t bx = (nthreads + 127) / 128;
-  // aim at ~12 CTAs of 128 threads per SM, but keep >= 255 rows per chunk when rows allow so
-  // that the 8-bit -> 32-bit flushes stay rare
-  uint32_t want_y = (static_cast<uint32_t>(sm_count()) * 12 + bx - 1) / bx;
+  // aim at ~12 (byte counters) / 6 (vertical counters: one wave at their occupancy, and every chunk ends
+  // with one atomic per sample) CTAs of 128 threads per SM, but keep >= 240 rows per chunk when rows allow
+  // (vertical counters: rounded DOWN so that the grid is one resident wave -- a 7th CTA on a few SMs would
+  // double the kernel time)
+  uint32_t want_y = byte_counters ? (static_cast<uint32_t>(sm_count()) * 12 + bx - 1) / bx
+                                  : static_cast<uint32_t>(sm_count()) * 6 / bx;
   if (want_y < 1) want_y = 1;
   uint32_t rpc = (rows.nrows + want_y - 1) / want_y;
-  if (rpc < 255) rpc = 255;
-  rpc = (rpc + 5) / 6 * 6;
+  if (rpc < 240) rpc = 240;
+  rpc = (rpc + 47) / 48 * 48;
   const uint32_t by = (rows.nrows + rpc - 1) / rpc;
   dim3 grid(bx, by);
+  const uintptr_t addr_bits = reinterpret_cast<uintptr_t>(rows.base) | static_cast<uintptr_t>(rows.stride);
+  if (st) st->launches++;
+  if (!byte_counters) {
+    const int mode = rows.ptrs ? 2 : (addr_bits % 8 == 0 ? 0 : (addr_bits % 4 == 0 ? 1 : 3));
+#define PD_LAUNCH_V(K, M) k_sample_acc_v<K, M><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis)
+    if (kinds == 4) {
+      if (mode == 0) PD_LAUNCH_V(4, 0);
+      else if (mode == 1) PD_LAUNCH_V(4, 1);
+      else if (mode == 2) PD_LAUNCH_V(4, 2);
+      else PD_LAUNCH_V(4, 3);
+    } else {
+      if (mode == 0) PD_LAUNCH_V(7, 0);
+      else if (mode == 1) PD_LAUNCH_V(7, 1);
+      else if (mode == 2) PD_LAUNCH_V(7, 2);
+      else PD_LAUNCH_V(7, 3);
+    }
+#undef PD_LAUNCH_V
+    return;
+  }
   const uint32_t align = 4 * vec;
-  const bool aligned = !rows.ptrs && (reinterpret_cast<uintptr_t>(rows.base) % align == 0) && (rows.stride % align == 0);
-  const int mode = rows.ptrs ? 2 : (aligned ? 0 : 1);
+  const int mode = rows.ptrs ? 2 : (addr_bits % align == 0 ? 0 : 1);
   if (kinds == 4) {
     if (mode == 0) k_sample_acc<4, 4, 0><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
     else if (mode == 1) k_sample_acc<4, 4, 1><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
@@ -494,7 +745,6 @@ void launch_sample_acc(const DenseRows& rows, uint32_t kinds, uint32_t* acc_het,
     else if (mode == 1) k_sample_acc<7, 2, 1><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
     else k_sample_acc<7, 2, 2><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
   }
-  if (st) st->launches++;
 }
 
 void launch_count_rows(const DenseRows& rows, const SubsetDev& sub, uint4* out, cudaStream_t s, LaunchStats* st) {
