@@ -137,8 +137,9 @@ namespace {
 // Parallel read of [off, off+len) into dst: page-cache pread (or memcpy from a pageable image)
 // is a few GB/s per thread, PCIe Gen5 wants ~50 GB/s.
 bool ParallelRead(const ByteSource& src, uint64_t off, uint8_t* dst, uint64_t len) {
-  const uint64_t kChunk = 8ull << 20;
-  const uint32_t nthreads = static_cast<uint32_t>(std::min<uint64_t>(8, (len + kChunk - 1) / kChunk));
+  const uint64_t kChunk = 4ull << 20;
+  static const uint32_t kMaxThreads = std::max(2u, std::min(16u, std::thread::hardware_concurrency()));
+  const uint32_t nthreads = static_cast<uint32_t>(std::min<uint64_t>(kMaxThreads, (len + kChunk - 1) / kChunk));
   if (nthreads <= 1) return src.ReadAt(off, dst, len);
   std::atomic<uint64_t> next(0);
   std::atomic<bool> ok(true);

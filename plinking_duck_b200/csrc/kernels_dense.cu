@@ -116,54 +116,66 @@ k_densify(RecIndex ix, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t
 }
 
 // ---------------------------------------------------------------------------------------------
-// k_expand_i8: the whole (nrows x n_out) int8 matrix as one flat byte array; each thread owns 16
-// consecutive output bytes (one 128-bit store).  Fast path: the 16 bytes sit inside one row and
-// no subset is active -> one 32-bit window load + bit tricks.  Otherwise per-byte gather.
+// k_expand_i8: blockIdx.y = row (no division), threads of a CTA stride over the row's 16-byte output
+// chunks (one 128-bit streaming store each; consecutive lanes = consecutive chunks).  The output is a
+// flat (nrows x n_out) byte matrix, so a row starts at any byte: its first chunk boundary is found
+// once per row, the few bytes before it and after the last full chunk are written singly.  A chunk
+// is 16 samples = one 32-bit window of the record at any 2-bit offset (two aligned loads + funnel
+// shift); 2 bits -> {0, 1, 2, -9} is a PRMT byte look-up: the codes are spread to one per nibble and
+// used as the selector into the constant 0xF7020100.  Subset gathers take the per-byte path.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t expand4(uint32_t b) {
-  // 4 genotypes (8 bits) -> 4 bytes {0,1,2,-9}
-  const uint32_t t = (b | (b << 6) | (b << 12) | (b << 18)) & 0x03030303u;
-  const uint32_t m = t & (t >> 1) & 0x01010101u;
-  return t ^ (m * 0xF4u);
+__device__ __forceinline__ uint32_t spread2to4(uint32_t x) {  // 16 bits -> 8 nibbles holding one 2-bit code each
+  x = (x | (x << 8)) & 0x00FF00FFu;
+  x = (x | (x << 4)) & 0x0F0F0F0Fu;
+  x = (x | (x << 2)) & 0x33333333u;
+  return x;
+}
+
+__device__ __forceinline__ uint4 expand16(uint32_t x) {
+  constexpr uint32_t kTable = 0xF7020100u;  // bytes 0, 1, 2, -9
+  const uint32_t lo = spread2to4(x & 0xffffu), hi = spread2to4(x >> 16);
+  uint4 o;
+  o.x = __byte_perm(kTable, 0u, lo);
+  o.y = __byte_perm(kTable, 0u, lo >> 16);
+  o.z = __byte_perm(kTable, 0u, hi);
+  o.w = __byte_perm(kTable, 0u, hi >> 16);
+  return o;
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_expand_i8(DenseRows rows, const uint32_t* __restrict__ subset_idx, uint32_t n_out, uint64_t total_bytes,
-            int8_t* __restrict__ out) {
-  const uint64_t nchunks = (total_bytes + 15) >> 4;
-  for (uint64_t c = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; c < nchunks;
-       c += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
-    const uint64_t f0 = c << 4;
-    uint32_t r = static_cast<uint32_t>(f0 / n_out);
-    uint32_t col = static_cast<uint32_t>(f0 - static_cast<uint64_t>(r) * n_out);
-    if (!subset_idx && col + 16 <= n_out && f0 + 16 <= total_bytes) {
-      const uint32_t x = load_bits32(row_ptr(rows, r), static_cast<uint64_t>(col) << 1);
-      uint4 o;
-      o.x = expand4(x & 0xffu);
-      o.y = expand4((x >> 8) & 0xffu);
-      o.z = expand4((x >> 16) & 0xffu);
-      o.w = expand4(x >> 24);
-      *reinterpret_cast<uint4*>(out + f0) = o;
-    } else {
-      const uint8_t* row = row_ptr(rows, r);
-      const uint32_t n = static_cast<uint32_t>(min(static_cast<uint64_t>(16), total_bytes - f0));
-      for (uint32_t k = 0; k < n; ++k) {
-        const uint32_t raw = subset_idx ? subset_idx[col] : col;
-        const uint32_t g = geno_at(row, raw);
-        out[f0 + k] = static_cast<int8_t>(g == 3 ? -9 : static_cast<int>(g));
-        if (++col == n_out) {
-          col = 0;
-          ++r;
-          if (f0 + k + 1 < total_bytes) row = row_ptr(rows, r);
-        }
+k_expand_i8(DenseRows rows, const uint32_t* __restrict__ subset_idx, uint32_t n_out, int8_t* __restrict__ out) {
+  for (uint32_t r = blockIdx.y; r < rows.nrows; r += gridDim.y) {
+    const uint8_t* row = row_ptr(rows, r);
+    int8_t* orow = out + static_cast<uint64_t>(r) * n_out;
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t nthr = gridDim.x * blockDim.x;
+    if (subset_idx) {
+      for (uint32_t j = tid; j < n_out; j += nthr) {
+        const uint32_t g = geno_at(row, subset_idx[j]);
+        orow[j] = static_cast<int8_t>(g == 3 ? -9 : static_cast<int>(g));
       }
+      continue;
+    }
+    uint32_t head = static_cast<uint32_t>((16u - (reinterpret_cast<uintptr_t>(orow) & 15u)) & 15u);
+    if (head > n_out) head = n_out;
+    const uint32_t nchunks = (n_out - head) >> 4;
+    const uint32_t tail0 = head + (nchunks << 4);
+    for (uint32_t k = tid; k < nchunks; k += nthr) {
+      const uint32_t col = head + (k << 4);
+      const uint32_t x = load_bits32(row, static_cast<uint64_t>(col) << 1);
+      __stcs(reinterpret_cast<uint4*>(orow + col), expand16(x));
+    }
+    // ragged ends: < 16 bytes each
+    if (tid < head) {
+      const uint32_t g = geno_at(row, tid);
+      orow[tid] = static_cast<int8_t>(g == 3 ? -9 : static_cast<int>(g));
+    }
+    if (tid < n_out - tail0) {
+      const uint32_t g = geno_at(row, tail0 + tid);
+      orow[tail0 + tid] = static_cast<int8_t>(g == 3 ? -9 : static_cast<int>(g));
     }
   }
 }
-
-}  // namespace
-
-namespace {
 
 // ---------------------------------------------------------------------------------------------
 // k_sample_acc: transposed pass.  A thread owns one 32-bit word column (16 samples) and walks
@@ -682,13 +694,16 @@ void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint
 
 void launch_expand_i8(const DenseRows& rows, const uint32_t* subset_idx, uint32_t n_out, int8_t* out, cudaStream_t s,
                       LaunchStats* st) {
-  const uint64_t total = static_cast<uint64_t>(rows.nrows) * n_out;
-  if (!total) return;
-  const uint64_t nchunks = (total + 15) >> 4;
-  uint64_t blocks = (nchunks + kThreads - 1) / kThreads;
-  const uint64_t max_blocks = static_cast<uint64_t>(sm_count()) * 32;
-  if (blocks > max_blocks) blocks = max_blocks;
-  k_expand_i8<<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(rows, subset_idx, n_out, total, out);
+  if (!rows.nrows || !n_out) return;
+  // x: enough threads that one covers at most a few 16-byte chunks of its row; y: rows
+  const uint32_t chunks = (n_out + 15) / 16;
+  uint32_t bx = (chunks + 4 * kThreads - 1) / (4 * kThreads);
+  if (bx < 1) bx = 1;
+  const uint32_t by = rows.nrows < 65535u ? rows.nrows : 65535u;
+  // short rows: no point in 256 threads for a handful of chunks (the ragged ends need <= 15 threads each)
+  uint32_t threads = subset_idx ? (n_out + 31) / 32 * 32 : (chunks + 31) / 32 * 32;
+  threads = threads < 32 ? 32 : (threads > kThreads ? kThreads : threads);
+  k_expand_i8<<<dim3(bx, by), threads, 0, s>>>(rows, subset_idx, n_out, out);
   if (st) st->launches++;
 }
 
