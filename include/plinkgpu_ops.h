@@ -82,6 +82,27 @@ int pdop_score(pd_ctx* ctx, const uint32_t* vidx, const uint8_t* flip, const dou
  * VariantPassesCountFilter: af / ac ranges evaluated from genotype counts.  Negative bound = unset. */
 int pdop_counts_pass(const uint32_t counts[4], double af_min, double af_max, int64_t ac_min, int64_t ac_max);
 
+/* CheckGenotypeRange (src/plink_common.cpp:1465-1493): allowed_mask bit g (g = 0 hom_ref, 1 het, 2 hom_alt)
+ * = category g is selected.  *any_pass: some kept sample falls in a selected category (or is missing while
+ * include_missing is set); *all_pass: no sample falls in an unselected hardcall category. */
+void pdop_genotype_range(const uint32_t counts[4], uint32_t allowed_mask, uint32_t include_missing, uint32_t* any_pass,
+                         uint32_t* all_pass);
+
+/* CheckPreDecompFilters (src/plink_common.cpp:1495-1515) over a variant range, on GPU counts: one pd_counts
+ * call (honouring the context's sample subset), then the two filters per variant.  skip[i] = 1: the variant
+ * is dropped before any decode; all_pass[i] = 1: no per-element null-out is needed.  use_count_filter = 0
+ * ignores the af / ac bounds, use_genotype_filter = 0 the category mask.  Either output may be NULL. */
+typedef struct pd_predecomp_filter {
+  uint32_t use_count_filter;
+  double af_min, af_max;   /* negative = unset */
+  int64_t ac_min, ac_max;  /* negative = unset */
+  uint32_t use_genotype_filter;
+  uint32_t allowed_mask;
+  uint32_t include_missing;
+} pd_predecomp_filter;
+int pdop_predecomp_filter(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, const pd_predecomp_filter* filter, uint8_t* skip,
+                          uint8_t* all_pass);
+
 #ifdef __cplusplus
 }
 #endif

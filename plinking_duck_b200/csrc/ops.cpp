@@ -177,6 +177,44 @@ int pdop_counts_pass(const uint32_t counts[4], double af_min, double af_max, int
   return 1;
 }
 
+void pdop_genotype_range(const uint32_t counts[4], uint32_t allowed_mask, uint32_t include_missing, uint32_t* any_pass,
+                         uint32_t* all_pass) {
+  uint32_t any = 0, all = 1;
+  for (uint32_t g = 0; g < 3; ++g) {
+    const bool selected = (allowed_mask >> g) & 1u;
+    if (selected && counts[g] > 0) any = 1;
+    if (!selected && counts[g] > 0) all = 0;
+  }
+  if (include_missing && counts[3] > 0) any = 1;
+  if (any_pass) *any_pass = any;
+  if (all_pass) *all_pass = all;
+}
+
+int pdop_predecomp_filter(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, const pd_predecomp_filter* f, uint8_t* skip,
+                          uint8_t* all_pass) {
+  if (!ctx || !f || v_begin > v_end) return PD_ERR_INVALID_ARG;
+  const uint32_t n = v_end - v_begin;
+  if (!n) return PD_OK;
+  std::vector<uint32_t> counts(4ull * n);
+  const int rc = pd_counts(ctx, v_begin, v_end, counts.data());
+  if (rc != PD_OK) return rc;
+  for (uint32_t i = 0; i < n; ++i) {
+    const uint32_t* c = &counts[4ull * i];
+    uint8_t sk = 0, ap = 1;
+    if (f->use_count_filter && !pdop_counts_pass(c, f->af_min, f->af_max, f->ac_min, f->ac_max)) {
+      sk = 1;
+    } else if (f->use_genotype_filter) {
+      uint32_t any = 0, all = 1;
+      pdop_genotype_range(c, f->allowed_mask, f->include_missing, &any, &all);
+      if (!any) sk = 1;
+      else ap = static_cast<uint8_t>(all);
+    }
+    if (skip) skip[i] = sk;
+    if (all_pass) all_pass[i] = ap;
+  }
+  return PD_OK;
+}
+
 int pdop_freq(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, const uint8_t* ploidy, const uint8_t* sex, uint32_t dosage,
               pd_freq_row* out) {
   if (!ctx || v_begin > v_end || (v_end > v_begin && !out)) return PD_ERR_INVALID_ARG;

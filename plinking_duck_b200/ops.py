@@ -32,7 +32,16 @@ _OPS = {
     "pdop_missing_sample": (C.c_int, [_vp, _u32, _u32, _vp]),
     "pdop_score": (C.c_int, [_vp, _vp, _vp, _vp, _u32, _u32, _vp]),
     "pdop_counts_pass": (C.c_int, [_vp, C.c_double, C.c_double, C.c_int64, C.c_int64]),
+    "pdop_genotype_range": (None, [_vp, _u32, _u32, _vp, _vp]),
+    "pdop_predecomp_filter": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),
 }
+
+
+class PredecompFilter(C.Structure):
+    """pd_predecomp_filter of include/plinkgpu_ops.h."""
+    _fields_ = [("use_count_filter", C.c_uint32), ("af_min", C.c_double), ("af_max", C.c_double),
+                ("ac_min", C.c_int64), ("ac_max", C.c_int64), ("use_genotype_filter", C.c_uint32),
+                ("allowed_mask", C.c_uint32), ("include_missing", C.c_uint32)]
 _bound = False
 
 
@@ -112,3 +121,30 @@ def plink_score(ctx: PgenContext, vidx: Sequence[int], weights, *, flip=None, no
 def counts_pass(counts, af_min=-1.0, af_max=-1.0, ac_min=-1, ac_max=-1) -> bool:
     c = np.ascontiguousarray(counts, dtype=np.uint32)
     return bool(_lib().pdop_counts_pass(_p(c), float(af_min), float(af_max), int(ac_min), int(ac_max)))
+
+
+def genotype_range(counts, allowed=(), include_missing=False):
+    """CheckGenotypeRange: allowed = iterable of categories 0 hom_ref / 1 het / 2 hom_alt -> (any_pass, all_pass)."""
+    c = np.ascontiguousarray(counts, dtype=np.uint32)
+    mask = sum(1 << int(g) for g in allowed)
+    a, b = C.c_uint32(0), C.c_uint32(0)
+    _lib().pdop_genotype_range(_p(c), mask, int(bool(include_missing)), C.addressof(a), C.addressof(b))
+    return bool(a.value), bool(b.value)
+
+
+def predecomp_filter(ctx, v0=0, v1=None, af=None, ac=None, allowed=None, include_missing=False):
+    """CheckPreDecompFilters over [v0, v1) on GPU counts -> (skip, all_pass) uint8 arrays.
+    af / ac: (min, max) with None for an open end; allowed: iterable of genotype categories or None."""
+    v0, v1 = ctx._range(v0, v1)
+    n = max(v1 - v0, 0)
+    f = PredecompFilter()
+    f.use_count_filter = int(af is not None or ac is not None)
+    f.af_min, f.af_max = [(-1.0 if x is None else float(x)) for x in (af or (None, None))]
+    f.ac_min, f.ac_max = [(-1 if x is None else int(x)) for x in (ac or (None, None))]
+    f.use_genotype_filter = int(allowed is not None)
+    f.allowed_mask = sum(1 << int(g) for g in (allowed or ()))
+    f.include_missing = int(bool(include_missing))
+    skip = np.zeros(n, dtype=np.uint8)
+    allp = np.zeros(n, dtype=np.uint8)
+    ctx._check(_lib().pdop_predecomp_filter(ctx._h, v0, v1, C.addressof(f), _p(skip), _p(allp)))
+    return skip, allp

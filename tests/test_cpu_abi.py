@@ -107,3 +107,9 @@ def test_ploidy_classification_matches_reference_rules(built):
         ops.classify_ploidy("X", 5, "GRCh99")
     assert ops.counts_pass([1, 1, 1, 1], af_min=0.4, af_max=0.6) and not ops.counts_pass([1, 1, 1, 1], af_min=0.6)
     assert not ops.counts_pass([0, 0, 0, 4]) and ops.counts_pass([2, 1, 1, 0], ac_min=3, ac_max=3)
+    # CheckGenotypeRange (src/plink_common.cpp:1465-1493)
+    assert ops.genotype_range([5, 0, 0, 2], allowed=(0,)) == (True, True)
+    assert ops.genotype_range([5, 1, 0, 0], allowed=(0,)) == (True, False)
+    assert ops.genotype_range([5, 0, 0, 0], allowed=(1, 2)) == (False, False)
+    assert ops.genotype_range([0, 0, 0, 3], allowed=(1,)) == (False, True)
+    assert ops.genotype_range([0, 0, 0, 3], allowed=(1,), include_missing=True) == (True, True)

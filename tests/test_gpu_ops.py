@@ -229,3 +229,29 @@ def test_xchr_exact_test_matches_reference():
                 assert abs(got[k] - max(bf, 0.0)) <= 1e-12, (t, got[k], exp, bf)
                 tie_quirks += 1
     assert tie_quirks <= 20
+
+
+def test_predecomp_filters_on_gpu_counts(golden):
+    """CheckPreDecompFilters (src/plink_common.cpp:1495-1515) over GPU counts: af / ac ranges and the
+    genotype-category filter vs the same rules evaluated with numpy on pgenlib's golden counts."""
+    from plinking_duck_b200 import ops
+
+    name = "syn_n1000"
+    cnt = golden[name + "/counts"].astype(np.int64)
+    nm = cnt[:, 0] + cnt[:, 1] + cnt[:, 2]
+    ac = cnt[:, 1] + 2 * cnt[:, 2]
+    af = np.where(nm > 0, ac / np.maximum(2.0 * nm, 1), 0.0)
+    with _ctx(name) as c:
+        skip, allp = ops.predecomp_filter(c, af=(0.05, 0.4))
+        exp = (nm == 0) | (af < 0.05) | (af > 0.4)
+        assert np.array_equal(skip.astype(bool), exp) and np.all(allp[~exp] == 1)
+        skip, _ = ops.predecomp_filter(c, ac=(10, None))
+        assert np.array_equal(skip.astype(bool), (nm == 0) | (ac < 10))
+        skip, allp = ops.predecomp_filter(c, allowed=(1, 2))
+        any_pass = (cnt[:, 1] > 0) | (cnt[:, 2] > 0)
+        assert np.array_equal(skip.astype(bool), ~any_pass)
+        assert np.array_equal(allp[any_pass].astype(bool), (cnt[:, 0] == 0)[any_pass])
+        skip, _ = ops.predecomp_filter(c, allowed=(2,), include_missing=True)
+        assert np.array_equal(skip.astype(bool), ~((cnt[:, 2] > 0) | (cnt[:, 3] > 0)))
+        skip, _ = ops.predecomp_filter(c, 10, 50, af=(0.0, 1.0), allowed=(0, 1, 2))
+        assert skip.shape == (40,) and np.array_equal(skip.astype(bool), (nm == 0)[10:50])
