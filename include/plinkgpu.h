@@ -71,6 +71,8 @@ typedef struct pd_stats_t {
   double total_ms;          /* CUDA-event time of the last call's whole device section          */
   uint64_t scan_launches;   /* launches of the dominant scan kernel in the last call            */
   double call_ms;           /* CUDA-event time of the last call, first enqueue to last result copy */
+  double host_stage_ms;     /* host wall time the last call spent filling staging buffers (reads, gathers) */
+  double host_wait_ms;      /* host wall time the last call spent waiting for a free staging buffer        */
 } pd_stats_t;
 
 /* ---- open / close : replaces PgfiInitPhase1 + PgfiInitPhase2 + PgrInit per scan thread

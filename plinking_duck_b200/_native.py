@@ -38,7 +38,8 @@ class Stats(C.Structure):
     _fields_ = [
         ("launches", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("record_bytes", C.c_uint64),
         ("kernel_ms", C.c_double), ("aux_kernel_ms", C.c_double), ("total_ms", C.c_double),
-        ("scan_launches", C.c_uint64), ("call_ms", C.c_double),
+        ("scan_launches", C.c_uint64), ("call_ms", C.c_double), ("host_stage_ms", C.c_double),
+        ("host_wait_ms", C.c_double),
     ]
 
 

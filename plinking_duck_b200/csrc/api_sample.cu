@@ -7,6 +7,7 @@
 #include <thread>
 
 #include "ctx.h"
+#include "host_pool.h"
 #include "outpipe.h"
 
 using namespace pdx;
@@ -22,24 +23,16 @@ bool IsPinnedHost(const void* p) {
 
 // memcpy split over a few threads: one thread moves ~10 GB/s, PCIe delivers ~55 GB/s.
 void ParallelMemcpy(void* dst, const void* src, size_t n) {
-  const size_t kChunk = 8u << 20;
-  const unsigned nthreads = static_cast<unsigned>(std::min<size_t>(8, (n + kChunk - 1) / kChunk));
-  if (nthreads <= 1) {
+  const size_t kChunk = 4u << 20;
+  const size_t nchunks = (n + kChunk - 1) / kChunk;
+  if (nchunks <= 1) {
     memcpy(dst, src, n);
     return;
   }
-  std::atomic<size_t> next(0);
-  auto worker = [&]() {
-    for (;;) {
-      const size_t o = next.fetch_add(kChunk);
-      if (o >= n) break;
-      memcpy(static_cast<char*>(dst) + o, static_cast<const char*>(src) + o, std::min(kChunk, n - o));
-    }
-  };
-  std::vector<std::thread> pool;
-  for (unsigned t = 1; t < nthreads; ++t) pool.emplace_back(worker);
-  worker();
-  for (auto& th : pool) th.join();
+  HostPool::Get().ParallelFor(nchunks, [&](uint64_t i) {
+    const size_t o = static_cast<size_t>(i) * kChunk;
+    memcpy(static_cast<char*>(dst) + o, static_cast<const char*>(src) + o, std::min(kChunk, n - o));
+  });
 }
 
 // Per-sample accumulation over [v_begin, v_end): kinds as pdk::launch_sample_acc.

@@ -55,6 +55,12 @@ int CountsToDevice(pd_ctx_impl* c, const SubsetState& sub, uint32_t v_begin, uin
   cudaError_t e = c->d_counts.Reserve(std::max<size_t>(16, static_cast<size_t>(v_end - v0) * 16));
   if (e != cudaSuccess) return CheckCuda(c, e, "counts allocation");
   uint4* out_dev = c->d_counts.as<uint4>();
+  // Unmasked counts never read the sample ids of a plain difflist record: stage those records trimmed.
+  struct TrimScope {
+    pd_ctx_impl* c;
+    ~TrimScope() { c->trim_scan = false; }
+  } scope{c};
+  c->trim_scan = !sub.active && !c->idx.fixed;
   return RunScan(c, v_begin, v_end, v_ext, [&](const Tile& t, const pdk::RecIndex& ix, cudaStream_t s) {
     return CountTile(c, sub, t, ix, v0, out_dev, s);
   });

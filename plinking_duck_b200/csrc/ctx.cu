@@ -5,9 +5,11 @@
 // ranges ("tiles", cut where no LD dependency crosses) read into page-locked buffers and pushed
 // with cudaMemcpyAsync on a copy stream while the previous tile's kernels run.
 #include "ctx.h"
+#include "host_pool.h"
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 
@@ -137,28 +139,95 @@ namespace {
 // Parallel read of [off, off+len) into dst: page-cache pread (or memcpy from a pageable image)
 // is a few GB/s per thread, PCIe Gen5 wants ~50 GB/s.
 bool ParallelRead(const ByteSource& src, uint64_t off, uint8_t* dst, uint64_t len) {
-  const uint64_t kChunk = 4ull << 20;
-  static const uint32_t kMaxThreads = std::max(2u, std::min(16u, std::thread::hardware_concurrency()));
-  const uint32_t nthreads = static_cast<uint32_t>(std::min<uint64_t>(kMaxThreads, (len + kChunk - 1) / kChunk));
-  if (nthreads <= 1) return src.ReadAt(off, dst, len);
-  std::atomic<uint64_t> next(0);
+  const uint64_t kChunk = 2ull << 20;
+  const uint64_t nchunks = (len + kChunk - 1) / kChunk;
+  if (nchunks <= 1) return src.ReadAt(off, dst, len);
   std::atomic<bool> ok(true);
-  auto worker = [&]() {
-    for (;;) {
-      const uint64_t o = next.fetch_add(kChunk);
-      if (o >= len) break;
-      const uint64_t n = std::min(kChunk, len - o);
-      if (!src.ReadAt(off + o, dst + o, n)) ok.store(false);
-    }
-  };
-  std::vector<std::thread> pool;
-  for (uint32_t t = 1; t < nthreads; ++t) pool.emplace_back(worker);
-  worker();
-  for (auto& th : pool) th.join();
+  HostPool::Get().ParallelFor(nchunks, [&](uint64_t i) {
+    const uint64_t o = i * kChunk;
+    if (!src.ReadAt(off + o, dst + o, std::min(kChunk, len - o))) ok.store(false);
+  });
   return ok.load();
 }
 
-void PlanTiles(const pd_ctx_impl* c, uint32_t v0, uint32_t v1, std::vector<Tile>* tiles) {
+// f(a, b) over [0, n) cut into pieces of about `per` items, on the host pool.
+template <class F>
+void ParallelRanges(uint64_t n, uint64_t per, const F& f) {
+  if (!n) return;
+  per = std::max<uint64_t>(1, per);
+  const uint64_t pieces = (n + per - 1) / per;
+  HostPool::Get().ParallelFor(pieces, [&](uint64_t i) { f(i * per, std::min(n, (i + 1) * per)); });
+}
+
+// Bytes of record v that genotype counting reads: everything for raw / 1-bit / LD records, LD bases and
+// records with extra tracks; for a plain difflist record (vrtype 4 / 6 / 7) only the length, the group
+// index and the 2-bit values -- not the sample-id deltas (layout: ParseDifflistHeader,
+// pgenlib_read.cc:2184-2218).
+uint64_t TrimmedLength(const PgenIndex& ix, const uint8_t* view, uint32_t v) {
+  const uint64_t full = ix.fpos[v + 1] - ix.fpos[v];
+  const uint32_t vt = ix.vrtypes[v];
+  if ((vt & ~7u) || (vt & 7u) < 4 || (vt & 7u) == 5) return full;
+  if (v + 1 < ix.variant_ct && ix.ldbase[v + 1] == v) return full;  // an LD record patches this one: ids needed
+  const uint8_t* p = view + ix.fpos[v];
+  uint32_t len = 0, shift = 0;
+  uint64_t used = 0;
+  for (;;) {  // varint
+    if (used >= full || shift > 28) return full;
+    const uint8_t b = p[used++];
+    len |= static_cast<uint32_t>(b & 127u) << shift;
+    if (!(b & 128u)) break;
+    shift += 7;
+  }
+  if (!len) return full;
+  const uint32_t n = ix.sample_ct;
+  const uint32_t idbytes = 1u + ((31u - static_cast<uint32_t>(__builtin_clz(n))) >> 3);  // BytesToRepresentNzU32
+  const uint64_t groups = (static_cast<uint64_t>(len) + 63) / 64;
+  const uint64_t want = used + groups * (idbytes + 1) - 1 + (static_cast<uint64_t>(len) + 3) / 4;
+  return want < full ? want : full;
+}
+
+// Builds c->trim_fpos once; usable only when the source is host-addressable and trimming saves >= 30 %.
+bool EnsureTrimIndex(pd_ctx_impl* c) {
+  if (c->trim_state) return c->trim_state > 0;
+  c->trim_state = -1;
+  const PgenIndex& ix = c->idx;
+  const uint8_t* view = c->pgen.view();
+  if (ix.fixed || !view || !ix.has_difflist || !ix.variant_ct) return false;
+  const uint32_t V = ix.variant_ct;
+  std::vector<uint64_t> pos(static_cast<size_t>(V) + 1);
+  ParallelRanges(V, 4096, [&](uint64_t a, uint64_t b) {
+    for (uint64_t v = a; v < b; ++v) pos[v + 1] = TrimmedLength(ix, view, static_cast<uint32_t>(v));
+  });
+  pos[0] = 0;
+  for (uint32_t v = 0; v < V; ++v) pos[v + 1] += pos[v];
+  if (pos[V] * 10 > ix.data_bytes * 7) return false;
+  if (c->d_trim_fpos.Reserve(pos.size() * 8) != cudaSuccess) return false;
+  if (cudaMemcpy(c->d_trim_fpos.p, pos.data(), pos.size() * 8, cudaMemcpyHostToDevice) != cudaSuccess) return false;
+  c->trim_fpos.swap(pos);
+  c->trim_state = 1;
+  return true;
+}
+
+// Copies the counted bytes of records [v0, v1) into dst (their compacted stream).
+void GatherTrimmed(const pd_ctx_impl* c, uint32_t v0, uint32_t v1, uint8_t* dst) {
+  const PgenIndex& ix = c->idx;
+  const uint8_t* view = c->pgen.view();
+  const std::vector<uint64_t>& tp = c->trim_fpos;
+  const uint64_t base = tp[v0];
+  ParallelRanges(v1 - v0, 512, [&](uint64_t a, uint64_t b) {
+    uint64_t v = v0 + a;
+    const uint64_t e = v0 + b;
+    while (v < e) {
+      // runs of untrimmed records are contiguous in the file as well: one memcpy
+      uint64_t w = v;
+      while (w + 1 < e && (tp[w + 1] - tp[w]) == (ix.fpos[w + 1] - ix.fpos[w])) ++w;
+      memcpy(dst + (tp[v] - base), view + ix.fpos[v], tp[w + 1] - tp[v]);
+      v = w + 1;
+    }
+  });
+}
+
+void PlanTiles(const pd_ctx_impl* c, uint32_t v0, uint32_t v1, std::vector<Tile>* tiles, bool trim) {
   const PgenIndex& ix = c->idx;
   if (ix.fixed) {
     uint64_t per = c->tile_bytes / ix.fixed_width;
@@ -174,8 +243,11 @@ void PlanTiles(const pd_ctx_impl* c, uint32_t v0, uint32_t v1, std::vector<Tile>
   while (a < v1) {
     uint32_t b = a + 1;
     // extend while under budget; never cut in front of an LD-compressed record
-    while (b < v1 && ((ix.fpos[b + 1] - ix.fpos[a] <= c->tile_bytes) || ix.ldbase[b] != b)) ++b;
-    tiles->push_back(Tile{a, b, ix.fpos[a], ix.fpos[b]});
+    const std::vector<uint64_t>& pos = trim ? c->trim_fpos : ix.fpos;
+    // trimmed tiles are gathered by the host before they can be copied: smaller tiles start the pipeline sooner
+    const uint64_t budget = trim ? std::min<uint64_t>(c->tile_bytes, 16ull << 20) : c->tile_bytes;
+    while (b < v1 && ((pos[b + 1] - pos[a] <= budget) || ix.ldbase[b] != b)) ++b;
+    tiles->push_back(Tile{a, b, pos[a], pos[b]});
     a = b;
   }
 }
@@ -202,6 +274,8 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
   c->stats.aux_kernel_ms = 0;
   c->stats.total_ms = 0;
   c->stats.scan_launches = 0;
+  c->stats.host_stage_ms = 0;
+  c->stats.host_wait_ms = 0;
   if (v_begin == v_end) return PD_OK;
 
   pdk::RecIndex ix{};
@@ -236,20 +310,23 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
       c->stats.kernel_ms = ms;
     }
   } else {
+    const bool trim = c->trim_scan && EnsureTrimIndex(c);
+    if (trim) ix.fpos = c->d_trim_fpos.as<uint64_t>();
     std::vector<Tile> tiles;
-    PlanTiles(c, v0, v_end, &tiles);
+    PlanTiles(c, v0, v_end, &tiles, trim);
     uint64_t max_len = 0;
     for (auto& t : tiles) max_len = std::max(max_len, t.f1 - t.f0);
     const uint32_t nbuf = c->n_staging;
     for (uint32_t b = 0; b < nbuf && rc == PD_OK; ++b) {
       cudaError_t e = c->d_stage[b].Reserve(max_len + 2 * kSlack);
-      if (e == cudaSuccess && !c->src_pinned) e = c->h_stage[b].Reserve(max_len);
+      if (e == cudaSuccess && (trim || !c->src_pinned)) e = c->h_stage[b].Reserve(max_len);
       if (e != cudaSuccess) rc = CheckCuda(c, e, "staging allocation");
     }
     for (size_t i = 0; i < tiles.size() && rc == PD_OK; ++i) {
       const Tile& t = tiles[i];
       const uint32_t b = static_cast<uint32_t>(i % nbuf);
       const uint64_t len = t.f1 - t.f0;
+      const auto tw0 = std::chrono::steady_clock::now();
       if (i >= nbuf) {
         cudaError_t e = cudaEventSynchronize(c->ev_done[b]);  // buffer b's previous tile fully consumed
         if (e != cudaSuccess) {
@@ -257,8 +334,13 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
           break;
         }
       }
+      const auto tw1 = std::chrono::steady_clock::now();
+      c->stats.host_wait_ms += std::chrono::duration<double, std::milli>(tw1 - tw0).count();
       const uint8_t* hsrc;
-      if (c->src_pinned) {
+      if (trim) {
+        GatherTrimmed(c, t.v0, t.v1, c->h_stage[b].as<uint8_t>());
+        hsrc = c->h_stage[b].as<uint8_t>();
+      } else if (c->src_pinned) {
         hsrc = c->pgen.mem() + t.f0;
       } else {
         if (!ParallelRead(c->pgen, t.f0, c->h_stage[b].as<uint8_t>(), len)) {
@@ -267,6 +349,7 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
         }
         hsrc = c->h_stage[b].as<uint8_t>();
       }
+      c->stats.host_stage_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tw1).count();
       cudaError_t e = cudaMemcpyAsync(c->d_stage[b].as<uint8_t>() + kSlack, hsrc, len, cudaMemcpyHostToDevice,
                                       c->copy_stream);
       if (e != cudaSuccess) {

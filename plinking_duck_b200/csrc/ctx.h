@@ -61,6 +61,13 @@ struct pd_ctx_impl {
   uint64_t tile_bytes = 64ull << 20;
   uint32_t n_staging = 3;
   bool src_pinned = false;  // memory image is page-locked: DMA straight from it
+  // Trimmed staging (unmasked genotype counts over variable-width files): difflist records that are not an
+  // LD base are staged without their sample-id deltas -- counting never reads them (K3), and they are
+  // ~85 % of such a record.  trim_fpos[v] = offset of record v in that compacted stream.
+  std::vector<uint64_t> trim_fpos;  // [V+1], built on first use
+  DevBuf d_trim_fpos;
+  int trim_state = 0;               // 0 not built, 1 usable, -1 not worth it / not possible
+  bool trim_scan = false;           // set by the caller around RunScan
 
   cudaStream_t stream = nullptr;       // compute
   cudaStream_t copy_stream = nullptr;  // H2D staging

@@ -4,6 +4,7 @@
 
 #include <cuda_runtime.h>
 #include <fcntl.h>
+#include <sys/mman.h>
 #include <sys/stat.h>
 #include <unistd.h>
 
@@ -16,6 +17,7 @@
 namespace pdx {
 
 ByteSource::~ByteSource() {
+  if (map_) munmap(const_cast<uint8_t*>(map_), size_);
   if (fd_ >= 0) close(fd_);
 }
 
@@ -31,6 +33,10 @@ bool ByteSource::OpenFile(const char* path, std::string* err) {
     return false;
   }
   size_ = static_cast<uint64_t>(st.st_size);
+  if (size_) {
+    void* m = mmap(nullptr, size_, PROT_READ, MAP_SHARED, fd_, 0);
+    if (m != MAP_FAILED) map_ = static_cast<const uint8_t*>(m);  // optional: only the trimmed scan needs it
+  }
   return true;
 }
 

@@ -26,12 +26,16 @@ class ByteSource {
   uint64_t size() const { return size_; }
   bool is_mem() const { return mem_ != nullptr; }
   const uint8_t* mem() const { return mem_; }
+  // Host-addressable bytes of the whole source: the caller's memory, or a read-only mapping of the
+  // file (nullptr if the mapping failed or the image lives on the device).
+  const uint8_t* view() const { return mem_ ? mem_ : map_; }
   // Reads exactly len bytes at off into dst; false on short read / error.
   bool ReadAt(uint64_t off, void* dst, uint64_t len) const;
 
  private:
   int fd_ = -1;
   const uint8_t* mem_ = nullptr;
+  const uint8_t* map_ = nullptr;
   const uint8_t* dev_ = nullptr;
   uint64_t size_ = 0;
 };
