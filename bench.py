@@ -47,6 +47,8 @@ def parse_args():
     ap.add_argument("--samples", type=int, default=100_000)
     ap.add_argument("--cpu-sample-variants", type=int, default=0)
     ap.add_argument("--e2e-variants", type=int, default=250_000, help="host-image variants per rank when N > 1")
+    ap.add_argument("--e2e-cap-variants", type=int, default=0,
+                    help="dev only: cap the host image at N = 1 (e.g. for the 125 GB configs[2] file)")
     ap.add_argument("--skip-cpu", action="store_true")
     return ap.parse_args()
 
@@ -278,6 +280,8 @@ def run_ours(args):
     # e2e: the same file as a page-locked HOST image.  At N = 1 it is the whole file (25 GB); with several
     # ranks sharing one host's RAM each rank stages the first 250k variants (6.25 GB) of its range.
     V_host = V if world == 1 else min(V, args.e2e_variants)
+    if args.e2e_cap_variants:
+        V_host = min(V_host, args.e2e_cap_variants)
     image = host_image_of(dev_image, V_host, N)
 
     out_counts = torch.empty((V, 4), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
