@@ -10,10 +10,11 @@
 // exact for the tensor cores by fixed-point limbs (the int8 "Ozaki" splitting):
 //     x ~ scale_c * q,   q = round(x / scale_c) a signed 55-bit integer = sum_l limb_l 256^l,
 // seven signed int8 limbs per weight.  int8 x int8 products accumulate EXACTLY in the int32 TMEM
-// accumulators (|sum| <= 2 * 128 * k-rows < 2^31 for up to 8M k-rows), the limbs are recombined in
-// 128-bit integer arithmetic, and a single rounding to fp64 happens per batch and column.  The result
-// is independent of summation order (bit-reproducible across tiles, launches and GPUs); its error is
-// the quantisation max|x| 2^-55 per term, i.e. tighter than the fp64 FMA loop it replaces.
+// accumulators (|sum| <= 2 * 128 * k-rows < 2^31 for up to 8M k-rows), the limbs are recombined as
+// hi * 2^24 + lo, and a single rounding to fp64 happens per batch (<= 65535 scored variants) and column;
+// batches are added in fp64.  Within a batch the result is independent of summation order
+// (bit-reproducible across sample tiles, k splits and launches); its error is the quantisation
+// max|x| 2^-55 per term, i.e. tighter than the fp64 FMA loop it replaces.
 //
 // GEMM shape per CTA:  D[128 x 256] (int32, 256 TMEM columns) += A[128 x 32] * B[32 x 256]  per slab
 //   A (M side) = weight limbs: row r = column c * 7 + limb l, K-major, prepared once per batch in
@@ -306,7 +307,7 @@ k_tc_quant(DenseRows rows, const ScoreRow* __restrict__ srow, const double* __re
 // k_score_mma: grid = (sample tiles, k splits).  Warps 0-3 unpack, warp 4 issues the MMAs and owns
 // the TMEM allocation, warp 5 copies the A slabs; after the last slab warps 0-3 drain the
 // accumulators (TMEM lane = limb row, column = sample) into acc32[sample][row] with integer
-// reductions, which is what makes k splits and batches order-independent.
+// reductions, which is what makes k splits order-independent.
 // ---------------------------------------------------------------------------------------------
 struct MmaSmem {
   alignas(128) uint8_t b[kStages][kBBytes];
