@@ -75,13 +75,16 @@ class ShardedPgen:
            oracle-backed stand-in to exercise the partition / reduction logic under gloo.
     """
 
-    def __init__(self, local, rank: int = 0, world: int = 1, group=None, device=None):
+    def __init__(self, local, rank: int = 0, world: int = 1, group=None, device=None, prepartitioned: bool = False):
+        """prepartitioned: `local` already holds only this rank's contiguous variant range (one shard file per
+        rank): every call works on the whole local range and only the reductions span the group."""
         self.local = local
         self.rank, self.world, self.group = rank, world, group
         self.device = device  # torch.device of this rank's GPU, or None for CPU (gloo) reductions
+        self.prepartitioned = prepartitioned
         self.vrtypes, self.fpos = local.index()
         self.V = int(self.fpos.size - 1)
-        self.ranges = partition_variants(self.fpos, self.vrtypes, world)
+        self.ranges = [(0, self.V)] * world if prepartitioned else partition_variants(self.fpos, self.vrtypes, world)
         self.v0, self.v1 = self.ranges[rank]
 
     # ---- reductions ----
@@ -159,7 +162,7 @@ class ShardedPgen:
         if W.ndim == 1:
             W = W.reshape(-1, 1)
         K = W.shape[1]
-        i0, i1 = partition_list(vidx, self.fpos, self.world)[self.rank]
+        i0, i1 = (0, vidx.size) if self.prepartitioned else partition_list(vidx, self.fpos, self.world)[self.rank]
         fl = None if flip is None else np.ascontiguousarray(flip, dtype=np.uint8)[i0:i1]
         n = self.local.sample_ct
         if self._on_gpu():

@@ -126,3 +126,54 @@ def test_two_rank_gloo_matches_single_process(name, golden, refmod, tmp_path):
         assert np.max(np.abs(r["s"][:, 1] - 2 * golden[name + "/score_m0_sum"])) <= 2e-12 * scale
         assert np.array_equal(r["a"], golden[name + "/score_m0_ct"])
         assert np.allclose(r["d"], golden[name + "/score_m0_dsum"], rtol=1e-12)
+
+
+def _worker_shards(rank, world, port, names, out_dir):
+    import sys
+
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+
+    from plinking_duck_b200.multi import ShardedPgen
+
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        name = names[rank]
+        sp = ShardedPgen(OracleLocal(fixture_path(name)), rank=rank, world=world, prepartitioned=True)
+        assert (sp.v0, sp.v1) == (0, sp.V)
+        mis = sp.missing_by_sample()
+        het, hom, mis2 = sp.sample_counts()
+        g = np.load(os.path.join(GOLDEN_DIR, "golden.npz"))
+        w, fl = g[name + "/score_w"], g[name + "/score_flip"]
+        s, d, a = sp.score(np.arange(w.size), fl, w, 0)
+        np.savez(os.path.join(out_dir, f"s{rank}.npz"), mis=mis, het=het, hom=hom, mis2=mis2, s=s, d=d, a=a,
+                 local_counts=sp.counts_local())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_gloo_prepartitioned_shard_files(golden, refmod, tmp_path):
+    """One shard FILE per rank (the reference's shard1 / shard2 fixtures, same 8 samples): per-variant outputs
+    stay local, per-sample accumulators and scores are summed over the ranks."""
+    import torch.multiprocessing as mp
+
+    names = ["shard1", "shard2"]
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mp.spawn(_worker_shards, args=(2, port, names, str(tmp_path)), nprocs=2, join=True)
+    res = [np.load(str(tmp_path / f"s{r}.npz")) for r in range(2)]
+    exp_mis = sum(golden[n + "/missing_by_sample"] for n in names)
+    exp_sc = sum(golden[n + "/sample_counts"].astype(np.int64) for n in names)
+    exp_s = sum(golden[n + "/score_m0_sum"] for n in names)
+    exp_a = sum(golden[n + "/score_m0_ct"].astype(np.int64) for n in names)
+    scale = sum(2.0 * np.abs(golden[n + "/score_w"]).sum() + 1.0 for n in names)
+    for r, n in zip(res, names):
+        assert np.array_equal(r["local_counts"], golden[n + "/counts"])
+        assert np.array_equal(r["mis"], exp_mis) and np.array_equal(r["mis2"], exp_sc[2])
+        assert np.array_equal(r["het"], exp_sc[0]) and np.array_equal(r["hom"], exp_sc[1])
+        assert np.max(np.abs(r["s"][:, 0] - exp_s)) <= 1e-12 * scale
+        assert np.array_equal(r["a"].astype(np.int64), exp_a)
