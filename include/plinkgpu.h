@@ -148,6 +148,15 @@ int pd_sample_counts(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t* ou
  *      row-major, values {0,1,2,-9}. ---- */
 int pd_decode_i8(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, int8_t* out);
 
+/* ---- phased hardcalls : replaces PgrGetP + UnpackPhasedGenotypes (src/plink_common.cpp:1549-1584; call
+ *      sites src/pgen_reader.cpp:705-733, src/pfile_reader.cpp:1722-1745, read_pgen / read_pfile with
+ *      phased := true).  out: (v_end - v_begin) x n_out x 2 int8 allele pairs in subset order:
+ *      hom-ref 0,0; hom-alt 1,1; missing -9,-9; het 1,0 when the record's hardcall-phase track marks the
+ *      sample phased with the ALT allele first, else 0,1 (phased REF|ALT and unphased hets alike, as the
+ *      reference).  Variants without a phase track decode every het as 0,1.  Multiallelic records with a
+ *      phase track return PD_ERR_NOT_SUPPORTED. ---- */
+int pd_decode_phased(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, int8_t* out);
+
 /* ---- dosage decode: replaces PgrGetD + Dosage16ToDoublesMinus9 (src/plink_score.cpp:587-596,
  *      src/pgen_reader.cpp:694-703).  out is n_var x effective sample_ct double, -9.0 = missing. ---- */
 int pd_dosage_f64(pd_ctx* ctx, const uint32_t* vidx, uint32_t n_var, double* out);

@@ -368,6 +368,86 @@ int po_decode_i8(po_file* f, uint32_t v0, uint32_t v1, int8_t* out) {
   return 0;
 }
 
+static void ignore_entry(void* ctx, uint32_t id, uint32_t geno, uint32_t ord) {
+  (void)ctx; (void)id; (void)geno; (void)ord;
+}
+
+/* End of the main genotype track of record v = start of aux2 when the record has no multiallelic
+ * patch sets (SkipAux1 / main-track layouts, pgenlib_read.cc:6844-6865 and the decoders above). */
+static const uint8_t* main_track_end(const po_file* f, uint32_t v) {
+  const uint32_t N = f->N;
+  const uint8_t* p = f->data + po_fpos(f, v);
+  const uint8_t* end = f->data + po_fpos(f, v + 1);
+  const uint32_t t = po_vrtype(f, v) & 7;
+  const uint8_t* q = p;
+  if (t == 0) return p + (N + 3) / 4 <= end ? p + (N + 3) / 4 : NULL;
+  if (t == 5) return p;
+  if (t == 1) {
+    q = p + 1 + (N + 7) / 8;
+    if (q > end) return NULL;
+  }
+  return walk_difflist(&q, end, N, 1, ignore_entry, NULL, NULL) ? q : NULL;
+}
+
+/* PgrGetP (ReadGenovecHphaseSubsetUnsafe, pgenlib_read.cc:6874-6962) + UnpackPhasedGenotypes
+ * (src/plink_common.cpp:1549-1584): out[(v - v0) * N + s][2] allele pairs.  hom-ref 0,0; hom-alt 1,1;
+ * missing -9,-9; het 1,0 iff the aux2 track marks it phased with ALT first, else 0,1.
+ * aux2 (vrtype bit 4): het_ct + 1 bits; bit 0 clear -> all hets phased, bits 1.. = phaseinfo;
+ * bit 0 set -> bits 1.. = phasepresent flags, and one phaseinfo bit per set flag follows at the next
+ * byte boundary (1 + het_ct / 8 bytes in). */
+int po_decode_phased(po_file* f, uint32_t v0, uint32_t v1, int8_t* out) {
+  if (v0 > v1 || v1 > f->V) return 2;
+  uint8_t* codes = (uint8_t*)malloc(f->N);
+  for (uint32_t v = v0; v < v1; ++v) {
+    int rc = po_read_codes(f, v, codes);
+    const uint32_t vt = po_vrtype(f, v);
+    const uint8_t* aux2 = NULL;
+    if (!rc && (vt & 0x10)) {
+      if (vt & 0x08) rc = 4; /* multiallelic + phase: not restated */
+      else if (!(aux2 = main_track_end(f, v))) rc = 3;
+    }
+    if (rc) {
+      free(codes);
+      return rc;
+    }
+    uint32_t het_ct = 0;
+    for (uint32_t s = 0; s < f->N; ++s) het_ct += codes[s] == 1;
+    const uint8_t* end = f->data + po_fpos(f, v + 1);
+    const int explicit_pp = aux2 && (aux2[0] & 1);
+    const uint8_t* second = aux2 ? aux2 + 1 + het_ct / 8 : NULL;
+    if (aux2 && second > end) {
+      free(codes);
+      return 3;
+    }
+    int8_t* o = out + (size_t)(v - v0) * f->N * 2;
+    uint32_t h = 0, k = 0; /* het ordinal, flagged-het ordinal */
+    for (uint32_t s = 0; s < f->N; ++s) {
+      int8_t a = -9, b = -9;
+      if (codes[s] == 0) { a = 0; b = 0; }
+      else if (codes[s] == 2) { a = 1; b = 1; }
+      else if (codes[s] == 1) {
+        int alt_first = 0;
+        if (aux2) {
+          const uint32_t bit = 1 + h;
+          const int flag = (aux2[bit >> 3] >> (bit & 7)) & 1;
+          if (!explicit_pp) alt_first = flag;
+          else if (flag) {
+            alt_first = (second[k >> 3] >> (k & 7)) & 1;
+            ++k;
+          }
+        }
+        ++h;
+        a = alt_first ? 1 : 0;
+        b = alt_first ? 0 : 1;
+      }
+      o[2 * s] = a;
+      o[2 * s + 1] = b;
+    }
+  }
+  free(codes);
+  return 0;
+}
+
 /* PlinkMissingScanSample phase 1 (src/plink_missing.cpp:585-611): PgrGetMissingness, then one
  * increment per set bit. */
 int po_missing_by_sample(po_file* f, uint32_t v0, uint32_t v1, uint32_t* out) {

@@ -34,6 +34,9 @@ int po_read_codes(po_file* f, uint32_t vidx, uint8_t* codes);
 int po_counts(po_file* f, uint32_t v0, uint32_t v1, const uint8_t* include, uint32_t* counts);
 /* out[(v - v0) * N + s] in {0, 1, 2, -9}.  (PgrGet + GenoarrToBytesMinus9.) */
 int po_decode_i8(po_file* f, uint32_t v0, uint32_t v1, int8_t* out);
+/* out[((v - v0) * N + s) * 2 + {0,1}] = allele pair: 0,0 / 0,1 or 1,0 / 1,1 / -9,-9.  (PgrGetP +
+ * UnpackPhasedGenotypes.) */
+int po_decode_phased(po_file* f, uint32_t v0, uint32_t v1, int8_t* out);
 /* out[s] = number of variants of [v0, v1) where sample s is missing.  (plink_missing sample mode.) */
 int po_missing_by_sample(po_file* f, uint32_t v0, uint32_t v1, uint32_t* out);
 /* Exact Hardy-Weinberg test p-value (autosomal, optional mid-p), clamped to [0, 1]. */

@@ -34,6 +34,7 @@ def lib():
         L.po_read_codes.argtypes = [vp, u32, vp]
         L.po_counts.argtypes = [vp, u32, u32, vp, vp]
         L.po_decode_i8.argtypes = [vp, u32, u32, vp]
+        L.po_decode_phased.argtypes = [vp, u32, u32, vp]
         L.po_missing_by_sample.argtypes = [vp, u32, u32, vp]
         L.po_hwe_exact.argtypes = [u32, u32, u32, C.c_int]
         L.po_hwe_exact.restype = C.c_double
@@ -99,6 +100,12 @@ class PortPgen:
         v1 = self.variant_ct if v1 is None else v1
         out = np.zeros((v1 - v0, self.sample_ct), dtype=np.int8)
         self._chk(lib().po_decode_i8(self._h, v0, v1, _p(out)))
+        return out
+
+    def decode_phased(self, v0=0, v1=None) -> np.ndarray:
+        v1 = self.variant_ct if v1 is None else v1
+        out = np.zeros((v1 - v0, self.sample_ct, 2), dtype=np.int8)
+        self._chk(lib().po_decode_phased(self._h, v0, v1, _p(out)))
         return out
 
     def missing_by_sample(self, v0=0, v1=None) -> np.ndarray:

@@ -56,6 +56,8 @@ def lib():
         L.ref_writer_open.argtypes = [C.c_char_p, u32, u32, u32, C.POINTER(vp)]
         L.ref_writer_append.argtypes = [vp, vp]
         L.ref_writer_append_dosage.argtypes = [vp, vp, vp, vp, u32]
+        L.ref_writer_append_phased.argtypes = [vp, vp, vp, vp]
+        L.ref_decode_phased.argtypes = [vp, u32, u32, vp]
         L.ref_writer_close.argtypes = [vp]
         _lib = L
     return _lib
@@ -141,6 +143,15 @@ class RefPgen:
         rc = lib().ref_decode_i8(self._h, v0, v1, _p(out))
         if rc:
             raise IOError(f"PgrGet rc={rc}")
+        return out
+
+    def decode_phased(self, v0=0, v1=None) -> np.ndarray:
+        """(v1-v0, sample_ct, 2) int8 allele pairs: PgrGetP + UnpackPhasedGenotypes."""
+        v0, v1 = self._rng(v0, v1)
+        out = np.zeros((v1 - v0, self.sample_ct, 2), dtype=np.int8)
+        rc = lib().ref_decode_phased(self._h, v0, v1, _p(out))
+        if rc:
+            raise IOError(f"PgrGetP rc={rc}")
         return out
 
     def missingness(self, v0=0, v1=None):
@@ -229,16 +240,20 @@ def bench_score(path, threads, vidx, flip, weights):
     return t, sums, cts
 
 
-def write_pgen(path: str, genovecs: np.ndarray, N: int, dosage=None):
+def write_pgen(path: str, genovecs: np.ndarray, N: int, dosage=None, phase=None):
     """Write a variable-width (mode 0x10) .pgen with pgenlib's own writer.
 
     genovecs: (V, ceil(N/32)) uint64, 2-bit codes, trailing bits zero.
     dosage:   optional list of (present_bits uint64[ceil(N/64)], u16 values) per variant or None.
+    phase:    optional list of (phasepresent uint64[ceil(N/64)], phaseinfo uint64[ceil(N/64)]) per variant or
+              None (hardcall phase, SpgwAppendBiallelicGenovecHphase); not combined with dosage here.
     """
     genovecs = np.ascontiguousarray(genovecs, dtype=np.uint64)
     V = genovecs.shape[0]
     h = C.c_void_p()
-    rc = lib().ref_writer_open(os.fsencode(path), V, N, 1 if dosage is not None else 0, C.byref(h))
+    assert dosage is None or phase is None
+    flags = (1 if dosage is not None else 0) | (2 if phase is not None else 0)
+    rc = lib().ref_writer_open(os.fsencode(path), V, N, flags, C.byref(h))
     if rc:
         raise IOError(f"SpgwInitPhase1 rc={rc}")
     for v in range(V):
@@ -248,6 +263,10 @@ def write_pgen(path: str, genovecs: np.ndarray, N: int, dosage=None):
             pres = np.ascontiguousarray(pres, dtype=np.uint64)
             vals = np.ascontiguousarray(vals, dtype=np.uint16)
             rc = lib().ref_writer_append_dosage(h, _p(row), _p(pres), _p(vals), vals.size)
+        elif phase is not None and phase[v] is not None:
+            pp = np.ascontiguousarray(phase[v][0], dtype=np.uint64)
+            pi = np.ascontiguousarray(phase[v][1], dtype=np.uint64)
+            rc = lib().ref_writer_append_phased(h, _p(row), _p(pp), _p(pi))
         else:
             rc = lib().ref_writer_append(h, _p(row))
         if rc:

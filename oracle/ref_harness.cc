@@ -255,6 +255,41 @@ int ref_decode_i8(void* h, uint32_t v0, uint32_t v1, int8_t* out) {
   return 0;
 }
 
+// PgrGetP + UnpackPhasedGenotypes (src/plink_common.cpp:1549-1584; call sites src/pgen_reader.cpp:705-733,
+// src/pfile_reader.cpp:1722-1745): out is (v1-v0) x sample_ct x 2 int8 allele pairs.  hom-ref 0,0;
+// hom-alt 1,1; missing -9,-9; het 1,0 when phasepresent and phaseinfo are both set, else 0,1.  The phase
+// buffers are zeroed per variant because PgrGetP leaves them untouched for variants without a phase track.
+int ref_decode_phased(void* h, uint32_t v0, uint32_t v1, int8_t* out) {
+  Reader* r = static_cast<Reader*>(h);
+  const uintptr_t words = BitCtToAlignedWordCt(r->N) + 8;
+  std::vector<uintptr_t> pp(words), pi(words);
+  std::vector<int8_t> bytes(static_cast<size_t>(r->sample_ct) + 64);
+  for (uint32_t v = v0; v < v1; ++v) {
+    std::fill(pp.begin(), pp.end(), 0);
+    std::fill(pi.begin(), pi.end(), 0);
+    uint32_t phasepresent_ct = 0;
+    PglErr e = PgrGetP(r->sample_include, r->pssi, r->sample_ct, v, &r->pgr, r->genovec, pp.data(), pi.data(),
+                       &phasepresent_ct);
+    if (e != kPglRetSuccess) return static_cast<int>(e);
+    GenoarrToBytesMinus9(r->genovec, r->sample_ct, bytes.data());
+    int8_t* o = &out[static_cast<size_t>(v - v0) * r->sample_ct * 2];
+    for (uint32_t s = 0; s < r->sample_ct; ++s) {
+      int8_t a = -9, b = -9;
+      switch (bytes[s]) {
+        case 0: a = 0; b = 0; break;
+        case 2: a = 1; b = 1; break;
+        case 1:
+          if (IsSet(pp.data(), s) && IsSet(pi.data(), s)) { a = 1; b = 0; } else { a = 0; b = 1; }
+          break;
+        default: break;
+      }
+      o[2 * s] = a;
+      o[2 * s + 1] = b;
+    }
+  }
+  return 0;
+}
+
 // PgrGetMissingness + PopcountWords (variant mode) and the ctz bit walk (sample mode).
 // Either output may be NULL.  per_sample must be zero-initialised by the caller.
 int ref_missingness(void* h, uint32_t v0, uint32_t v1, uint32_t* per_variant, uint32_t* per_sample) {
@@ -564,7 +599,9 @@ int ref_writer_open(const char* path, uint32_t V, uint32_t N, uint32_t dosage, v
   uintptr_t alloc_ct = 0;
   uint32_t max_vrec_len = 0;
   PglErr e = SpgwInitPhase1(path, nullptr, nullptr, V, N, 0, kPgenWriteBackwardSeek,
-                            dosage ? kfPgenGlobalDosagePresent : kfPgenGlobal0, 2, &w->spgw, &alloc_ct, &max_vrec_len);
+                            ((dosage & 1) ? kfPgenGlobalDosagePresent : kfPgenGlobal0) |
+                                ((dosage & 2) ? kfPgenGlobalHardcallPhasePresent : kfPgenGlobal0),
+                            2, &w->spgw, &alloc_ct, &max_vrec_len);
   if (e != kPglRetSuccess) {
     delete w;
     return static_cast<int>(e);
@@ -606,6 +643,17 @@ int ref_writer_append_dosage(void* h, const uint64_t* genovec, const uint64_t* d
   memcpy(w->dosage_main, dosage_main, static_cast<size_t>(dosage_ct) * sizeof(uint16_t));
   return static_cast<int>(SpgwAppendBiallelicGenovecDosage16(w->genovec, w->dosage_present, w->dosage_main, dosage_ct,
                                                              &w->spgw));
+}
+
+// phasepresent / phaseinfo: ceil(N/64) 64-bit words each (writer opened with flag bit 1).
+int ref_writer_append_phased(void* h, const uint64_t* genovec, const uint64_t* phasepresent, const uint64_t* phaseinfo) {
+  Writer* w = static_cast<Writer*>(h);
+  StageGenovec(w, genovec);
+  const uintptr_t aligned_words = BitCtToAlignedWordCt(w->N);
+  std::vector<uintptr_t> pp(aligned_words + 8, 0), pi(aligned_words + 8, 0);
+  memcpy(pp.data(), phasepresent, BitCtToWordCt(w->N) * sizeof(uintptr_t));
+  memcpy(pi.data(), phaseinfo, BitCtToWordCt(w->N) * sizeof(uintptr_t));
+  return static_cast<int>(SpgwAppendBiallelicGenovecHphase(w->genovec, pp.data(), pi.data(), &w->spgw));
 }
 
 int ref_writer_close(void* h) {

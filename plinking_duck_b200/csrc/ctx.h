@@ -66,6 +66,7 @@ struct pd_ctx_impl {
   // ~85 % of such a record.  trim_fpos[v] = offset of record v in that compacted stream.
   std::vector<uint64_t> trim_fpos;  // [V+1], built on first use
   DevBuf d_trim_fpos;
+  DevBuf d_phase_raw;               // pd_decode_phased with a sample subset: unsubsetted pair rows
   int trim_state = 0;               // 0 not built, 1 usable, -1 not worth it / not possible
   bool trim_scan = false;           // set by the caller around RunScan
 

@@ -104,6 +104,11 @@ struct SparseAcc {
 void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint32_t nrows, uint8_t* scratch,
                     uint32_t slot_stride, const uint8_t** ptrs, uint32_t* work_counter, int* err, cudaStream_t s,
                     LaunchStats* st, const SparseAcc* sparse = nullptr);
+// out[(r * n_out + j) * 2 + {0,1}] = allele pair of sample subset_idx[j] (or j) -- PgrGetP +
+// UnpackPhasedGenotypes.  raw_scratch: nrows x roundup8(N) x 2 bytes, only used with a subset.
+void launch_expand_phased(const RecIndex& ix, const DenseRows& rows, const uint32_t* vlist, uint32_t v0,
+                          const uint32_t* subset_idx, uint32_t n_out, int8_t* raw_scratch, int8_t* out, int* err,
+                          cudaStream_t s, LaunchStats* st);
 // out[r * n_out + j] = {0,1,2,-9} of sample subset_idx[j] (or j) -- PgrGet + GenoarrToBytesMinus9.
 void launch_expand_i8(const DenseRows& rows, const uint32_t* subset_idx, uint32_t n_out, int8_t* out, cudaStream_t s,
                       LaunchStats* st);

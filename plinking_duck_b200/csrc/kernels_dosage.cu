@@ -311,6 +311,179 @@ k_dosage_stats(DenseRows rows, const DosageLoc* __restrict__ loc, const uint32_t
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// k_expand_phased: PgrGetP + UnpackPhasedGenotypes (src/plink_common.cpp:1549-1584) -- one warp per
+// row; output row = N x 2 int8 allele pairs: hom-ref 0,0  hom-alt 1,1  missing -9,-9  het 0,1 unless
+// the aux2 track says "phased, ALT first" -> 1,0.
+// aux2 (pgen_spec.tex "hardcall phase", ReadGenovecHphaseSubsetUnsafe pgenlib_read.cc:6874-6962):
+// 1 + het_ct bits; bit 0 clear: every het is phased and bits 1.. are the phaseinfo bits; bit 0 set:
+// bits 1.. are phasepresent flags and a second bit array (one bit per set flag) follows at the next
+// byte.  A lane owns one 32-bit word of the dense row (16 samples) per step of 512 samples; the
+// index of its first het among the row's hets, and of its first set flag among the flags, come from
+// warp prefix sums carried across steps.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t warp_excl_scan(uint32_t x, int lane, uint32_t* total) {
+  uint32_t incl = x;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
+    if (lane >= off) incl += t;
+  }
+  *total = __shfl_sync(0xffffffffu, incl, 31);
+  return incl - x;
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_expand_phased(RecIndex ix, DenseRows rows, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t out_stride_pairs,
+                int8_t* __restrict__ out, int* __restrict__ err) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t N = ix.N;
+  const uint32_t nwords = (N + 15) >> 4;
+  const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < rows.nrows; r += nwarps) {
+    const uint32_t v = vlist ? vlist[r] : v0 + r;
+    uint32_t vrtype;
+    const uint8_t *p, *end;
+    if (ix.fpos) {
+      vrtype = ix.vrtypes[v];
+      p = ix.data + (ix.fpos[v] - ix.data_fpos);
+      end = ix.data + (ix.fpos[v + 1] - ix.data_fpos);
+    } else {
+      vrtype = ix.const_vrtype;
+      p = ix.data + (ix.fixed_start + static_cast<uint64_t>(v) * ix.fixed_width - ix.data_fpos);
+      end = p + ix.fixed_width;
+    }
+    const uint8_t* row = row_ptr(rows, r);
+    // ---- locate aux2 ----
+    const uint8_t* aux2 = nullptr;    // bit 0 = explicit flag, bits 1.. = flags or phaseinfo
+    const uint8_t* second = nullptr;  // phaseinfo of the flagged hets (explicit form)
+    bool explicit_pp = false;
+    int bad = 0;
+    if (vrtype & 0x10u) {
+      if (vrtype & 0x08u) {
+        bad = kErrNotSupported;  // multiallelic patch sets precede aux2; "next" row f4
+      } else {
+        const uint32_t main = vrtype & 7u;
+        const uint8_t* q = p;
+        bool ok = true;
+        if (main == 0) {
+          q = p + ((N + 3) >> 2);
+        } else if (main == 1) {
+          q = p + 1 + ((N + 7) >> 3);
+          ok = q <= end && difflist_end(q, end, N, true, lane, &q, nullptr);
+        } else if (main != 5) {
+          ok = difflist_end(q, end, N, true, lane, &q, nullptr);
+        }
+        ok = ok && q <= end;
+        if (ok) {
+          Planes c = {0u, 0u, 0u};
+          planes_2bit<32, 2, false>(row, N, lane, c);
+          const uint32_t het = group_sum<32>(c.e) - group_sum<32>(c.b);
+          const uint32_t first = 1 + (het >> 3);
+          ok = static_cast<uint64_t>(end - q) >= first;
+          if (ok) {
+            aux2 = q;
+            explicit_pp = q[0] & 1u;
+            if (explicit_pp) {
+              uint32_t pc = popcount_bits<32>(q, het + 1, nullptr, 0, lane);
+              pc = group_sum<32>(pc) - 1;  // minus the flag bit itself
+              second = q + first;
+              ok = static_cast<uint64_t>(end - second) >= ((pc + 7) >> 3);
+            }
+          }
+        }
+        if (!ok) bad = kErrMalformed;
+      }
+    }
+    if (bad) {
+      if (lane == 0) report_error(err, bad, v);
+      aux2 = nullptr;
+    }
+    // ---- expand ----
+    int8_t* orow = out + static_cast<uint64_t>(r) * out_stride_pairs * 2;
+    const bool vec_ok = (reinterpret_cast<uintptr_t>(orow) & 15u) == 0;
+    uint32_t het_base = 0, flag_base = 0;
+    for (uint32_t w0 = 0; w0 < nwords; w0 += 32) {
+      const uint32_t w = w0 + lane;
+      uint32_t x = 0;
+      if (w < nwords) {
+        x = load_bits32(row, static_cast<uint64_t>(w) << 5);
+        const uint32_t valid = N - (w << 4);
+        if (valid < 16) x &= (1u << (2 * valid)) - 1u;
+      }
+      const uint32_t hm = x & ~(x >> 1) & kM5;  // hets, one bit per sample at even positions
+      const uint32_t cnt = __popc(hm);
+      uint32_t tot_h = 0, tot_f = 0;
+      const uint32_t hoff = het_base + warp_excl_scan(cnt, lane, &tot_h);
+      uint32_t bits = 0;    // this lane's aux2 bits, bit j = het hoff + j
+      uint32_t nflag = 0;
+      if (aux2 && cnt) {
+        bits = load_bits32(aux2, 1ull + hoff) & ((cnt >= 32 ? 0u : (1u << cnt)) - 1u);
+        nflag = explicit_pp ? __popc(bits) : 0u;
+      }
+      uint32_t foff = 0;
+      if (explicit_pp) foff = flag_base + warp_excl_scan(nflag, lane, &tot_f);
+      uint32_t info = bits;  // all-phased form: the bits ARE the phaseinfo
+      if (explicit_pp) {
+        // spread the packed phaseinfo bits of the flagged hets back to het positions
+        const uint32_t packed = nflag ? load_bits32(second, foff) : 0u;
+        info = 0;
+        uint32_t k = 0;
+        for (uint32_t f = bits; f; f &= f - 1) {
+          const uint32_t j = __ffs(f) - 1;
+          info |= ((packed >> k) & 1u) << j;
+          ++k;
+        }
+      }
+      if (w < nwords) {
+        // 16 samples -> 16 pairs (32 bytes)
+        uint32_t o[8];
+        uint32_t hj = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          uint32_t word = 0;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const uint32_t g = (x >> (4 * i + 2 * h)) & 3u;
+            uint32_t pair = g == 0 ? 0x0000u : (g == 2 ? 0x0101u : (g == 3 ? 0xF7F7u : 0x0100u));
+            if (g == 1) {
+              if ((info >> hj) & 1u) pair = 0x0001u;
+              ++hj;
+            }
+            word |= pair << (16 * h);
+          }
+          o[i] = word;
+        }
+        const uint32_t s0 = w << 4;
+        if (vec_ok && s0 + 16 <= N) {
+          uint4* dst = reinterpret_cast<uint4*>(orow + 2ull * s0);
+          __stcs(dst, make_uint4(o[0], o[1], o[2], o[3]));
+          __stcs(dst + 1, make_uint4(o[4], o[5], o[6], o[7]));
+        } else {
+          for (uint32_t k = 0; k < 16 && s0 + k < N; ++k) {
+            const uint32_t pair = (o[k >> 1] >> (16 * (k & 1))) & 0xffffu;
+            orow[2ull * (s0 + k)] = static_cast<int8_t>(pair & 0xffu);
+            orow[2ull * (s0 + k) + 1] = static_cast<int8_t>(pair >> 8);
+          }
+        }
+      }
+      het_base += tot_h;
+      flag_base += tot_f;
+    }
+  }
+}
+
+// out[r, j] = raw[r, idx[j]] as 16-bit pairs (sample subset of a phased row).
+__global__ void k_gather_pairs(const uint16_t* __restrict__ raw, uint32_t raw_stride, const uint32_t* __restrict__ idx,
+                               uint32_t n_out, uint64_t total, uint16_t* __restrict__ out) {
+  for (uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
+    const uint64_t r = i / n_out;
+    const uint32_t j = static_cast<uint32_t>(i - r * n_out);
+    out[i] = raw[r * raw_stride + idx[j]];
+  }
+}
+
 }  // namespace
 
 void launch_dosage_locate(const RecIndex& ix, const DenseRows& rows, const uint32_t* vlist, uint32_t v0, DosageLoc* loc,
@@ -339,6 +512,28 @@ void launch_dosage_stats(const DenseRows& rows, const DosageLoc* loc, const uint
   const uint32_t blocks = (rows.nrows * 32 + kThreads - 1) / kThreads;
   k_dosage_stats<<<blocks, kThreads, 0, s>>>(rows, loc, rank, rank_stride, sub, n_out, stats);
   if (st) st->launches++;
+}
+
+void launch_expand_phased(const RecIndex& ix, const DenseRows& rows, const uint32_t* vlist, uint32_t v0,
+                          const uint32_t* subset_idx, uint32_t n_out, int8_t* raw_scratch, int8_t* out, int* err,
+                          cudaStream_t s, LaunchStats* st) {
+  if (!rows.nrows || !n_out) return;
+  uint64_t blocks = (static_cast<uint64_t>(rows.nrows) * 32 + kThreads - 1) / kThreads;
+  if (blocks > 148ull * 16) blocks = 148ull * 16;
+  if (!subset_idx) {
+    k_expand_phased<<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, rows, vlist, v0, ix.N, out, err);
+    if (st) st->launches++;
+    return;
+  }
+  // subset: expand all raw samples, then gather the kept pairs (phase is a per-sample property)
+  const uint32_t raw_stride = (ix.N + 7) & ~7u;  // keeps every scratch row 16-byte aligned
+  k_expand_phased<<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, rows, vlist, v0, raw_stride, raw_scratch, err);
+  const uint64_t total = static_cast<uint64_t>(rows.nrows) * n_out;
+  uint64_t gb = (total + 255) / 256;
+  if (gb > 148ull * 32) gb = 148ull * 32;
+  k_gather_pairs<<<static_cast<unsigned>(gb), 256, 0, s>>>(reinterpret_cast<const uint16_t*>(raw_scratch), raw_stride,
+                                                        subset_idx, n_out, total, reinterpret_cast<uint16_t*>(out));
+  if (st) st->launches += 2;
 }
 
 }  // namespace pdk

@@ -215,6 +215,13 @@ class PgenContext:
         self._check(self._lib.pd_decode_i8(self._h, v0, v1, _p(out)))
         return out
 
+    def decode_phased(self, v0=0, v1=None) -> np.ndarray:
+        """(v1 - v0, sample_ct, 2) int8 allele pairs (read_pgen / read_pfile with phased := true)."""
+        v0, v1 = self._range(v0, v1)
+        out = np.zeros((max(v1 - v0, 0), self.sample_ct, 2), dtype=np.int8)
+        self._check(self._lib.pd_decode_phased(self._h, v0, v1, _p(out)))
+        return out
+
     def dosage_f64(self, vidx) -> np.ndarray:
         vidx = np.ascontiguousarray(vidx, dtype=np.uint32)
         out = np.zeros((vidx.size, self.sample_ct), dtype=np.float64)

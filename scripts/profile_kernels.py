@@ -22,7 +22,7 @@ def main():
     ap.add_argument("--variants", type=int, default=200_000)
     ap.add_argument("--samples", type=int, default=100_000)
     ap.add_argument("--reps", type=int, default=3)
-    ap.add_argument("--ops", default="counts,counts_subset,hardy,missing_by_sample,sample_counts,decode_i8,score1,score16")
+    ap.add_argument("--ops", default="counts,counts_subset,hardy,missing_by_sample,sample_counts,decode_i8,decode_phased,score1,score16")
     ap.add_argument("--score-variants", type=int, default=20_000)
     ap.add_argument("--decode-variants", type=int, default=20_000)
     args = ap.parse_args()
@@ -91,6 +91,16 @@ def main():
             ctx._check(ctx._lib.pd_decode_i8(ctx._h, 0, Vd, out.ctypes.data_as(C.c_void_p)))
 
         report("decode_i8", dec, Vd * (W + N), Vd * N, {"note": "kernel_ms = expand kernels; call_ms includes D2H of N bytes/variant"})
+    if "decode_phased" in ops:
+        Vd = min(V, args.decode_variants // 2)
+        outp = torch.empty((Vd, N, 2), dtype=torch.int8, pin_memory=True).numpy()
+        import ctypes as C
+
+        def decp():
+            ctx._check(ctx._lib.pd_decode_phased(ctx._h, 0, Vd, outp.ctypes.data_as(C.c_void_p)))
+
+        report("decode_phased", decp, Vd * (W + 2 * N), Vd * N,
+               {"note": "kernel_ms = expand kernels; call_ms includes D2H of 2N bytes/variant"})
     for K in (1, 16):
         if f"score{K}" in ops:
             Vs = min(V, args.score_variants)

@@ -40,3 +40,11 @@ DOSAGE_IMP_R2 = [1.2900887786091624, 0.7374153374407626, 1.0, 0.3857199844561125
 XCHR_X1 = dict(fhom_ref=1, fhet=1, fhom_alt=1, male_ref=2, male_alt=1, p=1.0, p_midp=0.714286)
 # test/sql/plink_sexchr.test:45,54,63 -- ALT_FREQ / OBS_CT of x1, y1, mt1
 SEXCHR_FREQ = {"x1": (0.444444, 9), "y1": (0.666667, 3), "mt1": (0.666667, 6)}
+
+# test/sql/read_pgen_phased.test:45-63 -- read_pgen('test/data/phased_example.pgen', phased := true), NULL = -9,-9
+PHASED_EXAMPLE_PAIRS = [
+    [[0, 0], [0, 1], [1, 0], [-9, -9]],   # rs1: 0|0 0|1 1|0 ./.
+    [[0, 1], [1, 0], [0, 0], [1, 1]],     # rs2: 0/1 1|0 0|0 1|1
+    [[1, 1], [-9, -9], [1, 0], [0, 0]],   # rs3: 1|1 ./. 1|0 0|0
+    [[0, 0], [0, 0], [0, 1], [1, 1]],     # rs4: 0|0 0|0 0|1 1|1
+]

@@ -208,3 +208,38 @@ def rewrite_with_all_ref_records(src: str, dst: str) -> int:
     with open(dst, "wb") as f:
         f.write(bytes(out))
     return converted
+
+
+def gen_phase(g: np.ndarray, seed: int):
+    """Per-variant hardcall phase for oracle.ref.write_pgen(phase=...): a third of the variants carry no
+    phase track (None), a third have every het phased (pgenlib stores the implicit form), a third have a
+    random subset of their hets phased (explicit phasepresent form).  Returns (list, expected_pairs) with
+    expected_pairs (V, N, 2) int8 following UnpackPhasedGenotypes."""
+    rng = np.random.default_rng(seed)
+    V, N = g.shape
+    nw = (N + 63) // 64
+    phase = []
+    exp = np.zeros((V, N, 2), dtype=np.int8)
+    exp[g == 1] = (0, 1)
+    exp[g == 2] = (1, 1)
+    exp[g == 3] = (-9, -9)
+
+    def pack(bits):
+        b = np.zeros(nw * 64, dtype=np.uint8)
+        b[:N] = bits
+        return np.packbits(b, bitorder="little").view(np.uint64).copy()
+
+    for v in range(V):
+        het = g[v] == 1
+        kind = v % 3
+        if kind == 0 or not het.any():
+            phase.append(None)
+            continue
+        present = het.copy() if kind == 1 else (het & (rng.random(N) < 0.6))
+        if not present.any():
+            phase.append(None)
+            continue
+        info = present & (rng.random(N) < 0.5)
+        phase.append((pack(present), pack(info)))
+        exp[v, info] = (1, 0)
+    return phase, exp

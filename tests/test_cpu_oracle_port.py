@@ -99,3 +99,30 @@ def test_all_ref_vrtype5_records(port, tmp_path):
         assert np.array_equal(p.counts(), synth.counts_numpy(g))
         assert np.array_equal(p.missing_by_sample(), (g == 3).sum(0))
         assert np.array_equal(p.decode_i8(), np.where(g == 3, -9, g))
+
+
+def test_phased_decode_kat_and_pgenlib(port, tmp_path):
+    """PgrGetP + UnpackPhasedGenotypes: the reference's known answers for phased_example
+    (test/sql/read_pgen_phased.test:45-63), then pgenlib-written files with implicit (all hets phased) and
+    explicit (phasepresent) aux2 tracks on every main record type: pgenlib's reader, the port and the
+    generator's own expectation must agree."""
+    import synth
+    from oracle import ref
+
+    with port.PortPgen(fixture_path("phased_example")) as p:
+        assert p.decode_phased().tolist() == kat.PHASED_EXAMPLE_PAIRS
+    if not ref.available():
+        pytest.skip("oracle/_ref not built: no pgenlib writer")
+    with ref.RefPgen(fixture_path("phased_example")) as r:
+        assert r.decode_phased().tolist() == kat.PHASED_EXAMPLE_PAIRS
+    for (V, N) in [(90, 300), (60, 257), (30, 5000)]:
+        g = synth.gen_mixed_genotypes(V, N, seed=V)
+        phase, exp = synth.gen_phase(g, 7)
+        path = str(tmp_path / f"ph_{V}_{N}.pgen")
+        ref.write_pgen(path, synth.to_genovec_words(g), N, phase=phase)
+        with ref.RefPgen(path) as r:
+            assert np.array_equal(r.decode_phased(), exp)
+            assert any(int(x) & 0x10 for x in r.vrtypes())
+        with port.PortPgen(path) as p:
+            assert np.array_equal(p.decode_phased(), exp)
+            assert np.array_equal(p.decode_phased(5, 17), exp[5:17])

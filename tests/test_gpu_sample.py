@@ -183,3 +183,54 @@ def test_sparse_sample_accumulation_on_pgenlib_written_records(tmp_path):
                 assert np.array_equal(het, exp[0][sub]) and np.array_equal(hom, exp[1][sub])
                 assert np.array_equal(mis, exp[2][sub])
                 assert np.array_equal(c.missing_by_sample(), exp[2][sub])
+
+
+def test_decode_phased_known_answers():
+    """test/sql/read_pgen_phased.test:45-63."""
+    import kat
+
+    for kw in (dict(), dict(tile_bytes=64, n_staging=2)):
+        with _ctx("phased_example", **kw) as c:
+            assert c.decode_phased().tolist() == kat.PHASED_EXAMPLE_PAIRS
+            c.load_resident()
+            assert c.decode_phased(1, 3).tolist() == kat.PHASED_EXAMPLE_PAIRS[1:3]
+            c.set_subset(np.array([3, 1]))
+            exp = np.asarray(kat.PHASED_EXAMPLE_PAIRS, dtype=np.int8)[:, [1, 3]]
+            assert np.array_equal(c.decode_phased(), exp)
+
+
+def test_decode_phased_vs_pgenlib(tmp_path):
+    """pd_decode_phased (PgrGetP + UnpackPhasedGenotypes) on pgenlib-written files: implicit and explicit
+    aux2 tracks behind every main record type (vrtypes 0x10-0x17), records without a phase track, ragged N,
+    streamed / tiny tiles / resident, sub-range, sample subset; and a fixed-width file (no phase: hets 0,1)."""
+    import synth
+    from oracle import ref
+    from plinking_duck_b200.pgen import PgenContext
+
+    if not ref.available():
+        pytest.skip("oracle/_ref not built: no pgenlib writer")
+    for (V, N) in [(90, 300), (60, 257), (40, 5000), (12, 70001)]:
+        g = synth.gen_mixed_genotypes(V, N, seed=V)
+        phase, exp = synth.gen_phase(g, 7)
+        path = str(tmp_path / f"ph_{V}_{N}.pgen")
+        ref.write_pgen(path, synth.to_genovec_words(g), N, phase=phase)
+        with ref.RefPgen(path) as r:
+            assert np.array_equal(r.decode_phased(), exp)
+        for kw in (dict(), dict(tile_bytes=900, n_staging=2)):
+            with PgenContext(path, **kw) as c:
+                assert np.array_equal(c.decode_phased(), exp), (V, N, kw)
+                a, b = V // 4, V - 3
+                assert np.array_equal(c.decode_phased(a, b), exp[a:b]), (V, N, kw)
+                assert np.array_equal(c.decode_i8(), np.where(g == 3, -9, g))
+                c.load_resident()
+                assert np.array_equal(c.decode_phased(), exp), (V, N, kw, "resident")
+                sub = np.arange(1, N, 3)
+                c.set_subset(sub)
+                assert np.array_equal(c.decode_phased(), exp[:, sub]), (V, N, kw, "subset")
+    g = synth.gen_hwe_genotypes(50, 1003, seed=2)
+    exp = np.zeros((50, 1003, 2), dtype=np.int8)
+    exp[g == 1] = (0, 1)
+    exp[g == 2] = (1, 1)
+    exp[g == 3] = (-9, -9)
+    with PgenContext(image=synth.fixed_pgen_image(g)) as c:
+        assert np.array_equal(c.decode_phased(), exp)
