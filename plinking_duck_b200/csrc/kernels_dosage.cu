@@ -336,11 +336,20 @@ __device__ __forceinline__ uint32_t warp_excl_scan(uint32_t x, int lane, uint32_
 __global__ void __launch_bounds__(kThreads)
 k_expand_phased(RecIndex ix, DenseRows rows, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t out_stride_pairs,
                 int8_t* __restrict__ out, int* __restrict__ err) {
+  // One CTA (8 warps) per row: the row is cut into 8 contiguous parts of whole 512-sample steps; a warp
+  // first counts the hets of its part, the counts are exchanged through shared memory, and the flag
+  // offset of a part is a popcount over the aux2 bits before it -- so the parts expand independently.
+  constexpr int kWarps = kThreads / 32;
+  __shared__ uint32_t sm_het[kWarps];
+  __shared__ const uint8_t* sm_q;
+  __shared__ int sm_bad;
   const int lane = threadIdx.x & 31;
+  const int wid = threadIdx.x >> 5;
   const uint32_t N = ix.N;
   const uint32_t nwords = (N + 15) >> 4;
-  const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
-  for (uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < rows.nrows; r += nwarps) {
+  const uint32_t part = ((nwords + kWarps - 1) / kWarps + 31) & ~31u;  // words per warp, whole steps
+  const uint32_t wbeg = min(nwords, wid * part), wend = min(nwords, wbeg + part);
+  for (uint32_t r = blockIdx.x; r < rows.nrows; r += gridDim.x) {
     const uint32_t v = vlist ? vlist[r] : v0 + r;
     uint32_t vrtype;
     const uint8_t *p, *end;
@@ -354,88 +363,111 @@ k_expand_phased(RecIndex ix, DenseRows rows, const uint32_t* __restrict__ vlist,
       end = p + ix.fixed_width;
     }
     const uint8_t* row = row_ptr(rows, r);
-    // ---- locate aux2 ----
-    const uint8_t* aux2 = nullptr;    // bit 0 = explicit flag, bits 1.. = flags or phaseinfo
-    const uint8_t* second = nullptr;  // phaseinfo of the flagged hets (explicit form)
-    bool explicit_pp = false;
-    int bad = 0;
-    if (vrtype & 0x10u) {
-      if (vrtype & 0x08u) {
-        bad = kErrNotSupported;  // multiallelic patch sets precede aux2; "next" row f4
-      } else {
-        const uint32_t main = vrtype & 7u;
-        const uint8_t* q = p;
-        bool ok = true;
-        if (main == 0) {
-          q = p + ((N + 3) >> 2);
-        } else if (main == 1) {
-          q = p + 1 + ((N + 7) >> 3);
-          ok = q <= end && difflist_end(q, end, N, true, lane, &q, nullptr);
-        } else if (main != 5) {
-          ok = difflist_end(q, end, N, true, lane, &q, nullptr);
-        }
-        ok = ok && q <= end;
-        if (ok) {
-          Planes c = {0u, 0u, 0u};
-          planes_2bit<32, 2, false>(row, N, lane, c);
-          const uint32_t het = group_sum<32>(c.e) - group_sum<32>(c.b);
-          const uint32_t first = 1 + (het >> 3);
-          ok = static_cast<uint64_t>(end - q) >= first;
-          if (ok) {
-            aux2 = q;
-            explicit_pp = q[0] & 1u;
-            if (explicit_pp) {
-              uint32_t pc = popcount_bits<32>(q, het + 1, nullptr, 0, lane);
-              pc = group_sum<32>(pc) - 1;  // minus the flag bit itself
-              second = q + first;
-              ok = static_cast<uint64_t>(end - second) >= ((pc + 7) >> 3);
-            }
+    auto word_at = [&](uint32_t w) -> uint32_t {
+      uint32_t x = load_bits32(row, static_cast<uint64_t>(w) << 5);
+      const uint32_t valid = N - (w << 4);
+      if (valid < 16) x &= (1u << (2 * valid)) - 1u;
+      return x;
+    };
+    // ---- hets of my part; warp 0 also finds the end of the main track ----
+    uint32_t my_het = 0;
+    for (uint32_t w = wbeg + lane; w < wend; w += 32) {
+      const uint32_t x = word_at(w);
+      my_het += __popc(x & ~(x >> 1) & kM5);
+    }
+    my_het = group_sum<32>(my_het);
+    if (lane == 0) sm_het[wid] = my_het;
+    if (wid == 0) {
+      int bad = 0;
+      const uint8_t* q = nullptr;
+      if (vrtype & 0x10u) {
+        if (vrtype & 0x08u) {
+          bad = kErrNotSupported;  // multiallelic patch sets precede aux2; "next" row f4
+        } else {
+          const uint32_t main = vrtype & 7u;
+          q = p;
+          bool ok = true;
+          if (main == 0) {
+            q = p + ((N + 3) >> 2);
+          } else if (main == 1) {
+            q = p + 1 + ((N + 7) >> 3);
+            ok = q <= end && difflist_end(q, end, N, true, lane, &q, nullptr);
+          } else if (main != 5) {
+            ok = difflist_end(q, end, N, true, lane, &q, nullptr);
+          }
+          if (!ok || q > end) {
+            bad = kErrMalformed;
+            q = nullptr;
           }
         }
-        if (!ok) bad = kErrMalformed;
+      }
+      if (lane == 0) {
+        sm_q = q;
+        sm_bad = bad;
+      }
+    }
+    __syncthreads();
+    uint32_t het_total = 0, het_base = 0;
+#pragma unroll
+    for (int j = 0; j < kWarps; ++j) {
+      het_total += sm_het[j];
+      if (j < wid) het_base += sm_het[j];
+    }
+    const uint8_t* aux2 = sm_q;  // bit 0 = explicit flag, bits 1.. = flags or phaseinfo
+    const uint8_t* second = nullptr;
+    bool explicit_pp = false;
+    int bad = sm_bad;
+    uint32_t flag_base = 0;
+    if (aux2) {
+      const uint32_t first = 1 + (het_total >> 3);
+      if (static_cast<uint64_t>(end - aux2) < first) {
+        bad = kErrMalformed;
+      } else {
+        explicit_pp = aux2[0] & 1u;
+        if (explicit_pp) {
+          second = aux2 + first;
+          uint32_t pc = popcount_bits<32>(aux2, het_total + 1, nullptr, 0, lane);
+          pc = group_sum<32>(pc) - 1;  // flags in total (minus the form bit itself)
+          if (static_cast<uint64_t>(end - second) < ((pc + 7) >> 3)) bad = kErrMalformed;
+          uint32_t before = popcount_bits<32>(aux2, het_base + 1, nullptr, 0, lane);
+          flag_base = group_sum<32>(before) - 1;
+        }
       }
     }
     if (bad) {
-      if (lane == 0) report_error(err, bad, v);
+      if (wid == 0 && lane == 0) report_error(err, bad, v);
       aux2 = nullptr;
+      explicit_pp = false;
     }
-    // ---- expand ----
+    // ---- expand my part ----
     int8_t* orow = out + static_cast<uint64_t>(r) * out_stride_pairs * 2;
     const bool vec_ok = (reinterpret_cast<uintptr_t>(orow) & 15u) == 0;
-    uint32_t het_base = 0, flag_base = 0;
-    for (uint32_t w0 = 0; w0 < nwords; w0 += 32) {
+    for (uint32_t w0 = wbeg; w0 < wend; w0 += 32) {
       const uint32_t w = w0 + lane;
-      uint32_t x = 0;
-      if (w < nwords) {
-        x = load_bits32(row, static_cast<uint64_t>(w) << 5);
-        const uint32_t valid = N - (w << 4);
-        if (valid < 16) x &= (1u << (2 * valid)) - 1u;
-      }
+      const uint32_t x = w < wend ? word_at(w) : 0u;
       const uint32_t hm = x & ~(x >> 1) & kM5;  // hets, one bit per sample at even positions
       const uint32_t cnt = __popc(hm);
       uint32_t tot_h = 0, tot_f = 0;
       const uint32_t hoff = het_base + warp_excl_scan(cnt, lane, &tot_h);
-      uint32_t bits = 0;    // this lane's aux2 bits, bit j = het hoff + j
+      uint32_t bits = 0;  // this lane's aux2 bits, bit j = het hoff + j
       uint32_t nflag = 0;
       if (aux2 && cnt) {
-        bits = load_bits32(aux2, 1ull + hoff) & ((cnt >= 32 ? 0u : (1u << cnt)) - 1u);
+        bits = load_bits32(aux2, 1ull + hoff) & ((1u << cnt) - 1u);
         nflag = explicit_pp ? __popc(bits) : 0u;
       }
-      uint32_t foff = 0;
-      if (explicit_pp) foff = flag_base + warp_excl_scan(nflag, lane, &tot_f);
       uint32_t info = bits;  // all-phased form: the bits ARE the phaseinfo
       if (explicit_pp) {
+        const uint32_t foff = flag_base + warp_excl_scan(nflag, lane, &tot_f);
         // spread the packed phaseinfo bits of the flagged hets back to het positions
         const uint32_t packed = nflag ? load_bits32(second, foff) : 0u;
         info = 0;
         uint32_t k = 0;
         for (uint32_t f = bits; f; f &= f - 1) {
-          const uint32_t j = __ffs(f) - 1;
-          info |= ((packed >> k) & 1u) << j;
+          info |= ((packed >> k) & 1u) << (__ffs(f) - 1);
           ++k;
         }
       }
-      if (w < nwords) {
+      if (w < wend) {
         // 16 samples -> 16 pairs (32 bytes)
         uint32_t o[8];
         uint32_t hj = 0;
@@ -470,6 +502,7 @@ k_expand_phased(RecIndex ix, DenseRows rows, const uint32_t* __restrict__ vlist,
       het_base += tot_h;
       flag_base += tot_f;
     }
+    __syncthreads();  // sm_het / sm_q are rewritten for the next row
   }
 }
 
@@ -518,7 +551,7 @@ void launch_expand_phased(const RecIndex& ix, const DenseRows& rows, const uint3
                           const uint32_t* subset_idx, uint32_t n_out, int8_t* raw_scratch, int8_t* out, int* err,
                           cudaStream_t s, LaunchStats* st) {
   if (!rows.nrows || !n_out) return;
-  uint64_t blocks = (static_cast<uint64_t>(rows.nrows) * 32 + kThreads - 1) / kThreads;
+  uint64_t blocks = rows.nrows;  // one CTA per row
   if (blocks > 148ull * 16) blocks = 148ull * 16;
   if (!subset_idx) {
     k_expand_phased<<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, rows, vlist, v0, ix.N, out, err);
