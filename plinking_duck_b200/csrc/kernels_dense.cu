@@ -7,9 +7,7 @@
 //     LD cache (LdLoadAndCopyGenovecSubset :2808-2838): k_densify
 //   * GenoarrToBytesMinus9 (pgenlib_ffi_support.cc:25-43) + CopyNyparrNonemptySubset: k_expand_i8
 //   * PgrGetMissingness + the ctz walk (src/plink_missing.cpp:593-609) and the dense Phase-1
-//     loop of src/pfile_reader.cpp:3322-3428: k_sample_acc
-#include <cstdlib>
-#include <cstring>
+//     loop of src/pfile_reader.cpp:3322-3428: k_sample_acc_v
 #include <type_traits>
 
 #include "device_common.cuh"
@@ -177,60 +175,6 @@ k_expand_i8(DenseRows rows, const uint32_t* __restrict__ subset_idx, uint32_t n_
   }
 }
 
-// ---------------------------------------------------------------------------------------------
-// k_sample_acc: transposed pass.  A thread owns one 32-bit word column (16 samples) and walks
-// the rows of its chunk; loads of a warp are 128 contiguous bytes of one record.  Per-sample
-// counters are kept bit-sliced in registers and widened 2 -> 4 -> 8 bits (3 / 15 / 255 rows of
-// headroom), so the steady state costs ~5 integer ops per flag kind per word; only every 255
-// rows (or at chunk end) the 8-bit lanes are flushed to the global uint32 accumulators.
-// ---------------------------------------------------------------------------------------------
-struct Widen {
-  uint32_t b0, b1;  // 4-bit fields: samples 2j / 2j+1
-  uint32_t c[4];    // 8-bit fields: samples 4k, 4k+2, 4k+1, 4k+3
-  __device__ __forceinline__ void clear() {
-    b0 = b1 = 0;
-    c[0] = c[1] = c[2] = c[3] = 0;
-  }
-  __device__ __forceinline__ void add_a(uint32_t a) {  // a: 2-bit fields, each <= 3
-    b0 += a & 0x33333333u;
-    b1 += (a >> 2) & 0x33333333u;
-  }
-  __device__ __forceinline__ void b_to_c() {
-    c[0] += b0 & 0x0F0F0F0Fu;
-    c[1] += (b0 >> 4) & 0x0F0F0F0Fu;
-    c[2] += b1 & 0x0F0F0F0Fu;
-    c[3] += (b1 >> 4) & 0x0F0F0F0Fu;
-    b0 = b1 = 0;
-  }
-  __device__ __forceinline__ void flush(uint32_t* __restrict__ acc, uint32_t s0, uint32_t N) {
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const uint32_t x = c[q];
-      if (x) {
-        const uint32_t off = (q == 0) ? 0u : (q == 1) ? 2u : (q == 2) ? 1u : 3u;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const uint32_t val = (x >> (8 * k)) & 0xffu;
-          const uint32_t s = s0 + 4u * k + off;
-          if (val && s < N) atomicAdd(acc + s, val);
-        }
-      }
-      c[q] = 0;
-    }
-  }
-};
-
-// Bit planes of one word: E (low bits), O (high bits), B = E & O.  The accumulators count planes,
-// not categories: het = E - B, hom_alt = O - B, missing = B are formed once per sample at the end
-// (k_planes_to_counts), which saves two logic ops per word in the streaming loop.
-template <int KINDS>
-__device__ __forceinline__ void acc_flags(uint32_t x, uint32_t& pe, uint32_t& po, uint32_t& pb) {
-  const uint32_t e = x & kM5, o = (x >> 1) & kM5;
-  if (KINDS & 1) pe += e;
-  if (KINDS & 2) po += o;
-  if (KINDS & 4) pb += e & o;
-}
-
 // VEC consecutive 32-bit words (16 samples each) of a row starting at word w0.  ALIGNED (decided
 // on the host for the whole launch): one vector load.  Otherwise VEC + 1 aligned words
 // funnel-shifted into place.  Either way straight-line code, so the loads of several rows can be
@@ -259,133 +203,9 @@ __device__ __forceinline__ void load_words(const uint8_t* row, uint32_t w0, uint
   }
 }
 
-// MODE 0: rows at base + r * stride, vector-aligned; 1: same, any alignment; 2: row pointer table.
-template <int KINDS, int VEC, int MODE>
-__global__ void __launch_bounds__(128)
-k_sample_acc(DenseRows rows, uint32_t rows_per_chunk, uint32_t* __restrict__ acc_het, uint32_t* __restrict__ acc_hom,
-             uint32_t* __restrict__ acc_mis) {
-  constexpr int UNROLL = 6;  // two groups of three rows: the 2-bit stage holds three rows
-  const uint32_t N = rows.N;
-  const uint32_t ncols = (N + 15) >> 4;
-  const uint32_t w0 = (blockIdx.x * blockDim.x + threadIdx.x) * VEC;
-  if (w0 >= ncols) return;
-  uint32_t nrows = rows.nrows;
-  if (rows.nrows_dev) {  // packed rows of a sparse batch: spread what there is over the chunks of the grid
-    nrows = min(nrows, __ldg(rows.nrows_dev));
-    rows_per_chunk = ((nrows + gridDim.y - 1) / gridDim.y + UNROLL - 1) / UNROLL * UNROLL;
-    if (rows_per_chunk < 4 * UNROLL) rows_per_chunk = 4 * UNROLL;
-  }
-  const uint32_t r0 = blockIdx.y * rows_per_chunk;
-  if (r0 >= nrows) return;
-  const uint32_t r1 = min(nrows, r0 + rows_per_chunk);
-  Widen het[VEC], hom[VEC], mis[VEC];
-#pragma unroll
-  for (int k = 0; k < VEC; ++k) {
-    het[k].clear();
-    hom[k].clear();
-    mis[k].clear();
-  }
-  uint32_t nb = 0, nc = 0;
-  auto flush_all = [&]() {
-#pragma unroll
-    for (int k = 0; k < VEC; ++k) {
-      if (KINDS & 1) het[k].flush(acc_het, 16u * (w0 + k), N);
-      if (KINDS & 2) hom[k].flush(acc_hom, 16u * (w0 + k), N);
-      if (KINDS & 4) mis[k].flush(acc_mis, 16u * (w0 + k), N);
-    }
-  };
-  auto b_to_c_all = [&]() {
-#pragma unroll
-    for (int k = 0; k < VEC; ++k) {
-      if (KINDS & 1) het[k].b_to_c();
-      if (KINDS & 2) hom[k].b_to_c();
-      if (KINDS & 4) mis[k].b_to_c();
-    }
-  };
-  auto step_b = [&]() {
-    if (++nb == 5) {
-      nb = 0;
-      b_to_c_all();
-      if (++nc == 17) {
-        nc = 0;
-        flush_all();
-      }
-    }
-  };
-  // Software pipeline: the loads of the next UNROLL rows are issued before the current rows are
-  // consumed, so every warp always has a batch in flight.
-  auto load_batch = [&](uint32_t rr, uint32_t (&x)[UNROLL][VEC]) {
-    const uint8_t* rp[UNROLL];
-#pragma unroll
-    for (int j = 0; j < UNROLL; ++j) {
-      rp[j] = (MODE == 2) ? rows.ptrs[rr + j] : rows.base + static_cast<uint64_t>(rr + j) * rows.stride;
-    }
-#pragma unroll
-    for (int j = 0; j < UNROLL; ++j) load_words<VEC, MODE == 0>(rp[j], w0, x[j]);
-  };
-  auto consume = [&](uint32_t (&x)[UNROLL][VEC]) {
-#pragma unroll
-    for (int t = 0; t < UNROLL / 3; ++t) {
-#pragma unroll
-      for (int k = 0; k < VEC; ++k) {
-        uint32_t a_het = 0, a_hom = 0, a_mis = 0;
-#pragma unroll
-        for (int j = 0; j < 3; ++j) acc_flags<KINDS>(x[3 * t + j][k], a_het, a_hom, a_mis);
-        if (KINDS & 1) het[k].add_a(a_het);
-        if (KINDS & 2) hom[k].add_a(a_hom);
-        if (KINDS & 4) mis[k].add_a(a_mis);
-      }
-      step_b();
-    }
-  };
-  uint32_t r = r0;
-  if (r + UNROLL <= r1) {
-    uint32_t xa[UNROLL][VEC], xb[UNROLL][VEC];
-    load_batch(r, xa);
-    for (;;) {
-      if (r + 2 * UNROLL > r1) {
-        consume(xa);
-        r += UNROLL;
-        break;
-      }
-      load_batch(r + UNROLL, xb);
-      consume(xa);
-      r += UNROLL;
-      if (r + 2 * UNROLL > r1) {
-        consume(xb);
-        r += UNROLL;
-        break;
-      }
-      load_batch(r + UNROLL, xa);
-      consume(xb);
-      r += UNROLL;
-    }
-  }
-  while (r < r1) {
-    uint32_t a_het[VEC], a_hom[VEC], a_mis[VEC];
-#pragma unroll
-    for (int k = 0; k < VEC; ++k) a_het[k] = a_hom[k] = a_mis[k] = 0;
-    for (int j = 0; j < 3 && r < r1; ++j, ++r) {
-      uint32_t x[VEC];
-      load_words<VEC, MODE == 0>(row_ptr(rows, r), w0, x);
-#pragma unroll
-      for (int k = 0; k < VEC; ++k) acc_flags<KINDS>(x[k], a_het[k], a_hom[k], a_mis[k]);
-    }
-#pragma unroll
-    for (int k = 0; k < VEC; ++k) {
-      if (KINDS & 1) het[k].add_a(a_het[k]);
-      if (KINDS & 2) hom[k].add_a(a_hom[k]);
-      if (KINDS & 4) mis[k].add_a(a_mis[k]);
-    }
-    step_b();
-  }
-  b_to_c_all();
-  flush_all();
-}
-
 // ---------------------------------------------------------------------------------------------
-// k_sample_acc_v: the same transposed pass with VERTICAL counters and no global atomics in the
-// steady state.  A thread owns 2 consecutive 32-bit words of a record (32 samples).  The E / O / B
+// k_sample_acc_v: transposed pass with VERTICAL counters and no global atomics in the steady
+// state.  A thread owns 2 consecutive 32-bit words of a record (32 samples).  The E / O / B
 // planes of the two words are interleaved into full 32-bit words (bit 2j = sample j of word 0,
 // bit 2j+1 = sample j of word 1), so every bit of a register is a sample, and rows are added with
 // carry-save adders (Harley-Seal, 16 rows per block): 15 CSAs (two LOP3 each: majority and 3-input
@@ -393,8 +213,9 @@ k_sample_acc(DenseRows rows, uint32_t rows_per_chunk, uint32_t* __restrict__ acc
 // and plane.  Eight bit planes hold up to 255 rows; every 240 rows they are turned into per-sample
 // bytes (nibble * 0x00204081 spreads 4 bits into 4 bytes) and added to thread-private 16-bit
 // counters in shared memory; only at the end of the chunk (<= 65535 rows) each sample costs one
-// atomicAdd.  (The byte-counter kernel above flushes to global memory every 255 rows: at 100k samples
-// that is 0.4 atomics per record byte, which -- not the arithmetic -- is what bounded it.)
+// atomicAdd.  (The first version kept widening 2/4/8-bit counters and flushed them to global memory every
+// 255 rows: at 100k samples that is 0.4 atomics per record byte, which -- not the arithmetic -- bounded it
+// at 0.63 / 0.37 of the HBM peak; profiles/r01c_kernel_table_200kx100k.jsonl.)
 // The row pointer is carried, not recomputed, and full 16-row blocks run without bounds checks:
 // the loop is bound by the integer pipe, so every instruction per row counts.
 // MODE 0: rows 8-byte aligned (one 64-bit load); 1: 4-byte aligned (fixed-width files: records start
@@ -710,56 +531,35 @@ void launch_expand_i8(const DenseRows& rows, const uint32_t* subset_idx, uint32_
 void launch_sample_acc(const DenseRows& rows, uint32_t kinds, uint32_t* acc_het, uint32_t* acc_hom, uint32_t* acc_mis,
                        cudaStream_t s, LaunchStats* st) {
   if (!rows.nrows || !rows.N) return;
-  static const bool byte_counters = [] {
-    const char* e = getenv("PD_SAMPLE_ACC");  // "bytes": the widening byte-counter kernel, for A/B runs
-    return e && !strcmp(e, "bytes");
-  }();
   const uint32_t ncols = (rows.N + 15) >> 4;
-  const uint32_t vec = byte_counters ? ((kinds == 4) ? 4 : 2) : 2;  // 32-bit words of a record per thread
-  const uint32_t nthreads = (ncols + vec - 1) / vec;
+  const uint32_t nthreads = (ncols + 1) / 2;  // two 32-bit words of a record per thread
   const uint32_t bx = (nthreads + 127) / 128;
-  // aim at ~12 (byte counters) / 6 (vertical counters: one wave at their occupancy, and every chunk ends
-  // with one atomic per sample) CTAs of 128 threads per SM, but keep >= 240 rows per chunk when rows allow
-  // (vertical counters: rounded DOWN so that the grid is one resident wave -- a 7th CTA on a few SMs would
-  // double the kernel time)
-  uint32_t want_y = byte_counters ? (static_cast<uint32_t>(sm_count()) * 12 + bx - 1) / bx
-                                  : static_cast<uint32_t>(sm_count()) * 6 / bx;
+  // 6 CTAs of 128 threads fit an SM (80 registers, 24 KB of counters): the grid is exactly one resident
+  // wave -- rounded DOWN, a 7th CTA on a few SMs would double the kernel time -- and every chunk ends with
+  // one atomic per sample, so chunks are as long as that allows (>= 240 rows when rows allow).
+  uint32_t want_y = static_cast<uint32_t>(sm_count()) * 6 / bx;
   if (want_y < 1) want_y = 1;
   uint32_t rpc = (rows.nrows + want_y - 1) / want_y;
   if (rpc < 240) rpc = 240;
-  rpc = (rpc + 47) / 48 * 48;
+  rpc = (rpc + 15) / 16 * 16;
   const uint32_t by = (rows.nrows + rpc - 1) / rpc;
   dim3 grid(bx, by);
   const uintptr_t addr_bits = reinterpret_cast<uintptr_t>(rows.base) | static_cast<uintptr_t>(rows.stride);
-  if (st) st->launches++;
-  if (!byte_counters) {
-    const int mode = rows.ptrs ? 2 : (addr_bits % 8 == 0 ? 0 : (addr_bits % 4 == 0 ? 1 : 3));
+  const int mode = rows.ptrs ? 2 : (addr_bits % 8 == 0 ? 0 : (addr_bits % 4 == 0 ? 1 : 3));
 #define PD_LAUNCH_V(K, M) k_sample_acc_v<K, M><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis)
-    if (kinds == 4) {
-      if (mode == 0) PD_LAUNCH_V(4, 0);
-      else if (mode == 1) PD_LAUNCH_V(4, 1);
-      else if (mode == 2) PD_LAUNCH_V(4, 2);
-      else PD_LAUNCH_V(4, 3);
-    } else {
-      if (mode == 0) PD_LAUNCH_V(7, 0);
-      else if (mode == 1) PD_LAUNCH_V(7, 1);
-      else if (mode == 2) PD_LAUNCH_V(7, 2);
-      else PD_LAUNCH_V(7, 3);
-    }
-#undef PD_LAUNCH_V
-    return;
-  }
-  const uint32_t align = 4 * vec;
-  const int mode = rows.ptrs ? 2 : (addr_bits % align == 0 ? 0 : 1);
   if (kinds == 4) {
-    if (mode == 0) k_sample_acc<4, 4, 0><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
-    else if (mode == 1) k_sample_acc<4, 4, 1><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
-    else k_sample_acc<4, 4, 2><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
+    if (mode == 0) PD_LAUNCH_V(4, 0);
+    else if (mode == 1) PD_LAUNCH_V(4, 1);
+    else if (mode == 2) PD_LAUNCH_V(4, 2);
+    else PD_LAUNCH_V(4, 3);
   } else {
-    if (mode == 0) k_sample_acc<7, 2, 0><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
-    else if (mode == 1) k_sample_acc<7, 2, 1><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
-    else k_sample_acc<7, 2, 2><<<grid, 128, 0, s>>>(rows, rpc, acc_het, acc_hom, acc_mis);
+    if (mode == 0) PD_LAUNCH_V(7, 0);
+    else if (mode == 1) PD_LAUNCH_V(7, 1);
+    else if (mode == 2) PD_LAUNCH_V(7, 2);
+    else PD_LAUNCH_V(7, 3);
   }
+#undef PD_LAUNCH_V
+  if (st) st->launches++;
 }
 
 void launch_count_rows(const DenseRows& rows, const SubsetDev& sub, uint4* out, cudaStream_t s, LaunchStats* st) {
