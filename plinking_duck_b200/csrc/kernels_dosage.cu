@@ -231,83 +231,137 @@ k_dosage_scatter(DenseRows rows, const DosageLoc* __restrict__ loc, SubsetDev su
 }
 
 // ---------------------------------------------------------------------------------------------
-// k_dosage_stats: one warp per row -> integer sums over the (subset) samples that carry a
-// dosage: count, sum u16, sum u16^2 and the hardcall categories they replace.
+// k_dosage_stats: one CTA (8 warps) per row -> integer sums over the (subset) samples that carry a
+// dosage: count, sum u16, sum u16^2 and the hardcall categories they replace.  The sample range of
+// the unconditional (one u16 per sample) and bitarray forms is split over the warps; a lane of the
+// unconditional form takes 16 consecutive samples per step -- one word of the dense row and nine
+// aligned words holding their 16 values (the value track starts at any byte).  The list form is
+// short (<= N/8 entries) and stays on warp 0.  Warp partial sums meet in shared memory.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads)
 k_dosage_stats(DenseRows rows, const DosageLoc* __restrict__ loc, const uint32_t* __restrict__ rank,
                uint32_t rank_stride, SubsetDev sub, uint32_t n_out, DosageStats* __restrict__ stats) {
-  const uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  constexpr int kWarps = kThreads / 32;
+  __shared__ unsigned long long sm_sum[kWarps], sm_sq[kWarps];
+  __shared__ uint32_t sm_ct[kWarps][5];
   const int lane = threadIdx.x & 31;
-  if (r >= rows.nrows) return;
-  const DosageLoc L = loc[r];
-  const uint8_t* row = row_ptr(rows, r);
+  const int wid = threadIdx.x >> 5;
   const uint32_t N = rows.N;
-  unsigned long long sum = 0, sumsq = 0;
-  uint32_t ct = 0, r0 = 0, r1 = 0, r2 = 0, r3 = 0;
-  auto take = [&](uint32_t id, uint32_t u) {
-    sum += u;
-    sumsq += static_cast<unsigned long long>(u) * u;
-    ++ct;
-    const uint32_t g = geno_at(row, id);
-    r0 += (g == 0);
-    r1 += (g == 1);
-    r2 += (g == 2);
-    r3 += (g == 3);
-  };
-  if (L.kind == 1 && L.raw_ct) {
-    const uint8_t* q = L.track3;
-    Difflist d;
-    if (parse_difflist(q, L.values, N, false, d)) {
-      difflist_walk(d, N, lane, [&](uint32_t id, uint32_t, uint32_t k) {
-        uint32_t pos;
-        if (subset_pos(sub, id, pos)) take(id, ld_u16(L.values, k));
-      });
-    }
-  } else if (L.kind == 2) {
-    for (uint32_t j = lane; j < n_out; j += 32) {
-      const uint32_t raw = sub.subset_idx ? sub.subset_idx[j] : j;
-      const uint32_t u = ld_u16(L.values, raw);
-      if (u != 65535u) take(raw, u);
-    }
-  } else if (L.kind == 3) {
-    const uint32_t nw = (N + 31) >> 5;
-    const uint32_t* rk = rank + static_cast<uint64_t>(r) * rank_stride;
-    for (uint32_t w = lane; w < nw; w += 32) {
-      uint32_t all = load_bits32(L.track3, static_cast<uint64_t>(w) << 5);
-      const uint32_t valid = min(32u, N - 32u * w);
-      if (valid < 32) all &= (1u << valid) - 1u;
-      uint32_t bits = sub.include_words ? (all & sub.include_words[w]) : all;
-      const uint32_t base = rk[w];
-      while (bits) {
-        const uint32_t b = __ffs(bits) - 1;
-        take(32u * w + b, ld_u16(L.values, base + __popc(all & ((1u << b) - 1u))));
-        bits &= bits - 1;
+  for (uint32_t r = blockIdx.x; r < rows.nrows; r += gridDim.x) {
+    const DosageLoc L = loc[r];
+    const uint8_t* row = row_ptr(rows, r);
+    unsigned long long sum = 0, sumsq = 0;
+    uint32_t ct = 0, r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+    auto take = [&](uint32_t g, uint32_t u) {
+      sum += u;
+      sumsq += static_cast<unsigned long long>(u) * u;
+      ++ct;
+      r0 += (g == 0);
+      r1 += (g == 1);
+      r2 += (g == 2);
+      r3 += (g == 3);
+    };
+    if (L.kind == 1 && L.raw_ct) {
+      if (wid == 0) {
+        const uint8_t* q = L.track3;
+        Difflist d;
+        if (parse_difflist(q, L.values, N, false, d)) {
+          difflist_walk(d, N, lane, [&](uint32_t id, uint32_t, uint32_t k) {
+            uint32_t pos;
+            if (subset_pos(sub, id, pos)) take(geno_at(row, id), ld_u16(L.values, k));
+          });
+        }
+      }
+    } else if (L.kind == 2) {
+      if (!sub.subset_idx) {
+        const uint32_t nblk = (N + 15) >> 4;  // blocks of 16 samples
+        for (uint32_t blk = threadIdx.x; blk < nblk; blk += kThreads) {
+          const uint32_t x = load_bits32(row, static_cast<uint64_t>(blk) << 5);
+          const uintptr_t a = reinterpret_cast<uintptr_t>(L.values) + 32ull * blk;
+          const uint32_t* wp = reinterpret_cast<const uint32_t*>(a & ~static_cast<uintptr_t>(3));
+          const uint32_t sh = static_cast<uint32_t>(a & 3) << 3;
+          const uint32_t nval = min(16u, N - (blk << 4));
+          const uint32_t nwords = (2 * nval + (static_cast<uint32_t>(a & 3)) + 3) >> 2;  // words that hold them
+          uint32_t t[9];
+#pragma unroll
+          for (int k = 0; k < 9; ++k) t[k] = static_cast<uint32_t>(k) < nwords ? __ldg(wp + k) : 0u;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const uint32_t two = __funnelshift_r(t[k], t[k + 1], sh);
+            if (2u * k < nval) {
+              const uint32_t u = two & 0xffffu;
+              if (u != 65535u) take((x >> (4 * k)) & 3u, u);
+            }
+            if (2u * k + 1 < nval) {
+              const uint32_t u = two >> 16;
+              if (u != 65535u) take((x >> (4 * k + 2)) & 3u, u);
+            }
+          }
+        }
+      } else {
+        for (uint32_t j = threadIdx.x; j < n_out; j += kThreads) {
+          const uint32_t raw = sub.subset_idx[j];
+          const uint32_t u = ld_u16(L.values, raw);
+          if (u != 65535u) take(geno_at(row, raw), u);
+        }
+      }
+    } else if (L.kind == 3) {
+      const uint32_t nw = (N + 31) >> 5;
+      const uint32_t* rk = rank + static_cast<uint64_t>(r) * rank_stride;
+      for (uint32_t w = threadIdx.x; w < nw; w += kThreads) {
+        uint32_t all = load_bits32(L.track3, static_cast<uint64_t>(w) << 5);
+        const uint32_t valid = min(32u, N - 32u * w);
+        if (valid < 32) all &= (1u << valid) - 1u;
+        uint32_t bits = sub.include_words ? (all & sub.include_words[w]) : all;
+        const uint32_t base = rk[w];
+        // the 32 samples of this word are two words of the dense row
+        const uint32_t xlo = load_bits32(row, static_cast<uint64_t>(w) << 6);
+        const uint32_t xhi = load_bits32(row, (static_cast<uint64_t>(w) << 6) + 32);
+        while (bits) {
+          const uint32_t b = __ffs(bits) - 1;
+          const uint32_t g = b < 16 ? (xlo >> (2 * b)) & 3u : (xhi >> (2 * (b - 16))) & 3u;
+          take(g, ld_u16(L.values, base + __popc(all & ((1u << b) - 1u))));
+          bits &= bits - 1;
+        }
       }
     }
-  }
 #pragma unroll
-  for (int off = 16; off > 0; off >>= 1) {
-    sum += __shfl_xor_sync(0xffffffffu, sum, off);
-    sumsq += __shfl_xor_sync(0xffffffffu, sumsq, off);
-  }
-  ct = group_sum<32>(ct);
-  r0 = group_sum<32>(r0);
-  r1 = group_sum<32>(r1);
-  r2 = group_sum<32>(r2);
-  r3 = group_sum<32>(r3);
-  if (lane == 0) {
-    DosageStats s;
-    s.sum = sum;
-    s.sumsq = sumsq;
-    s.ct = ct;
-    s.replaced[0] = r0;
-    s.replaced[1] = r1;
-    s.replaced[2] = r2;
-    s.replaced[3] = r3;
-    s.kind = L.kind;
-    s.pad = 0;
-    stats[r] = s;
+    for (int off = 16; off > 0; off >>= 1) {
+      sum += __shfl_xor_sync(0xffffffffu, sum, off);
+      sumsq += __shfl_xor_sync(0xffffffffu, sumsq, off);
+    }
+    ct = group_sum<32>(ct);
+    r0 = group_sum<32>(r0);
+    r1 = group_sum<32>(r1);
+    r2 = group_sum<32>(r2);
+    r3 = group_sum<32>(r3);
+    if (lane == 0) {
+      sm_sum[wid] = sum;
+      sm_sq[wid] = sumsq;
+      sm_ct[wid][0] = ct;
+      sm_ct[wid][1] = r0;
+      sm_ct[wid][2] = r1;
+      sm_ct[wid][3] = r2;
+      sm_ct[wid][4] = r3;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      DosageStats st{};
+#pragma unroll
+      for (int j = 0; j < kWarps; ++j) {
+        st.sum += sm_sum[j];
+        st.sumsq += sm_sq[j];
+        st.ct += sm_ct[j][0];
+        st.replaced[0] += sm_ct[j][1];
+        st.replaced[1] += sm_ct[j][2];
+        st.replaced[2] += sm_ct[j][3];
+        st.replaced[3] += sm_ct[j][4];
+      }
+      st.kind = L.kind;
+      st.pad = 0;
+      stats[r] = st;
+    }
+    __syncthreads();
   }
 }
 
@@ -542,7 +596,7 @@ void launch_dosage_fill(const DenseRows& rows, const DosageLoc* loc, const uint3
 void launch_dosage_stats(const DenseRows& rows, const DosageLoc* loc, const uint32_t* rank, uint32_t rank_stride,
                          const SubsetDev& sub, uint32_t n_out, DosageStats* stats, cudaStream_t s, LaunchStats* st) {
   if (!rows.nrows) return;
-  const uint32_t blocks = (rows.nrows * 32 + kThreads - 1) / kThreads;
+  const uint32_t blocks = rows.nrows < 148u * 16 ? rows.nrows : 148u * 16;  // one CTA per row
   k_dosage_stats<<<blocks, kThreads, 0, s>>>(rows, loc, rank, rank_stride, sub, n_out, stats);
   if (st) st->launches++;
 }
