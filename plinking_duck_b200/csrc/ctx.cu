@@ -398,7 +398,11 @@ uint32_t DenseSlotStride(const pd_ctx_impl* c) { return ((c->idx.sample_ct + 3) 
 
 namespace {
 
-constexpr uint64_t kDenseScratchBytes = 64ull << 20;  // decoded rows of one batch: stays L2-resident
+// Decoded rows of one batch.  Measured on 2.5 KB difflist records (profiles/r01d_ncu_k_densify.txt): the
+// expansion is latency-bound per row (one warp walks one record), so what matters is rows in flight -- with
+// 64 MiB (L2-resident, 2.7k rows at 100k samples) the GPU ran 18 warps per SM; 1 GiB gives every SM a full
+// complement and cuts the per-batch fixed costs of the consumers (plink_score finishes once per batch).
+constexpr uint64_t kDenseScratchBytes = 1024ull << 20;
 constexpr uint32_t kMaxBatchRows = 65535;  // also the gridDim.y limit
 
 uint32_t ClampBatchRows(const pd_ctx_impl* c, uint32_t max_rows) {
@@ -428,7 +432,8 @@ struct TileBytesGuard {
 
 int RunRows(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t max_rows, uint64_t min_tile_bytes,
             const RowFn& fn) {
-  const uint32_t cap = ClampBatchRows(c, max_rows);
+  // never reserve scratch for more rows than the range holds (a 1 GiB batch for a 100-variant file)
+  const uint32_t cap = std::min(ClampBatchRows(c, max_rows), std::max(1u, v_end > v_begin ? v_end - v_begin : 1u));
   const bool fixed = c->idx.fixed;
   int rc = ReserveDense(c, cap, !fixed);
   if (rc != PD_OK) return rc;
