@@ -148,6 +148,16 @@ int pd_sample_counts(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t* ou
  *      row-major, values {0,1,2,-9}. ---- */
 int pd_decode_i8(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, int8_t* out);
 
+/* ---- genotype column in DuckDB's child-vector layout: replaces PgrGet + GenoarrToBytesMinus9 AND the fill
+ *      loop that follows it (src/pgen_reader.cpp:1008-1046: ARRAY(TINYINT, N) / LIST(TINYINT) child data +
+ *      validity).  out[(v - v_begin) * n + s] = the call where it is valid, 0 where it is not; bit
+ *      ((v - v_begin) * n + s) of validity (64-bit words, LSB first, as duckdb::ValidityMask) = 1 where
+ *      valid.  A call is valid when it is not missing and call_mask has bit g set for its category g in
+ *      {0,1,2} (GenotypeFilter::AllowsCall, src/include/plink_common.hpp:471-477; 7 = no genotype filter).
+ *      validity holds ceil(rows * n / 64) words and is written whole (bits past the last call are 0). ---- */
+int pd_decode_i8_valid(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t call_mask, int8_t* out,
+                       uint64_t* validity);
+
 /* ---- phased hardcalls : replaces PgrGetP + UnpackPhasedGenotypes (src/plink_common.cpp:1549-1584; call
  *      sites src/pgen_reader.cpp:705-733, src/pfile_reader.cpp:1722-1745, read_pgen / read_pfile with
  *      phased := true).  out: (v_end - v_begin) x n_out x 2 int8 allele pairs in subset order:

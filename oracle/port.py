@@ -124,3 +124,38 @@ class PortPgen:
         self._chk(lib().po_score(self._h, _p(vidx), _p(fl) if fl is not None else None, _p(w), vidx.size, mode,
                                  _p(s), _p(d), _p(a)))
         return s, d, a
+
+
+def child_vector_layout(i8: np.ndarray, allowed=(True, True, True)):
+    """The unphased genotype-column fill loop of the reference (src/pgen_reader.cpp:1008-1025 for
+    ARRAY(TINYINT, N), :1026-1046 for LIST(TINYINT)), restated on a decoded (rows x samples) int8 matrix:
+    a call is invalid when it is -9 or when GenotypeFilter::AllowsCall (src/include/plink_common.hpp:471-477)
+    rejects its category; child_data is 0 there and the call otherwise; child_validity bit (row * N + s)
+    is set where valid (duckdb::ValidityMask: 64-bit words, LSB first).  Returns (data, validity words)."""
+    g = np.asarray(i8, dtype=np.int8)
+    ok = np.zeros(g.shape, dtype=bool)
+    for cat in (0, 1, 2):
+        if allowed[cat]:
+            ok |= g == cat
+    data = np.where(ok, g, 0).astype(np.int8)
+    bits = np.packbits(ok.reshape(-1), bitorder="little")
+    words = np.zeros(((ok.size + 63) // 64) * 8, dtype=np.uint8)
+    words[: bits.size] = bits
+    return data, words.view(np.uint64)
+
+
+def child_vector_layout_loop(i8, allowed=(True, True, True)):
+    """Element-by-element form of the same loop (small cases only): pins child_vector_layout."""
+    rows, n = len(i8), (len(i8[0]) if len(i8) else 0)
+    data = [[0] * n for _ in range(rows)]
+    words = [0] * ((rows * n + 63) // 64)
+    for r in range(rows):
+        base = r * n
+        for s in range(n):
+            geno = int(i8[r][s])
+            if geno == -9 or not (0 <= geno <= 2 and allowed[geno]):
+                data[r][s] = 0
+            else:
+                data[r][s] = geno
+                words[(base + s) >> 6] |= 1 << ((base + s) & 63)
+    return np.array(data, dtype=np.int8).reshape(rows, n), np.array(words, dtype=np.uint64)

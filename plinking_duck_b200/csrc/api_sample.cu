@@ -172,6 +172,57 @@ int pd_decode_i8(pd_ctx* c, uint32_t v_begin, uint32_t v_end, int8_t* out) {
   return rc != PD_OK ? rc : rc2;
 }
 
+int pd_decode_i8_valid(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t call_mask, int8_t* out, uint64_t* validity) {
+  if (!c || ((!out || !validity) && v_end > v_begin)) return PD_ERR_INVALID_ARG;
+  std::lock_guard<std::mutex> lock(c->mu);
+  cudaSetDevice(c->device);
+  const uint32_t n_out = c->subset.active ? c->subset.count : c->idx.sample_ct;
+  if (v_begin >= v_end || !n_out) {
+    if (v_begin > v_end || v_end > c->idx.variant_ct) return c->SetError(PD_ERR_INVALID_ARG, "variant range out of bounds");
+    return PD_OK;
+  }
+  // Per batch and buffer: up to 128 MiB of calls, then (256-byte aligned) their validity words + one word of
+  // slack.  A batch starts at any bit of the caller's bitmap: the word it shares with the batch before is
+  // carried over on the device, so every download writes whole, final 64-bit words.
+  const uint64_t kOutBytes = 128ull << 20;
+  const uint32_t max_rows = static_cast<uint32_t>(std::max<uint64_t>(1, std::min<uint64_t>(65535, kOutBytes / n_out)));
+  const size_t data_cap = (static_cast<size_t>(max_rows) * n_out + 255) & ~static_cast<size_t>(255);
+  const size_t valid_cap = (data_cap / 64 + 2) * 8;
+  OutPipe pipe;
+  int rc = pipe.Init(c, out, data_cap + valid_cap, validity);
+  if (rc != PD_OK) return rc;
+  const uint32_t* idx = c->subset.active ? c->subset.d_idx.as<uint32_t>() : nullptr;
+  const char* prev_last_word = nullptr;  // device address of the last validity word of the batch before
+  cudaEventRecord(c->ev_c0, c->stream);
+  rc = RunRows(c, v_begin, v_end, max_rows, 0, [&](const RowBatch& b, const pdk::RecIndex&, cudaStream_t s) {
+    void* dev = nullptr;
+    int slot = 0;
+    int r = pipe.Acquire(&dev, &slot);
+    if (r != PD_OK) return r;
+    const uint64_t bit0 = static_cast<uint64_t>(b.row0) * n_out, bit1 = bit0 + static_cast<uint64_t>(b.n) * n_out;
+    const uint64_t w0 = bit0 >> 6, w1 = (bit1 + 63) >> 6;
+    char* vdev = static_cast<char*>(dev) + data_cap;
+    cudaMemsetAsync(vdev, 0, (w1 - w0 + 1) * 8, s);
+    if ((bit0 & 63u) && prev_last_word) cudaMemcpyAsync(vdev, prev_last_word, 8, cudaMemcpyDeviceToDevice, s);
+    pdk::launch_expand_i8_valid(b.rows, idx, n_out, call_mask, static_cast<int8_t*>(dev), reinterpret_cast<uint32_t*>(vdev),
+                                static_cast<uint32_t>(bit0 & 63u), s, &c->launch_stats);
+    prev_last_word = vdev + (w1 - w0 - 1) * 8;
+    c->stats.scan_launches += 1;
+    return pipe.Send(slot, s, out + static_cast<size_t>(b.row0) * n_out, static_cast<size_t>(b.n) * n_out, validity + w0,
+                     data_cap, (w1 - w0) * 8);
+  });
+  const int rc2 = pipe.Finish();
+  cudaEventRecord(c->ev_c1, c->stream);
+  cudaEventSynchronize(c->ev_c1);
+  if (rc == PD_OK && rc2 == PD_OK) {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev_c0, c->ev_c1);
+    c->stats.call_ms = ms;
+    c->stats.kernel_ms = pipe.produce_ms;
+  }
+  return rc != PD_OK ? rc : rc2;
+}
+
 int pd_decode_phased(pd_ctx* c, uint32_t v_begin, uint32_t v_end, int8_t* out) {
   if (!c || (!out && v_end > v_begin)) return PD_ERR_INVALID_ARG;
   std::lock_guard<std::mutex> lock(c->mu);

@@ -109,6 +109,10 @@ void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint
 void launch_expand_phased(const RecIndex& ix, const DenseRows& rows, const uint32_t* vlist, uint32_t v0,
                           const uint32_t* subset_idx, uint32_t n_out, int8_t* raw_scratch, int8_t* out, int* err,
                           cudaStream_t s, LaunchStats* st);
+// K5v: int8 calls (0 where invalid) + validity bits in DuckDB's child-vector layout; vbits must be zero-filled
+// except for bits below bitbase in its first word (the previous batch's calls).
+void launch_expand_i8_valid(const DenseRows& rows, const uint32_t* subset_idx, uint32_t n_out, uint32_t call_mask,
+                            int8_t* out, uint32_t* vbits, uint32_t bitbase, cudaStream_t s, LaunchStats* st = nullptr);
 // out[r * n_out + j] = {0,1,2,-9} of sample subset_idx[j] (or j) -- PgrGet + GenoarrToBytesMinus9.
 void launch_expand_i8(const DenseRows& rows, const uint32_t* subset_idx, uint32_t n_out, int8_t* out, cudaStream_t s,
                       LaunchStats* st);

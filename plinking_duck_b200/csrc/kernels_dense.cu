@@ -129,8 +129,7 @@ __device__ __forceinline__ uint32_t spread2to4(uint32_t x) {  // 16 bits -> 8 ni
   return x;
 }
 
-__device__ __forceinline__ uint4 expand16(uint32_t x) {
-  constexpr uint32_t kTable = 0xF7020100u;  // bytes 0, 1, 2, -9
+__device__ __forceinline__ uint4 expand16(uint32_t x, uint32_t kTable = 0xF7020100u) {  // bytes 0, 1, 2, -9
   const uint32_t lo = spread2to4(x & 0xffffu), hi = spread2to4(x >> 16);
   uint4 o;
   o.x = __byte_perm(kTable, 0u, lo);
@@ -171,6 +170,107 @@ k_expand_i8(DenseRows rows, const uint32_t* __restrict__ subset_idx, uint32_t n_
     if (tid < n_out - tail0) {
       const uint32_t g = geno_at(row, tail0 + tid);
       orow[tail0 + tid] = static_cast<int8_t>(g == 3 ? -9 : static_cast<int>(g));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_expand_i8_valid: the genotype column in DuckDB's child-vector layout (the fill loops of
+// src/pgen_reader.cpp:1008-1046 and src/pfile_reader.cpp's variant-orient emit): data byte = the call
+// where it is valid and 0 where it is not, validity bit (row * n_out + sample) = 1 where valid.  A call is
+// valid when it is not missing and GenotypeFilter::AllowsCall (src/include/plink_common.hpp:471-477)
+// selects its category: call_mask bit g.  Same chunking as k_expand_i8; the 16 validity bits of a chunk
+// are merged across the warp (512 consecutive bits) into 32-bit words: the 15 words that lie wholly inside
+// the warp's bit range are stored, the two at its ends -- shared with the neighbouring warp or row -- are
+// OR-ed atomically into the zero-filled bitmap.  bitbase = bit position of the batch's first call in vbits.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t valid16(uint32_t x, uint32_t call_mask) {
+  const uint32_t lo = x & 0x55555555u, hi = (x >> 1) & 0x55555555u;
+  uint32_t v = 0;
+  if (call_mask & 1u) v |= ~(lo | hi) & 0x55555555u;
+  if (call_mask & 2u) v |= lo & ~hi;
+  if (call_mask & 4u) v |= hi & ~lo;
+  v = (v | (v >> 1)) & 0x33333333u;
+  v = (v | (v >> 2)) & 0x0F0F0F0Fu;
+  v = (v | (v >> 4)) & 0x00FF00FFu;
+  v = (v | (v >> 8)) & 0x0000FFFFu;
+  return v;
+}
+
+__device__ __forceinline__ void or_bits(uint32_t* vbits, uint64_t bitpos, uint32_t bits) {
+  if (!bits) return;
+  const uint32_t sh = static_cast<uint32_t>(bitpos & 31u);
+  uint32_t* w = vbits + (bitpos >> 5);
+  atomicOr(w, bits << sh);
+  if (sh && (bits >> (32u - sh))) atomicOr(w + 1, bits >> (32u - sh));
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_expand_i8_valid(DenseRows rows, const uint32_t* __restrict__ subset_idx, uint32_t n_out, uint32_t call_mask,
+                  uint32_t table, int8_t* __restrict__ out, uint32_t* __restrict__ vbits, uint32_t bitbase) {
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t nthr = gridDim.x * blockDim.x;
+  for (uint32_t r = blockIdx.y; r < rows.nrows; r += gridDim.y) {
+    const uint8_t* row = row_ptr(rows, r);
+    int8_t* orow = out + static_cast<uint64_t>(r) * n_out;
+    const uint64_t p0 = bitbase + static_cast<uint64_t>(r) * n_out;  // bit of the row's first call
+    if (subset_idx) {
+      for (uint32_t j0 = tid - lane; j0 < n_out; j0 += nthr) {
+        const uint32_t j = j0 + lane;
+        bool ok = false;
+        if (j < n_out) {
+          const uint32_t g = geno_at(row, subset_idx[j]);
+          ok = (call_mask >> g) & 1u;
+          orow[j] = static_cast<int8_t>(ok ? g : 0u);
+        }
+        const uint32_t b = __ballot_sync(0xffffffffu, ok);
+        if (lane == 0) or_bits(vbits, p0 + j0, b);
+      }
+      continue;
+    }
+    uint32_t head = static_cast<uint32_t>((16u - (reinterpret_cast<uintptr_t>(orow) & 15u)) & 15u);
+    if (head > n_out) head = n_out;
+    const uint32_t nchunks = (n_out - head) >> 4;
+    const uint32_t tail0 = head + (nchunks << 4);
+    for (uint32_t k0 = tid - lane; k0 < nchunks; k0 += nthr) {
+      const uint32_t k = k0 + lane;
+      uint32_t m = 0;
+      if (k < nchunks) {
+        const uint32_t col = head + (k << 4);
+        const uint32_t x = load_bits32(row, static_cast<uint64_t>(col) << 1);
+        __stcs(reinterpret_cast<uint4*>(orow + col), expand16(x, table));
+        m = valid16(x, call_mask);
+      }
+      const uint32_t other = __shfl_xor_sync(0xffffffffu, m, 1);
+      const uint32_t m32 = (lane & 1u) ? 0u : (m | (other << 16));  // chunks k and k + 1
+      const uint32_t prev = __shfl_up_sync(0xffffffffu, m32, 2);
+      const uint64_t P = p0 + head + (static_cast<uint64_t>(k0) << 4);  // bit of the warp's first chunk
+      const uint32_t a = static_cast<uint32_t>(P & 31u);
+      const bool full = k0 + 32u <= nchunks;
+      if (!(lane & 1u)) {
+        uint32_t* w = vbits + (P >> 5) + (lane >> 1);
+        const uint32_t hi_part = a ? m32 >> (32u - a) : 0u;
+        if (full && lane >= 2) {
+          *w = (m32 << a) | (a ? prev >> (32u - a) : 0u);
+          if (lane == 30 && hi_part) atomicOr(w + 1, hi_part);
+        } else {
+          if (m32 << a) atomicOr(w, m32 << a);
+          if (!full && hi_part) atomicOr(w + 1, hi_part);
+        }
+      }
+    }
+    if (tid < head) {
+      const uint32_t g = geno_at(row, tid);
+      const bool ok = (call_mask >> g) & 1u;
+      orow[tid] = static_cast<int8_t>(ok ? g : 0u);
+      or_bits(vbits, p0 + tid, ok);
+    }
+    if (tid < n_out - tail0) {
+      const uint32_t g = geno_at(row, tail0 + tid);
+      const bool ok = (call_mask >> g) & 1u;
+      orow[tail0 + tid] = static_cast<int8_t>(ok ? g : 0u);
+      or_bits(vbits, p0 + tail0 + tid, ok);
     }
   }
 }
@@ -525,6 +625,21 @@ void launch_expand_i8(const DenseRows& rows, const uint32_t* subset_idx, uint32_
   uint32_t threads = subset_idx ? (n_out + 31) / 32 * 32 : (chunks + 31) / 32 * 32;
   threads = threads < 32 ? 32 : (threads > kThreads ? kThreads : threads);
   k_expand_i8<<<dim3(bx, by), threads, 0, s>>>(rows, subset_idx, n_out, out);
+  if (st) st->launches++;
+}
+
+void launch_expand_i8_valid(const DenseRows& rows, const uint32_t* subset_idx, uint32_t n_out, uint32_t call_mask,
+                            int8_t* out, uint32_t* vbits, uint32_t bitbase, cudaStream_t s, LaunchStats* st) {
+  if (!rows.nrows || !n_out) return;
+  call_mask &= 7u;  // a missing call is never valid
+  const uint32_t table = ((call_mask & 2u) ? 0x00000100u : 0u) | ((call_mask & 4u) ? 0x00020000u : 0u);
+  const uint32_t chunks = (n_out + 15) / 16;
+  uint32_t bx = (chunks + 4 * kThreads - 1) / (4 * kThreads);
+  if (bx < 1) bx = 1;
+  const uint32_t by = rows.nrows < 65535u ? rows.nrows : 65535u;
+  uint32_t threads = subset_idx ? (n_out + 31) / 32 * 32 : (chunks + 31) / 32 * 32;
+  threads = threads < 32 ? 32 : (threads > kThreads ? kThreads : threads);
+  k_expand_i8_valid<<<dim3(bx, by), threads, 0, s>>>(rows, subset_idx, n_out, call_mask, table, out, vbits, bitbase);
   if (st) st->launches++;
 }
 

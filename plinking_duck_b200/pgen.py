@@ -215,6 +215,16 @@ class PgenContext:
         self._check(self._lib.pd_decode_i8(self._h, v0, v1, _p(out)))
         return out
 
+    def decode_i8_valid(self, v0=0, v1=None, call_mask=7):
+        """Genotype column in DuckDB's child-vector layout: (int8 calls with 0 where invalid, uint64 validity
+        words over the flattened rows x samples calls).  call_mask bit g: category g in {0,1,2} is selected."""
+        v0, v1 = self._range(v0, v1)
+        rows = max(v1 - v0, 0)
+        out = np.full((rows, self.sample_ct), 0x55, dtype=np.int8)
+        validity = np.full((rows * self.sample_ct + 63) // 64, 0xAAAAAAAAAAAAAAAA, dtype=np.uint64)
+        self._check(self._lib.pd_decode_i8_valid(self._h, v0, v1, call_mask, _p(out), _p(validity)))
+        return out, validity
+
     def decode_phased(self, v0=0, v1=None) -> np.ndarray:
         """(v1 - v0, sample_ct, 2) int8 allele pairs (read_pgen / read_pfile with phased := true)."""
         v0, v1 = self._range(v0, v1)

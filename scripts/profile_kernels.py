@@ -22,7 +22,7 @@ def main():
     ap.add_argument("--variants", type=int, default=200_000)
     ap.add_argument("--samples", type=int, default=100_000)
     ap.add_argument("--reps", type=int, default=3)
-    ap.add_argument("--ops", default="counts,counts_subset,hardy,missing_by_sample,sample_counts,decode_i8,decode_phased,score1,score16")
+    ap.add_argument("--ops", default="counts,counts_subset,hardy,missing_by_sample,sample_counts,decode_i8,decode_i8_valid,decode_phased,score1,score16")
     ap.add_argument("--score-variants", type=int, default=20_000)
     ap.add_argument("--decode-variants", type=int, default=20_000)
     args = ap.parse_args()
@@ -91,6 +91,20 @@ def main():
             ctx._check(ctx._lib.pd_decode_i8(ctx._h, 0, Vd, out.ctypes.data_as(C.c_void_p)))
 
         report("decode_i8", dec, Vd * (W + N), Vd * N, {"note": "kernel_ms = expand kernels; call_ms includes D2H of N bytes/variant"})
+    if "decode_i8_valid" in ops:
+        Vd = min(V, args.decode_variants)
+        outv = torch.empty((Vd, N), dtype=torch.int8, pin_memory=True).numpy()
+        val = torch.empty(((Vd * N + 63) // 64,), dtype=torch.int64, pin_memory=True).numpy().view(np.uint64)
+        import ctypes as C
+
+        def decv():
+            ctx._check(ctx._lib.pd_decode_i8_valid(ctx._h, 0, Vd, 7, outv.ctypes.data_as(C.c_void_p), val.ctypes.data_as(C.c_void_p)))
+
+        report("decode_i8_valid", decv, Vd * (W + N + N // 8), Vd * N,
+               {"note": "kernel_ms = expand kernels (calls + validity bits); call_ms includes D2H of 1.125 N bytes/variant"})
+        plain = ctx.decode_i8(0, min(Vd, 2000))
+        bits = np.unpackbits(val.view(np.uint8), bitorder="little")[: min(Vd, 2000) * N].reshape(-1, N)
+        assert np.array_equal(bits.astype(bool), plain != -9) and np.array_equal(outv[: plain.shape[0]], np.where(plain == -9, 0, plain))
     if "decode_phased" in ops:
         Vd = min(V, args.decode_variants // 2)
         outp = torch.empty((Vd, N, 2), dtype=torch.int8, pin_memory=True).numpy()

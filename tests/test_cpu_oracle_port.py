@@ -126,3 +126,20 @@ def test_phased_decode_kat_and_pgenlib(port, tmp_path):
         with port.PortPgen(path) as p:
             assert np.array_equal(p.decode_phased(), exp)
             assert np.array_equal(p.decode_phased(5, 17), exp[5:17])
+
+
+def test_child_vector_layout_restatement(port, golden):
+    """The DuckDB child-vector fill loop (data + validity): vectorised restatement == the literal loop, on the
+    reference's own fixture and for every genotype-filter mask."""
+    g = golden["pgen_example/i8"]
+    d, v = port.child_vector_layout(g)
+    assert d.tolist() == np.where(g == -9, 0, g).tolist()
+    assert int(sum(bin(int(x)).count("1") for x in v)) == int((g != -9).sum())
+    rng = np.random.default_rng(3)
+    for rows, n in [(1, 1), (3, 7), (5, 64), (4, 129), (9, 100)]:
+        m = rng.choice(np.array([0, 1, 2, -9], dtype=np.int8), size=(rows, n))
+        for mask in range(8):
+            allowed = tuple(bool(mask >> k & 1) for k in range(3))
+            d1, v1 = port.child_vector_layout(m, allowed)
+            d2, v2 = port.child_vector_layout_loop(m, allowed)
+            assert np.array_equal(d1, d2) and np.array_equal(v1, v2)

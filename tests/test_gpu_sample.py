@@ -234,3 +234,69 @@ def test_decode_phased_vs_pgenlib(tmp_path):
     exp[g == 3] = (-9, -9)
     with PgenContext(image=synth.fixed_pgen_image(g)) as c:
         assert np.array_equal(c.decode_phased(), exp)
+
+
+@pytest.mark.parametrize("name", fixture_names())
+def test_decode_i8_valid_child_vector_layout(name, golden):
+    """pd_decode_i8_valid: DuckDB child data + validity (src/pgen_reader.cpp:1008-1046) for every genotype
+    filter mask, tiny tiles (batches start at any bit of the bitmap), sub-ranges and a sample subset."""
+    from oracle import port
+
+    key = name + "/i8"
+    if key not in golden:
+        pytest.skip("no int8 golden")
+    exp = golden[key]
+    V = exp.shape[0]
+    rng = np.random.default_rng(11)
+    with _ctx(name, tile_bytes=900, n_staging=2) as c:
+        for mask in (7, 0, 1, 2, 4, 6, 3, 5):
+            allowed = tuple(bool(mask >> k & 1) for k in range(3))
+            d, v = c.decode_i8_valid(call_mask=mask)
+            ed, ev = port.child_vector_layout(exp, allowed)
+            assert np.array_equal(d, ed), mask
+            assert np.array_equal(v, ev), mask
+        for _ in range(3):
+            a = int(rng.integers(0, V))
+            b = int(rng.integers(a, V + 1))
+            d, v = c.decode_i8_valid(a, b, call_mask=6)
+            ed, ev = port.child_vector_layout(exp[a:b], (False, True, True))
+            assert np.array_equal(d, ed) and np.array_equal(v, ev), (a, b)
+        if name + "/subset_i8" in golden:
+            c.set_subset(golden[name + "/subset"])
+            d, v = c.decode_i8_valid(call_mask=5)
+            ed, ev = port.child_vector_layout(golden[name + "/subset_i8"], (True, False, True))
+            assert np.array_equal(d, ed) and np.array_equal(v, ev)
+
+
+def test_decode_i8_valid_many_batches(tmp_path):
+    """Rows of 70001 samples (odd: every row starts at a new bit offset) over enough variants that the
+    128 MiB output batches and the tiles both split the call; resident and streamed agree with pgenlib."""
+    import synth
+    from oracle import port, ref
+
+    if not ref.available():
+        pytest.skip("oracle/_ref not built")
+    V, N = 4200, 70001
+    g = synth.gen_mixed_genotypes(V, N, seed=5)
+    path = str(tmp_path / "big.pgen")
+    ref.write_pgen(path, synth.to_genovec_words(g), N)
+    with ref.RefPgen(path) as r:
+        exp = r.decode_i8()
+    ed, ev = port.child_vector_layout(exp, (True, True, False))
+    from plinking_duck_b200.pgen import PgenContext
+
+    with PgenContext(path) as c:
+        d, v = c.decode_i8_valid(call_mask=3)
+        assert np.array_equal(d, ed) and np.array_equal(v, ev)
+        c.load_resident()
+        d, v = c.decode_i8_valid(call_mask=3)
+        assert np.array_equal(d, ed) and np.array_equal(v, ev)
+        # page-locked destinations: both streams are DMA-ed straight into the caller's arrays
+        import ctypes as C
+
+        import torch
+
+        pd_ = torch.full((V, N), 0x55, dtype=torch.int8).pin_memory().numpy()
+        pv = torch.full((ev.size,), -1, dtype=torch.int64).pin_memory().numpy().view(np.uint64)
+        c._check(c._lib.pd_decode_i8_valid(c._h, 0, V, 3, pd_.ctypes.data_as(C.c_void_p), pv.ctypes.data_as(C.c_void_p)))
+        assert np.array_equal(pd_, ed) and np.array_equal(pv, ev)
