@@ -157,6 +157,10 @@ int pd_decode_i8(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, int8_t* out);
  *      validity holds ceil(rows * n / 64) words and is written whole (bits past the last call are 0). ---- */
 int pd_decode_i8_valid(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t call_mask, int8_t* out,
                        uint64_t* validity);
+/* Same for a strictly ascending list of variants (read_pgen's effective_variant_indices, or the variants
+ * that survive CheckPreDecompFilters, src/pgen_reader.cpp:659-683): row i is variant vidx[i]. */
+int pd_decode_i8_valid_list(pd_ctx* ctx, const uint32_t* vidx, uint32_t n_var, uint32_t call_mask, int8_t* out,
+                            uint64_t* validity);
 
 /* ---- phased hardcalls : replaces PgrGetP + UnpackPhasedGenotypes (src/plink_common.cpp:1549-1584; call
  *      sites src/pgen_reader.cpp:705-733, src/pfile_reader.cpp:1722-1745, read_pgen / read_pfile with

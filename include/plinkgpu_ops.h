@@ -103,6 +103,15 @@ typedef struct pd_predecomp_filter {
 int pdop_predecomp_filter(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, const pd_predecomp_filter* filter, uint8_t* skip,
                           uint8_t* all_pass);
 
+/* ---- read_pgen / read_pfile genotype column for a range of variants, as the scan emits it
+ * (src/pgen_reader.cpp:659-683 filter, :727-733 decode, :1008-1046 fill): counts on the GPU ->
+ * CheckPreDecompFilters per variant -> the variants that are not skipped are decoded, in order, into
+ * DuckDB's child-vector layout (pd_decode_i8_valid_list; call mask = the genotype filter's categories, 7 when it
+ * is inactive).  kept[0 .. *n_kept) receives their variant indices; out / validity hold *n_kept rows and must
+ * be sized for v_end - v_begin.  filter may be NULL (nothing skipped, nothing nulled but missing calls). */
+int pdop_genotype_column(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, const pd_predecomp_filter* filter, int8_t* out,
+                         uint64_t* validity, uint32_t* kept, uint32_t* n_kept);
+
 #ifdef __cplusplus
 }
 #endif

@@ -172,15 +172,11 @@ int pd_decode_i8(pd_ctx* c, uint32_t v_begin, uint32_t v_end, int8_t* out) {
   return rc != PD_OK ? rc : rc2;
 }
 
-int pd_decode_i8_valid(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t call_mask, int8_t* out, uint64_t* validity) {
-  if (!c || ((!out || !validity) && v_end > v_begin)) return PD_ERR_INVALID_ARG;
-  std::lock_guard<std::mutex> lock(c->mu);
-  cudaSetDevice(c->device);
-  const uint32_t n_out = c->subset.active ? c->subset.count : c->idx.sample_ct;
-  if (v_begin >= v_end || !n_out) {
-    if (v_begin > v_end || v_end > c->idx.variant_ct) return c->SetError(PD_ERR_INVALID_ARG, "variant range out of bounds");
-    return PD_OK;
-  }
+}  // extern "C"
+
+// Shared body of pd_decode_i8_valid / pd_decode_i8_valid_list: run(max_rows, fn) feeds the row batches.
+static int DecodeI8Valid(pd_ctx* c, uint32_t n_out, uint32_t call_mask, int8_t* out, uint64_t* validity,
+                         const std::function<int(uint32_t, const RowFn&)>& run) {
   // Per batch and buffer: up to 128 MiB of calls, then (256-byte aligned) their validity words + one word of
   // slack.  A batch starts at any bit of the caller's bitmap: the word it shares with the batch before is
   // carried over on the device, so every download writes whole, final 64-bit words.
@@ -194,7 +190,7 @@ int pd_decode_i8_valid(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t cal
   const uint32_t* idx = c->subset.active ? c->subset.d_idx.as<uint32_t>() : nullptr;
   const char* prev_last_word = nullptr;  // device address of the last validity word of the batch before
   cudaEventRecord(c->ev_c0, c->stream);
-  rc = RunRows(c, v_begin, v_end, max_rows, 0, [&](const RowBatch& b, const pdk::RecIndex&, cudaStream_t s) {
+  rc = run(max_rows, [&](const RowBatch& b, const pdk::RecIndex&, cudaStream_t s) {
     void* dev = nullptr;
     int slot = 0;
     int r = pipe.Acquire(&dev, &slot);
@@ -221,6 +217,34 @@ int pd_decode_i8_valid(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t cal
     c->stats.kernel_ms = pipe.produce_ms;
   }
   return rc != PD_OK ? rc : rc2;
+}
+
+extern "C" {
+
+int pd_decode_i8_valid(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t call_mask, int8_t* out, uint64_t* validity) {
+  if (!c || ((!out || !validity) && v_end > v_begin)) return PD_ERR_INVALID_ARG;
+  std::lock_guard<std::mutex> lock(c->mu);
+  cudaSetDevice(c->device);
+  const uint32_t n_out = c->subset.active ? c->subset.count : c->idx.sample_ct;
+  if (v_begin >= v_end || !n_out) {
+    if (v_begin > v_end || v_end > c->idx.variant_ct) return c->SetError(PD_ERR_INVALID_ARG, "variant range out of bounds");
+    return PD_OK;
+  }
+  return DecodeI8Valid(c, n_out, call_mask, out, validity, [&](uint32_t max_rows, const RowFn& fn) {
+    return RunRows(c, v_begin, v_end, max_rows, 0, fn);
+  });
+}
+
+int pd_decode_i8_valid_list(pd_ctx* c, const uint32_t* vidx, uint32_t n_var, uint32_t call_mask, int8_t* out,
+                            uint64_t* validity) {
+  if (!c || ((!out || !validity || !vidx) && n_var)) return PD_ERR_INVALID_ARG;
+  std::lock_guard<std::mutex> lock(c->mu);
+  cudaSetDevice(c->device);
+  const uint32_t n_out = c->subset.active ? c->subset.count : c->idx.sample_ct;
+  if (!n_var || !n_out) return PD_OK;
+  return DecodeI8Valid(c, n_out, call_mask, out, validity, [&](uint32_t max_rows, const RowFn& fn) {
+    return RunRowsList(c, vidx, n_var, max_rows, fn);
+  });
 }
 
 int pd_decode_phased(pd_ctx* c, uint32_t v_begin, uint32_t v_end, int8_t* out) {

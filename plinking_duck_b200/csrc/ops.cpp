@@ -215,6 +215,32 @@ int pdop_predecomp_filter(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, const p
   return PD_OK;
 }
 
+int pdop_genotype_column(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, const pd_predecomp_filter* f, int8_t* out,
+                         uint64_t* validity, uint32_t* kept, uint32_t* n_kept) {
+  if (!ctx || v_begin > v_end || !kept || !n_kept) return PD_ERR_INVALID_ARG;
+  const uint32_t n = v_end - v_begin;
+  *n_kept = 0;
+  if (!n) return PD_OK;
+  const bool filtering = f && (f->use_count_filter || f->use_genotype_filter);
+  if (!filtering) {
+    for (uint32_t i = 0; i < n; ++i) kept[i] = v_begin + i;
+    *n_kept = n;
+    return pd_decode_i8_valid(ctx, v_begin, v_end, 7u, out, validity);
+  }
+  std::vector<uint8_t> skip(n);
+  const int rc = pdop_predecomp_filter(ctx, v_begin, v_end, f, skip.data(), nullptr);
+  if (rc != PD_OK) return rc;
+  uint32_t m = 0;
+  for (uint32_t i = 0; i < n; ++i) {
+    if (!skip[i]) kept[m++] = v_begin + i;
+  }
+  *n_kept = m;
+  // A variant whose calls all pass needs no null-out, and applying the mask to it changes nothing: one mask
+  // serves every kept row (the reference branches per row on geno_range_all_pass only to save work).
+  const uint32_t mask = f->use_genotype_filter ? (f->allowed_mask & 7u) : 7u;
+  return pd_decode_i8_valid_list(ctx, kept, m, mask, out, validity);
+}
+
 int pdop_freq(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, const uint8_t* ploidy, const uint8_t* sex, uint32_t dosage,
               pd_freq_row* out) {
   if (!ctx || v_begin > v_end || (v_end > v_begin && !out)) return PD_ERR_INVALID_ARG;

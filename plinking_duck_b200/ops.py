@@ -34,6 +34,7 @@ _OPS = {
     "pdop_counts_pass": (C.c_int, [_vp, C.c_double, C.c_double, C.c_int64, C.c_int64]),
     "pdop_genotype_range": (None, [_vp, _u32, _u32, _vp, _vp]),
     "pdop_predecomp_filter": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),
+    "pdop_genotype_column": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp, _vp, _vp]),
 }
 
 
@@ -148,3 +149,29 @@ def predecomp_filter(ctx, v0=0, v1=None, af=None, ac=None, allowed=None, include
     allp = np.zeros(n, dtype=np.uint8)
     ctx._check(_lib().pdop_predecomp_filter(ctx._h, v0, v1, C.addressof(f), _p(skip), _p(allp)))
     return skip, allp
+
+
+def _filter_struct(af, ac, allowed, include_missing):
+    f = PredecompFilter()
+    f.use_count_filter = int(af is not None or ac is not None)
+    f.af_min, f.af_max = [(-1.0 if x is None else float(x)) for x in (af or (None, None))]
+    f.ac_min, f.ac_max = [(-1 if x is None else int(x)) for x in (ac or (None, None))]
+    f.use_genotype_filter = int(allowed is not None)
+    f.allowed_mask = sum(1 << int(g) for g in (allowed or ()))
+    f.include_missing = int(bool(include_missing))
+    return f
+
+
+def genotype_column(ctx, v0=0, v1=None, af=None, ac=None, allowed=None, include_missing=False):
+    """read_pgen's genotype column over [v0, v1): (kept variant indices, int8 child data, uint64 validity
+    words) for the variants that survive CheckPreDecompFilters, rows compacted as the scan emits them."""
+    v0, v1 = ctx._range(v0, v1)
+    n = max(v1 - v0, 0)
+    f = _filter_struct(af, ac, allowed, include_missing)
+    out = np.full((n, ctx.sample_ct), 0x55, dtype=np.int8)
+    validity = np.full((n * ctx.sample_ct + 63) // 64, 0xAAAAAAAAAAAAAAAA, dtype=np.uint64)
+    kept = np.zeros(n, dtype=np.uint32)
+    nk = C.c_uint32(0)
+    ctx._check(_lib().pdop_genotype_column(ctx._h, v0, v1, C.addressof(f), _p(out), _p(validity), _p(kept), C.byref(nk)))
+    m = nk.value
+    return kept[:m], out[:m], validity[: (m * ctx.sample_ct + 63) // 64]

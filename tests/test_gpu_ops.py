@@ -255,3 +255,72 @@ def test_predecomp_filters_on_gpu_counts(golden):
         assert np.array_equal(skip.astype(bool), ~((cnt[:, 2] > 0) | (cnt[:, 3] > 0)))
         skip, _ = ops.predecomp_filter(c, 10, 50, af=(0.0, 1.0), allowed=(0, 1, 2))
         assert skip.shape == (40,) and np.array_equal(skip.astype(bool), (nm == 0)[10:50])
+
+
+def _scan_genotype_column(i8, counts, af, ac, allowed, include_missing):
+    """The per-variant flow of the reference's read_pgen scan restated on pgenlib's goldens:
+    CheckPreDecompFilters (src/plink_common.cpp:1495-1515) on the counts, skip, then the child-vector fill
+    (src/pgen_reader.cpp:1008-1025) with the per-row geno_range_all_pass short-cut."""
+    from oracle import port
+
+    kept, rows = [], []
+    for v in range(i8.shape[0]):
+        c = [int(x) for x in counts[v]]
+        nm = c[0] + c[1] + c[2]
+        all_pass = True
+        if af is not None or ac is not None:
+            a = c[1] + 2 * c[2]
+            if nm == 0:
+                continue
+            f = a / (2.0 * nm)
+            lo, hi = af or (None, None)
+            if (lo is not None and f < lo) or (hi is not None and f > hi):
+                continue
+            lo, hi = ac or (None, None)
+            if (lo is not None and a < lo) or (hi is not None and a > hi):
+                continue
+        if allowed is not None:
+            anyp = any(c[g] > 0 for g in allowed) or (include_missing and c[3] > 0)
+            if not anyp:
+                continue
+            all_pass = all(c[g] == 0 for g in (0, 1, 2) if g not in allowed) and (include_missing or c[3] == 0)
+        kept.append(v)
+        mask = (True, True, True) if (allowed is None or all_pass) else tuple(g in allowed for g in (0, 1, 2))
+        rows.append(port.child_vector_layout(i8[v : v + 1], mask)[0][0])
+    data = np.array(rows, dtype=np.int8).reshape(len(kept), i8.shape[1])
+    valid = data != 0
+    # validity from the same rule, flattened over the kept rows
+    ok = np.zeros(data.shape, dtype=bool)
+    for r, v in enumerate(kept):
+        g = i8[v]
+        m = (True, True, True) if allowed is None else tuple(gg in allowed for gg in (0, 1, 2))
+        ok[r] = (g != -9) & np.isin(g, [gg for gg in (0, 1, 2) if m[gg]])
+    bits = np.packbits(ok.reshape(-1), bitorder="little")
+    words = np.zeros(((ok.size + 63) // 64) * 8, dtype=np.uint8)
+    words[: bits.size] = bits
+    del valid
+    return np.array(kept, dtype=np.uint32), data, words.view(np.uint64)
+
+
+@pytest.mark.parametrize("name", ["pgen_example", "syn_n1000", "rare_small", "streaming_example", "pca_example", "all_missing"])
+def test_genotype_column_op_matches_scan_flow(name, golden):
+    """pdop_genotype_column = counts -> CheckPreDecompFilters -> compacted decode into DuckDB's child layout."""
+    from plinking_duck_b200 import ops
+
+    if name + "/i8" not in golden:
+        pytest.skip("no int8 golden")
+    i8, cnt = golden[name + "/i8"], golden[name + "/counts"]
+    cases = [
+        dict(af=None, ac=None, allowed=None, include_missing=False),
+        dict(af=(0.05, 0.45), ac=None, allowed=None, include_missing=False),
+        dict(af=None, ac=(2, None), allowed=(1, 2), include_missing=False),
+        dict(af=None, ac=None, allowed=(2,), include_missing=True),
+        dict(af=None, ac=None, allowed=(0,), include_missing=False),
+    ]
+    with _ctx(name, tile_bytes=1200, n_staging=2) as c:
+        for kw in cases:
+            ek, ed, ev = _scan_genotype_column(i8, cnt, **kw)
+            k, d, v = ops.genotype_column(c, **kw)
+            assert np.array_equal(k, ek), kw
+            assert np.array_equal(d, ed), kw
+            assert np.array_equal(v, ev), kw
