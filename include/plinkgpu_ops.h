@@ -112,6 +112,23 @@ int pdop_predecomp_filter(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, const p
 int pdop_genotype_column(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, const pd_predecomp_filter* filter, int8_t* out,
                          uint64_t* validity, uint32_t* kept, uint32_t* n_kept);
 
+/* ---- read_pgen / read_pfile with genotypes := 'counts' | 'stats' (MakeGenotypeCountsType /
+ * MakeGenotypeStatsType, src/plink_common.cpp:43-68).  Variant orient: one PgrGetCounts per variant, then the
+ * derived fields (src/pgen_reader.cpp:863-901, src/pfile_reader.cpp:2548-2600).  Sample orient: the per-sample
+ * het / hom_alt / missing tallies of Phase 1, hom_ref = variants scanned - het - hom_alt - missing
+ * (src/pfile_reader.cpp:3566-3607).  The counts mode is the first four fields of the same row.
+ * af / maf / het_rate are NaN when n == 0 and missing_rate is NaN when n + missing == 0, as in the reference. */
+typedef struct pd_geno_stats_row {
+  uint32_t hom_ref, het, hom_alt, missing;
+  uint32_t n;              /* hom_ref + het + hom_alt                  */
+  uint32_t carrier_count;  /* het + hom_alt                            */
+  double af, maf, missing_rate, het_rate;
+} pd_geno_stats_row;
+/* out[v_end - v_begin]; honours the context's sample subset. */
+int pdop_genotype_stats_variant(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, pd_geno_stats_row* out);
+/* out[effective sample_ct]; the variants scanned are [v_begin, v_end). */
+int pdop_genotype_stats_sample(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, pd_geno_stats_row* out);
+
 #ifdef __cplusplus
 }
 #endif

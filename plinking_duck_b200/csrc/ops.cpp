@@ -6,6 +6,7 @@
 #include <cctype>
 #include <cmath>
 #include <cstring>
+#include <limits>
 #include <numeric>
 #include <string>
 #include <vector>
@@ -466,6 +467,67 @@ int pdop_score(pd_ctx* ctx, const uint32_t* vidx, const uint8_t* flip, const dou
     out[i].named_allele_dosage_sum = d[i];
     out[i].score_sum = s[i];
     out[i].score_avg = a[i] ? s[i] / static_cast<double>(a[i]) : 0.0;  // src/plink_score.cpp:686-690
+  }
+  return PD_OK;
+}
+
+namespace {
+// the derived fields of MakeGenotypeStatsType (src/pgen_reader.cpp:875-899 == src/pfile_reader.cpp:3581-3605)
+void FillGenoStats(uint32_t hom_ref, uint32_t het, uint32_t hom_alt, uint32_t missing, pd_geno_stats_row* r) {
+  const double kNan = std::numeric_limits<double>::quiet_NaN();
+  r->hom_ref = hom_ref;
+  r->het = het;
+  r->hom_alt = hom_alt;
+  r->missing = missing;
+  const uint32_t n = hom_ref + het + hom_alt;
+  const uint32_t total = n + missing;
+  r->n = n;
+  r->carrier_count = het + hom_alt;
+  if (n == 0) {
+    r->af = r->maf = r->het_rate = kNan;
+  } else {
+    const double af = (static_cast<double>(het) + 2.0 * hom_alt) / (2.0 * n);
+    r->af = af;
+    r->maf = std::min(af, 1.0 - af);
+    r->het_rate = static_cast<double>(het) / static_cast<double>(n);
+  }
+  r->missing_rate = total ? static_cast<double>(missing) / static_cast<double>(total) : kNan;
+}
+}  // namespace
+
+int pdop_genotype_stats_variant(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, pd_geno_stats_row* out) {
+  if (!ctx || v_begin > v_end || (v_end > v_begin && !out)) return PD_ERR_INVALID_ARG;
+  const uint32_t n = v_end - v_begin;
+  if (!n) return PD_OK;
+  std::vector<uint32_t> counts(static_cast<size_t>(n) * 4);
+  const int rc = pd_counts(ctx, v_begin, v_end, counts.data());
+  if (rc != PD_OK) return rc;
+  for (uint32_t i = 0; i < n; ++i) {
+    const uint32_t* c = &counts[static_cast<size_t>(i) * 4];
+    FillGenoStats(c[0], c[1], c[2], c[3], &out[i]);
+  }
+  return PD_OK;
+}
+
+int pdop_genotype_stats_sample(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, pd_geno_stats_row* out) {
+  if (!ctx || v_begin > v_end || !out) return PD_ERR_INVALID_ARG;
+  pd_info_t info;
+  int rc = pd_info(ctx, &info);
+  if (rc != PD_OK) return rc;
+  uint32_t sample_ct = info.sample_ct;
+  if (info.variant_ct) {
+    uint32_t one[4];
+    rc = pd_counts(ctx, 0, 1, one);
+    if (rc != PD_OK) return rc;
+    sample_ct = EffectiveSampleCt(one);
+  }
+  const size_t cap = std::max<uint32_t>(sample_ct, 1);
+  std::vector<uint32_t> het(cap), hom_alt(cap), missing(cap);
+  rc = pd_sample_counts(ctx, v_begin, v_end, het.data(), hom_alt.data(), missing.data());
+  if (rc != PD_OK) return rc;
+  const uint32_t total_eff_variants = v_end - v_begin;  // smp_total_eff_variants, src/pfile_reader.cpp:3573
+  for (uint32_t s = 0; s < sample_ct; ++s) {
+    FillGenoStats(total_eff_variants - het[s] - hom_alt[s] - missing[s], het[s], hom_alt[s], missing[s], &out[s]);
   }
   return PD_OK;
 }

@@ -20,6 +20,9 @@ HARDY_DTYPE = np.dtype([("O_HET", "<f8"), ("E_HET", "<f8"), ("P_HWE", "<f8"), ("
                         ("HOM_ALT_CT", "<i4"), ("stats_are_null", "u1"), ("counts_are_null", "u1"), ("pad", "u1", (2,))],
                        align=True)
 MISSING_DTYPE = np.dtype([("MISSING_CT", "<u4"), ("OBS_CT", "<u4"), ("F_MISS", "<f8")], align=True)
+GENO_STATS_DTYPE = np.dtype([("hom_ref", "<u4"), ("het", "<u4"), ("hom_alt", "<u4"), ("missing", "<u4"), ("n", "<u4"),
+                             ("carrier_count", "<u4"), ("af", "<f8"), ("maf", "<f8"), ("missing_rate", "<f8"),
+                             ("het_rate", "<f8")], align=True)
 SCORE_DTYPE = np.dtype([("ALLELE_CT", "<u4"), ("DENOM", "<u4"), ("NAMED_ALLELE_DOSAGE_SUM", "<f8"), ("SCORE_SUM", "<f8"),
                         ("SCORE_AVG", "<f8")], align=True)
 
@@ -35,6 +38,8 @@ _OPS = {
     "pdop_genotype_range": (None, [_vp, _u32, _u32, _vp, _vp]),
     "pdop_predecomp_filter": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),
     "pdop_genotype_column": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp, _vp, _vp]),
+    "pdop_genotype_stats_variant": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "pdop_genotype_stats_sample": (C.c_int, [_vp, _u32, _u32, _vp]),
 }
 
 
@@ -175,3 +180,18 @@ def genotype_column(ctx, v0=0, v1=None, af=None, ac=None, allowed=None, include_
     ctx._check(_lib().pdop_genotype_column(ctx._h, v0, v1, C.addressof(f), _p(out), _p(validity), _p(kept), C.byref(nk)))
     m = nk.value
     return kept[:m], out[:m], validity[: (m * ctx.sample_ct + 63) // 64]
+
+
+def genotype_stats(ctx: PgenContext, v0=0, v1=None, *, orient="variant") -> np.ndarray:
+    """read_pfile(..., genotypes := 'stats' [, orient := 'sample']): the STRUCT column as a record array
+    (genotypes := 'counts' is its first four fields)."""
+    v0, v1 = _range(ctx, v0, v1)
+    if orient == "variant":
+        out = np.zeros(max(v1 - v0, 0), dtype=GENO_STATS_DTYPE)
+        ctx._check(_lib().pdop_genotype_stats_variant(ctx._h, v0, v1, _p(out)))
+    elif orient == "sample":
+        out = np.zeros(ctx.sample_ct, dtype=GENO_STATS_DTYPE)
+        ctx._check(_lib().pdop_genotype_stats_sample(ctx._h, v0, v1, _p(out)))
+    else:
+        raise ValueError("genotype_stats: orient must be 'variant' or 'sample'")
+    return out

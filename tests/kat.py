@@ -48,3 +48,23 @@ PHASED_EXAMPLE_PAIRS = [
     [[1, 1], [-9, -9], [1, 0], [0, 0]],   # rs3: 1|1 ./. 1|0 0|0
     [[0, 0], [0, 0], [0, 1], [1, 1]],     # rs4: 0|0 0|0 0|1 1|1
 ]
+
+# test/sql/read_pfile_genotypes_stats.test:15-33 -- genotypes := 'stats', variant orient, pgen_example:
+# hom_ref het hom_alt missing n af maf missing_rate carrier_count het_rate (doubles ROUNDed to 6 places)
+GENO_STATS_VARIANT = [
+    (1, 1, 1, 1, 3, 0.5, 0.5, 0.25, 2, 0.333333),
+    (1, 2, 1, 0, 4, 0.5, 0.5, 0.0, 3, 0.5),
+    (1, 1, 1, 1, 3, 0.5, 0.5, 0.25, 2, 0.333333),
+    (2, 1, 1, 0, 4, 0.375, 0.375, 0.0, 2, 0.25),
+]
+# test/sql/read_pfile_genotypes_stats.test:114-125 -- sample orient: n, af (4 places), missing_rate, carrier_count
+GENO_STATS_SAMPLE = [(4, 0.375, 0.0, 2), (3, 0.3333, 0.25, 2), (4, 0.5, 0.0, 3), (3, 0.6667, 0.25, 2)]
+# test/sql/read_pfile_genotypes_stats.test:129-141 -- samples := ['SAMPLE1','SAMPLE3']: hom_ref, het, af, missing_rate
+GENO_STATS_SUBSET_1_3 = [(1, 0, 0.5, 0.0), (1, 1, 0.25, 0.0), (0, 1, 0.75, 0.0), (1, 1, 0.25, 0.0)]
+# test/sql/read_pfile_genotypes_counts.test:66-78 -- sample orient counts: hom_ref het hom_alt missing per sample
+GENO_COUNTS_SAMPLE = [(2, 1, 1, 0), (1, 2, 0, 1), (1, 2, 1, 0), (1, 0, 2, 1)]
+# test/sql/read_pfile_genotypes_counts.test:33-47 -- variant orient counts under samples := ['SAMPLE1','SAMPLE3']
+GENO_COUNTS_SUBSET_1_3 = [(1, 0, 1, 0), (1, 1, 0, 0), (0, 1, 1, 0), (1, 1, 0, 0)]
+# test/sql/read_pfile_sample_counts_sparse.test:37-41 -- rare_small, orient := 'sample', genotypes := 'stats':
+# sum(n), sum(carrier_count), round(sum(het) / sum(n), 6)
+RARE_SMALL_STATS = (101388, 2171, 0.019203)

@@ -101,3 +101,23 @@ def test_goldens_are_current(name, golden, refmod):
         if name + "/dcounts" in golden:
             dc, ad, r2 = r.dcounts()
             assert np.array_equal(ad, golden[name + "/all_dosages"])
+
+
+def test_genotype_counts_struct_kat(refmod):
+    """genotypes := 'counts' / 'stats' known answers (test/sql/read_pfile_genotypes_counts.test,
+    read_pfile_genotypes_stats.test) against the reference's own pgenlib."""
+    with refmod.RefPgen(fixture_path("pgen_example")) as r:
+        c = r.counts()
+        het, hom, mis = r.sample_counts(sparse=False)
+    assert [tuple(int(x) for x in row) for row in c] == [k[:4] for k in kat.GENO_STATS_VARIANT]
+    hom_ref = c.shape[0] - het - hom - mis  # src/pfile_reader.cpp:3573
+    assert list(zip(hom_ref.tolist(), het.tolist(), hom.tolist(), mis.tolist())) == kat.GENO_COUNTS_SAMPLE
+    n = hom_ref + het + hom
+    af = (het + 2.0 * hom) / (2.0 * n)
+    assert [(int(a), round(float(b), 4), round(float(m) / 4, 4), int(cc)) for a, b, m, cc in zip(n, af, mis, het + hom)] \
+        == kat.GENO_STATS_SAMPLE
+    with refmod.RefPgen(fixture_path("rare_small")) as r:
+        het, hom, mis = r.sample_counts(sparse=True)
+        nv = r.counts().shape[0]
+    n = nv * het.size - int(mis.sum())
+    assert (n, int(het.sum() + hom.sum()), round(float(het.sum()) / n, 6)) == kat.RARE_SMALL_STATS

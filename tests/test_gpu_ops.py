@@ -231,6 +231,57 @@ def test_xchr_exact_test_matches_reference():
     assert tie_quirks <= 20
 
 
+
+def test_genotype_counts_and_stats_struct_known_answers(golden):
+    """read_pfile / read_pgen with genotypes := 'counts' | 'stats', both orients
+    (test/sql/read_pfile_genotypes_stats.test, read_pfile_genotypes_counts.test,
+    read_pfile_sample_counts_sparse.test:37-41)."""
+    from plinking_duck_b200 import ops
+
+    cnt = ("hom_ref", "het", "hom_alt", "missing")
+    with _ctx("pgen_example") as c:
+        v = ops.genotype_stats(c)
+        for r, k in zip(v, kat.GENO_STATS_VARIANT):
+            assert tuple(int(r[f]) for f in cnt) == k[:4] and int(r["n"]) == k[4] and int(r["carrier_count"]) == k[8]
+            assert (round(float(r["af"]), 6), round(float(r["maf"]), 6), round(float(r["missing_rate"]), 6),
+                    round(float(r["het_rate"]), 6)) == (k[5], k[6], k[7], k[9])
+        # "Cross-check af against plink_freq -- values must match exactly" (:56-66)
+        assert np.array_equal(v["af"], ops.plink_freq(c)["ALT_FREQ"])
+        s = ops.genotype_stats(c, orient="sample")
+        assert [tuple(int(r[f]) for f in cnt) for r in s] == kat.GENO_COUNTS_SAMPLE
+        assert [(int(r["n"]), round(float(r["af"]), 4), round(float(r["missing_rate"]), 4), int(r["carrier_count"]))
+                for r in s] == kat.GENO_STATS_SAMPLE
+        # variant counts and sample counts tally the same carriers (read_pfile_genotypes_counts.test:105-113)
+        assert int(v["carrier_count"].sum()) == int(s["carrier_count"].sum())
+        c.set_subset([0, 2])
+        v = ops.genotype_stats(c)
+        assert [tuple(int(r[f]) for f in cnt) for r in v] == kat.GENO_COUNTS_SUBSET_1_3
+        assert [(int(r["hom_ref"]), int(r["het"]), round(float(r["af"]), 4), round(float(r["missing_rate"]), 4))
+                for r in v] == kat.GENO_STATS_SUBSET_1_3
+        s = ops.genotype_stats(c, orient="sample")
+        assert len(s) == 2 and [tuple(int(r[f]) for f in cnt) for r in s] == [kat.GENO_COUNTS_SAMPLE[0], kat.GENO_COUNTS_SAMPLE[2]]
+        with pytest.raises(ValueError):
+            ops.genotype_stats(c, orient="genotype")
+    with _ctx("rare_small") as c:
+        s = ops.genotype_stats(c, orient="sample")
+        assert tuple(int(s[f].sum()) for f in cnt) == kat.RARE_SMALL_SUMS
+        n_, cc_, hr_ = kat.RARE_SMALL_STATS
+        assert (int(s["n"].sum()), int(s["carrier_count"].sum())) == (n_, cc_)
+        assert round(float(s["het"].sum()) / float(s["n"].sum()), 6) == hr_
+        # empty variant range: all-zero counts, NaN rates (read_pfile_sample_counts_sparse.test:49-53)
+        e = ops.genotype_stats(c, 0, 0, orient="sample")
+        assert len(e) == 256 and int(e["het"].sum()) == 0 and int(e["hom_ref"].sum()) == 0
+        assert np.isnan(e["af"]).all() and np.isnan(e["missing_rate"]).all()
+    with _ctx("all_missing") as c:  # n == 0: NaN af / maf / het_rate, missing_rate 1
+        v = ops.genotype_stats(c)
+        assert np.isnan(v["af"]).all() and np.isnan(v["maf"]).all() and np.isnan(v["het_rate"]).all()
+        assert list(v["missing_rate"]) == [1.0, 1.0] and list(v["n"]) == [0, 0]
+    with _ctx("large_example") as c:  # read_pfile_genotypes_stats.test:145-148 and the pgenlib golden counts
+        v = ops.genotype_stats(c)
+        assert len(v) == 3000
+        assert np.array_equal(np.stack([v[f] for f in cnt], axis=1), golden["large_example/counts"])
+
+
 def test_predecomp_filters_on_gpu_counts(golden):
     """CheckPreDecompFilters (src/plink_common.cpp:1495-1515) over GPU counts: af / ac ranges and the
     genotype-category filter vs the same rules evaluated with numpy on pgenlib's golden counts."""
