@@ -166,12 +166,73 @@ int ParsePgenIndex(const ByteSource& pgen, const ByteSource* pgi, PgenIndex* out
     return Fail(err, PD_ERR_NOT_SUPPORTED, "third byte does not correspond to a supported storage mode");
   }
   const uint32_t storage = ctrl & 15;
-  if (storage >= 8) {
-    // Single-sample compact encodings (pgenlib_read.cc:928-957): SURVEY row f2, next round.
-    return Fail(err, PD_ERR_NOT_SUPPORTED, "compact header_ctrl modes 8-15 are not supported yet");
-  }
   const uint32_t allele_ct_bytes = (ctrl >> 4) & 3;
   if (allele_ct_bytes > 1) return Fail(err, PD_ERR_NOT_SUPPORTED, ">254 alternate alleles are not supported");
+  // Compact header_ctrl modes 8-14 (pgenlib_read.cc:928-957 what they mean, :1260-1355 how a variant block is
+  // read): one 1-, 2- or 4-bit code per variant that fixes both the record type and its length.
+  // kNoCode marks the codes pgenlib leaves undefined.
+  constexpr uint32_t kNoCode = 0xffffffffu;
+  uint32_t compact_bits = 0;
+  uint8_t compact_type[16];
+  uint32_t compact_len[16];
+  if (storage >= 8) {
+    if (storage == 13 || storage == 15) {
+      return Fail(err, PD_ERR_NOT_SUPPORTED, "twelfth byte does not correspond to a supported format (header_ctrl mode 13 / 15)");
+    }
+    if ((storage == 12 || storage == 14) && N != 1) {
+      return Fail(err, PD_ERR_MALFORMED, "single-sample header_ctrl mode on a multi-sample file");
+    }
+    const uint32_t n4 = (N + 3) / 4;
+    for (int i = 0; i < 16; ++i) {
+      compact_type[i] = 0;
+      compact_len[i] = kNoCode;
+    }
+    compact_type[0] = 5;
+    compact_len[0] = 0;
+    compact_type[1] = 0;
+    compact_len[1] = n4;
+    compact_bits = 2;
+    if (storage == 8) {
+      compact_bits = 1;
+    } else if (storage == 9) {
+      compact_type[2] = compact_type[3] = 8;
+      compact_len[2] = n4 + 2;
+      compact_len[3] = n4 + 3;
+    } else if (storage == 10) {
+      compact_type[2] = compact_type[3] = 16;
+      compact_len[2] = n4 + 1;
+      compact_len[3] = n4 + 2;
+    } else if (storage == 11) {
+      compact_bits = 4;
+      for (uint32_t i = 2; i < 8; ++i) {
+        compact_type[i] = 8;
+        compact_len[i] = n4 + i;
+        compact_type[i + 8] = 24;
+        compact_len[i + 8] = n4 + 1 + i;
+      }
+      compact_type[9] = 16;
+      compact_len[9] = n4 + 1;
+    } else if (storage == 12) {
+      compact_type[2] = 0x45;
+      compact_len[2] = 2;
+      compact_type[3] = 0x40;
+      compact_len[3] = 3;
+    } else {  // 14
+      compact_bits = 4;
+      compact_type[3] = 0x10;
+      compact_len[3] = 2;
+      compact_type[4] = 0x45;
+      compact_len[4] = 2;
+      compact_type[5] = 0x40;
+      compact_len[5] = 3;
+      compact_type[12] = 0xc5;
+      compact_len[12] = 4;
+      compact_type[13] = 0xc0;
+      compact_len[13] = 5;
+      compact_type[15] = 0xe0;
+      compact_len[15] = 6;
+    }
+  }
   const bool wide_types = (storage & 4) != 0;       // 8-bit vs 4-bit vrtypes
   const uint32_t len_bytes = 1 + (storage & 3);
 
@@ -191,8 +252,8 @@ int ParsePgenIndex(const ByteSource& pgen, const ByteSource* pgi, PgenIndex* out
   for (uint32_t b = 0; b < vblock_ct; ++b) {
     const uint32_t v0 = b * kVblock;
     const uint32_t n = (V - v0 < kVblock) ? V - v0 : kVblock;
-    const uint64_t type_bytes = wide_types ? n : (n + 1) / 2;
-    const uint64_t lens_bytes = static_cast<uint64_t>(n) * len_bytes;
+    const uint64_t type_bytes = compact_bits ? (static_cast<uint64_t>(n) * compact_bits + 7) / 8 : (wide_types ? n : (n + 1) / 2);
+    const uint64_t lens_bytes = compact_bits ? 0 : static_cast<uint64_t>(n) * len_bytes;
     const uint64_t total = type_bytes + lens_bytes;
     buf.resize(total + 4);
     if (!hdr->ReadAt(pos, buf.data(), total)) return Fail(err, PD_ERR_READ, "header read failure (record types/lengths)");
@@ -201,13 +262,21 @@ int ParsePgenIndex(const ByteSource& pgen, const ByteSource* pgi, PgenIndex* out
     const uint8_t* lp = buf.data() + type_bytes;
     for (uint32_t i = 0; i < n; ++i) {
       uint32_t vt;
-      if (wide_types) {
-        vt = tp[i];
-      } else {
-        vt = (tp[i >> 1] >> (4 * (i & 1))) & 15;
-      }
       uint32_t len = 0;
-      memcpy(&len, lp + static_cast<size_t>(i) * len_bytes, len_bytes);
+      if (compact_bits) {
+        const uint64_t bit = static_cast<uint64_t>(i) * compact_bits;
+        const uint32_t code = (tp[bit >> 3] >> (bit & 7)) & ((1u << compact_bits) - 1);
+        if (compact_len[code] == kNoCode) return Fail(err, PD_ERR_MALFORMED, "undefined record code in a compact .pgen header");
+        vt = compact_type[code];
+        len = compact_len[code];
+      } else {
+        if (wide_types) {
+          vt = tp[i];
+        } else {
+          vt = (tp[i >> 1] >> (4 * (i & 1))) & 15;
+        }
+        memcpy(&len, lp + static_cast<size_t>(i) * len_bytes, len_bytes);
+      }
       ix.vrtypes[v0 + i] = static_cast<uint8_t>(vt);
       ix.fpos[v0 + i] = fpos;
       fpos += len;

@@ -243,3 +243,62 @@ def gen_phase(g: np.ndarray, seed: int):
         phase.append((pack(present), pack(info)))
         exp[v, info] = (1, 0)
     return phase, exp
+
+
+# header_ctrl modes 8-14 (pgenlib_read.cc:928-957): code -> (vrtype, bytes beyond / instead of the main track).
+# n4 = ceil(N / 4) is added where the record has a main 2-bit track.
+_COMPACT = {
+    8: (1, {0: (5, None), 1: (0, 0)}),
+    9: (2, {0: (5, None), 1: (0, 0), 2: (8, 2), 3: (8, 3)}),
+    10: (2, {0: (5, None), 1: (0, 0), 2: (16, 1), 3: (16, 2)}),
+    11: (4, dict([(0, (5, None)), (1, (0, 0)), (9, (16, 1))] + [(i, (8, i)) for i in range(2, 8)]
+                 + [(i + 8, (24, 1 + i)) for i in range(2, 8)])),
+    12: (2, {0: (5, None), 1: (0, 0), 2: (0x45, -2), 3: (0x40, -3)}),
+    14: (4, {0: (5, None), 1: (0, 0), 3: (0x10, -2), 4: (0x45, -2), 5: (0x40, -3), 12: (0xc5, -4), 13: (0xc0, -5),
+             15: (0xe0, -6)}),
+}
+
+
+def compact_pgen_image(storage: int, g: np.ndarray, seed: int = 0):
+    """A .pgen in one of the compact header_ctrl modes 8-14, built by hand (pgenlib's writer never emits them):
+    g is (V, N) genotypes in {0,1,2,3}; a variant whose calls are all hom-ref may get code 0 (vrtype 5, empty
+    record), the others a random code of the mode whose record starts with the 2-bit main track, followed by
+    random bytes where the code says the record carries more (those tracks are not parsed by counts / PgrGet).
+    Single-sample modes 12 / 14: codes without a main track (vrtype 0x45 / 0xc5, 2-4 bytes) stand for all-ref
+    variants too.  Returns (image, vrtypes, fpos)."""
+    bits, table = _COMPACT[storage]
+    V, N = g.shape
+    n4 = (N + 3) // 4
+    rng = np.random.default_rng(seed)
+    packed = pack_2bit_bytes(g)
+    with_main = [c for c, (vt, extra) in table.items() if (vt & 7) != 5 and (extra is None or extra >= 0 or -extra > n4)]
+    no_main = [c for c, (vt, extra) in table.items() if (vt & 7) == 5]
+    codes = np.zeros(V, dtype=np.uint8)
+    recs, vrtypes, lens = [], np.zeros(V, np.uint8), np.zeros(V, np.uint64)
+    for v in range(V):
+        if not g[v].any() and rng.random() < 0.5:
+            c = int(rng.choice(no_main))
+        else:
+            c = int(rng.choice(with_main))
+        vt, extra = table[c]
+        if (vt & 7) == 5:
+            rec = b"" if extra is None else bytes(rng.integers(0, 256, -extra, dtype=np.uint8))
+        else:
+            total = n4 + extra if extra >= 0 else -extra
+            rec = packed[v].tobytes() + bytes(rng.integers(0, 256, total - n4, dtype=np.uint8))
+        codes[v], vrtypes[v], lens[v] = c, vt, len(rec)
+        recs.append(rec)
+    nblk = (V + 65535) // 65536
+    hdr = bytearray(b"\x6c\x1b\x10") + np.array([V, N], "<u4").tobytes() + bytes([0x40 | storage])
+    blocks = bytearray()
+    for b in range(nblk):
+        cb = codes[b * 65536:(b + 1) * 65536]
+        out = np.zeros((len(cb) * bits + 7) // 8, dtype=np.uint8)
+        for i, c in enumerate(cb):
+            out[(i * bits) >> 3] |= int(c) << ((i * bits) & 7)
+        blocks += out.tobytes()
+    first = len(hdr) + 8 * nblk + len(blocks)
+    fpos = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64) + np.uint64(first)
+    offs = np.array([fpos[b * 65536] for b in range(nblk)], "<u8").tobytes()
+    image = np.frombuffer(bytes(hdr) + offs + bytes(blocks) + b"".join(recs), dtype=np.uint8).copy()
+    return image, vrtypes, fpos
