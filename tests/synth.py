@@ -286,6 +286,9 @@ def compact_pgen_image(storage: int, g: np.ndarray, seed: int = 0):
         else:
             total = n4 + extra if extra >= 0 else -extra
             rec = packed[v].tobytes() + bytes(rng.integers(0, 256, total - n4, dtype=np.uint8))
+        if storage == 12 and (vt & 0x60) == 0x40:  # single sample, unconditional dosage: one valid u16 (65535 = missing)
+            d16 = 65535 if rng.random() < 0.1 else int(rng.integers(0, 32769))
+            rec = rec[:-2] + int(d16).to_bytes(2, "little")
         codes[v], vrtypes[v], lens[v] = c, vt, len(rec)
         recs.append(rec)
     nblk = (V + 65535) // 65536

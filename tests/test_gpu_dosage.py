@@ -228,3 +228,33 @@ def test_score_tensor_core_path_vs_fp64_loop(N, K, mode, tmp_path):
             rs, rd, ra = r.score(np.arange(V, dtype=np.uint32), fl, w[:, 0], mode)
         assert np.array_equal(A, ra)
         assert np.all(np.abs(S[:, 0] - np.asarray(rs).reshape(-1)) <= bound[0])
+
+
+def test_single_sample_compact_dosage_mode_vs_pgenlib(tmp_path):
+    """header_ctrl mode 12 (pgenlib_read.cc:946-948): a single-sample file whose 2-bit codes select vrtype 5 / 0 /
+    0x45 (no hardcall track, one unconditional dosage value) / 0x40 (hardcall byte + dosage value): doubles,
+    genotype counts, dosage sums and IMP_R2 against PgrGetD / PgrGetDCounts."""
+    import synth
+    from oracle import ref
+    from plinking_duck_b200.pgen import PgenContext
+
+    if not ref.available():
+        pytest.skip("oracle/_ref not built")
+    V = 3000
+    g = synth.gen_hwe_genotypes(V, 1, seed=12, missing=0.05)
+    g[::2] = 0
+    image, vrtypes, _ = synth.compact_pgen_image(12, g, seed=5)
+    assert {0, 5, 0x40, 0x45} <= set(int(x) for x in vrtypes)
+    path = str(tmp_path / "compact12.pgen")
+    image.tofile(path)
+    with ref.RefPgen(path) as r:
+        exp_c, exp_ad, exp_r2 = r.dcounts()
+        exp_d = np.stack([r.dosage(v) for v in range(V)])
+    with PgenContext(path) as c:
+        got_c, got_ad, got_r2 = c.dosage_counts()
+        got_d = c.dosage_f64(np.arange(V))
+    assert np.array_equal(got_c, exp_c) and np.array_equal(got_ad, exp_ad)
+    assert np.array_equal(got_d, exp_d)
+    assert np.array_equal(np.isnan(got_r2), np.isnan(exp_r2))
+    ok = ~np.isnan(exp_r2)
+    assert np.array_equal(got_r2[ok], exp_r2[ok])
