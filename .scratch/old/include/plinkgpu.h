@@ -1,0 +1,217 @@
+/*
+ * plinkgpu.h -- C ABI of libplinkgpu.so, the B200 (sm_100a) genotype hot path that
+ * PlinkingDuck's table functions call instead of pgenlib.
+ *
+ * Conventions follow the reference's own C-ABI shim (src/plinking_pgen_vfs.hpp:25-47):
+ * extern "C", POD arguments, caller-owned output arrays, no exceptions, no exit(), no
+ * printing.  Every function returns 0 on success or one of PD_ERR_* (mirroring pgenlib's
+ * PglErr classes the extension already maps to IOException / InvalidInputException); a
+ * human-readable message is left in the context and readable with pd_last_error().
+ *
+ * There is NO CPU fallback: if no CUDA device is usable, pd_open* fails with PD_ERR_CUDA.
+ *
+ * Thread-safety: a pd_ctx may be shared by DuckDB's scan threads; blocking calls serialise on
+ * the context's CUDA stream.  pd_counts_fetch may be called concurrently from any number of
+ * threads on one job (src/plink_freq.cpp:434-441 keeps its fetch_add claim loop).
+ *
+ * Each entry point names the reference call site(s) it replaces.  Paths are relative to the
+ * reference repository root.
+ */
+#ifndef PLINKGPU_H_
+#define PLINKGPU_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PD_OK 0
+#define PD_ERR_OPEN 1            /* kPglRetOpenFail */
+#define PD_ERR_READ 2            /* kPglRetReadFail */
+#define PD_ERR_MALFORMED 3       /* kPglRetMalformedInput */
+#define PD_ERR_NOT_SUPPORTED 4   /* kPglRetNotYetSupported */
+#define PD_ERR_NOMEM 5           /* kPglRetNomem */
+#define PD_ERR_INVALID_ARG 6     /* kPglRetImproperFunctionCall */
+#define PD_ERR_CUDA 7            /* CUDA runtime / device failure */
+
+typedef struct pd_ctx pd_ctx;
+typedef struct pd_job pd_job;
+
+typedef struct pd_open_opts {
+  int32_t device;           /* CUDA device ordinal; -1 = current device                        */
+  uint64_t tile_bytes;      /* record bytes per staged tile; 0 = default (64 MiB)               */
+  uint32_t n_staging;       /* pinned staging buffers (>= 2, double buffering); 0 = default (3) */
+  uint32_t reserved;
+} pd_open_opts;
+
+typedef struct pd_info_t {
+  uint32_t variant_ct;      /* raw_variant_ct                                                   */
+  uint32_t sample_ct;       /* raw_sample_ct                                                    */
+  uint32_t mode;            /* storage mode byte (0x02, 0x03, 0x10, 0x11, 0x20, 0x21, 0x01)     */
+  uint32_t fixed_width;     /* record width in bytes for fixed-width modes, else 0             */
+  uint32_t has_ld;          /* any vrtype 2/3 record (kfPgenGlobalLdCompressionPresent)         */
+  uint32_t has_difflist;    /* any vrtype 1/4/6/7 record                                        */
+  uint32_t has_dosage;      /* any record with dosage bits 5-6 (kfPgenGlobalDosagePresent)      */
+  uint32_t has_phase;       /* any record with bit 4                                            */
+  uint32_t has_multiallelic;/* any record with bit 3                                            */
+  uint32_t resident;        /* 1 if a variant range is currently held in HBM                    */
+  uint64_t data_bytes;      /* sum of record widths                                             */
+  uint64_t resident_bytes;  /* bytes held in HBM                                                */
+} pd_info_t;
+
+typedef struct pd_stats_t {
+  uint64_t launches;        /* kernels launched by this library since pd_open / last reset      */
+  uint64_t h2d_bytes;       /* bytes copied host->device                                        */
+  uint64_t d2h_bytes;       /* bytes copied device->host                                        */
+  uint64_t record_bytes;    /* algorithmic record bytes scanned by the last call                */
+  double kernel_ms;         /* CUDA-event time of the dominant scan kernel(s) of the last call  */
+  double aux_kernel_ms;     /* CUDA-event time of follow-up kernels (LD fix-up, HWE, ...)       */
+  double total_ms;          /* CUDA-event time of the last call's whole device section          */
+  uint64_t scan_launches;   /* launches of the dominant scan kernel in the last call            */
+  double call_ms;           /* CUDA-event time of the last call, first enqueue to last result copy */
+  double host_stage_ms;     /* host wall time the last call spent filling staging buffers (reads, gathers) */
+  double host_wait_ms;      /* host wall time the last call spent waiting for a free staging buffer        */
+} pd_stats_t;
+
+/* ---- open / close : replaces PgfiInitPhase1 + PgfiInitPhase2 + PgrInit per scan thread
+ *      (src/plink_freq.cpp:342-390 and the same block in every *InitLocal); the header and
+ *      per-variant index are parsed ONCE. ---- */
+int pd_open(const char* pgen_path, const pd_open_opts* opts, pd_ctx** out, char* errbuf, size_t errbuf_len);
+/* Same, over a .pgen image already in host memory (not copied; must outlive the context).
+ * pgi/pgi_len: the external index for modes 0x20/0x21, else NULL/0.
+ * pgen_bytes may also be DEVICE memory on the context's device (an image produced by an upstream
+ * GPU stage): it is then used in place, permanently resident; the allocation must extend at least
+ * 64 readable bytes past len. */
+int pd_open_mem(const void* pgen_bytes, uint64_t len, const void* pgi_bytes, uint64_t pgi_len,
+                const pd_open_opts* opts, pd_ctx** out, char* errbuf, size_t errbuf_len);
+/* Header-only probe, no device needed: what the bind phase does with PgfiInitPhase1/2 to read V, N
+ * and validate the file (src/plink_freq.cpp:175-208).  vrtypes (cap entries) / fpos (cap + 1
+ * entries) are filled when non-NULL and cap >= variant_ct. */
+int pd_probe(const char* pgen_path, pd_info_t* out, uint8_t* vrtypes, uint64_t* fpos, uint32_t cap, char* errbuf,
+             size_t errbuf_len);
+void pd_close(pd_ctx* ctx);
+const char* pd_last_error(const pd_ctx* ctx);
+int pd_info(const pd_ctx* ctx, pd_info_t* out);
+/* Per-variant index, as GetPgfiVrtype / GetPgfiFpos (pgenlib_read.h:195-214).
+ * vrtypes[variant_ct], fpos[variant_ct + 1]; either may be NULL. */
+int pd_index(const pd_ctx* ctx, uint8_t* vrtypes, uint64_t* fpos);
+
+/* ---- HBM residency: stage the records of [v_begin, v_end) into device memory once and keep
+ *      them for every later call (the whole 125 GB fileset fits one B200). ---- */
+int pd_load_resident(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end);
+int pd_unload(pd_ctx* ctx);
+
+/* ---- sample subset: replaces BuildSampleSubset (src/plink_common.cpp:1222-1250).
+ *      sample_include = raw_sample_ct bits, LSB-first in little-endian 64-bit words, or NULL
+ *      for all samples.  Effective sample order = ascending raw index. ---- */
+int pd_set_sample_subset(pd_ctx* ctx, const uint64_t* sample_include, uint32_t subset_sample_ct);
+
+/* ---- per-variant genotype counts: replaces PgrGetCounts (src/plink_freq.cpp:482,
+ *      src/plink_hardy.cpp:510, src/pgen_reader.cpp:673,864, src/pfile_reader.cpp:2374).
+ *      out_counts[4*(v - v_begin) + {0,1,2,3}] = hom_ref, het, hom_alt, missing. ---- */
+int pd_counts(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t* out_counts);
+/* Counts restricted to an extra stratum mask (male / female strata of ComputeSexAwareCounts,
+ * src/plink_common.cpp:1996-2108); stratum is AND-ed with the context's subset. */
+int pd_counts_masked(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, const uint64_t* stratum_include,
+                     uint32_t* out_counts);
+/* Asynchronous form for DuckDB's claim loop: start once, fetch row ranges from any thread. */
+int pd_counts_start(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, pd_job** out);
+int pd_counts_fetch(pd_job* job, uint32_t v_begin, uint32_t v_end, uint32_t* out_counts);
+void pd_job_free(pd_job* job);
+
+/* ---- plink_hardy: counts + exact-test p-value on the device: replaces PgrGetCounts +
+ *      HweExactTestAutosomal/plink2::HweLnP (src/plink_hardy.cpp:67-79,510,572-589).
+ *      out_p[v - v_begin] = P_HWE clamped to [0,1] (1.0 when no observations).
+ *      out_counts may be NULL. ---- */
+int pd_hardy(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_t* out_counts, double* out_p);
+/* Exact-test p-values for caller-supplied counts (n x 4, as pd_counts), computed on the device. */
+int pd_hwe_from_counts(pd_ctx* ctx, const uint32_t* counts, uint32_t n, uint32_t midp, double* out_p);
+
+/* chrX non-PAR exact test on the device: replaces HweExactTestXchr -> plink2::HweXchrLnP
+ * (src/plink_hardy.cpp:83-95).  c5[5*i + {0..4}] = female hom_ref, female het, female hom_alt,
+ * male REF-hemizygous, male ALT-hemizygous. */
+int pd_hwe_xchr_from_counts(pd_ctx* ctx, const uint32_t* c5, uint32_t n, uint32_t midp, double* out_p);
+
+/* ---- plink_missing sample mode: replaces PgrGetMissingness + the ctz bit walk + mutex merge
+ *      (src/plink_missing.cpp:585-619).  out_missing[effective sample_ct]. ---- */
+int pd_missing_by_sample(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t* out_missing);
+
+/* ---- read_pfile(orient := 'sample', genotypes := 'counts'): replaces the dense and sparse
+ *      Phase-1 loops (src/pfile_reader.cpp:3322-3445).  Each array is [effective sample_ct]. ---- */
+int pd_sample_counts(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t* out_het, uint32_t* out_hom_alt,
+                     uint32_t* out_missing);
+
+/* ---- genotype decode: replaces PgrGet + GenoarrToBytesMinus9 (src/pgen_reader.cpp:727-733,
+ *      src/pfile_reader.cpp:2426-2432).  out is (v_end - v_begin) x effective sample_ct int8,
+ *      row-major, values {0,1,2,-9}. ---- */
+int pd_decode_i8(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, int8_t* out);
+
+/* ---- genotype column in DuckDB's child-vector layout: replaces PgrGet + GenoarrToBytesMinus9 AND the fill
+ *      loop that follows it (src/pgen_reader.cpp:1008-1046: ARRAY(TINYINT, N) / LIST(TINYINT) child data +
+ *      validity).  out[(v - v_begin) * n + s] = the call where it is valid, 0 where it is not; bit
+ *      ((v - v_begin) * n + s) of validity (64-bit words, LSB first, as duckdb::ValidityMask) = 1 where
+ *      valid.  A call is valid when it is not missing and call_mask has bit g set for its category g in
+ *      {0,1,2} (GenotypeFilter::AllowsCall, src/include/plink_common.hpp:471-477; 7 = no genotype filter).
+ *      validity holds ceil(rows * n / 64) words and is written whole (bits past the last call are 0). ---- */
+int pd_decode_i8_valid(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t call_mask, int8_t* out,
+                       uint64_t* validity);
+/* Same for a strictly ascending list of variants (read_pgen's effective_variant_indices, or the variants
+ * that survive CheckPreDecompFilters, src/pgen_reader.cpp:659-683): row i is variant vidx[i]. */
+int pd_decode_i8_valid_list(pd_ctx* ctx, const uint32_t* vidx, uint32_t n_var, uint32_t call_mask, int8_t* out,
+                            uint64_t* validity);
+
+/* ---- phased hardcalls : replaces PgrGetP + UnpackPhasedGenotypes (src/plink_common.cpp:1549-1584; call
+ *      sites src/pgen_reader.cpp:705-733, src/pfile_reader.cpp:1722-1745, read_pgen / read_pfile with
+ *      phased := true).  out: (v_end - v_begin) x n_out x 2 int8 allele pairs in subset order:
+ *      hom-ref 0,0; hom-alt 1,1; missing -9,-9; het 1,0 when the record's hardcall-phase track marks the
+ *      sample phased with the ALT allele first, else 0,1 (phased REF|ALT and unphased hets alike, as the
+ *      reference).  Variants without a phase track decode every het as 0,1.  Multiallelic records with a
+ *      phase track return PD_ERR_NOT_SUPPORTED. ---- */
+int pd_decode_phased(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, int8_t* out);
+
+/* ---- dosage decode: replaces PgrGetD + Dosage16ToDoublesMinus9 (src/plink_score.cpp:587-596,
+ *      src/pgen_reader.cpp:694-703).  out is n_var x effective sample_ct double, -9.0 = missing. ---- */
+int pd_dosage_f64(pd_ctx* ctx, const uint32_t* vidx, uint32_t n_var, double* out);
+
+/* ---- plink_freq(dosage := true): replaces PgrGetDCounts (src/plink_freq.cpp:475).
+ *      out_all_dosages[2*(v-v_begin)+{0,1}] in units of 1/16384 allele; out_imp_r2 may be NULL. ---- */
+int pd_dosage_counts(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t* out_counts,
+                     uint64_t* out_all_dosages, double* out_imp_r2);
+
+/* ---- plink_score: replaces the Phase-1 loop + merge (src/plink_score.cpp:562-664),
+ *      generalised to K weight columns (the reference is K = 1).
+ *      vidx[n_var] ascending scored variants, flip[n_var] (may be NULL), weights n_var x K
+ *      row-major.  mode: 0 mean-impute, 1 no_mean_imputation, 2 center.
+ *      score_sums: sample_ct x K row-major; dosage_sums[sample_ct] (NAMED_ALLELE_DOSAGE_SUM,
+ *      weight-independent; may be NULL); allele_cts[sample_ct] (may be NULL). ---- */
+#define PD_SCORE_MEAN_IMPUTE 0
+#define PD_SCORE_NO_MEAN_IMPUTATION 1
+#define PD_SCORE_CENTER 2
+int pd_score(pd_ctx* ctx, const uint32_t* vidx, const uint8_t* flip, const double* weights, uint32_t n_var,
+             uint32_t K, uint32_t mode, double* score_sums, double* dosage_sums, uint32_t* allele_cts);
+
+/* ---- device-side results for multi-GPU reductions.  After pd_score / pd_missing_by_sample /
+ *      pd_sample_counts (whose host output pointers may then be NULL), the accumulators of the last
+ *      call stay in HBM; the caller all-reduces them in place over NVLink (NCCL) and reads them back
+ *      once, instead of bouncing every rank's partial sums through host memory.
+ *      which: PD_RESULT_SCORE (double[sample_ct x K]), PD_RESULT_DOSAGE_SUM (double[sample_ct]),
+ *      PD_RESULT_ALLELE_CT (uint32[sample_ct]), PD_RESULT_SAMPLE_COUNTS (uint32[3 x sample_ct]:
+ *      het, hom_alt, missing).  The pointers are valid until the next call on the context. ---- */
+#define PD_RESULT_SCORE 0
+#define PD_RESULT_DOSAGE_SUM 1
+#define PD_RESULT_ALLELE_CT 2
+#define PD_RESULT_SAMPLE_COUNTS 3
+int pd_device_result(pd_ctx* ctx, uint32_t which, void** dev_ptr, uint64_t* bytes);
+
+/* ---- instrumentation (the reference has only BindPhaseTimer, src/include/plink_profile.hpp) ---- */
+int pd_get_stats(const pd_ctx* ctx, pd_stats_t* out);
+int pd_reset_stats(pd_ctx* ctx);
+/* Library / build identification: "plinkgpu <version> sm_100a". */
+const char* pd_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PLINKGPU_H_ */

@@ -1,0 +1,70 @@
+// Host-side .pgen header / per-variant index (parsed once per context).
+//
+// Replaces the per-thread PgfiInitPhase1 + PgfiInitPhase2Ex of the reference
+// (third_party/plink-ng/2.0/include/pgenlib_read.cc:689-961, 1099-1680) with one parse whose
+// result (vrtypes[V], fpos[V+1], ldbase[V]) is uploaded to the GPU.  Written from the format
+// specification (third_party/plink-ng/pgen_spec/pgen_spec.tex:122-320); not a port of pgenlib.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace pdx {
+
+// Random-access byte source over either a file descriptor or a caller-owned memory image.
+class ByteSource {
+ public:
+  ByteSource() = default;
+  ~ByteSource();
+  ByteSource(const ByteSource&) = delete;
+  ByteSource& operator=(const ByteSource&) = delete;
+  bool OpenFile(const char* path, std::string* err);
+  void OpenMem(const void* p, uint64_t len);
+  // A .pgen image that already lives in device memory (reads go through cudaMemcpy).
+  void OpenDevice(const void* p, uint64_t len);
+  const uint8_t* dev() const { return dev_; }
+  uint64_t size() const { return size_; }
+  bool is_mem() const { return mem_ != nullptr; }
+  const uint8_t* mem() const { return mem_; }
+  // Host-addressable bytes of the whole source: the caller's memory, or a read-only mapping of the
+  // file (nullptr if the mapping failed or the image lives on the device).
+  const uint8_t* view() const { return mem_ ? mem_ : map_; }
+  // Reads exactly len bytes at off into dst; false on short read / error.
+  bool ReadAt(uint64_t off, void* dst, uint64_t len) const;
+
+ private:
+  int fd_ = -1;
+  const uint8_t* mem_ = nullptr;
+  const uint8_t* map_ = nullptr;
+  const uint8_t* dev_ = nullptr;
+  uint64_t size_ = 0;
+};
+
+struct PgenIndex {
+  uint32_t variant_ct = 0;
+  uint32_t sample_ct = 0;
+  uint32_t mode = 0;
+  uint32_t header_ctrl = 0;
+  bool fixed = false;          // storage modes 0x02-0x04
+  uint32_t fixed_width = 0;    // bytes per record when fixed
+  uint32_t const_vrtype = 0;   // vrtype of every record when fixed
+  uint64_t data_start = 0;     // file offset of record 0
+  uint64_t data_bytes = 0;     // sum of record widths
+  // Variable-width modes only (empty when fixed):
+  std::vector<uint8_t> vrtypes;   // [V]
+  std::vector<uint64_t> fpos;     // [V+1]
+  // ldbase[v] = index of the last variant <= v whose main track is not LD-compressed
+  // (semantics of GetLdbaseVidx, pgenlib_read.cc:1846-1894); ldbase[v] == v for non-LD records.
+  std::vector<uint32_t> ldbase;   // [V]
+  bool has_ld = false, has_difflist = false, has_dosage = false, has_phase = false, has_multiallelic = false;
+  uint32_t max_width = 0;
+
+  uint64_t RecOff(uint32_t v) const { return fixed ? data_start + static_cast<uint64_t>(v) * fixed_width : fpos[v]; }
+  uint32_t Vrtype(uint32_t v) const { return fixed ? const_vrtype : vrtypes[v]; }
+  uint32_t Ldbase(uint32_t v) const { return fixed ? v : ldbase[v]; }
+};
+
+// Error codes match include/plinkgpu.h PD_ERR_*.
+int ParsePgenIndex(const ByteSource& pgen, const ByteSource* pgi, PgenIndex* out, std::string* err);
+
+}  // namespace pdx

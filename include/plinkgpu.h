@@ -128,6 +128,11 @@ void pd_job_free(pd_job* job);
 int pd_hardy(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_t* out_counts, double* out_p);
 /* Exact-test p-values for caller-supplied counts (n x 4, as pd_counts), computed on the device. */
 int pd_hwe_from_counts(pd_ctx* ctx, const uint32_t* counts, uint32_t n, uint32_t midp, double* out_p);
+/* Same test, but out_lnp[i] = ln p: what plink2::HweLnP itself returns (plink2_stats.cc:1784-2166) before
+ * LnPToPvalue exponentiates and clamps it (src/plink_hardy.cpp:52-64).  Finite where p underflows to 0
+ * (an observed table 10^-400 vs 10^-40000 under HWE), -inf only for a mid-p of exactly 0; 0.0 for tables
+ * without observations. */
+int pd_hwe_lnp_from_counts(pd_ctx* ctx, const uint32_t* counts, uint32_t n, uint32_t midp, double* out_lnp);
 
 /* chrX non-PAR exact test on the device: replaces HweExactTestXchr -> plink2::HweXchrLnP
  * (src/plink_hardy.cpp:83-95).  c5[5*i + {0..4}] = female hom_ref, female het, female hom_alt,

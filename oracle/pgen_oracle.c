@@ -526,6 +526,103 @@ double po_hwe_exact(uint32_t obs_hets, uint32_t obs_hom1, uint32_t obs_hom2, int
   return p;
 }
 
+/* ---- exact Hardy-Weinberg test, ln p, extended precision -----------------------------------------
+ * Same definition as po_hwe_exact (HweLnP's result before LnPToPvalue, plink2_stats.cc:1784-2166;
+ * src/plink_hardy.cpp:52-79), but (1) in x87 long double (64-bit mantissa: the ~1e5 recurrence steps of
+ * a biobank-sized table cost < 1e-14 relative) and (2) with every quantity carried as mantissa x 2^e with a
+ * 64-bit exponent, so the answer is ln p all the way down (HweLnP returns e.g. -40000 where p underflows).
+ * This is the yardstick the parity tests use to state what the reference's own log-factorial noise is and
+ * what the device kernel's error is.  Tables with probability within 2^-38 of the observed one count as ties. */
+typedef struct {
+  long double m; /* 0 or in [2^-4000, 2^4000) after xf_norm */
+  long long e;
+} xf_t;
+
+static xf_t xf_norm(xf_t a) {
+  if (a.m == 0.0L) {
+    a.e = 0;
+    return a;
+  }
+  while (a.m >= 0x1p4000L) {
+    a.m *= 0x1p-4000L;
+    a.e += 4000;
+  }
+  while (a.m < 0x1p-4000L) {
+    a.m *= 0x1p4000L;
+    a.e -= 4000;
+  }
+  return a;
+}
+
+static xf_t xf_add(xf_t a, xf_t b) {
+  if (a.m == 0.0L) return b;
+  if (b.m == 0.0L) return a;
+  if (a.e < b.e) {
+    const xf_t t = a;
+    a = b;
+    b = t;
+  }
+  const long long d = a.e - b.e; /* multiple of 4000 */
+  if (d >= 12000) return a;
+  long double bm = b.m;
+  for (long long i = 0; i < d; i += 4000) bm *= 0x1p-4000L;
+  a.m += bm;
+  return xf_norm(a);
+}
+
+/* a <= b * (1 + rel) ? */
+static int xf_le1(xf_t a, long double bound) {
+  if (a.m == 0.0L) return 1;
+  if (a.e != 0) return a.e < 0;
+  return a.m <= bound;
+}
+
+double po_hwe_lnp_exact(uint32_t obs_hets, uint32_t obs_hom1, uint32_t obs_hom2, int midp) {
+  const long double r0 = obs_hom1 < obs_hom2 ? obs_hom1 : obs_hom2;
+  const long double c0 = obs_hom1 < obs_hom2 ? obs_hom2 : obs_hom1;
+  if (2.0L * r0 + obs_hets < 2.0L) return midp ? -0.6931471805599453094 : 0.0;
+  const long double eps = 3.637978807091713e-12L;
+  xf_t tail = {1.0L, 0}, center = {0.0L, 0};
+  long double ties = 1.0L;
+  for (int dir = 0; dir < 2; ++dir) {
+    long double k = obs_hets, r = r0, c = c0;
+    xf_t t = {1.0L, 0};
+    for (;;) {
+      if (dir == 0) { /* fewer heterozygotes */
+        if (k < 1.5L) break;
+        r += 1.0L;
+        c += 1.0L;
+        t.m *= (k * (k - 1.0L)) / (4.0L * r * c);
+        k -= 2.0L;
+      } else { /* more heterozygotes */
+        if (r < 0.5L) break;
+        k += 2.0L;
+        t.m *= (4.0L * r * c) / (k * (k - 1.0L));
+        r -= 1.0L;
+        c -= 1.0L;
+      }
+      t = xf_norm(t);
+      if (!xf_le1(t, 1.0L + eps)) {
+        center = xf_add(center, t);
+      } else {
+        if (t.e == 0 && t.m >= 1.0L - eps) ties += 1.0L;
+        const xf_t before = tail;
+        tail = xf_add(tail, t);
+        if (tail.e == before.e && tail.m == before.m) break; /* unimodal: every later term is smaller */
+      }
+    }
+  }
+  const xf_t total = xf_add(tail, center);
+  xf_t num = tail;
+  if (midp) { /* tail.e == 0: it is a sum of at most 2^31 terms <= 1 + eps */
+    num.m -= 0.5L * ties;
+    if (num.m <= 0.0L) return -INFINITY;
+    num = xf_norm(num);
+  }
+  const long double lnp = logl(num.m / total.m) + (long double)(num.e - total.e) * 0.693147180559945309417232121458L;
+  return lnp > 0.0L ? 0.0 : (double)lnp;
+}
+
 /* ---- plink_score ---------------------------------------------------------------------------------
  * The Phase-1 loop of src/plink_score.cpp:582-653 for one weight vector, hardcall records
  * (PgrGetD + Dosage16ToDoublesMinus9 yield 0.0 / 1.0 / 2.0 / -9.0 for them), same operation order,

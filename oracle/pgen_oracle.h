@@ -41,6 +41,8 @@ int po_decode_phased(po_file* f, uint32_t v0, uint32_t v1, int8_t* out);
 int po_missing_by_sample(po_file* f, uint32_t v0, uint32_t v1, uint32_t* out);
 /* Exact Hardy-Weinberg test p-value (autosomal, optional mid-p), clamped to [0, 1]. */
 double po_hwe_exact(uint32_t obs_hets, uint32_t obs_hom1, uint32_t obs_hom2, int midp);
+/* ln p of the same test in x87 long double with a 64-bit exponent (no underflow): the parity yardstick. */
+double po_hwe_lnp_exact(uint32_t obs_hets, uint32_t obs_hom1, uint32_t obs_hom2, int midp);
 /* plink_score accumulation for one weight column.  mode 0 mean-impute, 1 no_mean_imputation,
  * 2 center.  score/dosage_sum/allele_ct: [N], accumulated into (caller zeroes them). */
 int po_score(po_file* f, const uint32_t* vidx, const uint8_t* flip, const double* weights, uint32_t n, int mode,

@@ -38,6 +38,8 @@ def lib():
         L.po_missing_by_sample.argtypes = [vp, u32, u32, vp]
         L.po_hwe_exact.argtypes = [u32, u32, u32, C.c_int]
         L.po_hwe_exact.restype = C.c_double
+        L.po_hwe_lnp_exact.argtypes = [u32, u32, u32, C.c_int]
+        L.po_hwe_lnp_exact.restype = C.c_double
         L.po_score.argtypes = [vp, vp, vp, vp, u32, C.c_int, vp, vp, vp]
         _lib = L
     return _lib
@@ -49,6 +51,11 @@ def _p(a):
 
 def hwe_exact(hets: int, hom1: int, hom2: int, midp: bool = False) -> float:
     return float(lib().po_hwe_exact(hets, hom1, hom2, 1 if midp else 0))
+
+
+def hwe_lnp_exact(hets: int, hom1: int, hom2: int, midp: bool = False) -> float:
+    """ln p in x87 long double with an unbounded exponent (po_hwe_lnp_exact): the yardstick for HWE parity."""
+    return float(lib().po_hwe_lnp_exact(int(hets), int(hom1), int(hom2), 1 if midp else 0))
 
 
 class PortPgen:

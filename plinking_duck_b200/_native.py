@@ -63,6 +63,7 @@ SYMBOLS = {
     "pd_job_free": (None, [_vp]),
     "pd_hardy": (C.c_int, [_vp, _u32, _u32, _u32, _vp, _vp]),
     "pd_hwe_from_counts": (C.c_int, [_vp, _vp, _u32, _u32, _vp]),
+    "pd_hwe_lnp_from_counts": (C.c_int, [_vp, _vp, _u32, _u32, _vp]),
     "pd_hwe_xchr_from_counts": (C.c_int, [_vp, _vp, _u32, _u32, _vp]),
     "pd_missing_by_sample": (C.c_int, [_vp, _u32, _u32, _vp]),
     "pd_sample_counts": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),

@@ -28,7 +28,7 @@ void DestroyCtx(pd_ctx* c) {
   for (auto e : c->ev_copied) cudaEventDestroy(e);
   for (auto e : c->ev_done) cudaEventDestroy(e);
   for (auto e : c->ev_pool) cudaEventDestroy(e);
-  c->d_counts.Free(); c->d_scratch.Free(); c->d_misc.Free(); c->d_pvals.Free(); c->d_acc.Free(); c->d_ready.Free(); c->d_trim_fpos.Free(); c->d_phase_raw.Free();
+  c->d_counts.Free(); c->d_scratch.Free(); c->d_misc.Free(); c->d_pvals.Free(); c->d_acc.Free(); c->d_ready.Free(); c->d_hweq.Free(); c->d_trim_fpos.Free(); c->d_phase_raw.Free();
   c->d_dense.Free(); c->d_rowptrs.Free(); c->d_vlist.Free();
   c->d_loc.Free(); c->d_rank.Free(); c->d_dstats.Free(); c->d_srow.Free(); c->d_weights.Free(); c->d_flip.Free();
   c->d_score.Free(); c->d_dsum.Free(); c->d_act.Free(); c->d_tc.Free();
@@ -70,6 +70,8 @@ int InitDevice(pd_ctx* c, const pd_open_opts* opts) {
   if (dev >= ndev) return c->SetError(PD_ERR_INVALID_ARG, "device ordinal out of range");
   c->device = dev;
   if ((e = cudaSetDevice(dev)) != cudaSuccess) return CheckCuda(c, e, "cudaSetDevice");
+  cudaDeviceGetAttribute(&c->launch_stats.sm_count, cudaDevAttrMultiProcessorCount, dev);
+  pdk::configure_device_kernels();
   if (opts && opts->tile_bytes) c->tile_bytes = opts->tile_bytes;
   if (opts && opts->n_staging) c->n_staging = std::max<uint32_t>(2, opts->n_staging);
   if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return CheckCuda(c, e, "stream");

@@ -232,6 +232,7 @@ int pd_hardy(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_
     // so rows start at v_begin).
     e = c->d_counts.Reserve(static_cast<size_t>(n) * 16);
     if (e == cudaSuccess) e = c->d_ready.Reserve(static_cast<size_t>(n) * 4);
+    if (e == cudaSuccess) e = c->d_hweq.Reserve((static_cast<size_t>(n) + pdk::kHweQueueWords) * 4);
     if (e != cudaSuccess) return CheckCuda(c, e, "counts allocation");
     const pdk::SubsetDev sd = c->subset.Dev();
     uint4* out_dev = c->d_counts.as<uint4>();
@@ -254,7 +255,7 @@ int pd_hardy(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_
     bool all_fused = true;
     rc = RunScan(c, v_begin, v_end, &v_ext, [&](const Tile& t, const pdk::RecIndex& ix, cudaStream_t s) {
       const uint32_t off = t.v0 - v_begin;
-      if (!pdk::launch_hardy_fixed(ix, sd, t.v0, t.v1, out_dev + off, p_dev + off, midp, DevWorkCounter(c),
+      if (!pdk::launch_hardy_fixed(ix, sd, t.v0, t.v1, out_dev + off, p_dev + off, midp, c->d_hweq.as<uint32_t>(),
                                    ready + off, s, &c->launch_stats, host_counts ? host_counts + off : nullptr)) {
         all_fused = false;
         pdk::launch_count_fixed(ix, sd, t.v0, t.v1, out_dev + off, s, &c->launch_stats);
@@ -270,8 +271,12 @@ int pd_hardy(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_
   }
   if (!n) return PD_OK;
   const uint4* counts = c->d_counts.as<uint4>() + (v_begin - v_ext);
+  if (!fused) {
+    e = c->d_hweq.Reserve((static_cast<size_t>(n) + pdk::kHweQueueWords) * 4);
+    if (e != cudaSuccess) return CheckCuda(c, e, "exact-test queue allocation");
+  }
   cudaEventRecord(c->ev_a, c->stream);
-  if (!fused) pdk::launch_hwe(counts, n, midp, c->d_pvals.as<double>(), DevWorkCounter(c), c->stream, &c->launch_stats);
+  if (!fused) pdk::launch_hwe(counts, n, midp, c->d_pvals.as<double>(), c->d_hweq.as<uint32_t>(), c->stream, &c->launch_stats);
   cudaEventRecord(c->ev_b, c->stream);
   e = cudaSuccess;
   if (!(direct && fused)) {
@@ -292,27 +297,37 @@ int pd_hardy(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_
   return PD_OK;
 }
 
-int pd_hwe_from_counts(pd_ctx* c, const uint32_t* counts, uint32_t n, uint32_t midp, double* out_p) {
-  if (!c || (n && (!counts || !out_p))) return PD_ERR_INVALID_ARG;
+static int HweFromCounts(pd_ctx* c, const uint32_t* counts, uint32_t n, uint32_t midp, double* out, bool want_lnp) {
+  if (!c || (n && (!counts || !out))) return PD_ERR_INVALID_ARG;
   if (!n) return PD_OK;
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   cudaError_t e = c->d_counts.Reserve(static_cast<size_t>(n) * 16);
   if (e == cudaSuccess) e = c->d_pvals.Reserve(static_cast<size_t>(n) * 8);
+  if (e == cudaSuccess) e = c->d_hweq.Reserve((static_cast<size_t>(n) + pdk::kHweQueueWords) * 4);
   if (e != cudaSuccess) return CheckCuda(c, e, "allocation");
   e = cudaMemcpyAsync(c->d_counts.p, counts, static_cast<size_t>(n) * 16, cudaMemcpyHostToDevice, c->stream);
   if (e != cudaSuccess) return CheckCuda(c, e, "counts upload");
   c->stats.h2d_bytes += static_cast<size_t>(n) * 16;
   cudaEventRecord(c->ev_a, c->stream);
-  pdk::launch_hwe(c->d_counts.as<uint4>(), n, midp, c->d_pvals.as<double>(), DevWorkCounter(c), c->stream, &c->launch_stats);
+  pdk::launch_hwe(c->d_counts.as<uint4>(), n, midp, c->d_pvals.as<double>(), c->d_hweq.as<uint32_t>(), c->stream,
+                  &c->launch_stats, want_lnp);
   cudaEventRecord(c->ev_b, c->stream);
-  int rc = DownloadRows(c, c->d_pvals.p, static_cast<size_t>(n) * 8, out_p);
+  int rc = DownloadRows(c, c->d_pvals.p, static_cast<size_t>(n) * 8, out);
   if (rc == PD_OK) {
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev_a, c->ev_b);
     c->stats.aux_kernel_ms = ms;
   }
   return rc;
+}
+
+int pd_hwe_from_counts(pd_ctx* c, const uint32_t* counts, uint32_t n, uint32_t midp, double* out_p) {
+  return HweFromCounts(c, counts, n, midp, out_p, false);
+}
+
+int pd_hwe_lnp_from_counts(pd_ctx* c, const uint32_t* counts, uint32_t n, uint32_t midp, double* out_lnp) {
+  return HweFromCounts(c, counts, n, midp, out_lnp, true);
 }
 
 int pd_hwe_xchr_from_counts(pd_ctx* c, const uint32_t* c5, uint32_t n, uint32_t midp, double* out_p) {

@@ -94,7 +94,7 @@ struct pd_ctx_impl {
   std::vector<cudaEvent_t> ev_copied, ev_done;
 
   // work buffers
-  DevBuf d_counts, d_scratch, d_misc, d_pvals, d_acc, d_ready;
+  DevBuf d_counts, d_scratch, d_misc, d_pvals, d_acc, d_ready, d_hweq;  // d_hweq: exact-test queue words + overflow list
   const pdk::SparseAcc* sparse_acc = nullptr;  // set by SampleAccumulate around RunRows: difflist records skip densify
   DevBuf d_dense, d_rowptrs, d_vlist, d_out[2];  // dense-row batches and their outputs
   DevBuf d_loc, d_rank, d_dstats, d_srow, d_weights, d_flip, d_score, d_dsum, d_act, d_tc;  // dosage / score

@@ -19,15 +19,17 @@
 //  * The two directions are independent dependency chains; they are stepped together, which halves
 //    the number of loop trips and gives every lane two fp64 chains to overlap.
 //  * The walk length differs by ~4x between variants (it scales with sqrt(N p q)), so the lanes
-//    of a warp pull variants from a warp-local queue (hwe_warp_queue): a lane that finishes its
+//    of a warp pull variants from a window of 32 claimed by the warp (hwe_consume): a lane that finishes its
 //    table takes the next variant while its neighbours keep walking theirs.
 #pragma once
 #include <cuda_runtime.h>
+#include <math_constants.h>
 #include <stdint.h>
 
 namespace pdk {
 
 constexpr double kHweTieEps = 3.637978807091713e-12;  // 2^-38: relative window for "same probability"
+constexpr int kHweCenterHiLimit = 0x7de00000;         // high word of 2^991
 
 struct HweDir {
   double t;              // probability of the current table relative to the observed one (0 once finished)
@@ -121,7 +123,9 @@ __device__ __forceinline__ bool hwe_walk_t(HweLane& s, bool on, int max_steps) {
     if (on) {
       hwe_dir_step<MIDP>(dn, tail, center, ties);
       hwe_dir_step<MIDP>(up, tail, center, ties);
-      fin = (__double2hiint(dn.t) | __double2hiint(up.t)) == 0;
+      // also leave when the centre mass nears the top of the fp64 range (>= 2^991, inf and NaN included):
+      // the table is finished by hwe_scaled_lnp instead
+      fin = ((__double2hiint(dn.t) | __double2hiint(up.t)) == 0) | (__double2hiint(center) >= kHweCenterHiLimit);
     }
   }
   s.dn = dn;
@@ -136,52 +140,92 @@ __device__ __forceinline__ bool hwe_walk(HweLane& s, bool on, int max_steps, boo
   return midp ? hwe_walk_t<true>(s, on, max_steps) : hwe_walk_t<false>(s, on, max_steps);
 }
 
-// p-value of a finished table.
-__device__ __forceinline__ double hwe_finish(const HweLane& s, bool midp) {
-  double q = 0.0;  // center overflowed: the observed table is > 1e308 times less likely than the mode
-  if (s.center < 1.7e308) {
-    double tail = s.tail;
-    if (midp) tail -= 0.5 * static_cast<double>(s.ties);
-    q = tail / (s.tail + s.center);
-    if (q < 0.0) q = 0.0;
-    if (q > 1.0) q = 1.0;
+// A table whose observed cell is more than ~2^990 times less likely than the mode (p below ~1e-298): the plain
+// walk above overflows.  This one carries the running term and the centre mass as mantissa x 2^(512 e), so
+// it returns ln p however small p is (HweLnP returns -40000 just the same, plink2_stats.cc:1845-1849
+// "A p-value of 1e-400 may be worth distinguishing from 1e-40000").  One lane, both directions in turn; rare.
+__device__ __forceinline__ double hwe_scaled_lnp(uint32_t obs_hets, uint32_t hom_a, uint32_t hom_b, bool midp) {
+  const uint32_t r0 = hom_a < hom_b ? hom_a : hom_b;
+  const uint32_t c0 = hom_a < hom_b ? hom_b : hom_a;
+  const double k = static_cast<double>(obs_hets), r = static_cast<double>(r0), c = static_cast<double>(c0);
+  constexpr double kUp = 1.3407807929942597e154, kDown = 7.458340731200207e-155;  // 2^512, 2^-512
+  double tail = 1.0, cm = 0.0;
+  int ce = 0;  // centre mass = cm * 2^(512 ce)
+  uint32_t ties = 1;
+#pragma unroll 1
+  for (int dir = 0; dir < 2; ++dir) {
+    double A, dA, B, dB, t;
+    if (dir == 0) {
+      A = k * (k - 1.0); dA = 6.0 - 4.0 * k; B = 4.0 * (r + 1.0) * (c + 1.0); dB = 4.0 * (r + c) + 12.0;
+      t = obs_hets >= 2 ? 1.0 : 0.0;
+    } else {
+      A = 4.0 * r * c; dA = 4.0 - 4.0 * (r + c); B = (k + 2.0) * (k + 1.0); dB = 4.0 * k + 10.0;
+      t = r0 ? 1.0 : 0.0;
+    }
+    int te = 0;  // term = t * 2^(512 te)
+#pragma unroll 1
+    while (t != 0.0) {
+      t *= A * hwe_rcp(B);
+      A += dA; dA += 8.0; B += dB; dB += 8.0;
+      if (t == 0.0) break;  // end of the range (A reached 0)
+      if (t >= kUp) {
+        t *= kDown;
+        ++te;
+      } else if (te > 0 && t < kDown) {
+        t *= kUp;
+        --te;
+      }
+      if (te > 0 || t > 1.0 + kHweTieEps) {
+        if (te == ce) {
+          cm += t;
+        } else if (te > ce) {
+          const int d = te - ce;
+          cm = d == 1 ? fma(cm, kDown, t) : (d == 2 ? fma(cm * kDown, kDown, t) : t);
+          ce = te;
+        } else {
+          const int d = ce - te;
+          if (d == 1) cm = fma(t, kDown, cm);
+          else if (d == 2) cm = fma(t * kDown, kDown, cm);
+        }
+        if (cm >= kUp) {
+          cm *= kDown;
+          ++ce;
+        }
+      } else {
+        ties += (t >= 1.0 - kHweTieEps) ? 1u : 0u;
+        const double nt = tail + t;
+        if (!(nt > tail)) break;  // unimodal: every later term is smaller still
+        tail = nt;
+      }
+    }
   }
-  return q;
+  double num = tail;
+  if (midp) num -= 0.5 * static_cast<double>(ties);
+  if (!(num > 0.0)) return -CUDART_INF;
+  double total = cm;
+  if (ce == 0) total += tail;
+  else if (ce == 1) total = fma(tail, kDown, cm);
+  else if (ce == 2) total = fma(tail * kDown, kDown, cm);
+  const double lnp = log(num / total) - static_cast<double>(ce) * 354.89135644669199843;  // 512 ln 2
+  return lnp < 0.0 ? lnp : 0.0;
 }
 
-// Whole-warp call: p-values of items [0, n) -- get(i) returns the item's (hom_ref, het, hom_alt, *)
-// counts, put(i, p) stores its result.  All 32 lanes must call it with the same n.
-template <class Get, class Put>
-__device__ __forceinline__ void hwe_warp_queue(uint32_t n, bool midp, Get get, Put put) {
-  const uint32_t lane = threadIdx.x & 31u;
-  uint32_t next = 0;      // warp-uniform: first item nobody has taken yet
-  uint32_t mine = ~0u;    // item this lane is walking
-  HweLane s;
-  s.dn.t = s.up.t = 0.0;
-  for (;;) {
-    const uint32_t idle = __ballot_sync(0xffffffffu, mine == ~0u);
-    if (idle && next < n) {
-      if (mine == ~0u) {
-        const uint32_t i = next + __popc(idle & ((1u << lane) - 1u));
-        if (i < n) {
-          const uint4 cnt = get(i);
-          double p;
-          if (hwe_begin(cnt.y, cnt.x, cnt.z, midp, s, &p)) {
-            put(i, p);
-          } else {
-            mine = i;
-          }
-        }
-      }
-      next += __popc(idle);
-      continue;  // lanes whose item was trivial try again
-    }
-    if (idle == 0xffffffffu) break;  // queue empty and nobody walking
-    if (hwe_walk(s, mine != ~0u, 0x7fffffff, midp)) {
-      put(mine, hwe_finish(s, midp));
-      mine = ~0u;
-    }
+// Stores the result of a table hwe_walk reported finished: p clamped to [0,1] (LnPToPvalue,
+// src/plink_hardy.cpp:52-64) or ln p.  A table that left the walk because its centre mass neared the top of
+// the fp64 range is appended to the overflow list instead (ovf[0] = count, ovf[2 + i] = item) and finished by
+// k_hwe_scaled right after this kernel -- keeping that rare, long path out of the hot kernels' register budget.
+template <bool LNP>
+__device__ __forceinline__ void hwe_store(const HweLane& s, bool midp, uint32_t item, double* out_p, uint32_t* ovf) {
+  if (__double2hiint(s.center) >= kHweCenterHiLimit) {
+    ovf[2u + atomicAdd(ovf, 1u)] = item;
+    return;
   }
+  double tail = s.tail;
+  if (midp) tail -= 0.5 * static_cast<double>(s.ties);
+  double q = tail / (s.tail + s.center);
+  if (q < 0.0) q = 0.0;
+  if (q > 1.0) q = 1.0;
+  out_p[item] = LNP ? log(q) : q;
 }
 
 __device__ __forceinline__ uint32_t hwe_ld_acquire(const uint32_t* p) {
@@ -191,9 +235,11 @@ __device__ __forceinline__ uint32_t hwe_ld_acquire(const uint32_t* p) {
 }
 
 // Whole-warp call, any number of warps of a grid at once: exact tests of variants [0, n), claimed
-// in windows of 32 from the device counter *next_window.  ready (optional): variant v may only be
+// in windows of 32 from the device counter *next_window; next_window + 1 is the overflow list of hwe_store
+// (count, pad, then up to n items).  ready (optional): variant v may only be
 // read once ready[v] != 0 (release-published by the warp that counted it); lanes whose variant is
 // not ready yet keep polling while the others walk.
+template <bool LNP = false>
 __device__ __forceinline__ void hwe_consume(uint32_t* next_window, uint32_t n, const uint32_t* ready,
                                             const uint4* counts, double* out_p, bool midp) {
   const uint32_t lane = threadIdx.x & 31u;
@@ -235,7 +281,7 @@ __device__ __forceinline__ void hwe_consume(uint32_t* next_window, uint32_t n, c
         const uint4 cnt = __ldcg(counts + mine);
         double pv;
         if (hwe_begin(cnt.y, cnt.x, cnt.z, midp, s, &pv)) {
-          out_p[mine] = pv;
+          out_p[mine] = LNP ? log(pv) : pv;
           mine = ~0u;
         } else {
           started = true;
@@ -248,7 +294,7 @@ __device__ __forceinline__ void hwe_consume(uint32_t* next_window, uint32_t n, c
     }
     // walk until a lane needs attention (bounded when lanes still waiting for counts must be polled again)
     if (hwe_walk(s, mine != ~0u && started, ready ? 64 : 0x7fffffff, midp)) {
-      out_p[mine] = hwe_finish(s, midp);
+      hwe_store<LNP>(s, midp, mine, out_p, next_window + 1);
       mine = ~0u;
     }
   }

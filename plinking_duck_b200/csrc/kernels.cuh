@@ -38,9 +38,15 @@ struct LdScratch {
   uint32_t slot_lo;
 };
 
+// Per-context launch state: every launch wrapper receives the owning context's copy, so one process can
+// drive several devices (no process-wide caches of device properties).
 struct LaunchStats {
   uint64_t launches = 0;
+  int sm_count = 0;  // multiprocessors of the context's device (set at pd_open)
 };
+inline int sm_of(const LaunchStats* st) { return st && st->sm_count > 0 ? st->sm_count : 148; }
+// Per-device function attributes (dynamic shared memory of k_score_mma); call with the device current.
+void configure_device_kernels();
 
 // ---- subset mask construction ----
 void launch_build_masks(const uint32_t* include_words, uint32_t N, uint8_t* mask2_shifts, uint32_t mask2_stride,
@@ -55,7 +61,7 @@ void launch_count_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_beg
 
 // ---- K1h: plink_hardy over fixed-width records, counts and exact test in one kernel ----
 // Returns false (nothing launched) when the records are too short for the fused form; the caller
-// then runs launch_count_fixed + launch_hwe.  queue: device uint32[2]; ready: device uint32[nrec].
+// then runs launch_count_fixed + launch_hwe.  queue: as launch_hwe (kHweQueueWords + nrec words); ready: device uint32[nrec].
 // out_p may be the device view of page-locked host memory (p-values are write-only for the kernel);
 // host_out, when given, is such a view for the counts, written in addition to out.
 bool hardy_fused_applicable(uint32_t N);
@@ -190,9 +196,15 @@ void launch_score_tc(const DenseRows& rows, const uint4* counts, const ScoreRow*
 
 // ---- K8: exact Hardy-Weinberg test on the device ----
 // counts[n] as produced by the count kernels; out_p[n] = p-value clamped to [0,1].
-// queue: device uint32 work counter (zeroed by the wrapper).
+// queue: device uint32[kHweQueueWords + n], zeroed by the wrapper: [0] K1h record-chunk counter, [1] window
+// counter of the exact-test warps, [2] number of tables set aside for k_hwe_scaled, [3] pad, [4..] those tables.
+constexpr uint32_t kHweQueueWords = 4;
+// Finishes the tables the walk kernels set aside (queue as above, filled by the preceding launch on s).
+void launch_hwe_scaled(const uint4* counts, const uint32_t* queue, uint32_t midp, double* out_p, bool want_lnp,
+                       cudaStream_t s, LaunchStats* st);
+// want_lnp: store ln p (HweLnP's own return value; finite where p underflows) instead of p.
 void launch_hwe(const uint4* counts, uint32_t n, uint32_t midp, double* out_p, uint32_t* queue, cudaStream_t s,
-                LaunchStats* st);
+                LaunchStats* st, bool want_lnp = false);
 // chrX exact test: c5[n][5] = female hom_ref, het, hom_alt, male ref, male alt.
 void launch_hwe_xchr(const uint32_t* c5, uint32_t n, uint32_t midp, double* out_p, cudaStream_t s, LaunchStats* st);
 

@@ -57,7 +57,7 @@ k_count_fixed(const uint8_t* __restrict__ data, uint64_t first_off, uint32_t wid
 // chunks of records from a counter and count them exactly like K1 (a whole warp per record); each
 // finished record is published with a release store to ready[r].  The other warps walk exact-test
 // tables: they claim windows of 32 variants, and every lane that finishes a table takes the next
-// variant of the window (hwe_warp_queue's scheme), waiting only for that variant's ready flag.
+// variant of the window (hwe_consume), waiting only for that variant's ready flag.
 // Counting warps never wait for anything, so the kernel cannot deadlock whatever the residency.
 // ---------------------------------------------------------------------------------------------
 constexpr uint32_t kHardyChunk = 8;   // records per claim of a counting warp
@@ -376,25 +376,14 @@ int pick_lanes(uint32_t N) {
   return 4;
 }
 
-int g_sm_count = 0;
-int sm_count() {
-  if (!g_sm_count) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
-    if (g_sm_count <= 0) g_sm_count = 148;
-  }
-  return g_sm_count;
-}
-
 template <int LANES>
 void launch_fixed_t(const RecIndex& ix, const SubsetDev& sub, uint32_t v_begin, uint32_t nrec, uint4* out,
-                    cudaStream_t s) {
+                    cudaStream_t s, int sms) {
   const uint64_t first_off = ix.fixed_start + static_cast<uint64_t>(v_begin) * ix.fixed_width - ix.data_fpos;
   // Persistent grid: 8 CTAs of 256 threads per SM (64 resident warps), a multiple of the SM count.
   const uint64_t groups_needed = nrec;
   uint64_t blocks = (groups_needed * LANES + kThreads - 1) / kThreads;
-  const uint64_t max_blocks = static_cast<uint64_t>(sm_count()) * 8;
+  const uint64_t max_blocks = static_cast<uint64_t>(sms) * 8;
   if (blocks > max_blocks) blocks = max_blocks;
   if (blocks == 0) blocks = 1;
   if (sub.mask2_shifts) {
@@ -431,10 +420,10 @@ void launch_count_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_beg
   const uint32_t nrec = v_end - v_begin;
   if (!nrec) return;
   switch (pick_lanes(ix.N)) {
-    case 32: launch_fixed_t<32>(ix, sub, v_begin, nrec, out, s); break;
-    case 16: launch_fixed_t<16>(ix, sub, v_begin, nrec, out, s); break;
-    case 8: launch_fixed_t<8>(ix, sub, v_begin, nrec, out, s); break;
-    default: launch_fixed_t<4>(ix, sub, v_begin, nrec, out, s); break;
+    case 32: launch_fixed_t<32>(ix, sub, v_begin, nrec, out, s, sm_of(st)); break;
+    case 16: launch_fixed_t<16>(ix, sub, v_begin, nrec, out, s, sm_of(st)); break;
+    case 8: launch_fixed_t<8>(ix, sub, v_begin, nrec, out, s, sm_of(st)); break;
+    default: launch_fixed_t<4>(ix, sub, v_begin, nrec, out, s, sm_of(st)); break;
   }
   if (st) st->launches++;
 }
@@ -446,11 +435,11 @@ bool launch_hardy_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_beg
   if (!nrec) return true;
   if (!hardy_fused_applicable(ix.N)) return false;
   const uint64_t first_off = ix.fixed_start + static_cast<uint64_t>(v_begin) * ix.fixed_width - ix.data_fpos;
-  cudaMemsetAsync(queue, 0, 2 * sizeof(uint32_t), s);
+  cudaMemsetAsync(queue, 0, kHweQueueWords * sizeof(uint32_t), s);
   cudaMemsetAsync(ready, 0, static_cast<size_t>(nrec) * sizeof(uint32_t), s);
   // One resident wave: 4 CTAs per SM (launch bounds); 6 warps of a CTA count, 2 test.
   uint64_t blocks = (static_cast<uint64_t>(nrec) + kHardyChunk * kHardyCountWarps - 1) / (kHardyChunk * kHardyCountWarps);
-  const uint64_t max_blocks = static_cast<uint64_t>(sm_count()) * 4;
+  const uint64_t max_blocks = static_cast<uint64_t>(sm_of(st)) * 4;
   if (blocks > max_blocks) blocks = max_blocks;
   if (sub.mask2_shifts) {
     k_hardy_fixed<true, kHardyCountWarps><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(
@@ -460,6 +449,7 @@ bool launch_hardy_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_beg
         ix.data, first_off, ix.fixed_width, ix.N, nrec, sub, out, out_p, midp, queue, ready, host_out);
   }
   if (st) st->launches++;
+  launch_hwe_scaled(out, queue, midp, out_p, false, s, st);
   return true;
 }
 
@@ -478,7 +468,7 @@ void launch_count_var(const RecIndex& ix, const SubsetDev& sub, const LdScratch&
   if (!nrec) return;
   cudaMemsetAsync(work_counter, 0, sizeof(uint32_t), s);
   uint64_t blocks = (static_cast<uint64_t>(nrec) * 32 + kThreads - 1) / kThreads;
-  const uint64_t max_blocks = static_cast<uint64_t>(sm_count()) * 8;
+  const uint64_t max_blocks = static_cast<uint64_t>(sm_of(st)) * 8;
   if (blocks > max_blocks) blocks = max_blocks;
   if (sub.mask2_shifts) {
     k_count_var<true><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, sub, scratch, v_begin, v_end, out,

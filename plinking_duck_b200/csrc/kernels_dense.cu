@@ -581,17 +581,6 @@ k_count_rows(DenseRows rows, SubsetDev sub, uint4* __restrict__ out) {
   }
 }
 
-int g_sm = 0;
-int sm_count() {
-  if (!g_sm) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_sm, cudaDevAttrMultiProcessorCount, dev);
-    if (g_sm <= 0) g_sm = 148;
-  }
-  return g_sm;
-}
-
 }  // namespace
 
 void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint32_t nrows, uint8_t* scratch,
@@ -601,7 +590,7 @@ void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint
   if (!nrows) return;
   cudaMemsetAsync(work_counter, 0, sizeof(uint32_t), s);
   uint64_t blocks = (static_cast<uint64_t>(nrows) * 32 + kThreads - 1) / kThreads;
-  const uint64_t max_blocks = static_cast<uint64_t>(sm_count()) * 8;
+  const uint64_t max_blocks = static_cast<uint64_t>(sm_of(st)) * 8;
   if (blocks > max_blocks) blocks = max_blocks;
   if (sparse) {
     k_densify<true><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, vlist, v0, nrows, scratch, slot_stride, ptrs,
@@ -652,7 +641,7 @@ void launch_sample_acc(const DenseRows& rows, uint32_t kinds, uint32_t* acc_het,
   // 6 CTAs of 128 threads fit an SM (80 registers, 24 KB of counters): the grid is exactly one resident
   // wave -- rounded DOWN, a 7th CTA on a few SMs would double the kernel time -- and every chunk ends with
   // one atomic per sample, so chunks are as long as that allows (>= 240 rows when rows allow).
-  uint32_t want_y = static_cast<uint32_t>(sm_count()) * 6 / bx;
+  uint32_t want_y = static_cast<uint32_t>(sm_of(st)) * 6 / bx;
   if (want_y < 1) want_y = 1;
   uint32_t rpc = (rows.nrows + want_y - 1) / want_y;
   if (rpc < 240) rpc = 240;
@@ -680,7 +669,7 @@ void launch_sample_acc(const DenseRows& rows, uint32_t kinds, uint32_t* acc_het,
 void launch_count_rows(const DenseRows& rows, const SubsetDev& sub, uint4* out, cudaStream_t s, LaunchStats* st) {
   if (!rows.nrows) return;
   uint64_t blocks = (static_cast<uint64_t>(rows.nrows) * 32 + kThreads - 1) / kThreads;
-  const uint64_t max_blocks = static_cast<uint64_t>(sm_count()) * 8;
+  const uint64_t max_blocks = static_cast<uint64_t>(sm_of(st)) * 8;
   if (blocks > max_blocks) blocks = max_blocks;
   if (sub.mask2_shifts) {
     k_count_rows<true><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(rows, sub, out);

@@ -2,7 +2,7 @@
 //
 // Replaces HweExactTestAutosomal -> plink2::HweLnP + LnPToPvalue (src/plink_hardy.cpp:52-79;
 // plink2_stats.cc:1784-2166) for the autosomal / diploid-stratum test.  One warp owns a contiguous
-// run of variants and its lanes pull tables from it as they finish (hwe_warp_queue), so a warp is
+// run of variants and its lanes pull tables from it as they finish (hwe_consume), so a warp is
 // not held up by its slowest table.
 #include "hwe_device.cuh"
 #include "kernels.cuh"
@@ -13,9 +13,24 @@ namespace {
 
 constexpr double kTieEps = kHweTieEps;
 // Persistent grid; every warp pulls windows of 32 variants from the device counter *queue.
+// LNP: store ln p (what HweLnP returns, unclamped by exp) instead of p.
+template <bool LNP>
 __global__ void __launch_bounds__(256, 4) k_hwe(const uint4* __restrict__ counts, uint32_t n, uint32_t midp,
                                                 double* __restrict__ out_p, uint32_t* __restrict__ queue) {
-  hwe_consume(queue, n, nullptr, counts, out_p, midp != 0);
+  hwe_consume<LNP>(queue + 1, n, nullptr, counts, out_p, midp != 0);
+}
+
+// The tables hwe_store set aside (observed cell > 2^990 times less likely than the mode): one lane each.
+template <bool LNP>
+__global__ void __launch_bounds__(32) k_hwe_scaled(const uint4* __restrict__ counts, const uint32_t* __restrict__ ovf,
+                                                   uint32_t midp, double* __restrict__ out_p) {
+  const uint32_t n = ovf[0];
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t item = ovf[2u + i];
+    const uint4 cnt = counts[item];
+    const double lnp = hwe_scaled_lnp(cnt.y, cnt.x, cnt.z, midp != 0);
+    out_p[item] = LNP ? lnp : exp(lnp);
+  }
 }
 
 
@@ -159,19 +174,29 @@ __global__ void __launch_bounds__(256) k_hwe_xchr(const uint32_t* __restrict__ c
 }  // namespace
 
 void launch_hwe(const uint4* counts, uint32_t n, uint32_t midp, double* out_p, uint32_t* queue, cudaStream_t s,
-                LaunchStats* st) {
+                LaunchStats* st, bool want_lnp) {
   if (!n) return;
-  cudaMemsetAsync(queue, 0, sizeof(uint32_t), s);
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (sms <= 0) sms = 148;
-  }
+  cudaMemsetAsync(queue, 0, kHweQueueWords * sizeof(uint32_t), s);
+  const int sms = st && st->sm_count > 0 ? st->sm_count : 148;
   uint32_t blocks = (n + 255) / 256;  // 8 warps x 32 variants per CTA at least
   if (blocks > static_cast<uint32_t>(sms) * 4) blocks = sms * 4;
-  k_hwe<<<blocks, 256, 0, s>>>(counts, n, midp, out_p, queue);
+  if (want_lnp) {
+    k_hwe<true><<<blocks, 256, 0, s>>>(counts, n, midp, out_p, queue);
+  } else {
+    k_hwe<false><<<blocks, 256, 0, s>>>(counts, n, midp, out_p, queue);
+  }
+  if (st) st->launches++;
+  launch_hwe_scaled(counts, queue, midp, out_p, want_lnp, s, st);
+}
+
+void launch_hwe_scaled(const uint4* counts, const uint32_t* queue, uint32_t midp, double* out_p, bool want_lnp,
+                       cudaStream_t s, LaunchStats* st) {
+  const unsigned blocks = static_cast<unsigned>(sm_of(st)) * 4u;
+  if (want_lnp) {
+    k_hwe_scaled<true><<<blocks, 32, 0, s>>>(counts, queue + 2, midp, out_p);
+  } else {
+    k_hwe_scaled<false><<<blocks, 32, 0, s>>>(counts, queue + 2, midp, out_p);
+  }
   if (st) st->launches++;
 }
 

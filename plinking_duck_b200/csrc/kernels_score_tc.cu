@@ -594,15 +594,7 @@ void launch_score_tc(const DenseRows& rows, const uint4* counts, const ScoreRow*
                                                                           w.col_scale, w.meta, nk_batch, w.a_tiles,
                                                                           w.krow_ptr);
   const uint32_t tiles = (n_samples + kTileN - 1) / kTileN;
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (sms <= 0) sms = 148;
-    cudaFuncSetAttribute(k_score_mma, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         static_cast<int>(sizeof(MmaSmem) + 128));
-  }
+  const int sms = sm_of(st);
   // k splits: the smallest count that fills whole waves of 2 CTAs per SM to >= 90 % (each split pays one
   // accumulator drain per tile), keeping at least 32 slabs per CTA.
   const uint32_t slots = static_cast<uint32_t>(sms) * 2;
@@ -626,6 +618,10 @@ void launch_score_tc(const DenseRows& rows, const uint4* counts, const ScoreRow*
                                                                            n_samples, K, mode, score, dosage_sums,
                                                                            allele_cts);
   if (st) st->launches += 4;
+}
+
+void configure_device_kernels() {
+  cudaFuncSetAttribute(k_score_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(MmaSmem) + 128));
 }
 
 }  // namespace pdk

@@ -186,6 +186,13 @@ class PgenContext:
         self._check(self._lib.pd_hwe_from_counts(self._h, _p(counts), counts.shape[0], int(bool(midp)), _p(p)))
         return p
 
+    def hwe_lnp_from_counts(self, counts, midp=False) -> np.ndarray:
+        """ln p of the exact test (plink2::HweLnP's own return value) for (n, 4) counts."""
+        counts = np.ascontiguousarray(counts, dtype=np.uint32).reshape(-1, 4)
+        out = np.zeros(counts.shape[0], dtype=np.float64)
+        self._check(self._lib.pd_hwe_lnp_from_counts(self._h, _p(counts), counts.shape[0], int(bool(midp)), _p(out)))
+        return out
+
     def hwe_xchr_from_counts(self, c5, midp=False) -> np.ndarray:
         """c5: (n, 5) female hom_ref / het / hom_alt, male ref / alt."""
         c5 = np.ascontiguousarray(c5, dtype=np.uint32).reshape(-1, 5)

@@ -305,3 +305,18 @@ def compact_pgen_image(storage: int, g: np.ndarray, seed: int = 0):
     offs = np.array([fpos[b * 65536] for b in range(nblk)], "<u8").tobytes()
     image = np.frombuffer(bytes(hdr) + offs + bytes(blocks) + b"".join(recs), dtype=np.uint8).copy()
     return image, vrtypes, fpos
+
+
+def genotypes_from_counts(counts: np.ndarray, seed: int) -> np.ndarray:
+    """(V, N) int8 genotype matrix whose per-variant tallies are exactly counts[v] = (hom_ref, het, hom_alt,
+    missing), samples shuffled: lets a test dictate the table an exact test sees."""
+    counts = np.asarray(counts, dtype=np.int64)
+    N = int(counts[0].sum())
+    rng = np.random.default_rng(seed)
+    g = np.empty((counts.shape[0], N), dtype=np.int8)
+    for v, c in enumerate(counts):
+        assert int(c.sum()) == N
+        row = np.repeat(np.arange(4, dtype=np.int8), c)
+        rng.shuffle(row)
+        g[v] = row
+    return g
