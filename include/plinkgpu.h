@@ -11,7 +11,8 @@
  * There is NO CPU fallback: if no CUDA device is usable, pd_open* fails with PD_ERR_CUDA.
  *
  * Thread-safety: a pd_ctx may be shared by DuckDB's scan threads; blocking calls serialise on
- * the context's CUDA stream.  pd_counts_fetch may be called concurrently from any number of
+ * the context's CUDA stream(s).  A multi-GPU context (pd_open_opts.n_devices) lives in the same single
+ * process: it owns one sub-context, stream set and staging ring per GPU plus the NCCL communicator.  pd_counts_fetch may be called concurrently from any number of
  * threads on one job (src/plink_freq.cpp:434-441 keeps its fetch_add claim loop).
  *
  * Each entry point names the reference call site(s) it replaces.  Paths are relative to the
@@ -40,10 +41,18 @@ typedef struct pd_ctx pd_ctx;
 typedef struct pd_job pd_job;
 
 typedef struct pd_open_opts {
-  int32_t device;           /* CUDA device ordinal; -1 = current device                        */
+  int32_t device;           /* CUDA device ordinal; -1 = current device (unused when n_devices > 0) */
   uint64_t tile_bytes;      /* record bytes per staged tile; 0 = default (64 MiB)               */
   uint32_t n_staging;       /* pinned staging buffers (>= 2, double buffering); 0 = default (3) */
-  uint32_t reserved;
+  uint32_t n_devices;       /* > 0: ONE context over the GPUs devices[0 .. n_devices) of this box:
+                             * every call splits its variant range (or variant list) into contiguous
+                             * pieces of equal record bytes, one per GPU; per-variant outputs land in
+                             * disjoint slices of the caller's arrays; the per-sample accumulators of
+                             * pd_missing_by_sample / pd_sample_counts / pd_score are summed with one
+                             * ncclAllReduce over NVLink (the mutex merges of src/plink_missing.cpp:614-619,
+                             * src/plink_score.cpp:657-664, src/pfile_reader.cpp:3432-3445).  NCCL is
+                             * loaded at run time (libnccl.so.2) when n_devices > 1. */
+  const int32_t* devices;   /* distinct CUDA device ordinals; read during pd_open* only        */
 } pd_open_opts;
 
 typedef struct pd_info_t {
@@ -58,7 +67,9 @@ typedef struct pd_info_t {
   uint32_t has_multiallelic;/* any record with bit 3                                            */
   uint32_t resident;        /* 1 if a variant range is currently held in HBM                    */
   uint64_t data_bytes;      /* sum of record widths                                             */
-  uint64_t resident_bytes;  /* bytes held in HBM                                                */
+  uint64_t resident_bytes;  /* bytes held in HBM (all devices)                                  */
+  uint32_t effective_sample_ct; /* samples the outputs cover: the subset's size, else sample_ct  */
+  uint32_t n_devices;       /* GPUs behind this context                                         */
 } pd_info_t;
 
 typedef struct pd_stats_t {
@@ -73,6 +84,11 @@ typedef struct pd_stats_t {
   double call_ms;           /* CUDA-event time of the last call, first enqueue to last result copy */
   double host_stage_ms;     /* host wall time the last call spent filling staging buffers (reads, gathers) */
   double host_wait_ms;      /* host wall time the last call spent waiting for a free staging buffer        */
+  double allreduce_ms;      /* CUDA-event time of the last call's NCCL all-reduce(s), first device          */
+  uint64_t allreduce_bytes; /* bytes all-reduced by the last call (per device)                              */
+  uint32_t n_devices;       /* GPUs behind this context; with several, counters are summed over them and
+                             * the *_ms fields are the slowest device's (the devices run side by side)      */
+  uint32_t reserved;
 } pd_stats_t;
 
 /* ---- open / close : replaces PgfiInitPhase1 + PgfiInitPhase2 + PgrInit per scan thread
@@ -91,6 +107,12 @@ int pd_open_mem(const void* pgen_bytes, uint64_t len, const void* pgi_bytes, uin
  * entries) are filled when non-NULL and cap >= variant_ct. */
 int pd_probe(const char* pgen_path, pd_info_t* out, uint8_t* vrtypes, uint64_t* fpos, uint32_t cap, char* errbuf,
              size_t errbuf_len);
+/* The plan a multi-GPU context uses for [v_begin, v_end) over k GPUs, without a device: cuts[0..k], GPU i takes
+ * variants [cuts[i], cuts[i+1]).  Pieces hold (nearly) equal record BYTES and start on a variant whose main track
+ * is not LD-compressed (what the 128-variant fetch_add claims of src/plink_freq.cpp:434-441 balance
+ * dynamically on the CPU). */
+int pd_plan_partition(const char* pgen_path, uint32_t v_begin, uint32_t v_end, uint32_t k, uint32_t* cuts, char* errbuf,
+                      size_t errbuf_len);
 void pd_close(pd_ctx* ctx);
 const char* pd_last_error(const pd_ctx* ctx);
 int pd_info(const pd_ctx* ctx, pd_info_t* out);

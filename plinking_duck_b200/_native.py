@@ -22,7 +22,17 @@ ERR_NAMES = {
 
 
 class OpenOpts(C.Structure):
-    _fields_ = [("device", C.c_int32), ("tile_bytes", C.c_uint64), ("n_staging", C.c_uint32), ("reserved", C.c_uint32)]
+    _fields_ = [("device", C.c_int32), ("tile_bytes", C.c_uint64), ("n_staging", C.c_uint32), ("n_devices", C.c_uint32),
+                ("devices", C.POINTER(C.c_int32))]
+
+
+def open_opts(device: int = -1, tile_bytes: int = 0, n_staging: int = 0, devices=None):
+    """pd_open_opts; `devices` (a list of CUDA ordinals) asks for ONE context over several GPUs.  Returns
+    (opts, keepalive) -- the device array must outlive the pd_open call."""
+    if devices is None:
+        return OpenOpts(device, tile_bytes, n_staging, 0, None), None
+    arr = (C.c_int32 * len(devices))(*[int(d) for d in devices])
+    return OpenOpts(-1, tile_bytes, n_staging, len(devices), C.cast(arr, C.POINTER(C.c_int32))), arr
 
 
 class Info(C.Structure):
@@ -30,7 +40,7 @@ class Info(C.Structure):
         ("variant_ct", C.c_uint32), ("sample_ct", C.c_uint32), ("mode", C.c_uint32), ("fixed_width", C.c_uint32),
         ("has_ld", C.c_uint32), ("has_difflist", C.c_uint32), ("has_dosage", C.c_uint32), ("has_phase", C.c_uint32),
         ("has_multiallelic", C.c_uint32), ("resident", C.c_uint32), ("data_bytes", C.c_uint64),
-        ("resident_bytes", C.c_uint64),
+        ("resident_bytes", C.c_uint64), ("effective_sample_ct", C.c_uint32), ("n_devices", C.c_uint32),
     ]
 
 
@@ -39,7 +49,8 @@ class Stats(C.Structure):
         ("launches", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("record_bytes", C.c_uint64),
         ("kernel_ms", C.c_double), ("aux_kernel_ms", C.c_double), ("total_ms", C.c_double),
         ("scan_launches", C.c_uint64), ("call_ms", C.c_double), ("host_stage_ms", C.c_double),
-        ("host_wait_ms", C.c_double),
+        ("host_wait_ms", C.c_double), ("allreduce_ms", C.c_double), ("allreduce_bytes", C.c_uint64),
+        ("n_devices", C.c_uint32), ("reserved", C.c_uint32),
     ]
 
 
@@ -49,6 +60,7 @@ SYMBOLS = {
     "pd_open": (C.c_int, [C.c_char_p, C.POINTER(OpenOpts), C.POINTER(_vp), C.c_char_p, C.c_size_t]),
     "pd_open_mem": (C.c_int, [_vp, _u64, _vp, _u64, C.POINTER(OpenOpts), C.POINTER(_vp), C.c_char_p, C.c_size_t]),
     "pd_probe": (C.c_int, [C.c_char_p, C.POINTER(Info), _vp, _vp, _u32, C.c_char_p, C.c_size_t]),
+    "pd_plan_partition": (C.c_int, [C.c_char_p, _u32, _u32, _u32, _vp, C.c_char_p, C.c_size_t]),
     "pd_close": (None, [_vp]),
     "pd_last_error": (C.c_char_p, [_vp]),
     "pd_info": (C.c_int, [_vp, C.POINTER(Info)]),

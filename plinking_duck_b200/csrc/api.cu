@@ -6,6 +6,7 @@
 #include <new>
 
 #include "ctx.h"
+#include "group.h"
 
 using namespace pdx;
 
@@ -17,6 +18,11 @@ void CopyErr(char* errbuf, size_t n, const std::string& msg) {
 
 void DestroyCtx(pd_ctx* c) {
   if (!c) return;
+  if (c->group) {  // multi-GPU context: the shards own every device resource
+    GroupDestroy(c);
+    delete c;
+    return;
+  }
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
@@ -137,13 +143,31 @@ int InitDevice(pd_ctx* c, const pd_open_opts* opts) {
   return PD_OK;
 }
 
-int FinishOpen(pd_ctx* c, const pd_open_opts* opts, pd_ctx** out, char* errbuf, size_t errbuf_len) {
+int FinishOpen(pd_ctx* c, const pd_open_opts* opts, pd_ctx** out, char* errbuf, size_t errbuf_len,
+               const char* path = nullptr) {
   std::string err;
   int rc = ParsePgenIndex(c->pgen, c->have_pgi ? &c->pgi : nullptr, &c->idx, &err);
   if (rc != PD_OK) {
     CopyErr(errbuf, errbuf_len, err);
     delete c;
     return rc;
+  }
+  if (opts && opts->n_devices) {
+    // one context over several GPUs: this object keeps the index (to partition calls), the shards do the work
+    if (!opts->devices) {
+      CopyErr(errbuf, errbuf_len, "pd_open_opts.n_devices is set but devices is NULL");
+      delete c;
+      return PD_ERR_INVALID_ARG;
+    }
+    rc = GroupOpen(c, opts, path, path ? nullptr : c->pgen.mem(), c->pgen.size(), c->have_pgi ? c->pgi.mem() : nullptr,
+                   c->have_pgi ? c->pgi.size() : 0);
+    if (rc != PD_OK) {
+      CopyErr(errbuf, errbuf_len, c->last_error);
+      DestroyCtx(c);
+      return rc;
+    }
+    *out = c;
+    return PD_OK;
   }
   rc = InitDevice(c, opts);
   if (rc != PD_OK) {
@@ -159,7 +183,7 @@ int FinishOpen(pd_ctx* c, const pd_open_opts* opts, pd_ctx** out, char* errbuf, 
 
 extern "C" {
 
-const char* pd_version(void) { return "plinkgpu 0.1 sm_100a"; }
+const char* pd_version(void) { return "plinkgpu 0.2 sm_100a"; }
 
 int pd_open(const char* pgen_path, const pd_open_opts* opts, pd_ctx** out, char* errbuf, size_t errbuf_len) {
   if (!out || !pgen_path) return PD_ERR_INVALID_ARG;
@@ -183,7 +207,7 @@ int pd_open(const char* pgen_path, const pd_open_opts* opts, pd_ctx** out, char*
     }
     c->have_pgi = true;
   }
-  return FinishOpen(c, opts, out, errbuf, errbuf_len);
+  return FinishOpen(c, opts, out, errbuf, errbuf_len, pgen_path);
 }
 
 int pd_open_mem(const void* pgen_bytes, uint64_t len, const void* pgi_bytes, uint64_t pgi_len,
@@ -207,6 +231,11 @@ int pd_open_mem(const void* pgen_bytes, uint64_t len, const void* pgi_bytes, uin
     c->dev_image = true;
   } else {
     cudaGetLastError();  // unregistered host memory reports an error on some drivers
+  }
+  if (opts && opts->n_devices && c->dev_image) {
+    CopyErr(errbuf, errbuf_len, "a device-memory image cannot back a multi-GPU context");
+    delete c;
+    return PD_ERR_INVALID_ARG;
   }
   int rc = FinishOpen(c, opts, out, errbuf, errbuf_len);
   if (rc == PD_OK && c->dev_image) {
@@ -276,10 +305,45 @@ int pd_probe(const char* pgen_path, pd_info_t* out, uint8_t* vrtypes, uint64_t* 
   return PD_OK;
 }
 
+int pd_plan_partition(const char* pgen_path, uint32_t v_begin, uint32_t v_end, uint32_t k, uint32_t* cuts, char* errbuf,
+                      size_t errbuf_len) {
+  if (!pgen_path || !cuts || !k) return PD_ERR_INVALID_ARG;
+  ByteSource pgen, pgi;
+  std::string err;
+  if (!pgen.OpenFile(pgen_path, &err)) {
+    CopyErr(errbuf, errbuf_len, err);
+    return PD_ERR_OPEN;
+  }
+  bool have_pgi = false;
+  uint8_t magic[3] = {0, 0, 0};
+  if (pgen.size() >= 3 && pgen.ReadAt(0, magic, 3) && (magic[2] & 0xfe) == 0x20) {
+    if (!pgi.OpenFile((std::string(pgen_path) + ".pgi").c_str(), &err)) {
+      CopyErr(errbuf, errbuf_len, err);
+      return PD_ERR_OPEN;
+    }
+    have_pgi = true;
+  }
+  PgenIndex ix;
+  const int rc = ParsePgenIndex(pgen, have_pgi ? &pgi : nullptr, &ix, &err);
+  if (rc != PD_OK) {
+    CopyErr(errbuf, errbuf_len, err);
+    return rc;
+  }
+  if (v_begin > v_end || v_end > ix.variant_ct) {
+    CopyErr(errbuf, errbuf_len, "variant range out of bounds");
+    return PD_ERR_INVALID_ARG;
+  }
+  const std::vector<VRange> r = PartitionByBytes(ix, v_begin, v_end, k);
+  for (uint32_t i = 0; i < k; ++i) cuts[i] = r[i].v0;
+  cuts[k] = v_end;
+  return PD_OK;
+}
+
 const char* pd_last_error(const pd_ctx* ctx) { return ctx ? ctx->last_error.c_str() : "null context"; }
 
 int pd_info(const pd_ctx* c, pd_info_t* out) {
   if (!c || !out) return PD_ERR_INVALID_ARG;
+  if (c->group) return GroupInfo(c, out);
   const PgenIndex& ix = c->idx;
   memset(out, 0, sizeof(*out));
   out->variant_ct = ix.variant_ct;
@@ -294,6 +358,8 @@ int pd_info(const pd_ctx* c, pd_info_t* out) {
   out->resident = c->resident;
   out->data_bytes = ix.data_bytes;
   out->resident_bytes = c->resident ? c->res_f1 - c->res_f0 : 0;
+  out->effective_sample_ct = c->subset.active ? c->subset.count : ix.sample_ct;
+  out->n_devices = 1;
   return PD_OK;
 }
 
@@ -313,13 +379,16 @@ int pd_index(const pd_ctx* c, uint8_t* vrtypes, uint64_t* fpos) {
 
 int pd_get_stats(const pd_ctx* c, pd_stats_t* out) {
   if (!c || !out) return PD_ERR_INVALID_ARG;
+  if (c->group) return GroupGetStats(c, out);
   *out = c->stats;
   out->launches = c->launch_stats.launches;
+  out->n_devices = 1;
   return PD_OK;
 }
 
 int pd_reset_stats(pd_ctx* c) {
   if (!c) return PD_ERR_INVALID_ARG;
+  if (c->group) return GroupResetStats(c);
   std::lock_guard<std::mutex> lock(c->mu);
   memset(&c->stats, 0, sizeof(c->stats));
   c->launch_stats.launches = 0;
@@ -328,6 +397,7 @@ int pd_reset_stats(pd_ctx* c) {
 
 int pd_set_sample_subset(pd_ctx* c, const uint64_t* sample_include, uint32_t subset_sample_ct) {
   if (!c) return PD_ERR_INVALID_ARG;
+  if (c->group) return GroupSetSubset(c, sample_include, subset_sample_ct);
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   if (!sample_include) {
@@ -347,6 +417,7 @@ int pd_set_sample_subset(pd_ctx* c, const uint64_t* sample_include, uint32_t sub
 
 int pd_load_resident(pd_ctx* c, uint32_t v_begin, uint32_t v_end) {
   if (!c) return PD_ERR_INVALID_ARG;
+  if (c->group) return GroupLoadResident(c, v_begin, v_end);
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   const PgenIndex& ix = c->idx;
@@ -402,6 +473,7 @@ int pd_load_resident(pd_ctx* c, uint32_t v_begin, uint32_t v_end) {
 
 int pd_unload(pd_ctx* c) {
   if (!c) return PD_ERR_INVALID_ARG;
+  if (c->group) return GroupUnload(c);
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   if (c->dev_image) return PD_OK;

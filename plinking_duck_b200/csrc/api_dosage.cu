@@ -8,6 +8,7 @@
 #include <limits>
 
 #include "ctx.h"
+#include "group.h"
 #include "outpipe.h"
 
 using namespace pdx;
@@ -119,6 +120,13 @@ extern "C" {
 
 int pd_dosage_f64(pd_ctx* c, const uint32_t* vidx, uint32_t n_var, double* out) {
   if (!c || (n_var && (!vidx || !out))) return PD_ERR_INVALID_ARG;
+  if (c->group) {
+    const pd_ctx* s0 = c->group->shards[0];
+    const size_t n = s0->subset.active ? s0->subset.count : s0->idx.sample_ct;
+    return GroupRunList(c, vidx, n_var, 1, [&](pd_ctx* s, uint32_t i0, uint32_t i1) {
+      return pd_dosage_f64(s, vidx + i0, i1 - i0, out + i0 * n);
+    });
+  }
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   const uint32_t n_out = c->subset.active ? c->subset.count : c->idx.sample_ct;
@@ -162,6 +170,12 @@ int pd_dosage_counts(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* out_
   const uint32_t n = v_end - v_begin;
   if (!n) return PD_OK;
   if (!out_counts || !out_all_dosages) return PD_ERR_INVALID_ARG;
+  if (c->group) {
+    return GroupRunRanges(c, v_begin, v_end, 1, [&](pd_ctx* s, uint32_t a, uint32_t b, uint32_t row) {
+      return pd_dosage_counts(s, a, b, out_counts + 4ull * row, out_all_dosages + 2ull * row,
+                              out_imp_r2 ? out_imp_r2 + row : nullptr);
+    });
+  }
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   const uint32_t sample_ct = c->subset.active ? c->subset.count : c->idx.sample_ct;
@@ -214,6 +228,7 @@ int pd_dosage_counts(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* out_
 int pd_score(pd_ctx* c, const uint32_t* vidx, const uint8_t* flip, const double* weights, uint32_t n_var, uint32_t K,
              uint32_t mode, double* score_sums, double* dosage_sums, uint32_t* allele_cts) {
   if (!c || !K || mode > 2 || (n_var && (!vidx || !weights))) return PD_ERR_INVALID_ARG;
+  if (c->group) return GroupScore(c, vidx, flip, weights, n_var, K, mode, score_sums, dosage_sums, allele_cts);
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   const uint32_t n_out = c->subset.active ? c->subset.count : c->idx.sample_ct;

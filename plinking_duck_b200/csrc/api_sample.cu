@@ -7,6 +7,7 @@
 #include <thread>
 
 #include "ctx.h"
+#include "group.h"
 #include "host_pool.h"
 #include "outpipe.h"
 
@@ -82,6 +83,7 @@ extern "C" {
 
 int pd_missing_by_sample(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* out_missing) {
   if (!c) return PD_ERR_INVALID_ARG;
+  if (c->group) return GroupMissingBySample(c, v_begin, v_end, out_missing);
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   cudaEventRecord(c->ev_c0, c->stream);
@@ -109,6 +111,7 @@ int pd_sample_counts(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* out_
   if (!c) return PD_ERR_INVALID_ARG;
   const bool want = out_het || out_hom_alt || out_missing;
   if (want && !(out_het && out_hom_alt && out_missing)) return PD_ERR_INVALID_ARG;
+  if (c->group) return GroupSampleCounts(c, v_begin, v_end, out_het, out_hom_alt, out_missing);
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   cudaEventRecord(c->ev_c0, c->stream);
@@ -134,8 +137,20 @@ int pd_sample_counts(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* out_
   return PD_OK;
 }
 
+// Samples per output row: the subset's size, else the raw sample count (a group asks its first shard).
+static uint32_t EffectiveSamples(const pd_ctx* c) {
+  if (c->group) c = c->group->shards[0];
+  return c->subset.active ? c->subset.count : c->idx.sample_ct;
+}
+
 int pd_decode_i8(pd_ctx* c, uint32_t v_begin, uint32_t v_end, int8_t* out) {
   if (!c || (!out && v_end > v_begin)) return PD_ERR_INVALID_ARG;
+  if (c->group) {
+    const size_t n = EffectiveSamples(c);
+    return GroupRunRanges(c, v_begin, v_end, 1, [&](pd_ctx* s, uint32_t a, uint32_t b, uint32_t row) {
+      return pd_decode_i8(s, a, b, out + row * n);
+    });
+  }
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   const uint32_t n_out = c->subset.active ? c->subset.count : c->idx.sample_ct;
@@ -223,6 +238,13 @@ extern "C" {
 
 int pd_decode_i8_valid(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t call_mask, int8_t* out, uint64_t* validity) {
   if (!c || ((!out || !validity) && v_end > v_begin)) return PD_ERR_INVALID_ARG;
+  if (c->group) {
+    // pieces start at multiples of 64 rows, so no 64-bit validity word is shared between two GPUs
+    const size_t n = EffectiveSamples(c);
+    return GroupRunRanges(c, v_begin, v_end, 64, [&](pd_ctx* s, uint32_t a, uint32_t b, uint32_t row) {
+      return pd_decode_i8_valid(s, a, b, call_mask, out + row * n, validity + row * n / 64);
+    });
+  }
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   const uint32_t n_out = c->subset.active ? c->subset.count : c->idx.sample_ct;
@@ -238,6 +260,12 @@ int pd_decode_i8_valid(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t cal
 int pd_decode_i8_valid_list(pd_ctx* c, const uint32_t* vidx, uint32_t n_var, uint32_t call_mask, int8_t* out,
                             uint64_t* validity) {
   if (!c || ((!out || !validity || !vidx) && n_var)) return PD_ERR_INVALID_ARG;
+  if (c->group) {
+    const size_t n = EffectiveSamples(c);
+    return GroupRunList(c, vidx, n_var, 64, [&](pd_ctx* s, uint32_t i0, uint32_t i1) {
+      return pd_decode_i8_valid_list(s, vidx + i0, i1 - i0, call_mask, out + i0 * n, validity + i0 * n / 64);
+    });
+  }
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   const uint32_t n_out = c->subset.active ? c->subset.count : c->idx.sample_ct;
@@ -249,6 +277,12 @@ int pd_decode_i8_valid_list(pd_ctx* c, const uint32_t* vidx, uint32_t n_var, uin
 
 int pd_decode_phased(pd_ctx* c, uint32_t v_begin, uint32_t v_end, int8_t* out) {
   if (!c || (!out && v_end > v_begin)) return PD_ERR_INVALID_ARG;
+  if (c->group) {
+    const size_t n = EffectiveSamples(c);
+    return GroupRunRanges(c, v_begin, v_end, 1, [&](pd_ctx* s, uint32_t a, uint32_t b, uint32_t row) {
+      return pd_decode_phased(s, a, b, out + 2 * row * n);
+    });
+  }
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   const uint32_t N = c->idx.sample_ct;
@@ -294,6 +328,11 @@ int pd_decode_phased(pd_ctx* c, uint32_t v_begin, uint32_t v_end, int8_t* out) {
 
 int pd_device_result(pd_ctx* c, uint32_t which, void** dev_ptr, uint64_t* bytes) {
   if (!c || !dev_ptr || !bytes) return PD_ERR_INVALID_ARG;
+  if (c->group) {  // after the all-reduce every device holds the totals: hand out the first device's copy
+    const int rc = pd_device_result(c->group->shards[0], which, dev_ptr, bytes);
+    if (rc != PD_OK) c->last_error = c->group->shards[0]->last_error;
+    return rc;
+  }
   std::lock_guard<std::mutex> lock(c->mu);
   switch (which) {
     case PD_RESULT_SCORE:

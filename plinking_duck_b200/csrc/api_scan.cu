@@ -5,6 +5,7 @@
 #include <new>
 
 #include "ctx.h"
+#include "group.h"
 
 using namespace pdx;
 
@@ -77,22 +78,15 @@ int DownloadRows(pd_ctx_impl* c, const void* dev, size_t bytes, void* host) {
 
 }  // namespace pdx
 
-struct pd_job {
-  pd_ctx* ctx = nullptr;
-  uint32_t v_begin = 0, v_end = 0;
-  std::vector<uint32_t> counts;  // 4 x rows
-  std::mutex mu;
-  std::condition_variable cv;
-  uint32_t rows_ready = 0;       // rows [0, rows_ready) of counts are final
-  int status = PD_OK;
-  bool finished = false;
-  std::thread worker;
-};
-
 extern "C" {
 
 int pd_counts(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* out_counts) {
   if (!c || (!out_counts && v_end > v_begin)) return PD_ERR_INVALID_ARG;
+  if (c->group) {
+    return GroupRunRanges(c, v_begin, v_end, 1, [&](pd_ctx* s, uint32_t a, uint32_t b, uint32_t row) {
+      return pd_counts(s, a, b, out_counts + 4ull * row);
+    });
+  }
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   cudaEventRecord(c->ev_c0, c->stream);
@@ -116,6 +110,11 @@ int pd_counts(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* out_counts)
 int pd_counts_masked(pd_ctx* c, uint32_t v_begin, uint32_t v_end, const uint64_t* stratum_include,
                      uint32_t* out_counts) {
   if (!c || !stratum_include || (!out_counts && v_end > v_begin)) return PD_ERR_INVALID_ARG;
+  if (c->group) {
+    return GroupRunRanges(c, v_begin, v_end, 1, [&](pd_ctx* s, uint32_t a, uint32_t b, uint32_t row) {
+      return pd_counts_masked(s, a, b, stratum_include, out_counts + 4ull * row);
+    });
+  }
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   SubsetState st;
@@ -135,6 +134,7 @@ int pd_counts_masked(pd_ctx* c, uint32_t v_begin, uint32_t v_end, const uint64_t
 int pd_counts_start(pd_ctx* c, uint32_t v_begin, uint32_t v_end, pd_job** out) {
   if (!c || !out) return PD_ERR_INVALID_ARG;
   *out = nullptr;
+  if (c->group) return GroupCountsStart(c, v_begin, v_end, out);
   if (v_begin > v_end || v_end > c->idx.variant_ct) return c->SetError(PD_ERR_INVALID_ARG, "variant range out of bounds");
   pd_job* j = new (std::nothrow) pd_job();
   if (!j) return PD_ERR_NOMEM;
@@ -198,6 +198,18 @@ int pd_counts_fetch(pd_job* j, uint32_t v_begin, uint32_t v_end, uint32_t* out_c
   if (!j || v_begin > v_end || v_begin < j->v_begin || v_end > j->v_end) return PD_ERR_INVALID_ARG;
   if (v_begin == v_end) return PD_OK;
   if (!out_counts) return PD_ERR_INVALID_ARG;
+  if (!j->subs.empty() || (j->ctx && j->ctx->group)) {
+    for (pd_job* sub : j->subs) {
+      const uint32_t a = std::max(v_begin, sub->v_begin), b = std::min(v_end, sub->v_end);
+      if (a >= b) continue;
+      const int rc = pd_counts_fetch(sub, a, b, out_counts + 4ull * (a - v_begin));
+      if (rc != PD_OK) {
+        j->ctx->last_error = sub->ctx->last_error;
+        return rc;
+      }
+    }
+    return PD_OK;
+  }
   std::unique_lock<std::mutex> lock(j->mu);
   const uint32_t need = v_end - j->v_begin;
   j->cv.wait(lock, [&]() { return j->finished || j->rows_ready >= need; });
@@ -210,12 +222,18 @@ int pd_counts_fetch(pd_job* j, uint32_t v_begin, uint32_t v_end, uint32_t* out_c
 
 void pd_job_free(pd_job* j) {
   if (!j) return;
+  for (pd_job* sub : j->subs) pd_job_free(sub);
   if (j->worker.joinable()) j->worker.join();
   delete j;
 }
 
 int pd_hardy(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_t* out_counts, double* out_p) {
   if (!c || (!out_p && v_end > v_begin)) return PD_ERR_INVALID_ARG;
+  if (c->group) {
+    return GroupRunRanges(c, v_begin, v_end, 1, [&](pd_ctx* s, uint32_t a, uint32_t b, uint32_t row) {
+      return pd_hardy(s, a, b, midp, out_counts ? out_counts + 4ull * row : nullptr, out_p + row);
+    });
+  }
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   cudaEventRecord(c->ev_c0, c->stream);
@@ -300,6 +318,7 @@ int pd_hardy(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_
 static int HweFromCounts(pd_ctx* c, const uint32_t* counts, uint32_t n, uint32_t midp, double* out, bool want_lnp) {
   if (!c || (n && (!counts || !out))) return PD_ERR_INVALID_ARG;
   if (!n) return PD_OK;
+  if (c->group) return HweFromCounts(c->group->shards[0], counts, n, midp, out, want_lnp);  // no file data involved
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   cudaError_t e = c->d_counts.Reserve(static_cast<size_t>(n) * 16);
@@ -333,6 +352,7 @@ int pd_hwe_lnp_from_counts(pd_ctx* c, const uint32_t* counts, uint32_t n, uint32
 int pd_hwe_xchr_from_counts(pd_ctx* c, const uint32_t* c5, uint32_t n, uint32_t midp, double* out_p) {
   if (!c || (n && (!c5 || !out_p))) return PD_ERR_INVALID_ARG;
   if (!n) return PD_OK;
+  if (c->group) return pd_hwe_xchr_from_counts(c->group->shards[0], c5, n, midp, out_p);
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
   cudaError_t e = c->d_counts.Reserve(static_cast<size_t>(n) * 20);

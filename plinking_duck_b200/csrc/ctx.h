@@ -14,7 +14,12 @@
 #include "kernels.cuh"
 #include "pgen_index.h"
 
+struct pd_ctx;
+struct pd_job;
+
 namespace pdx {
+
+struct GroupState;  // group.h
 
 constexpr uint32_t kSlack = 64;  // readable bytes before/after every record buffer (aligned 16 B loads)
 
@@ -112,6 +117,7 @@ struct pd_ctx_impl {
 
   pdk::LaunchStats launch_stats;
   pd_stats_t stats{};
+  GroupState* group = nullptr;  // multi-GPU context: this object only holds the index; the shards do the work
 
   int SetError(int code, const std::string& msg) {
     last_error = msg;
@@ -161,3 +167,17 @@ int DownloadRows(pd_ctx_impl* c, const void* dev, size_t bytes, void* host);
 }  // namespace pdx
 
 struct pd_ctx : pdx::pd_ctx_impl {};
+
+// Asynchronous counts job (pd_counts_start / pd_counts_fetch).
+struct pd_job {
+  pd_ctx* ctx = nullptr;
+  uint32_t v_begin = 0, v_end = 0;
+  std::vector<uint32_t> counts;  // 4 x rows
+  std::mutex mu;
+  std::condition_variable cv;
+  uint32_t rows_ready = 0;       // rows [0, rows_ready) of counts are final
+  int status = PD_OK;
+  bool finished = false;
+  std::thread worker;
+  std::vector<pd_job*> subs;     // multi-GPU context: one job per shard with a non-empty range
+};

@@ -40,15 +40,30 @@ def probe(path: str):
     return info, vt, fpos
 
 
+def plan_partition(path: str, k: int, v0: int = 0, v1: Optional[int] = None) -> np.ndarray:
+    """cuts[k + 1]: the variant ranges a k-GPU context gives its GPUs (pd_plan_partition; no device needed)."""
+    lib = nat.load()
+    if v1 is None:
+        v1 = probe(path)[0].variant_ct
+    cuts = np.zeros(k + 1, dtype=np.uint32)
+    err = C.create_string_buffer(512)
+    rc = lib.pd_plan_partition(os.fsencode(path), int(v0), int(v1), int(k), _p(cuts), err, 512)
+    if rc:
+        raise nat.PlinkGpuError(rc, err.value.decode(errors="replace"))
+    return cuts
+
+
 class PgenContext:
     """Owns a pd_ctx.  All heavy lifting happens in libplinkgpu.so on the GPU."""
 
     def __init__(self, path: Optional[str] = None, *, image: Optional[np.ndarray] = None, pgi: Optional[np.ndarray] = None,
-                 device: int = -1, tile_bytes: int = 0, n_staging: int = 0):
+                 device: int = -1, tile_bytes: int = 0, n_staging: int = 0, devices=None):
+        """devices: list of CUDA ordinals for ONE context over several GPUs of this box (pd_open_opts.n_devices):
+        variant ranges of equal record bytes per GPU, per-sample sums all-reduced with NCCL inside the library."""
         self._lib = nat.load()
         self._h = C.c_void_p()
-        self._keep = (image, pgi)
-        opts = nat.OpenOpts(device, tile_bytes, n_staging, 0)
+        opts, dev_keep = nat.open_opts(device, tile_bytes, n_staging, devices)
+        self._keep = (image, pgi, dev_keep)
         err = C.create_string_buffer(512)
         if image is not None:
             pg = pgi.ctypes.data_as(C.c_void_p) if pgi is not None else None
@@ -77,7 +92,7 @@ class PgenContext:
         self._lib = nat.load()
         self._h = C.c_void_p()
         self._keep = None
-        opts = nat.OpenOpts(device, kw.get("tile_bytes", 0), kw.get("n_staging", 0), 0)
+        opts, _ = nat.open_opts(device, kw.get("tile_bytes", 0), kw.get("n_staging", 0))
         err = C.create_string_buffer(512)
         rc = self._lib.pd_open_mem(C.c_void_p(ptr), nbytes, None, 0, C.byref(opts), C.byref(self._h), err, 512)
         if rc:

@@ -63,7 +63,8 @@ def test_k8_lnp_far_from_equilibrium(N, midp):
     assert small.sum() >= 10  # p-values an HWE filter acts on are really compared
     # p-values below fp64: the ln-p entry point still resolves them, the p entry point returns exactly 0
     deep = ex < -800.0
-    assert deep.sum() >= 5 and np.all(p[deep] == 0.0) and np.all(np.isfinite(lnp[deep]))
+    assert np.all(p[deep] == 0.0) and np.all(np.isfinite(lnp[deep]))
+    assert N < 100000 or deep.sum() >= 20
 
 
 @pytest.mark.parametrize("N", [100003, 500000])
