@@ -138,7 +138,8 @@ def test_group_dosage_and_ops(k, golden):
             d1 = c1.dosage_f64(np.arange(V, dtype=np.uint32))
             rows1 = ops.plink_freq(c1, dosage=True)
         assert np.array_equal(c.dosage_f64(np.arange(V, dtype=np.uint32)), d1)
-        assert np.array_equal(d1[0], golden[name + "/dosage_first"])
+        gd = golden[name + "/dosage_first"]
+        assert np.array_equal(d1[: gd.shape[0]], gd)
         # the operator layer only sees the C ABI: a multi-GPU context is a drop-in
         rows = ops.plink_freq(c, dosage=True)
         assert rows.tobytes() == rows1.tobytes()
