@@ -13,8 +13,10 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "_ref", "libpgenref.so")
+_SO_AVX2 = os.path.join(_HERE, "_ref", "avx2", "libpgenref.so")  # `make ref_avx2`: -march=x86-64-v3 build
 
 _lib = None
+_lib_avx2 = None
 
 
 def available() -> bool:
@@ -217,9 +219,26 @@ def lnp_to_pvalue(lnp):
     return p
 
 
-def bench_scan(path, threads, v0, v1, kind):
+def avx2_available() -> bool:
+    return os.path.exists(_SO_AVX2)
+
+
+def _bench_lib(avx2: bool):
+    """The library a timed scan runs in: the reference-flags (SSE2) build, or the AVX2 build (timing only)."""
+    global _lib_avx2
+    if not avx2:
+        return lib()
+    if _lib_avx2 is None:
+        L = C.CDLL(_SO_AVX2)
+        L.ref_bench_scan.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
+        L.ref_bench_scan.restype = C.c_double
+        _lib_avx2 = L
+    return _lib_avx2
+
+
+def bench_scan(path, threads, v0, v1, kind, avx2: bool = False):
     cs = C.c_uint64()
-    t = lib().ref_bench_scan(os.fsencode(path), threads, v0, v1, kind, C.byref(cs))
+    t = _bench_lib(avx2).ref_bench_scan(os.fsencode(path), threads, v0, v1, kind, C.byref(cs))
     if t < 0:
         raise IOError("ref_bench_scan: open failed")
     return t, cs.value

@@ -145,6 +145,13 @@ int pd_counts_start(pd_ctx* c, uint32_t v_begin, uint32_t v_end, pd_job** out) {
   j->worker = std::thread([j]() {
     pd_ctx* c = j->ctx;
     std::lock_guard<std::mutex> lock(c->mu);
+    {
+      // pd_counts_start returns only now: the job owns the context (and the sample subset it was started
+      // with) until it finishes; a pd_set_sample_subset issued right after the start waits for it
+      std::lock_guard<std::mutex> l2(j->mu);
+      j->started = true;
+    }
+    j->cv.notify_all();
     cudaSetDevice(c->device);
     const uint32_t v0 = (j->v_begin < j->v_end) ? ExtendToBase(c, j->v_begin) : j->v_begin;
     int rc = PD_OK;
@@ -153,8 +160,16 @@ int pd_counts_start(pd_ctx* c, uint32_t v_begin, uint32_t v_end, pd_job** out) {
     // Rows are published tile by tile: tile i's rows are copied out while tile i+1 is staged.
     struct Pending { Tile t; cudaEvent_t ev; };
     std::vector<Pending> pending;
+    bool bad = false;  // a malformed record was flagged: nothing from that tile on is published
     auto publish = [&](const Pending& p) {
+      if (bad) return;
       cudaEventSynchronize(p.ev);
+      int flag[2] = {0, 0};
+      cudaMemcpy(flag, DevErr(c), sizeof(flag), cudaMemcpyDeviceToHost);  // the tile's kernels are done: final for it
+      if (flag[0]) {
+        bad = true;
+        return;
+      }
       const uint32_t a = std::max(p.t.v0, j->v_begin), b = p.t.v1;
       if (b > a) {
         cudaMemcpy(j->counts.data() + static_cast<size_t>(a - j->v_begin) * 4, c->d_counts.as<uint4>() + (a - v0),
@@ -190,6 +205,10 @@ int pd_counts_start(pd_ctx* c, uint32_t v_begin, uint32_t v_end, pd_job** out) {
     }
     j->cv.notify_all();
   });
+  {
+    std::unique_lock<std::mutex> lk(j->mu);
+    j->cv.wait(lk, [&] { return j->started; });
+  }
   *out = j;
   return PD_OK;
 }

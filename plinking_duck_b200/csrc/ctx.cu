@@ -290,6 +290,9 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
   c->stats.record_bytes = ixh.RecOff(v_end - 1) + (ixh.fixed ? ixh.fixed_width : ixh.fpos[v_end] - ixh.fpos[v_end - 1]) -
                           ixh.RecOff(v_begin);
 
+  // a failed earlier call may have left its malformed-record flag behind: every scan starts clean
+  cudaMemsetAsync(DevErr(c), 0, 2 * sizeof(int), c->stream);
+  memset(c->h_misc.as<int>() + 8, 0, 24 * sizeof(int));
   cudaEventRecord(c->ev_t0, c->stream);
   int rc = PD_OK;
   if (c->resident && v0 >= c->res_v0 && v_end <= c->res_v1) {
@@ -333,6 +336,16 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
           rc = CheckCuda(c, e, "tile completion");
           break;
         }
+        // that tile's copy of the device error word has landed too: a malformed record stops the scan here
+        // (nbuf tiles after it was met) instead of at the end of a 125 GB file (pgenlib_read.cc:2195-2198
+        // fails at the record)
+        const int* flag = c->h_misc.as<int>() + 8 + 2 * (b < 12 ? b : 0);
+        if (b < 12 && flag[0]) {
+          char buf[128];
+          snprintf(buf, sizeof(buf), "malformed or unsupported variant record at variant %d", flag[1]);
+          rc = c->SetError(flag[0], buf);
+          break;
+        }
       }
       const auto tw1 = std::chrono::steady_clock::now();
       c->stats.host_wait_ms += std::chrono::duration<double, std::milli>(tw1 - tw0).count();
@@ -365,6 +378,9 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
       cudaEventRecord(k0, c->stream);
       rc = fn(t, ix, c->stream);
       cudaEventRecord(k1, c->stream);
+      if (b < 12) {  // h_misc holds 12 per-buffer copies of the error word behind the 8 ints CheckDeviceError uses
+        cudaMemcpyAsync(c->h_misc.as<int>() + 8 + 2 * b, DevErr(c), 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream);
+      }
       cudaEventRecord(c->ev_done[b], c->stream);
       if (after_tile) after_tile(t, k1);
     }
@@ -387,6 +403,9 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
     cudaEventElapsedTime(&ms, c->ev_t0, c->ev_t1);
     c->stats.total_ms = ms;
     rc = CheckDeviceError(c);
+  } else {
+    cudaStreamSynchronize(c->stream);  // tiles still in flight must not outlive the buffers / the call
+    cudaMemsetAsync(DevErr(c), 0, 2 * sizeof(int), c->stream);
   }
   return rc;
 }

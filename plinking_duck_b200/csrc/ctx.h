@@ -178,6 +178,7 @@ struct pd_job {
   uint32_t rows_ready = 0;       // rows [0, rows_ready) of counts are final
   int status = PD_OK;
   bool finished = false;
+  bool started = false;          // the worker holds the context
   std::thread worker;
   std::vector<pd_job*> subs;     // multi-GPU context: one job per shard with a non-empty range
 };

@@ -46,7 +46,7 @@ class HostPool {
 
  private:
   HostPool() {
-    const uint32_t hw = std::max(2u, std::min(16u, std::thread::hardware_concurrency()));
+    const uint32_t hw = std::max(2u, std::min(64u, std::thread::hardware_concurrency()));
     for (uint32_t t = 1; t < hw; ++t) workers_.emplace_back([this] { Loop(); });
   }
   ~HostPool() {

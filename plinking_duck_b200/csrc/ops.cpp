@@ -407,17 +407,10 @@ int pdop_missing_variant(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, pd_missi
 
 int pdop_missing_sample(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, pd_missing_row* out) {
   if (!ctx || v_begin > v_end || !out) return PD_ERR_INVALID_ARG;
-  // effective sample count: counts of any one variant sum to it; use the subset-independent probe
   pd_info_t info;
   int rc = pd_info(ctx, &info);
   if (rc != PD_OK) return rc;
-  uint32_t sample_ct = info.sample_ct;
-  if (info.variant_ct) {
-    uint32_t one[4];
-    rc = pd_counts(ctx, 0, 1, one);
-    if (rc != PD_OK) return rc;
-    sample_ct = EffectiveSampleCt(one);
-  }
+  const uint32_t sample_ct = info.effective_sample_ct;  // the subset's size, else raw_sample_ct
   std::vector<uint32_t> miss(std::max<uint32_t>(sample_ct, 1));
   rc = pd_missing_by_sample(ctx, v_begin, v_end, miss.data());
   if (rc != PD_OK) return rc;
@@ -450,13 +443,7 @@ int pdop_score(pd_ctx* ctx, const uint32_t* vidx, const uint8_t* flip, const dou
   pd_info_t info;
   int rc = pd_info(ctx, &info);
   if (rc != PD_OK) return rc;
-  uint32_t sample_ct = info.sample_ct;
-  if (info.variant_ct) {
-    uint32_t one[4];
-    rc = pd_counts(ctx, 0, 1, one);
-    if (rc != PD_OK) return rc;
-    sample_ct = EffectiveSampleCt(one);
-  }
+  const uint32_t sample_ct = info.effective_sample_ct;  // the subset's size, else raw_sample_ct
   std::vector<double> s(std::max<uint32_t>(sample_ct, 1)), d(std::max<uint32_t>(sample_ct, 1));
   std::vector<uint32_t> a(std::max<uint32_t>(sample_ct, 1));
   rc = pd_score(ctx, v.data(), f.data(), w.data(), static_cast<uint32_t>(v.size()), 1, mode, s.data(), d.data(), a.data());
@@ -514,13 +501,7 @@ int pdop_genotype_stats_sample(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, pd
   pd_info_t info;
   int rc = pd_info(ctx, &info);
   if (rc != PD_OK) return rc;
-  uint32_t sample_ct = info.sample_ct;
-  if (info.variant_ct) {
-    uint32_t one[4];
-    rc = pd_counts(ctx, 0, 1, one);
-    if (rc != PD_OK) return rc;
-    sample_ct = EffectiveSampleCt(one);
-  }
+  const uint32_t sample_ct = info.effective_sample_ct;  // the subset's size, else raw_sample_ct
   const size_t cap = std::max<uint32_t>(sample_ct, 1);
   std::vector<uint32_t> het(cap), hom_alt(cap), missing(cap);
   rc = pd_sample_counts(ctx, v_begin, v_end, het.data(), hom_alt.data(), missing.data());
