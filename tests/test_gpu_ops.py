@@ -194,8 +194,8 @@ def test_xchr_exact_test_matches_reference():
     one, but finds ties through accumulated log() sums and misses some exact ties at small counts (about 6 % of
     tied tables in a random sweep); the kernel counts every tie, so where the two differ the kernel must equal
     the full enumeration of the test's definition."""
+    import hwe_check as hc
     from oracle import ref
-    from test_gpu_counts import hwe_tolerance
 
     if not ref.available():
         pytest.skip("oracle/_ref not built")
@@ -213,6 +213,7 @@ def test_xchr_exact_test_matches_reference():
     tabs += [[1, 1, 1, 2, 1], [0, 0, 0, 0, 0], [5, 0, 0, 3, 0], [0, 0, 0, 4, 3], [2, 3, 1, 0, 0], [2, 4, 3, 6, 4]]
     tabs = np.array(tabs, dtype=np.uint32)
     tie_quirks = 0
+    worst = 0.0
     with _ctx("pgen_example") as c:
         for midp in (False, True):
             got = c.hwe_xchr_from_counts(tabs, midp=midp)
@@ -220,15 +221,24 @@ def test_xchr_exact_test_matches_reference():
                 if t.sum() == 0:
                     assert got[k] == 1.0
                     continue
-                exp = float(ref.lnp_to_pvalue(ref.hwe_xchr_lnp(t[1], t[0], t[2], t[3], t[4], midp)))
-                tol = 64 * hwe_tolerance(int(t.sum()))
-                if abs(got[k] - exp) <= tol + tol * exp:
+                lnp = ref.hwe_xchr_lnp(t[1], t[0], t[2], t[3], t[4], midp)
+                exp = float(ref.lnp_to_pvalue(lnp))
+                # RELATIVE bound (no absolute floor: small p-values are compared too).  Both sides anchor rows
+                # with log-gamma sums of magnitude ~ 2n ln 2n, so the bound is stated in ulps of that:
+                # 128 x the autosomal reference noise, floored at 1e-12; p below fp64 must come out 0.
+                tol = max(1e-12, 128.0 * float(hc.ref_bound(int(t.sum()))))
+                if lnp < hc.LN_1E300:
+                    assert got[k] <= 2e-300, (t, midp, got[k], lnp)
+                    continue
+                if abs(got[k] - exp) <= tol * exp:
+                    worst = max(worst, abs(got[k] - exp) / exp if exp > 0 else 0.0)
                     continue
                 assert midp and int(t.sum()) <= 100, (t, midp, got[k], exp)
                 bf = _xchr_bruteforce(*[int(x) for x in t], True)
                 assert abs(got[k] - max(bf, 0.0)) <= 1e-12, (t, got[k], exp, bf)
                 tie_quirks += 1
     assert tie_quirks <= 20
+    print(f"xchr: worst relative error vs HweXchrLnP {worst:.3g}")
 
 
 
