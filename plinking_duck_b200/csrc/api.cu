@@ -152,6 +152,17 @@ int FinishOpen(pd_ctx* c, const pd_open_opts* opts, pd_ctx** out, char* errbuf, 
     delete c;
     return rc;
   }
+  if (path && opts && (opts->flags & PD_OPEN_PIN_FILE) && c->pgen.map_writable()) {
+    // PD_OPEN_PIN_FILE: page-lock the mapping once; scans then DMA straight from the page cache
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) == cudaSuccess && ndev > 0) {
+      int dev = opts->n_devices ? opts->devices[0] : opts->device;
+      if (dev >= 0 && dev < ndev) cudaSetDevice(dev);
+      if (c->pgen.PinMapping()) c->src_pinned = true;
+    } else {
+      cudaGetLastError();
+    }
+  }
   if (opts && opts->n_devices) {
     // one context over several GPUs: this object keeps the index (to partition calls), the shards do the work
     if (!opts->devices) {
@@ -159,8 +170,27 @@ int FinishOpen(pd_ctx* c, const pd_open_opts* opts, pd_ctx** out, char* errbuf, 
       delete c;
       return PD_ERR_INVALID_ARG;
     }
-    rc = GroupOpen(c, opts, path, path ? nullptr : c->pgen.mem(), c->pgen.size(), c->have_pgi ? c->pgi.mem() : nullptr,
-                   c->have_pgi ? c->pgi.size() : 0);
+    // a page-locked mapping is shared by the shards as a memory image (registered once, portable)
+    const bool as_mem = !path || c->src_pinned;
+    std::vector<uint8_t> pgi_copy;
+    const void* pgi_ptr = nullptr;
+    uint64_t pgi_len = 0;
+    if (c->have_pgi) {
+      if (c->pgi.mem()) {
+        pgi_ptr = c->pgi.mem();
+        pgi_len = c->pgi.size();
+      } else if (as_mem) {  // file-backed .pgi next to a pinned .pgen: the shards need it in memory
+        c->pgi_image.resize(c->pgi.size());
+        if (!c->pgi.ReadAt(0, c->pgi_image.data(), c->pgi.size())) {
+          CopyErr(errbuf, errbuf_len, ".pgi read failure");
+          delete c;
+          return PD_ERR_READ;
+        }
+        pgi_ptr = c->pgi_image.data();
+        pgi_len = c->pgi_image.size();
+      }
+    }
+    rc = GroupOpen(c, opts, as_mem ? nullptr : path, as_mem ? c->pgen.mem() : nullptr, c->pgen.size(), pgi_ptr, pgi_len);
     if (rc != PD_OK) {
       CopyErr(errbuf, errbuf_len, c->last_error);
       DestroyCtx(c);
@@ -191,7 +221,8 @@ int pd_open(const char* pgen_path, const pd_open_opts* opts, pd_ctx** out, char*
   pd_ctx* c = new (std::nothrow) pd_ctx();
   if (!c) return PD_ERR_NOMEM;
   std::string err;
-  if (!c->pgen.OpenFile(pgen_path, &err)) {
+  const bool want_pin = opts && (opts->flags & PD_OPEN_PIN_FILE);
+  if (!c->pgen.OpenFile(pgen_path, &err, want_pin)) {
     CopyErr(errbuf, errbuf_len, err);
     delete c;
     return PD_ERR_OPEN;
@@ -360,6 +391,7 @@ int pd_info(const pd_ctx* c, pd_info_t* out) {
   out->resident_bytes = c->resident ? c->res_f1 - c->res_f0 : 0;
   out->effective_sample_ct = c->subset.active ? c->subset.count : ix.sample_ct;
   out->n_devices = 1;
+  out->pinned_file = c->pgen.pinned() ? 1u : 0u;
   return PD_OK;
 }
 

@@ -376,6 +376,7 @@ int GroupInfo(const pd_ctx* c, pd_info_t* out) {
     out->resident_bytes += si.resident_bytes;
   }
   out->n_devices = static_cast<uint32_t>(g->shards.size());
+  out->pinned_file = c->pgen.pinned() ? 1u : 0u;
   return PD_OK;
 }
 

@@ -60,6 +60,7 @@ struct Tile {
 
 struct pd_ctx_impl {
   ByteSource pgen, pgi;
+  std::vector<uint8_t> pgi_image;  // multi-GPU context over a pinned file: the .pgi bytes its shards parse
   bool have_pgi = false;
   PgenIndex idx;
   int device = 0;

@@ -45,11 +45,6 @@ __global__ void __launch_bounds__(32) k_hwe_scaled(const uint4* __restrict__ cou
 // log-gamma, then walks the row in both directions with the autosomal two-term recurrences.
 // All terms are in units of the observed table's probability.
 // ---------------------------------------------------------------------------------------------
-struct XRow {
-  double tail, center;
-  uint32_t ties;
-};
-
 __device__ __forceinline__ double xchr_lnp(double mb, double nm, double f0, double fh, double f2) {
   return fh * 0.6931471805599453 - lgamma(mb + 1.0) - lgamma(nm - mb + 1.0) - lgamma(f0 + 1.0) - lgamma(fh + 1.0) -
          lgamma(f2 + 1.0);
@@ -70,22 +65,20 @@ __global__ void __launch_bounds__(256) k_hwe_xchr(const uint32_t* __restrict__ c
   const uint64_t nB = 2ull * of2 + ofh + omb;  // ALT alleles
   const uint64_t nt = 2ull * nf + nm;
   const double l_obs = xchr_lnp(omb, nm, of0, ofh, of2);
-  // rows: mb in [max(0, nB - 2 nf), min(nm, nB)], trimmed to mean +- (40 sd + 16)
-  uint64_t lo = nB > 2ull * nf ? nB - 2ull * nf : 0;
-  uint64_t hi = nB < nm ? nB : nm;
-  {
-    const double mean = static_cast<double>(nm) * static_cast<double>(nB) / static_cast<double>(nt);
-    const double span = 20.0 * sqrt(static_cast<double>(nm) + 1.0) + 16.0;
-    const double a = floor(mean - span), b = ceil(mean + span);
-    if (a > static_cast<double>(lo)) lo = static_cast<uint64_t>(a);
-    if (b < static_cast<double>(hi)) hi = static_cast<uint64_t>(b);
-    if (omb < lo) lo = omb;
-    if (omb > hi) hi = omb;
-  }
+  // rows: mb in [max(0, nB - 2 nf), min(nm, nB)].  The row maxima are unimodal in mb, so the rows are taken
+  // from the most likely one outwards, 256 at a time, and a thread stops in a direction once its row's maximum
+  // is below e^-64 of the observed table (every later row of that direction is smaller still).  Rows on the
+  // far side of the observed one are part of the tail and must not be cut at the observed row.
+  const int64_t lo = nB > 2ull * nf ? static_cast<int64_t>(nB - 2ull * nf) : 0;
+  const int64_t hi = static_cast<int64_t>(nB < nm ? nB : nm);
+  int64_t mid = static_cast<int64_t>(static_cast<double>(nm) * static_cast<double>(nB) / static_cast<double>(nt) + 0.5);
+  mid = mid < lo ? lo : (mid > hi ? hi : mid);
   double tail = 0.0, center = 0.0;
   uint32_t ties = 0;
   bool overflow = false;
-  for (uint64_t mb = lo + threadIdx.x; mb <= hi; mb += blockDim.x) {
+  // one row; returns false when the row (and every row further out) is negligible
+  auto row = [&](int64_t mbi) -> bool {
+    const uint64_t mb = static_cast<uint64_t>(mbi);
     const uint64_t fb = nB - mb;  // ALT alleles carried by females
     const uint64_t fa = 2ull * nf - fb;
     const uint64_t fh_max = fb < fa ? fb : fa;
@@ -100,15 +93,15 @@ __global__ void __launch_bounds__(256) k_hwe_xchr(const uint32_t* __restrict__ c
     const double l0 = xchr_lnp(static_cast<double>(mb), nm, f0s, static_cast<double>(fh0), f2s) - l_obs;
     if (l0 > 700.0) {
       overflow = true;  // the observed table is > e^700 times less likely than this one: p = 0
-      break;
+      return false;
     }
-    if (l0 < -800.0) continue;
+    if (l0 < -64.0 && mb != omb) return false;
     const double t0 = (mb == omb) ? 1.0 : exp(l0);
-    auto put = [&](double t, bool is_obs) {
+    auto put = [&](double t) {
       if (t > 1.0 + kTieEps) {
         center += t;
       } else {
-        if (!is_obs && t >= 1.0 - kTieEps) ++ties;
+        if (t >= 1.0 - kTieEps) ++ties;
         tail += t;
       }
     };
@@ -116,8 +109,10 @@ __global__ void __launch_bounds__(256) k_hwe_xchr(const uint32_t* __restrict__ c
       tail += 1.0;
       ++ties;
     } else {
-      put(t0, false);
+      put(t0);
     }
+    // Both walks move away from the row's maximum, so the terms only shrink: below 1e-24 of the observed
+    // table they can change neither the tail (>= 1) nor the total.
     {  // fewer heterozygotes
       double k = static_cast<double>(fh0), r = f0s, c = f2s, t = t0;
       while (k > 1.5) {
@@ -125,8 +120,8 @@ __global__ void __launch_bounds__(256) k_hwe_xchr(const uint32_t* __restrict__ c
         c += 1.0;
         t *= (k * (k - 1.0)) / (4.0 * r * c);
         k -= 2.0;
-        put(t, false);
-        if (t < 1e-18 * (tail + center) && t < 1.0) break;
+        put(t);
+        if (t < 1e-24) break;
       }
     }
     {  // more heterozygotes
@@ -136,14 +131,23 @@ __global__ void __launch_bounds__(256) k_hwe_xchr(const uint32_t* __restrict__ c
         t *= (4.0 * r * c) / (k * (k - 1.0));
         r -= 1.0;
         c -= 1.0;
-        put(t, false);
-        if (t < 1e-18 * (tail + center) && t < 1.0) break;
+        put(t);
+        if (t < 1e-24) break;
       }
     }
     if (!(center < 1.0e300)) {
       overflow = true;
-      break;
+      return false;
     }
+    return true;
+  };
+  // Every row between the most likely one and the observed one has a maximum >= the observed table, so no
+  // direction stops before it has passed the observed row.
+  for (int64_t mb = mid + threadIdx.x; mb <= hi; mb += blockDim.x) {
+    if (!row(mb)) break;
+  }
+  for (int64_t mb = mid - 1 - static_cast<int64_t>(threadIdx.x); mb >= lo; mb -= blockDim.x) {
+    if (!row(mb)) break;
   }
   s_tail[threadIdx.x] = overflow ? -1.0 : tail;
   s_center[threadIdx.x] = center;

@@ -8,21 +8,67 @@
 #include <sys/stat.h>
 #include <unistd.h>
 
+#include <algorithm>
+#include <atomic>
 #include <cerrno>
 #include <cstdio>
 #include <cstring>
+#include <thread>
 
 #include "../../include/plinkgpu.h"
 
 namespace pdx {
 
 ByteSource::~ByteSource() {
+  for (auto& pc : pinned_pieces_) cudaHostUnregister(pc.first);
   if (map_) munmap(const_cast<uint8_t*>(map_), size_);
   if (fd_ >= 0) close(fd_);
 }
 
-bool ByteSource::OpenFile(const char* path, std::string* err) {
-  fd_ = open(path, O_RDONLY | O_CLOEXEC);
+bool ByteSource::PinMapping() {
+  if (!map_ || !map_writable_ || !size_) return false;
+  // 1 GiB pieces on 2 MiB boundaries, registered from a few threads at once (the driver pins ~6.6 GiB/s per call)
+  const uint64_t kPiece = 1ull << 30;
+  uint8_t* base = const_cast<uint8_t*>(map_);
+  std::vector<std::pair<uint8_t*, uint64_t>> pieces;
+  for (uint64_t off = 0; off < size_; off += kPiece) pieces.emplace_back(base + off, std::min(kPiece, size_ - off));
+  std::atomic<size_t> next(0);
+  std::atomic<bool> ok(true);
+  std::vector<char> done(pieces.size(), 0);
+  auto work = [&] {
+    for (;;) {
+      const size_t i = next.fetch_add(1);
+      if (i >= pieces.size() || !ok.load()) break;
+      if (cudaHostRegister(pieces[i].first, pieces[i].second, cudaHostRegisterPortable) == cudaSuccess) {
+        done[i] = 1;
+      } else {
+        cudaGetLastError();
+        ok.store(false);
+      }
+    }
+  };
+  const unsigned nt = static_cast<unsigned>(std::min<size_t>(8, pieces.size()));
+  std::vector<std::thread> th;
+  for (unsigned t = 1; t < nt; ++t) th.emplace_back(work);
+  work();
+  for (auto& x : th) x.join();
+  if (!ok.load()) {
+    for (size_t i = 0; i < pieces.size(); ++i) {
+      if (done[i]) cudaHostUnregister(pieces[i].first);
+    }
+    return false;
+  }
+  pinned_pieces_ = pieces;
+  mem_ = map_;  // from here on: a page-locked memory image
+  return true;
+}
+
+bool ByteSource::OpenFile(const char* path, std::string* err, bool want_writable_map) {
+  if (want_writable_map) {
+    fd_ = open(path, O_RDWR | O_CLOEXEC);
+    map_writable_ = fd_ >= 0;
+  }
+  if (fd_ < 0) fd_ = open(path, O_RDONLY | O_CLOEXEC);
   if (fd_ < 0) {
     if (err) *err = std::string("Failed to open ") + path + " : " + strerror(errno);
     return false;
@@ -34,8 +80,13 @@ bool ByteSource::OpenFile(const char* path, std::string* err) {
   }
   size_ = static_cast<uint64_t>(st.st_size);
   if (size_) {
-    void* m = mmap(nullptr, size_, PROT_READ, MAP_SHARED, fd_, 0);
-    if (m != MAP_FAILED) map_ = static_cast<const uint8_t*>(m);  // optional: only the trimmed scan needs it
+    void* m = MAP_FAILED;
+    if (map_writable_) m = mmap(nullptr, size_, PROT_READ | PROT_WRITE, MAP_SHARED, fd_, 0);
+    if (m == MAP_FAILED) {
+      map_writable_ = false;
+      m = mmap(nullptr, size_, PROT_READ, MAP_SHARED, fd_, 0);
+    }
+    if (m != MAP_FAILED) map_ = static_cast<const uint8_t*>(m);  // optional: the trimmed scan and pinning need it
   }
   return true;
 }

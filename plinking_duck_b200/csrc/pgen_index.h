@@ -7,6 +7,7 @@
 #pragma once
 #include <cstdint>
 #include <string>
+#include <utility>
 #include <vector>
 
 namespace pdx {
@@ -18,7 +19,14 @@ class ByteSource {
   ~ByteSource();
   ByteSource(const ByteSource&) = delete;
   ByteSource& operator=(const ByteSource&) = delete;
-  bool OpenFile(const char* path, std::string* err);
+  // want_writable_map: map the file PROT_READ|PROT_WRITE, MAP_SHARED (needed to page-lock it in place; it is
+  // never written); falls back to a read-only mapping.
+  bool OpenFile(const char* path, std::string* err, bool want_writable_map = false);
+  bool map_writable() const { return map_writable_; }
+  // Page-locks the whole mapping for DMA (cudaHostRegister, in parallel pieces); afterwards the source behaves
+  // like a page-locked memory image (mem() == the mapping).  False (nothing left registered) on any failure.
+  bool PinMapping();
+  bool pinned() const { return !pinned_pieces_.empty(); }
   void OpenMem(const void* p, uint64_t len);
   // A .pgen image that already lives in device memory (reads go through cudaMemcpy).
   void OpenDevice(const void* p, uint64_t len);
@@ -34,6 +42,8 @@ class ByteSource {
 
  private:
   int fd_ = -1;
+  bool map_writable_ = false;
+  std::vector<std::pair<uint8_t*, uint64_t>> pinned_pieces_;
   const uint8_t* mem_ = nullptr;
   const uint8_t* map_ = nullptr;
   const uint8_t* dev_ = nullptr;

@@ -119,6 +119,90 @@ int main(int argc, char** argv) {
     first = false;
   }
   printf("}");
+  // (4) small page-locked chunks that stay cache-resident between the host copy and the DMA: T threads, each
+  //     with its own stream and a ring of 3 chunks; pread (or memcpy from a mapping) -> cudaMemcpyAsync.
+  {
+    void* view = mmap(nullptr, file_bytes, PROT_READ, MAP_SHARED | MAP_POPULATE, fd, 0);
+    printf(", \"chunked_file_to_device_gbs\": {");
+    bool first_c = true;
+    for (int use_memcpy = 0; use_memcpy < 2; ++use_memcpy) {
+      if (use_memcpy && view == MAP_FAILED) break;
+      for (size_t chunk_mib : {1, 2, 4, 8}) {
+        for (unsigned T : {8u, 16u, 24u}) {
+          if (T > std::thread::hardware_concurrency()) continue;
+          const size_t chunk = chunk_mib << 20;
+          const size_t nchunks = file_bytes / chunk;
+          std::atomic<size_t> next{0};
+          std::vector<std::thread> th;
+          const double t0 = now();
+          for (unsigned t = 0; t < T; ++t) {
+            th.emplace_back([&, t] {
+              const int dev = static_cast<int>(t % ndev);
+              cudaSetDevice(dev);
+              cudaStream_t s;
+              cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking);
+              char* ring;
+              cudaHostAlloc(reinterpret_cast<void**>(&ring), 3 * chunk, cudaHostAllocPortable);
+              cudaEvent_t ev[3];
+              for (auto& e : ev) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+              size_t k = 0;
+              for (;;) {
+                const size_t i = next.fetch_add(1);
+                if (i >= nchunks) break;
+                const int slot = static_cast<int>(k % 3);
+                if (k >= 3) cudaEventSynchronize(ev[slot]);
+                char* buf = ring + slot * chunk;
+                if (use_memcpy) memcpy(buf, static_cast<char*>(view) + i * chunk, chunk);
+                else if (pread(fd, buf, chunk, static_cast<off_t>(i * chunk)) != static_cast<ssize_t>(chunk)) break;
+                cudaMemcpyAsync(static_cast<char*>(d[dev]) + (i * chunk) % gib, buf, chunk, cudaMemcpyHostToDevice, s);
+                cudaEventRecord(ev[slot], s);
+                ++k;
+              }
+              cudaStreamSynchronize(s);
+              for (auto& e : ev) cudaEventDestroy(e);
+              cudaFreeHost(ring);
+              cudaStreamDestroy(s);
+            });
+          }
+          for (auto& x : th) x.join();
+          printf("%s\"%s_%zuMiB_T%u\": %.1f", first_c ? "" : ", ", use_memcpy ? "memcpy" : "pread", chunk_mib, T,
+                 static_cast<double>(file_bytes) / (now() - t0) / 1e9);
+          first_c = false;
+        }
+      }
+    }
+    printf("}");
+    if (view != MAP_FAILED) munmap(view, file_bytes);
+  }
+  // (5) a writable shared mapping, page-locked in place without the read-only flag
+  {
+    void* mw = mmap(nullptr, file_bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    if (mw != MAP_FAILED) {
+      cudaSetDevice(0);
+      const double t0 = now();
+      cudaError_t e = cudaHostRegister(mw, file_bytes, cudaHostRegisterPortable);
+      const double reg_s = now() - t0;
+      if (e == cudaSuccess) {
+        printf(", \"register_rw_s_per_gib\": %.4f", reg_s / (static_cast<double>(file_bytes) / gib));
+        double best = 0;
+        for (int rep = 0; rep < 3; ++rep) {
+          const double t1 = now();
+          for (size_t off = 0; off < file_bytes; off += gib) {
+            cudaMemcpyAsync(d[0], static_cast<char*>(mw) + off, gib, cudaMemcpyHostToDevice, st[0]);
+          }
+          cudaStreamSynchronize(st[0]);
+          const double gbs = static_cast<double>(file_bytes) / (now() - t1) / 1e9;
+          if (gbs > best) best = gbs;
+        }
+        printf(", \"registered_rw_file_h2d_gbs\": %.1f", best);
+        cudaHostUnregister(mw);
+      } else {
+        cudaGetLastError();
+        printf(", \"register_rw\": \"%s\"", cudaGetErrorString(e));
+      }
+      munmap(mw, file_bytes);
+    }
+  }
   // (2) map + register in place
   void* m = mmap(nullptr, file_bytes, PROT_READ, MAP_SHARED, fd, 0);
   if (m == MAP_FAILED) {

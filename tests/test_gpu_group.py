@@ -147,6 +147,23 @@ def test_group_dosage_and_ops(k, golden):
         assert np.array_equal(m1["MISSING_CT"], golden[name + "/missing_by_sample"])
 
 
+@pytest.mark.parametrize("k", K)
+def test_group_over_pinned_file(k, tmp_path, golden):
+    """A multi-GPU context over a PD_OPEN_PIN_FILE mapping: registered once, shared by every shard."""
+    import shutil
+
+    from plinking_duck_b200.pgen import PgenContext
+
+    name = "streaming_example"
+    dst = str(tmp_path / (name + ".pgen"))
+    shutil.copyfile(fixture_path(name), dst)
+    with PgenContext(dst, devices=_devices(k), pin_file=True, tile_bytes=4096) as c:
+        info = c.info()
+        assert info.pinned_file == 1 and info.n_devices == k
+        assert np.array_equal(c.counts(), golden[name + "/counts"])
+        assert np.array_equal(c.missing_by_sample(), golden[name + "/missing_by_sample"])
+
+
 def test_group_rejects_bad_device_lists():
     from plinking_duck_b200 import _native as nat
     from plinking_duck_b200.pgen import PgenContext
