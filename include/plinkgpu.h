@@ -64,7 +64,7 @@ typedef struct pd_open_opts {
  * life of the context: meant for files scanned more than once (a DuckDB session over a page-cache-hot fileset).
  * The file is never written.  Falls back to the pread pipeline, silently, when the file cannot be opened
  * read-write or the driver refuses the registration; pd_info_t.pinned_file tells which path is in use. */
-#define PD_OPEN_PIN_FILE 1u
+#define PD_OPEN_PIN_FILE 1u  /* shared-memory (tmpfs / hugetlbfs) files: the kernel refuses to page-lock other file mappings */
 
 typedef struct pd_info_t {
   uint32_t variant_ct;      /* raw_variant_ct                                                   */

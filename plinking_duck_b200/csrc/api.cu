@@ -469,7 +469,7 @@ int pd_load_resident(pd_ctx* c, uint32_t v_begin, uint32_t v_end) {
   cudaMemsetAsync(c->d_resident.p, 0, kSlack, c->stream);
   cudaMemsetAsync(dst + len, 0, kSlack, c->stream);
   if (c->src_pinned) {
-    e = cudaMemcpyAsync(dst, c->pgen.mem() + f0, len, cudaMemcpyHostToDevice, c->stream);
+    e = CopyFromPinnedSource(c, dst, f0, len, c->stream);
     if (e != cudaSuccess) return CheckCuda(c, e, "resident copy");
   } else {
     // double-buffered chunks through the pinned staging ring

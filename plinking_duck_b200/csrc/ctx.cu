@@ -73,6 +73,22 @@ int CheckCuda(pd_ctx_impl* c, cudaError_t e, const char* what) {
   return c->SetError(PD_ERR_CUDA, buf);
 }
 
+cudaError_t CopyFromPinnedSource(pd_ctx_impl* c, void* dst, uint64_t off, uint64_t len, cudaStream_t s) {
+  const uint8_t* src = c->pgen.mem();
+  if (!c->pgen.pinned()) return cudaMemcpyAsync(dst, src + off, len, cudaMemcpyHostToDevice, s);
+  uint8_t* d = static_cast<uint8_t*>(dst);
+  while (len) {
+    const uint64_t room = ByteSource::kPinPiece - (off % ByteSource::kPinPiece);
+    const uint64_t n = len < room ? len : room;
+    const cudaError_t e = cudaMemcpyAsync(d, src + off, n, cudaMemcpyHostToDevice, s);
+    if (e != cudaSuccess) return e;
+    d += n;
+    off += n;
+    len -= n;
+  }
+  return cudaSuccess;
+}
+
 int* DevErr(pd_ctx_impl* c) { return c->d_misc.as<int>(); }
 uint32_t* DevWorkCounter(pd_ctx_impl* c) { return reinterpret_cast<uint32_t*>(c->d_misc.as<int>() + 4); }
 uint32_t* DevSparseWords(pd_ctx_impl* c) { return reinterpret_cast<uint32_t*>(c->d_misc.as<int>() + 8); }
@@ -349,12 +365,12 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
       }
       const auto tw1 = std::chrono::steady_clock::now();
       c->stats.host_wait_ms += std::chrono::duration<double, std::milli>(tw1 - tw0).count();
-      const uint8_t* hsrc;
+      const uint8_t* hsrc = nullptr;
       if (trim) {
         GatherTrimmed(c, t.v0, t.v1, c->h_stage[b].as<uint8_t>());
         hsrc = c->h_stage[b].as<uint8_t>();
       } else if (c->src_pinned) {
-        hsrc = c->pgen.mem() + t.f0;
+        // DMA straight from the caller's page-locked image / the pinned file mapping
       } else {
         if (!ParallelRead(c->pgen, t.f0, c->h_stage[b].as<uint8_t>(), len)) {
           rc = c->SetError(PD_ERR_READ, ".pgen read failure");
@@ -363,8 +379,9 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
         hsrc = c->h_stage[b].as<uint8_t>();
       }
       c->stats.host_stage_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tw1).count();
-      cudaError_t e = cudaMemcpyAsync(c->d_stage[b].as<uint8_t>() + kSlack, hsrc, len, cudaMemcpyHostToDevice,
-                                      c->copy_stream);
+      cudaError_t e = hsrc ? cudaMemcpyAsync(c->d_stage[b].as<uint8_t>() + kSlack, hsrc, len, cudaMemcpyHostToDevice,
+                                             c->copy_stream)
+                           : CopyFromPinnedSource(c, c->d_stage[b].as<uint8_t>() + kSlack, t.f0, len, c->copy_stream);
       if (e != cudaSuccess) {
         rc = CheckCuda(c, e, "H2D staging copy");
         break;

@@ -137,6 +137,9 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
             const std::function<void(const Tile&, cudaEvent_t)>& after_tile = nullptr);
 
 int CheckCuda(pd_ctx_impl* c, cudaError_t e, const char* what);
+// H2D copy of file bytes [off, off + len) of a page-locked source (memory image or pinned mapping); split where
+// the mapping's separately registered pieces meet.
+cudaError_t CopyFromPinnedSource(pd_ctx_impl* c, void* dst, uint64_t off, uint64_t len, cudaStream_t s);
 int CheckDeviceError(pd_ctx_impl* c);  // reads the device error word after a synchronize
 int* DevErr(pd_ctx_impl* c);
 uint32_t* DevWorkCounter(pd_ctx_impl* c);

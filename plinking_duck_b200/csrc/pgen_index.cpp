@@ -28,7 +28,7 @@ ByteSource::~ByteSource() {
 bool ByteSource::PinMapping() {
   if (!map_ || !map_writable_ || !size_) return false;
   // 1 GiB pieces on 2 MiB boundaries, registered from a few threads at once (the driver pins ~6.6 GiB/s per call)
-  const uint64_t kPiece = 1ull << 30;
+  const uint64_t kPiece = kPinPiece;
   uint8_t* base = const_cast<uint8_t*>(map_);
   std::vector<std::pair<uint8_t*, uint64_t>> pieces;
   for (uint64_t off = 0; off < size_; off += kPiece) pieces.emplace_back(base + off, std::min(kPiece, size_ - off));

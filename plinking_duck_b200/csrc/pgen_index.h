@@ -27,6 +27,8 @@ class ByteSource {
   // like a page-locked memory image (mem() == the mapping).  False (nothing left registered) on any failure.
   bool PinMapping();
   bool pinned() const { return !pinned_pieces_.empty(); }
+  // Page-locked pieces are separate registrations: one DMA must not span two of them.
+  static constexpr uint64_t kPinPiece = 1ull << 30;
   void OpenMem(const void* p, uint64_t len);
   // A .pgen image that already lives in device memory (reads go through cudaMemcpy).
   void OpenDevice(const void* p, uint64_t len);
