@@ -24,33 +24,10 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
 def make_file(path, V, N, seed, device):
-    import torch
+    """The C4 fileset of tests/c4.py: rare-variant MAF model + LD blocks + ALT-major + one-bit rows."""
+    import c4
 
-    from oracle import ref
-
-    gen = torch.Generator(device=device)
-    gen.manual_seed(seed)
-    W64 = (N + 31) // 32
-    rows = np.zeros((V, W64), dtype=np.uint64)
-    chunk = max(1, (256 << 20) // N)
-    for v0 in range(0, V, chunk):
-        vt = min(chunk, V - v0)
-        common = torch.rand((vt, 1), device=device, generator=gen) >= 0.95
-        u = torch.rand((vt, 1), device=device, generator=gen)
-        lo = torch.where(common, torch.full_like(u, np.log(0.01)), torch.full_like(u, np.log(1.0 / (2 * N))))
-        hi = torch.where(common, torch.full_like(u, np.log(0.5)), torch.full_like(u, np.log(0.01)))
-        maf = torch.exp(lo + u * (hi - lo))
-        x = torch.rand((vt, W64 * 32), device=device, generator=gen)
-        p2 = maf * maf
-        code = (x < p2).to(torch.int64) * 2 + ((x >= p2) & (x < p2 + 2 * maf * (1 - maf))).to(torch.int64)
-        miss = torch.rand((vt, W64 * 32), device=device, generator=gen) < 0.01
-        code = torch.where(miss, torch.full_like(code, 3), code)
-        code[:, N:] = 0
-        sh = (torch.arange(32, device=device, dtype=torch.int64) * 2).view(1, 1, 32)
-        words = (code.view(vt, W64, 32) << sh).sum(dim=2)  # < 2^64 as two's complement int64
-        rows[v0:v0 + vt] = words.cpu().numpy().view(np.uint64)
-        del x, code, miss, words
-    ref.write_pgen(path, rows, N)
+    c4.make_c4_file(path, V, N, seed, device)
 
 
 def main():

@@ -230,6 +230,55 @@ def test_score_tensor_core_path_vs_fp64_loop(N, K, mode, tmp_path):
         assert np.all(np.abs(S[:, 0] - np.asarray(rs).reshape(-1)) <= bound[0])
 
 
+def test_score_tensor_core_multibatch_ksplit_vs_reference_loop(tmp_path):
+    """K7t at scale: 150 000 scored variants (three batches of <= 65 535, accumulated across launches) x 20 011
+    samples (79 sample tiles -> the k-rows of a batch are split 7 ways over the grid, partial sums meet in the int32
+    accumulators) x 16 weight columns, against the reference's own loop (PgrGetD + Dosage16ToDoublesMinus9 + the
+    accumulation of src/plink_score.cpp:598-653 run per column on every host thread, oracle/ref_harness.cc) for the
+    default mode, and against exact integer identities for no_mean_imputation.  Tolerance: 1e-12 (2 sum|w| + 1)."""
+    import os
+    import tempfile
+
+    import torch
+
+    from bench import generate_records_gpu
+    from oracle import ref
+    from plinking_duck_b200.pgen import PgenContext
+
+    if not ref.available():
+        pytest.skip("oracle/_ref not built")
+    V, N, K = 150_000, 20_011, 16
+    Wb = (N + 3) // 4
+    dev = torch.device("cuda", 0)
+    body = torch.empty(V * Wb, dtype=torch.uint8, device=dev)
+    generate_records_gpu(V, N, 4242, dev, body)
+    img = np.concatenate([np.frombuffer(synth.fixed_header(V, N), dtype=np.uint8), body.cpu().numpy()])
+    del body
+    rng = np.random.default_rng(99)
+    vidx = np.arange(V, dtype=np.uint32)
+    w = rng.standard_normal((V, K)) * np.exp(rng.uniform(-3, 3, size=(1, K)))
+    fl = (rng.random(V) < 0.1).astype(np.uint8)
+    shm = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+    with tempfile.TemporaryDirectory(dir=shm or str(tmp_path)) as d:
+        path = os.path.join(d, "score_scale.pgen")
+        img.tofile(path)
+        with PgenContext(path) as c:
+            c.load_resident()
+            S, D, A = c.score(vidx, fl, w, 0)
+            st = c.stats()
+            assert st.scan_launches >= 3  # > 65 535 scored variants: several batches
+            S1, D1, A1 = c.score(vidx, None, w, 1)
+            het, hom, mis = c.sample_counts()
+        _t, rs, ra = ref.bench_score(path, os.cpu_count() or 1, vidx, fl, w)
+    assert np.array_equal(A, ra)
+    bound = 1e-12 * (np.abs(w).sum(axis=0) * 2.0 + 1.0)
+    err = np.abs(S - rs) / bound[None, :]
+    assert err.max() <= 1.0, float(err.max())
+    # no_mean_imputation, no flips: dosage sums and allele counts are exact integers
+    assert np.array_equal(D1, het.astype(np.float64) + 2.0 * hom.astype(np.float64))
+    assert np.array_equal(A1, (2 * (V - mis.astype(np.int64))).astype(np.uint32))
+
+
 def test_single_sample_compact_dosage_mode_vs_pgenlib(tmp_path):
     """header_ctrl mode 12 (pgenlib_read.cc:946-948): a single-sample file whose 2-bit codes select vrtype 5 / 0 /
     0x45 (no hardcall track, one unconditional dosage value) / 0x40 (hardcall byte + dosage value): doubles,

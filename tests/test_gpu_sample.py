@@ -300,3 +300,50 @@ def test_decode_i8_valid_many_batches(tmp_path):
         pv = torch.full((ev.size,), -1, dtype=torch.int64).pin_memory().numpy().view(np.uint64)
         c._check(c._lib.pd_decode_i8_valid(c._h, 0, V, 3, pd_.ctypes.data_as(C.c_void_p), pv.ctypes.data_as(C.c_void_p)))
         assert np.array_equal(pd_, ed) and np.array_equal(pv, ev)
+
+
+def test_c4_compressed_fileset_at_scale(tmp_path):
+    """BASELINE.json configs[3] shape at test scale (24 000 variants x 50 000 samples, tests/c4.py): a pgenlib-written
+    file that really holds LD-compressed (2 / 3), difflist (4 / 6), one-bit and raw records; genotype counts,
+    per-sample missingness and per-sample het / hom-alt / missing counts bit-exact against the reference's own
+    pgenlib on every variant and sample -- streamed in default and tiny tiles, and resident."""
+    import os
+    import tempfile
+
+    import torch
+
+    import c4
+    from oracle import ref
+    from plinking_duck_b200.pgen import PgenContext
+
+    if not ref.available():
+        pytest.skip("oracle/_ref not built: no pgenlib writer")
+    V, N = 24_000, 50_000
+    shm = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+    with tempfile.TemporaryDirectory(dir=shm or str(tmp_path)) as d:
+        path = os.path.join(d, "c4.pgen")
+        c4.make_c4_file(path, V, N, 777, torch.device("cuda", 0))
+        hist = c4.vrtype_histogram(path)
+        assert hist.get(2, 0) > 500 and hist.get(3, 0) > 100, hist   # LD-compressed records at scale
+        assert hist.get(4, 0) > 5000 and hist.get(6, 0) > 500 and hist.get(1, 0) > 500, hist
+        assert os.path.getsize(path) < 0.35 * V * ((N + 3) // 4)
+        with ref.RefPgen(path) as r:
+            exp_counts = r.counts()
+            _, exp_ms = r.missingness()
+            eh, ea, em = r.sample_counts(sparse=True)
+            a, b = 4000, 4200
+            exp_i8 = r.decode_i8(a, b)
+        for kw in (dict(), dict(tile_bytes=1 << 16, n_staging=2)):
+            with PgenContext(path, **kw) as c:
+                for resident in (False, True):
+                    if resident:
+                        c.load_resident()
+                    assert np.array_equal(c.counts(), exp_counts)
+                    assert np.array_equal(c.missing_by_sample(), exp_ms)
+                    h, al, m = c.sample_counts()
+                    assert np.array_equal(h, eh) and np.array_equal(al, ea) and np.array_equal(m, em)
+                assert np.array_equal(c.decode_i8(a, b), exp_i8)
+                lo, hi = 7001, 19003   # a range that starts and ends inside LD blocks
+                assert np.array_equal(c.counts(lo, hi), exp_counts[lo:hi])
+                counts, p = c.hardy(lo, hi)
+                assert np.array_equal(counts, exp_counts[lo:hi]) and np.all((p >= 0) & (p <= 1))
