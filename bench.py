@@ -148,6 +148,15 @@ def generate_records_gpu(V: int, N: int, seed: int, device, out_u8):
     torch.cuda.synchronize(device)
 
 
+def generate_image_gpu(V: int, N: int, seed: int, device, out_u8):
+    """Whole mode-0x02 file image (12-byte header + records) into out_u8 on `device` (development scripts)."""
+    import synth
+    import torch
+
+    out_u8[:12].copy_(torch.from_numpy(np.frombuffer(synth.fixed_header(V, N), dtype=np.uint8).copy()))
+    generate_records_gpu(V, N, seed, device, out_u8[12:])
+
+
 def write_fileset(path: str, V_per_gpu: int, N: int, n_gpus: int, seed: int = SEED):
     """One mode-0x02 .pgen of n_gpus x V_per_gpu variants on tmpfs: range r is generated on GPU r (seed + r),
     brought back through a page-locked ring and written with parallel pwrite."""

@@ -24,6 +24,11 @@
 //                from the packed 2-bit rows (PRMT table look-up on nibble-spread codes).
 // One tcgen05.mma (M=128, N=256, K=32, kind::i8) per slab, issued by one thread; stages are handed
 // over with mbarriers (producers -> MMA) and tcgen05.commit (MMA -> producers).
+//
+// The unit of producer work is a STEP = 32 variants.  Variants with missing calls come first in the batch's
+// k-row list ("pair" steps): their packed bytes are fetched and aligned ONCE and unpacked twice, into the G slab
+// and the M slab of the same 32 variants (two MMAs per step); variants without missing calls follow ("single"
+// steps, G slab only).  The order of k-rows inside a batch is free: the int32 sums are exact.
 #include "device_common.cuh"
 #include "kernels.cuh"
 
@@ -35,15 +40,16 @@ constexpr uint32_t kTileN = 256;    // samples per CTA tile (MMA N)
 constexpr uint32_t kSlabK = 32;     // k-rows per MMA (K of kind::i8)
 constexpr uint32_t kRowsM = 128;    // MMA M: weight-limb rows
 constexpr uint32_t kLimbs = 7;
-constexpr uint32_t kStages = 4;     // B slabs (8 KB each) between the unpackers and the MMA
-constexpr uint32_t kAStages = 6;    // A slabs (4 KB bulk copies): deep enough to cover their L2 latency
+constexpr uint32_t kStages = 6;     // B slabs (8 KB each) between the unpackers and the MMA
+constexpr uint32_t kAStages = 2 * kStages;  // A slabs (4 KB bulk copies from L2): their latency under load is ~2 us, so they run further ahead than the B slabs
 constexpr uint32_t kBBytes = kTileN * kSlabK;  // 8 KB
 constexpr uint32_t kABytes = kRowsM * kSlabK;  // 4 KB
 constexpr uint32_t kProducers = 128;  // threads that unpack one slab
 constexpr uint32_t kGroups = 2;       // producer groups; group g unpacks slabs g, g + kGroups, ... of the CTA
 constexpr uint32_t kProdWarps = kGroups * kProducers / 32;
-constexpr uint32_t kMmaThreads = kGroups * kProducers + 64;  // + one warp (MMA issue, TMEM) + one warp (A copies)
-constexpr uint32_t kPrefetch = 3;   // steps of packed bytes a producer group keeps in flight (cp.async ring)
+constexpr uint32_t kMmaThreads = kGroups * kProducers + 64 + 32 * kGroups;  // + MMA issue / TMEM warp, A-copy warp, one packed-row loader warp per group
+constexpr uint32_t kPStages = 6;    // steps of packed rows in flight between the loader warp and the converters
+constexpr uint32_t kPRow = 80;      // bytes staged per row and step: the 64 wanted ones at any 16-byte misalignment
 constexpr uint32_t kPlaneM = 0x80000000u;
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -72,6 +78,33 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "r"(parity)
       : "memory");
 }
+__device__ __forceinline__ void mbar_wait_addr(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_addr(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "elect.sync _|p, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                    smem_u32(dst)),
@@ -81,6 +114,10 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 // 16-byte asynchronous copy global -> shared (LDGSTS); src_bytes = 0 zero-fills without reading.
 __device__ __forceinline__ void cp_async16(void* dst, const void* src, uint32_t src_bytes) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
+}
+// Arrives on the mbarrier (without raising its pending count) once all cp.async of this thread so far are done.
+__device__ __forceinline__ void cp_async_mbar_arrive(uint64_t* bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
@@ -116,6 +153,9 @@ __device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t a_desc, uint64
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
+}
+__device__ __forceinline__ void umma_commit_addr(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
   asm volatile(
@@ -172,50 +212,52 @@ k_tc_plan(const uint4* __restrict__ counts, const ScoreRow* __restrict__ srow, c
           double* __restrict__ col_const, uint32_t* __restrict__ meta) {
   __shared__ uint32_t s_scan[kPlanThreads];
   __shared__ double s_red[kPlanThreads];
-  __shared__ uint32_t s_base, s_active;
   const uint32_t t = threadIdx.x;
   const uint32_t ncols = K + 2;
   if (blockIdx.x == ncols) {
-    // ---- block K+2: the k-row list ----
-    if (t == 0) {
-      s_base = 0;
-      s_active = 0;
-    }
-    __syncthreads();
-    for (uint32_t r0 = 0; r0 < nrows; r0 += kPlanThreads) {
-      const uint32_t r = r0 + t;
-      uint32_t n = 0;
-      bool act = false, mis = false;
-      if (r < nrows) {
-        act = (srow[r].flags & kScoreActive) != 0;
-        mis = act && counts[r].w != 0;
-        n = (act ? 1u : 0u) + (mis ? 1u : 0u);
-      }
-      s_scan[t] = n;
-      __syncthreads();
-      for (uint32_t off = 1; off < kPlanThreads; off <<= 1) {
-        const uint32_t add = t >= off ? s_scan[t - off] : 0u;
+    // ---- block K+2: the k-row list: active variants with missing calls (pair steps), then those without ----
+    uint32_t region_base = 0, n_real[2] = {0, 0}, n_steps[2] = {0, 0};
+    uint32_t nact_total = 0;
+    const uint32_t lane = t & 31u, wid = t >> 5;
+    uint32_t* warp_tot = s_scan;  // [32] per-warp totals of the current chunk
+    for (uint32_t pass = 0; pass < 2; ++pass) {
+      uint32_t base = 0;  // entries of this pass so far (same value in every thread)
+      for (uint32_t r0 = 0; r0 < nrows; r0 += kPlanThreads) {
+        const uint32_t r = r0 + t;
+        bool take = false;
+        if (r < nrows) {
+          const bool act = (srow[r].flags & kScoreActive) != 0;
+          const bool mis = counts[r].w != 0;
+          take = act && (pass == 0 ? mis : !mis);
+        }
+        const uint32_t bal = __ballot_sync(0xffffffffu, take);
+        if (lane == 0) warp_tot[wid] = __popc(bal);
         __syncthreads();
-        s_scan[t] += add;
+        uint32_t before = 0, total = 0;
+#pragma unroll 4
+        for (uint32_t w = 0; w < kPlanThreads / 32; ++w) {
+          const uint32_t c = warp_tot[w];
+          before += w < wid ? c : 0u;
+          total += c;
+        }
+        if (take) krow[region_base + base + before + __popc(bal & ((1u << lane) - 1u))] = r;
+        base += total;
         __syncthreads();
       }
-      const uint32_t pos = s_base + s_scan[t] - n;
-      if (act) krow[pos] = r;
-      if (mis) krow[pos + 1] = r | kPlaneM;
-      const uint32_t nact = __syncthreads_count(act);
-      if (t == 0) {
-        s_base += s_scan[kPlanThreads - 1];
-        s_active += nact;
-      }
-      __syncthreads();
+      const uint32_t n = base;
+      const uint32_t n_pad = (n + kSlabK - 1) / kSlabK * kSlabK;
+      for (uint32_t i = n + t; i < n_pad; i += kPlanThreads) krow[region_base + i] = 0;  // zero weights; any valid row will do
+      n_real[pass] = n;
+      n_steps[pass] = n_pad / kSlabK;
+      nact_total += n;
+      region_base += n_pad;
     }
-    const uint32_t nk = s_base;
-    const uint32_t nk_pad = (nk + kSlabK - 1) / kSlabK * kSlabK;
-    for (uint32_t i = nk + t; i < nk_pad; i += kPlanThreads) krow[i] = 0;  // zero weights; any valid row will do
     if (t == 0) {
-      meta[0] = nk_pad;
-      meta[1] = s_active;
-      meta[2] = nk;
+      meta[0] = n_steps[0];   // pair steps (two slabs each)
+      meta[1] = nact_total;   // active variants
+      meta[2] = n_steps[1];   // single steps
+      meta[3] = n_real[0];
+      meta[4] = n_real[1];
     }
     return;
   }
@@ -268,38 +310,41 @@ k_tc_plan(const uint4* __restrict__ counts, const ScoreRow* __restrict__ srow, c
 __global__ void __launch_bounds__(256)
 k_tc_quant(DenseRows rows, const ScoreRow* __restrict__ srow, const double* __restrict__ weights, uint32_t K,
            uint32_t mode, const uint32_t* __restrict__ krow, const double* __restrict__ col_scale,
-           const uint32_t* __restrict__ meta, uint32_t nk_cap, int8_t* __restrict__ a_tiles,
+           const uint32_t* __restrict__ meta, uint32_t slot_cap, int8_t* __restrict__ a_tiles,
            unsigned long long* __restrict__ krow_ptr) {
   const uint32_t ncols = K + 2;
   const uint64_t tid = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const uint32_t i = static_cast<uint32_t>(tid / ncols);
+  const uint32_t i = static_cast<uint32_t>(tid / ncols);  // slot in the k-row list
   const uint32_t c = static_cast<uint32_t>(tid % ncols);
-  if (i >= nk_cap || i >= meta[0]) return;
-  const uint32_t kr = krow[i];
-  if (c == 0) {  // where the k-row's packed genotypes start, plane flag in bit 63
-    const uint32_t rr = kr & ~kPlaneM;
-    const uint8_t* row = rows.ptrs ? rows.ptrs[rr] : rows.base + static_cast<uint64_t>(rr) * rows.stride;
-    krow_ptr[i] = reinterpret_cast<unsigned long long>(row) | ((kr & kPlaneM) ? (1ull << 63) : 0ull);
+  const uint32_t pair_slots = meta[0] * kSlabK, single_slots = meta[2] * kSlabK;
+  if (i >= slot_cap || i >= pair_slots + single_slots) return;
+  const uint32_t r = krow[i];
+  if (c == 0) {  // where the variant's packed genotypes start
+    const uint8_t* row = rows.ptrs ? rows.ptrs[r] : rows.base + static_cast<uint64_t>(r) * rows.stride;
+    krow_ptr[i] = reinterpret_cast<unsigned long long>(row);
   }
-  if (i >= meta[2]) return;  // padding k-rows keep their zero limbs
-  const uint32_t r = kr & ~kPlaneM;
-  const bool plane_m = (kr & kPlaneM) != 0;
+  const bool pair = i < pair_slots;
+  const uint32_t j = pair ? i : i - pair_slots;                 // slot inside its region
+  if (j >= (pair ? meta[3] : meta[4])) return;                  // padding slots keep their zero limbs
+  const uint32_t slab_g = pair ? 2u * (j / kSlabK) : 2u * meta[0] + j / kSlabK;
+  const uint32_t k = j % kSlabK;
   const ScoreRow& R = srow[r];
-  long long q;
-  if (c == K + 1) {
-    q = (plane_m && mode != 0) ? 1 : 0;
-  } else {
-    const double w = col_weight(weights, K, mode, r, c);
-    const double x = plane_m ? w * (R.T[3] - R.T[0]) : w * (0.5 * (R.T[2] - R.T[0]));
-    q = __double2ll_rn(x / col_scale[c]);  // scale is a power of two: the division is exact
-  }
-  int8_t* slab = a_tiles + static_cast<uint64_t>(i / kSlabK) * kABytes;
-  const uint32_t k = i % kSlabK;
+  for (uint32_t plane = 0; plane < (pair ? 2u : 1u); ++plane) {
+    long long q;
+    if (c == K + 1) {
+      q = (plane && mode != 0) ? 1 : 0;
+    } else {
+      const double w = col_weight(weights, K, mode, r, c);
+      const double x = plane ? w * (R.T[3] - R.T[0]) : w * (0.5 * (R.T[2] - R.T[0]));
+      q = __double2ll_rn(x / col_scale[c]);  // scale is a power of two: the division is exact
+    }
+    int8_t* slab = a_tiles + static_cast<uint64_t>(slab_g + plane) * kABytes;
 #pragma unroll
-  for (uint32_t l = 0; l < kLimbs; ++l) {
-    const long long b = static_cast<long long>(static_cast<int8_t>(q & 0xff));
-    slab[a_offset(c * kLimbs + l, k)] = static_cast<int8_t>(b);
-    q = (q - b) >> 8;
+    for (uint32_t l = 0; l < kLimbs; ++l) {
+      const long long b = static_cast<long long>(static_cast<int8_t>(q & 0xff));
+      slab[a_offset(c * kLimbs + l, k)] = static_cast<int8_t>(b);
+      q = (q - b) >> 8;
+    }
   }
 }
 
@@ -312,12 +357,15 @@ k_tc_quant(DenseRows rows, const ScoreRow* __restrict__ srow, const double* __re
 struct MmaSmem {
   alignas(128) uint8_t b[kStages][kBBytes];
   alignas(128) uint8_t a[kAStages][kABytes];
-  // packed 2-bit bytes in flight: per group and step, two 16-byte chunks per producer thread
-  alignas(128) uint4 p[kGroups][kPrefetch][2][kProducers];
-  alignas(8) uint64_t full[kStages];
-  uint64_t empty[kStages];
-  uint64_t a_full[kAStages];
-  uint64_t a_empty[kAStages];
+  // packed 2-bit rows of a step (32 variants x 64 samples' bytes, in aligned 16-byte chunks) + each row's misalignment
+  alignas(16) uint8_t pk[kPStages][kSlabK][kPRow];
+  uint32_t pk_mis[kPStages][kSlabK];
+  alignas(8) uint64_t p_full[kPStages];   // loader: 32 cp.async completion arrivals + 1 plain arrival
+  uint64_t p_empty[kPStages];             // the 4 converter warps of the step's group have the bytes in registers
+  uint64_t full[kStages];              // 4 producer-warp arrivals
+  uint64_t empty[kStages];             // tcgen05.commit: the MMA has read B stage s
+  uint64_t a_full[kAStages];           // the A copy's expect_tx arrival and its bytes
+  uint64_t a_empty[kAStages];          // tcgen05.commit: the MMA has read A stage s
   uint64_t acc_ready;
   uint32_t tmem_base;
 };
@@ -337,18 +385,65 @@ __device__ __forceinline__ uint4 unpack16(uint32_t w, uint32_t tab) {
   return o;
 }
 
+__device__ __forceinline__ uint4 ldg128_stream(const uint8_t* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p));
+  return v;
+}
+
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// The steps a CTA (k split y of ksplit) works through: its share of the pair steps, then its share of the
+// single steps.  Virtual step j -> (first variant slot, first slab, planes).
+struct StepRange {
+  uint32_t p0, np, s0, ns;       // pair steps [p0, p0 + np), single steps [s0, s0 + ns)
+  uint32_t pair_total;           // pair steps of the whole batch
+  __device__ __forceinline__ uint32_t steps() const { return np + ns; }
+  __device__ __forceinline__ uint32_t planes(uint32_t j) const { return j < np ? 2u : 1u; }
+  __device__ __forceinline__ uint32_t slot0(uint32_t j) const {
+    return (j < np ? p0 + j : pair_total + s0 + (j - np)) * kSlabK;
+  }
+  __device__ __forceinline__ uint32_t slab0(uint32_t j) const {   // index into a_tiles
+    return j < np ? 2u * (p0 + j) : 2u * pair_total + s0 + (j - np);
+  }
+  __device__ __forceinline__ uint32_t seq0(uint32_t j) const {    // the CTA's own slab counter at step j
+    return j < np ? 2u * j : 2u * np + (j - np);
+  }
+  __device__ __forceinline__ uint32_t slabs() const { return 2u * np + ns; }
+};
+
+__device__ __forceinline__ StepRange step_range(const uint32_t* __restrict__ meta, uint32_t y, uint32_t ksplit) {
+  StepRange r;
+  const uint32_t P = meta[0], S = meta[2];
+  const uint32_t pp = (P + ksplit - 1) / ksplit, ps = (S + ksplit - 1) / ksplit;
+  r.pair_total = P;
+  r.p0 = min(P, y * pp);
+  r.np = min(P, r.p0 + pp) - r.p0;
+  r.s0 = min(S, y * ps);
+  r.ns = min(S, r.s0 + ps) - r.s0;
+  return r;
+}
+
 __global__ void __launch_bounds__(kMmaThreads, 2)
 k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, const int8_t* __restrict__ a_tiles,
-            const uint32_t* __restrict__ meta, uint32_t ksplit, int32_t* __restrict__ acc32, uint32_t n_samples) {
+            const uint32_t* __restrict__ meta, uint32_t ksplit, int32_t* __restrict__ acc32, uint32_t n_samples,
+            uint32_t acc_stride) {
   extern __shared__ uint8_t smem_raw[];
   MmaSmem& sm = *reinterpret_cast<MmaSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
   const uint32_t tile = blockIdx.x;
-  const uint32_t nslab_all = meta[0] / kSlabK;
-  const uint32_t per = (nslab_all + ksplit - 1) / ksplit;
-  const uint32_t s0 = blockIdx.y * per;
-  const uint32_t s1 = min(nslab_all, s0 + per);
-  if (s0 >= s1) return;  // uniform for the CTA
+  const StepRange sr = step_range(meta, blockIdx.y, ksplit);
+  const uint32_t nsteps = sr.steps();
+  if (!nsteps) return;  // uniform for the CTA
 
   if (warp == kProdWarps) {
     if (lane == 0) {
@@ -359,6 +454,10 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
       for (uint32_t i = 0; i < kAStages; ++i) {
         mbar_init(&sm.a_full[i], 1);
         mbar_init(&sm.a_empty[i], 1);
+      }
+      for (uint32_t i = 0; i < kPStages; ++i) {
+        mbar_init(&sm.p_full[i], 33);
+        mbar_init(&sm.p_empty[i], kProducers / 32);
       }
       mbar_init(&sm.acc_ready, 1);
       fence_barrier_init();
@@ -374,82 +473,67 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
   if (warp < kProdWarps) {
     // ================= producers: packed 2-bit rows -> int8 B slabs =================
     const uint32_t grp = warp >> 2, wq = warp & 3u;
-    const uint32_t kk = wq * 8 + (lane & 7u);     // k-row within the slab
+    const uint32_t kk = wq * 8 + (lane & 7u);     // variant within the step = k-row within its slab(s)
     const uint32_t gq = lane >> 3;                // which 64 samples of the 256
     const uint32_t row_bytes = (n_raw + 3) >> 2;
     const uint32_t off = tile * (kTileN / 4) + gq * 16;  // byte offset of this quarter inside a row
-    const uint32_t nit = s1 - s0;
-    const uint32_t tg = threadIdx.x & (kProducers - 1);
-    // Pipeline: the k-row's pointer is requested 2 x kPrefetch steps ahead (one register load), its
-    // packed bytes kPrefetch steps ahead with cp.async into this thread's own ring slots -- rows start
-    // at any byte, so the 32 aligned bytes around the 16 wanted ones are copied.  Asynchronous copies
-    // hold no registers and no scoreboard, which is what lets ~20 KB per SM stay in flight.
-    // Step j of group grp is the CTA's slab it = grp + j * kGroups.
-    auto it_of = [&](uint32_t j) { return grp + j * kGroups; };
-    auto fetch_ptr = [&](uint32_t j) {
-      return it_of(j) < nit ? __ldg(krow_ptr + static_cast<uint64_t>(s0 + it_of(j)) * kSlabK + kk) : 0ull;
-    };
-    auto issue = [&](uint32_t j, unsigned long long kp) -> uint32_t {
-      uint32_t sp = 0;
-      if (it_of(j) < nit) {
-        const uintptr_t p = static_cast<uintptr_t>(kp & ~(1ull << 63)) + off;
-        const uint8_t* src = reinterpret_cast<const uint8_t*>(p & ~uintptr_t(15));
-        const uint32_t nb = off < row_bytes ? 16u : 0u;  // quarters past the end of the row: zeros
-        cp_async16(&sm.p[grp][j % kPrefetch][0][tg], src, nb);
-        cp_async16(&sm.p[grp][j % kPrefetch][1][tg], src + 16, nb);
-        sp = (static_cast<uint32_t>(p & 15) << 3) | ((kp >> 63) ? kPlaneM : 0u);
-      }
-      cp_async_commit();  // one group per step, empty past the end, so that wait_group counts stay aligned
-      return sp;
-    };
-    auto emit = [&](uint32_t j, uint32_t sp) {
-      const uint32_t it = it_of(j);
-      const uint32_t stage = it % kStages;
-      const uint4 x0 = sm.p[grp][j % kPrefetch][0][tg], x1 = sm.p[grp][j % kPrefetch][1][tg];
-      // the 16 wanted bytes start (sp >> 3) & 15 bytes into the 32: whole words first, then a funnel shift
-      uint32_t w[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
-      if (sp & 64u) {
+    // The packed rows of a step arrive through the loader warp (cp.async into sm.pk, below): these warps never
+    // have a global load in flight, so the proxy fence in front of every slab hand-over (a MEMBAR that waits for
+    // all of the thread's outstanding memory operations) costs shared-memory latency, not HBM latency -- with the
+    // loads prefetched by the unpacking threads themselves every fence waited for them and a step took ~2500
+    // cycles (profiles/r02_ncu_k_score_mma_*).  Step i of group grp is the CTA's step j = grp + i * kGroups.
+    const uint32_t b_thread = smem_u32(sm.b[0]) + (kk & 7u) * 16u + (kk >> 3) * kBLbo + (gq * 4u) * kBSbo;
+    const bool in_row = off < row_bytes;  // quarters past the end of the row: zeros
+    const uint32_t pk_row = smem_u32(&sm.pk[0][kk][0]) + gq * 16u;
+    const uint32_t pk_mis = smem_u32(&sm.pk_mis[0][kk]);
+    const uint32_t p_full0 = smem_u32(&sm.p_full[0]), p_empty0 = smem_u32(&sm.p_empty[0]);
+    const uint32_t full0 = smem_u32(&sm.full[0]), empty0 = smem_u32(&sm.empty[0]);
+    // ring positions advance by addition (the stage counts are not powers of two: no divisions in the loop)
+    uint32_t pst = grp, pphase = 0;                 // packed stage of step j = j % kPStages
+    uint32_t stage = sr.seq0(grp) % kStages;        // B stage of the step's first slab
+    uint32_t sphase = (sr.seq0(grp) / kStages) & 1u;
+    for (uint32_t j = grp; j < nsteps; j += kGroups) {
+      mbar_wait_addr(p_full0 + pst * 8u, pphase);
+      const uint32_t mis = lds32(pk_mis + pst * (kSlabK * 4u));
+      const uint32_t src = pk_row + pst * (kSlabK * kPRow) + (mis & ~3u);  // first wanted byte, rounded down to a word
+      uint32_t w[5];
 #pragma unroll
-        for (int i = 0; i < 6; ++i) w[i] = w[i + 2];
-      }
-      if (sp & 32u) {
+      for (int u = 0; u < 5; ++u) w[u] = in_row ? lds32(src + 4u * u) : 0u;
+      const uint32_t sh = (mis & 3u) * 8u;
 #pragma unroll
-        for (int i = 0; i < 5; ++i) w[i] = w[i + 1];
-      }
-      const uint32_t sh = sp & 31u;
-      const uint32_t tab = (sp & kPlaneM) ? 0x01000000u : 0x00020100u;  // M: [3] -> 1;  G: 0, 1, 2, missing -> 0
-      mbar_wait(&sm.empty[stage], ((it / kStages) & 1u) ^ 1u);
-      uint8_t* dst = sm.b[stage] + (kk & 7u) * 16u + (kk >> 3) * kBLbo + (gq * 4u) * kBSbo;
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        *reinterpret_cast<uint4*>(dst + u * kBSbo) = unpack16(__funnelshift_r(w[u], w[u + 1], sh), tab);
-      }
-      fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
+      for (int u = 0; u < 4; ++u) w[u] = __funnelshift_r(w[u], w[u + 1], sh);
       __syncwarp();
-      if (lane == 0) mbar_arrive(&sm.full[stage]);  // one arrival per warp: 32 would serialise on the barrier word
-    };
-    uint32_t sps[kPrefetch];
-    unsigned long long ptrs[kPrefetch];
+      if (lane == 0) mbar_arrive_addr(p_empty0 + pst * 8u);  // the bytes are in registers
+      const uint32_t planes = sr.planes(j);
+      // G plane: 0, 1, 2, missing -> 0.  M plane (pair steps): missing -> 1.  Same bytes, two tables.
+      uint32_t st = stage, ph = sphase;
+      for (uint32_t pl = 0; pl < planes; ++pl) {
+        const uint32_t tab = pl ? 0x01000000u : 0x00020100u;
+        mbar_wait_addr(empty0 + st * 8u, ph ^ 1u);
+        const uint32_t dst = b_thread + st * kBBytes;
 #pragma unroll
-    for (uint32_t d = 0; d < kPrefetch; ++d) ptrs[d] = fetch_ptr(d);
-#pragma unroll
-    for (uint32_t d = 0; d < kPrefetch; ++d) {
-      sps[d] = issue(d, ptrs[d]);
-      ptrs[d] = fetch_ptr(kPrefetch + d);
-    }
-    for (uint32_t jb = 0; it_of(jb) < nit; jb += kPrefetch) {
-#pragma unroll
-      for (uint32_t d = 0; d < kPrefetch; ++d) {
-        const uint32_t j = jb + d;
-        if (it_of(j) < nit) {  // uniform for the group
-          cp_async_wait<kPrefetch - 1>();  // step j's copies have landed (this thread reads only its own)
-          emit(j, sps[d]);
-          sps[d] = issue(j + kPrefetch, ptrs[d]);
-          ptrs[d] = fetch_ptr(j + 2 * kPrefetch);
+        for (int u = 0; u < 4; ++u) sts128(dst + u * kBSbo, unpack16(w[u], tab));
+        fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
+        __syncwarp();
+        if (lane == 0) mbar_arrive_addr(full0 + st * 8u);  // one arrival per warp: 32 would serialise on the barrier word
+        if (++st == kStages) {
+          st = 0;
+          ph ^= 1u;
         }
       }
+      // this group's next step is j + kGroups: skip the other group's step in between
+      const uint32_t adv = planes + (j + 1 < nsteps ? sr.planes(j + 1) : 0u);  // <= 4 < kStages
+      stage += adv;
+      if (stage >= kStages) {
+        stage -= kStages;
+        sphase ^= 1u;
+      }
+      pst += kGroups;
+      if (pst >= kPStages) {
+        pst -= kPStages;
+        pphase ^= 1u;
+      }
     }
-    cp_async_wait<0>();
     // ================= epilogue: TMEM -> acc32 =================
     mbar_wait(&sm.acc_ready, 0);
     tc_fence_after();
@@ -458,39 +542,111 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
       uint32_t v[16];
       tmem_ld16(tmem + ((wq * 32u) << 16) + c0, v);
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const uint32_t s = tile * kTileN + c0 + j;
-        if (s < n_samples && v[j] != 0u) {
-          atomicAdd(acc32 + static_cast<uint64_t>(s) * kRowsM + r, static_cast<int32_t>(v[j]));
+      for (int u = 0; u < 16; ++u) {
+        const uint32_t s = tile * kTileN + c0 + u;
+        if (s < n_samples && v[u] != 0u) {
+          atomicAdd(acc32 + static_cast<uint64_t>(r) * acc_stride + s, static_cast<int32_t>(v[u]));
         }
       }
     }
     tc_fence_before();
   } else if (warp == kProdWarps) {
     // ================= MMA issuer =================
-    if (lane == 0) {
-      for (uint32_t it = 0; it < s1 - s0; ++it) {
-        const uint32_t stage = it % kStages, astage = it % kAStages;
-        mbar_wait(&sm.a_full[astage], (it / kAStages) & 1u);
-        mbar_wait(&sm.full[stage], (it / kStages) & 1u);
-        tc_fence_after();
-        const uint64_t a_desc = smem_desc(smem_u32(sm.a[astage]), kALbo, kASbo);
-        const uint64_t b_desc = smem_desc(smem_u32(sm.b[stage]), kBLbo, kBSbo);
-        umma_i8(tmem, a_desc, b_desc, kIdesc, it ? 1u : 0u);
-        umma_commit(&sm.empty[stage]);  // frees the stages once the MMA has read them
-        umma_commit(&sm.a_empty[astage]);
+    // The whole warp walks the slabs (uniform control flow), one elected lane issues.  Stage = slab % kStages for
+    // both operands, so the ring is unrolled with compile-time descriptor offsets: per slab one barrier wait, one
+    // MMA, one commit.  (A leaner loop matters: with ~65 dependent instructions per slab in one thread the issuer,
+    // not the tensor pipe, set the pace -- profiles/r02_ncu_k_score_mma_*.)
+    const uint32_t nslabs = sr.slabs();
+    const uint64_t a_desc0 = smem_desc(smem_u32(sm.a[0]), kALbo, kASbo);
+    const uint64_t b_desc0 = smem_desc(smem_u32(sm.b[0]), kBLbo, kBSbo);
+    const uint32_t full0 = smem_u32(&sm.full[0]), empty0 = smem_u32(&sm.empty[0]);
+    const uint32_t a_full0 = smem_u32(&sm.a_full[0]), a_empty0 = smem_u32(&sm.a_empty[0]);
+    uint32_t aphase = 0;
+    for (uint32_t base = 0; base < nslabs; base += kAStages) {
+#pragma unroll
+      for (uint32_t st = 0; st < kAStages; ++st) {
+        if (base + st < nslabs) {  // warp-uniform
+          constexpr uint32_t kRounds = kAStages / kStages;
+          const uint32_t bst = st % kStages;
+          const uint32_t bphase = (aphase * kRounds + st / kStages) & 1u;
+          mbar_wait_addr(a_full0 + st * 8u, aphase);
+          mbar_wait_addr(full0 + bst * 8u, bphase);
+          tc_fence_after();
+          if (elect_one()) {
+            umma_i8(tmem, a_desc0 + ((st * kABytes) >> 4), b_desc0 + ((bst * kBBytes) >> 4), kIdesc, base + st ? 1u : 0u);
+            umma_commit_addr(empty0 + bst * 8u);    // frees the stages once the MMA has read them
+            umma_commit_addr(a_empty0 + st * 8u);
+          }
+          __syncwarp();
+        }
       }
-      umma_commit(&sm.acc_ready);
+      aphase ^= 1u;
     }
+    if (elect_one()) umma_commit(&sm.acc_ready);
     __syncwarp();
+  } else if (warp >= kProdWarps + 2) {
+    // ================= loaders: packed rows of every step, global -> shared with cp.async =================
+    // One loader warp per converter group (steps j = g, g + kGroups, ...).  Lane l owns row l of the step (its
+    // pointer, its misalignment); the 32 x 5 aligned 16-byte chunks of a step are then copied by consecutive lanes
+    // (5 lanes per row: contiguous global reads).  Row pointers are requested two of the warp's steps ahead.
+    const uint32_t g = warp - (kProdWarps + 2);
+    const uint32_t row_bytes = (n_raw + 3) >> 2;
+    const uint32_t tile_off = tile * (kTileN / 4);
+    const uint32_t len = min(kTileN / 4, row_bytes - tile_off);  // wanted bytes of a row (the last tile is ragged)
+    uint32_t row_q[5], ch16_q[5], dst_q[5];
+#pragma unroll
+    for (uint32_t q = 0; q < 5; ++q) {
+      const uint32_t idx = q * 32u + lane;
+      row_q[q] = idx / 5u;
+      ch16_q[q] = (idx - row_q[q] * 5u) * 16u;
+      dst_q[q] = smem_u32(&sm.pk[0][row_q[q]][0]) + ch16_q[q];
+    }
+    auto ptr_of = [&](uint32_t j) { return j < nsteps ? __ldg(krow_ptr + sr.slot0(j) + lane) : 0ull; };
+    unsigned long long kp0 = ptr_of(g), kp1 = ptr_of(g + kGroups);
+    const uint32_t p_full0 = smem_u32(&sm.p_full[0]), p_empty0 = smem_u32(&sm.p_empty[0]);
+    const uint32_t mis0 = smem_u32(&sm.pk_mis[0][lane]);
+    uint32_t pst = g, pphase = 0;
+    for (uint32_t j = g; j < nsteps; j += kGroups) {
+      const unsigned long long kp = kp0;
+      kp0 = kp1;
+      kp1 = ptr_of(j + 2 * kGroups);
+      mbar_wait_addr(p_empty0 + pst * 8u, pphase ^ 1u);
+      const uintptr_t p = static_cast<uintptr_t>(kp) + tile_off;
+      const uint32_t mis = static_cast<uint32_t>(p & 15);
+      const unsigned long long base = static_cast<unsigned long long>(p & ~uintptr_t(15));
+      asm volatile("st.shared.u32 [%0], %1;" ::"r"(mis0 + pst * (kSlabK * 4u)), "r"(mis) : "memory");
+      __syncwarp();
+      const uint32_t pk_off = pst * (kSlabK * kPRow);
+#pragma unroll
+      for (uint32_t q = 0; q < 5; ++q) {
+        const unsigned long long rb = __shfl_sync(0xffffffffu, base, row_q[q]);
+        const uint32_t rmis = __shfl_sync(0xffffffffu, mis, row_q[q]);
+        const uint32_t nb = ch16_q[q] < rmis + len ? 16u : 0u;  // chunks past the wanted bytes: zero-filled, not read
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst_q[q] + pk_off),
+                     "l"(rb + ch16_q[q]), "r"(nb)
+                     : "memory");
+      }
+      asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(p_full0 + pst * 8u) : "memory");
+      if (lane == 0) mbar_arrive_addr(p_full0 + pst * 8u);  // publishes pk_mis (ordered behind the __syncwarp)
+      pst += kGroups;
+      if (pst >= kPStages) {
+        pst -= kPStages;
+        pphase ^= 1u;
+      }
+    }
+    cp_async_wait<0>();
   } else {
-    // ================= A slabs: one 4 KB bulk copy per stage =================
+    // ================= A slabs: one 4 KB bulk copy per slab, into the stage its B slab uses =================
     if (lane == 0) {
-      for (uint32_t it = 0; it < s1 - s0; ++it) {
-        const uint32_t astage = it % kAStages;
-        mbar_wait(&sm.a_empty[astage], ((it / kAStages) & 1u) ^ 1u);
-        mbar_arrive_expect_tx(&sm.a_full[astage], kABytes);
-        bulk_g2s(sm.a[astage], a_tiles + static_cast<uint64_t>(s0 + it) * kABytes, kABytes, &sm.a_full[astage]);
+      uint32_t sq = 0;
+      for (uint32_t j = 0; j < nsteps; ++j) {
+        const uint32_t planes = sr.planes(j);
+        for (uint32_t pl = 0; pl < planes; ++pl, ++sq) {
+          const uint32_t stage = sq % kAStages;
+          mbar_wait(&sm.a_empty[stage], ((sq / kAStages) & 1u) ^ 1u);
+          mbar_arrive_expect_tx(&sm.a_full[stage], kABytes);
+          bulk_g2s(sm.a[stage], a_tiles + static_cast<uint64_t>(sr.slab0(j) + pl) * kABytes, kABytes, &sm.a_full[stage]);
+        }
       }
     }
     __syncwarp();
@@ -508,20 +664,19 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
 // term, accumulates into the fp64 results and clears acc32 for the next batch.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-k_tc_finish(int32_t* __restrict__ acc32, const double* __restrict__ col_scale, const double* __restrict__ col_const,
-            const uint32_t* __restrict__ meta, uint32_t n_samples, uint32_t K, uint32_t mode, double* __restrict__ score,
-            double* __restrict__ dosage_sums, uint32_t* __restrict__ allele_cts) {
-  const uint32_t ncols = K + 2;
-  const uint64_t tid = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const uint32_t s = static_cast<uint32_t>(tid / ncols);
-  const uint32_t c = static_cast<uint32_t>(tid % ncols);
+k_tc_finish(int32_t* __restrict__ acc32, uint32_t acc_stride, const double* __restrict__ col_scale,
+            const double* __restrict__ col_const, const uint32_t* __restrict__ meta, uint32_t n_samples, uint32_t K,
+            uint32_t mode, double* __restrict__ score, double* __restrict__ dosage_sums, uint32_t* __restrict__ allele_cts) {
+  // acc32 is [limb row][sample]: consecutive threads take consecutive samples of one column (blockIdx.y)
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t c = blockIdx.y;
   if (s >= n_samples) return;
-  int32_t* a = acc32 + static_cast<uint64_t>(s) * kRowsM + c * kLimbs;
+  int32_t* a = acc32 + static_cast<uint64_t>(c * kLimbs) * acc_stride + s;
   long long limb[kLimbs];
 #pragma unroll
   for (uint32_t l = 0; l < kLimbs; ++l) {
-    limb[l] = a[l];
-    a[l] = 0;
+    limb[l] = a[static_cast<uint64_t>(l) * acc_stride];
+    a[static_cast<uint64_t>(l) * acc_stride] = 0;
   }
   if (c == K + 1) {
     const uint32_t n_active = meta[1];
@@ -549,10 +704,16 @@ struct TcWorkspace {
   double* col_const;
   uint32_t* meta;
   int32_t* acc32;
+  uint32_t acc_stride;  // samples per limb row of acc32, padded
   size_t bytes;
 };
+// Slots of the k-row list: both regions are padded to whole steps.
+size_t slot_cap_of(uint32_t max_rows) { return (static_cast<size_t>(max_rows) + kSlabK - 1) / kSlabK * kSlabK + kSlabK; }
+// A slabs: two per pair step, one per single step.
+size_t slab_cap_of(uint32_t max_rows) { return 2 * (slot_cap_of(max_rows) / kSlabK); }
+
 TcWorkspace carve(void* base, uint32_t max_rows, uint32_t n_samples) {
-  const size_t nk_cap = (2ull * max_rows + kSlabK - 1) / kSlabK * kSlabK;
+  const size_t nk_cap = slot_cap_of(max_rows);
   uint8_t* p = static_cast<uint8_t*>(base);
   size_t off = 0;
   auto take = [&](size_t n) {
@@ -563,11 +724,12 @@ TcWorkspace carve(void* base, uint32_t max_rows, uint32_t n_samples) {
   TcWorkspace w;
   w.krow = reinterpret_cast<uint32_t*>(take(nk_cap * 4));
   w.krow_ptr = reinterpret_cast<unsigned long long*>(take(nk_cap * 8));
-  w.a_tiles = reinterpret_cast<int8_t*>(take(nk_cap / kSlabK * kABytes));
+  w.a_tiles = reinterpret_cast<int8_t*>(take(slab_cap_of(max_rows) * kABytes));
   w.col_scale = reinterpret_cast<double*>(take(kMaxCols * 8));
   w.col_const = reinterpret_cast<double*>(take(kMaxCols * 8));
-  w.meta = reinterpret_cast<uint32_t*>(take(16));
-  w.acc32 = reinterpret_cast<int32_t*>(take(static_cast<size_t>(n_samples) * kRowsM * 4));
+  w.meta = reinterpret_cast<uint32_t*>(take(32));
+  w.acc_stride = (n_samples + 63u) & ~63u;
+  w.acc32 = reinterpret_cast<int32_t*>(take(static_cast<size_t>(w.acc_stride) * kRowsM * 4));
   w.bytes = off;
   return w;
 }
@@ -584,14 +746,15 @@ void launch_score_tc(const DenseRows& rows, const uint4* counts, const ScoreRow*
                      double* score, double* dosage_sums, uint32_t* allele_cts, cudaStream_t s, LaunchStats* st) {
   if (!rows.nrows || !n_samples) return;
   const TcWorkspace w = carve(workspace, max_rows, n_samples);
-  if (first_batch) cudaMemsetAsync(w.acc32, 0, static_cast<size_t>(n_samples) * kRowsM * 4, s);
-  const uint32_t nk_batch = (2u * rows.nrows + kSlabK - 1) / kSlabK * kSlabK;
-  cudaMemsetAsync(w.a_tiles, 0, static_cast<size_t>(nk_batch) / kSlabK * kABytes, s);
+  if (first_batch) cudaMemsetAsync(w.acc32, 0, static_cast<size_t>(w.acc_stride) * kRowsM * 4, s);
+  const uint32_t slot_cap = static_cast<uint32_t>(slot_cap_of(rows.nrows));
+  const uint32_t nk_batch = 2u * slot_cap;  // upper bound of the batch's k-rows (every variant a pair)
+  cudaMemsetAsync(w.a_tiles, 0, slab_cap_of(rows.nrows) * kABytes, s);
   k_tc_plan<<<K + 3, kPlanThreads, 0, s>>>(counts, srow, weights, rows.nrows, K, mode, w.krow, w.col_scale, w.col_const,
                                        w.meta);
-  const uint64_t qthreads = static_cast<uint64_t>(nk_batch) * (K + 2);
+  const uint64_t qthreads = static_cast<uint64_t>(slot_cap) * (K + 2);
   k_tc_quant<<<static_cast<unsigned>((qthreads + 255) / 256), 256, 0, s>>>(rows, srow, weights, K, mode, w.krow,
-                                                                          w.col_scale, w.meta, nk_batch, w.a_tiles,
+                                                                          w.col_scale, w.meta, slot_cap, w.a_tiles,
                                                                           w.krow_ptr);
   const uint32_t tiles = (n_samples + kTileN - 1) / kTileN;
   const int sms = sm_of(st);
@@ -612,11 +775,9 @@ void launch_score_tc(const DenseRows& rows, const uint4* counts, const ScoreRow*
     if (eff >= 0.9) break;
   }
   k_score_mma<<<dim3(tiles, ksplit), kMmaThreads, sizeof(MmaSmem) + 128, s>>>(w.krow_ptr, rows.N, w.a_tiles, w.meta,
-                                                                            ksplit, w.acc32, n_samples);
-  const uint64_t fthreads = static_cast<uint64_t>(n_samples) * (K + 2);
-  k_tc_finish<<<static_cast<unsigned>((fthreads + 255) / 256), 256, 0, s>>>(w.acc32, w.col_scale, w.col_const, w.meta,
-                                                                           n_samples, K, mode, score, dosage_sums,
-                                                                           allele_cts);
+                                                                            ksplit, w.acc32, n_samples, w.acc_stride);
+  k_tc_finish<<<dim3((n_samples + 255) / 256, K + 2), 256, 0, s>>>(w.acc32, w.acc_stride, w.col_scale, w.col_const, w.meta,
+                                                                  n_samples, K, mode, score, dosage_sums, allele_cts);
   if (st) st->launches += 4;
 }
 
