@@ -220,16 +220,18 @@ k_tc_plan(const uint4* __restrict__ counts, const ScoreRow* __restrict__ srow, c
     uint32_t nact_total = 0;
     const uint32_t lane = t & 31u, wid = t >> 5;
     uint32_t* warp_tot = s_scan;  // [32] per-warp totals of the current chunk
+    // which of this thread's rows (t, t + 1024, ...; at most 64 for a batch of 65 535) go to which list: all
+    // loads are issued before the first barrier
+    unsigned long long want[2] = {0ull, 0ull};
+    for (uint32_t r0 = 0, i = 0; r0 < nrows; r0 += kPlanThreads, ++i) {
+      const uint32_t r = r0 + t;
+      if (r < nrows && (srow[r].flags & kScoreActive)) want[counts[r].w != 0 ? 0 : 1] |= 1ull << i;
+    }
     for (uint32_t pass = 0; pass < 2; ++pass) {
       uint32_t base = 0;  // entries of this pass so far (same value in every thread)
-      for (uint32_t r0 = 0; r0 < nrows; r0 += kPlanThreads) {
+      for (uint32_t r0 = 0, i = 0; r0 < nrows; r0 += kPlanThreads, ++i) {
         const uint32_t r = r0 + t;
-        bool take = false;
-        if (r < nrows) {
-          const bool act = (srow[r].flags & kScoreActive) != 0;
-          const bool mis = counts[r].w != 0;
-          take = act && (pass == 0 ? mis : !mis);
-        }
+        const bool take = (want[pass] >> i) & 1ull;
         const uint32_t bal = __ballot_sync(0xffffffffu, take);
         if (lane == 0) warp_tot[wid] = __popc(bal);
         __syncthreads();
@@ -372,18 +374,19 @@ struct MmaSmem {
 
 // 16 packed 2-bit codes -> 16 bytes through the 4-entry byte table `tab`.  A code sitting in the low
 // bits of a nibble IS a PRMT selector, so the even codes (w & 0x3333..) and the odd codes
-// ((w >> 2) & 0x3333..) are looked up four at a time and the two byte streams interleaved by PRMT.
+// ((w >> 2) & 0x3333..) are looked up four at a time.  The two byte streams are NOT interleaved back: the
+// MMA does not care in which order the 16 samples of a group sit along N, so column j of a group holds sample
+// kGroupPerm(j) = 0,2,4,6, 1,3,5,7, 8,10,12,14, 9,11,13,15 and the epilogue undoes it (half the PRMTs).
 __device__ __forceinline__ uint4 unpack16(uint32_t w, uint32_t tab) {
   const uint32_t ev = w & 0x33333333u, od = (w >> 2) & 0x33333333u;
-  const uint32_t e0 = __byte_perm(tab, 0u, ev), o0 = __byte_perm(tab, 0u, od);              // codes 0,2,4,6 / 1,3,5,7
-  const uint32_t e1 = __byte_perm(tab, 0u, ev >> 16), o1 = __byte_perm(tab, 0u, od >> 16);  // codes 8,10,.. / 9,11,..
   uint4 o;
-  o.x = __byte_perm(e0, o0, 0x5140u);
-  o.y = __byte_perm(e0, o0, 0x7362u);
-  o.z = __byte_perm(e1, o1, 0x5140u);
-  o.w = __byte_perm(e1, o1, 0x7362u);
+  o.x = __byte_perm(tab, 0u, ev);        // samples 0, 2, 4, 6
+  o.y = __byte_perm(tab, 0u, od);        // samples 1, 3, 5, 7
+  o.z = __byte_perm(tab, 0u, ev >> 16);  // samples 8, 10, 12, 14
+  o.w = __byte_perm(tab, 0u, od >> 16);  // samples 9, 11, 13, 15
   return o;
 }
+__device__ __forceinline__ uint32_t group_perm(uint32_t j) { return (j & 8u) | ((j & 3u) << 1) | ((j >> 2) & 1u); }
 
 __device__ __forceinline__ uint4 ldg128_stream(const uint8_t* p) {
   uint4 v;
@@ -543,9 +546,9 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
       tmem_ld16(tmem + ((wq * 32u) << 16) + c0, v);
 #pragma unroll
       for (int u = 0; u < 16; ++u) {
-        const uint32_t s = tile * kTileN + c0 + u;
+        const uint32_t s = tile * kTileN + c0 + group_perm(u);
         if (s < n_samples && v[u] != 0u) {
-          atomicAdd(acc32 + static_cast<uint64_t>(r) * acc_stride + s, static_cast<int32_t>(v[u]));
+          atomicAdd(acc32 + static_cast<uint64_t>(s) * kRowsM + r, static_cast<int32_t>(v[u]));
         }
       }
     }
@@ -664,19 +667,20 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
 // term, accumulates into the fp64 results and clears acc32 for the next batch.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-k_tc_finish(int32_t* __restrict__ acc32, uint32_t acc_stride, const double* __restrict__ col_scale,
-            const double* __restrict__ col_const, const uint32_t* __restrict__ meta, uint32_t n_samples, uint32_t K,
-            uint32_t mode, double* __restrict__ score, double* __restrict__ dosage_sums, uint32_t* __restrict__ allele_cts) {
-  // acc32 is [limb row][sample]: consecutive threads take consecutive samples of one column (blockIdx.y)
-  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
-  const uint32_t c = blockIdx.y;
+k_tc_finish(int32_t* __restrict__ acc32, const double* __restrict__ col_scale, const double* __restrict__ col_const,
+            const uint32_t* __restrict__ meta, uint32_t n_samples, uint32_t K, uint32_t mode, double* __restrict__ score,
+            double* __restrict__ dosage_sums, uint32_t* __restrict__ allele_cts) {
+  const uint32_t ncols = K + 2;
+  const uint64_t tid = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const uint32_t s = static_cast<uint32_t>(tid / ncols);
+  const uint32_t c = static_cast<uint32_t>(tid % ncols);
   if (s >= n_samples) return;
-  int32_t* a = acc32 + static_cast<uint64_t>(c * kLimbs) * acc_stride + s;
+  int32_t* a = acc32 + static_cast<uint64_t>(s) * kRowsM + c * kLimbs;
   long long limb[kLimbs];
 #pragma unroll
   for (uint32_t l = 0; l < kLimbs; ++l) {
-    limb[l] = a[static_cast<uint64_t>(l) * acc_stride];
-    a[static_cast<uint64_t>(l) * acc_stride] = 0;
+    limb[l] = a[l];
+    a[l] = 0;
   }
   if (c == K + 1) {
     const uint32_t n_active = meta[1];
@@ -776,8 +780,10 @@ void launch_score_tc(const DenseRows& rows, const uint4* counts, const ScoreRow*
   }
   k_score_mma<<<dim3(tiles, ksplit), kMmaThreads, sizeof(MmaSmem) + 128, s>>>(w.krow_ptr, rows.N, w.a_tiles, w.meta,
                                                                             ksplit, w.acc32, n_samples, w.acc_stride);
-  k_tc_finish<<<dim3((n_samples + 255) / 256, K + 2), 256, 0, s>>>(w.acc32, w.acc_stride, w.col_scale, w.col_const, w.meta,
-                                                                  n_samples, K, mode, score, dosage_sums, allele_cts);
+  const uint64_t fthreads = static_cast<uint64_t>(n_samples) * (K + 2);
+  k_tc_finish<<<static_cast<unsigned>((fthreads + 255) / 256), 256, 0, s>>>(w.acc32, w.col_scale, w.col_const, w.meta,
+                                                                           n_samples, K, mode, score, dosage_sums,
+                                                                           allele_cts);
   if (st) st->launches += 4;
 }
 

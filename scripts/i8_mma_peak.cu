@@ -11,14 +11,17 @@
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
 
-template <int KIND>  // 0 = i8, 1 = f8f6f4 (e4m3 x e4m3, f32 accumulate), 2 = f16 (bf16 x bf16, f32 accumulate, K = 16)
+template <int KIND>  // 0 = i8, 1 = f8f6f4 (e4m3), 2 = f16 (bf16, K = 16), 3 = i8 with two tcgen05.commit after every MMA
 __global__ void __launch_bounds__(128) k_peak(uint32_t iters, uint32_t* sink) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t bar;
+  __shared__ uint64_t bar2[2];
   __shared__ uint32_t tmem_slot;
   for (uint32_t i = threadIdx.x; i < 12288 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0u;
   if (threadIdx.x == 0) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar2[0])));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar2[1])));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -41,13 +44,17 @@ __global__ void __launch_bounds__(128) k_peak(uint32_t iters, uint32_t* sink) {
     // c format (S32 = 2, F32 = 1) at [4,6); a / b format at [7,10) / [10,13); B MN-major: bit 16; N >> 3 at [17,23);
     // M >> 4 at [24,29)
     const uint32_t shape = (1u << 16) | ((256u >> 3) << 17) | ((128u >> 4) << 24);
-    const uint32_t idesc = KIND == 0 ? ((2u << 4) | (1u << 7) | (1u << 10) | shape)
+    const uint32_t idesc = (KIND == 0 || KIND == 3) ? ((2u << 4) | (1u << 7) | (1u << 10) | shape)
                                      : (KIND == 1 ? ((1u << 4) | shape) : ((1u << 4) | (1u << 7) | (1u << 10) | shape));
     for (uint32_t it = 0; it < iters; ++it) {
-      if (KIND == 0) {
+      if (KIND == 0 || KIND == 3) {
         asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n}\n" ::"r"(tmem),
                      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(it)
                      : "memory");
+        if (KIND == 3) {
+          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar2[0])) : "memory");
+          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar2[1])) : "memory");
+        }
       } else if (KIND == 1) {
         asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n}\n" ::"r"(tmem),
                      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(it)
@@ -106,6 +113,7 @@ int main() {
     printf(", \"i8_K32_%dcta_per_sm_pops\": %.3f", c, run<0>(c, sms, 200000, sink, 32));
     printf(", \"e4m3_K32_%dcta_per_sm_pflops\": %.3f", c, run<1>(c, sms, 200000, sink, 32));
     printf(", \"bf16_K16_%dcta_per_sm_pflops\": %.3f", c, run<2>(c, sms, 200000, sink, 16));
+    printf(", \"i8_K32_two_commits_per_mma_%dcta_per_sm_pops\": %.3f", c, run<3>(c, sms, 200000, sink, 32));
   }
   cudaError_t e = cudaGetLastError();
   printf(", \"cuda\": \"%s\"}\n", cudaGetErrorString(e));
