@@ -161,6 +161,11 @@ void pd_job_free(pd_job* job);
  *      out_p[v - v_begin] = P_HWE clamped to [0,1] (1.0 when no observations).
  *      out_counts may be NULL. ---- */
 int pd_hardy(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t midp, uint32_t* out_counts, double* out_p);
+/* Asynchronous form, as pd_counts_start / pd_counts_fetch: PlinkHardyScan's threads claim 128-variant batches with
+ * fetch_add (src/plink_hardy.cpp:481-510) and fetch exactly their rows; tiles are staged, counted and tested while
+ * earlier rows are being emitted.  out_counts may be NULL.  Free with pd_job_free. */
+int pd_hardy_start(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t midp, pd_job** out);
+int pd_hardy_fetch(pd_job* job, uint32_t v_begin, uint32_t v_end, uint32_t* out_counts, double* out_p);
 /* Exact-test p-values for caller-supplied counts (n x 4, as pd_counts), computed on the device. */
 int pd_hwe_from_counts(pd_ctx* ctx, const uint32_t* counts, uint32_t n, uint32_t midp, double* out_p);
 /* Same test, but out_lnp[i] = ln p: what plink2::HweLnP itself returns (plink2_stats.cc:1784-2166) before
@@ -187,6 +192,14 @@ int pd_sample_counts(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t* ou
  *      src/pfile_reader.cpp:2426-2432).  out is (v_end - v_begin) x effective sample_ct int8,
  *      row-major, values {0,1,2,-9}. ---- */
 int pd_decode_i8(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, int8_t* out);
+/* Asynchronous form for the scan callbacks of read_pgen / read_pfile, whose threads claim batches of variants from
+ * an atomic counter (src/pgen_reader.cpp:635-736, src/pfile_reader.cpp:2790-2835): a job thread decodes the range
+ * chunk by chunk (64 MiB of int8 per chunk, four page-locked chunk buffers) ahead of the fetches; pd_decode_fetch
+ * blocks until rows [v_begin, v_end) are decoded and copies them to out ((v_end - v_begin) x effective sample_ct).
+ * Thread-safe; every row may be fetched once, and fetches must keep up with the claim order (a chunk buffer is
+ * reused when all of its rows were fetched).  The sample subset must not change while the job runs. */
+int pd_decode_start(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, pd_job** out);
+int pd_decode_fetch(pd_job* job, uint32_t v_begin, uint32_t v_end, int8_t* out);
 
 /* ---- genotype column in DuckDB's child-vector layout: replaces PgrGet + GenoarrToBytesMinus9 AND the fill
  *      loop that follows it (src/pgen_reader.cpp:1008-1046: ARRAY(TINYINT, N) / LIST(TINYINT) child data +

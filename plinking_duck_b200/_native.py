@@ -78,12 +78,16 @@ SYMBOLS = {
     "pd_counts_fetch": (C.c_int, [_vp, _u32, _u32, _vp]),
     "pd_job_free": (None, [_vp]),
     "pd_hardy": (C.c_int, [_vp, _u32, _u32, _u32, _vp, _vp]),
+    "pd_hardy_start": (C.c_int, [_vp, _u32, _u32, _u32, C.POINTER(_vp)]),
+    "pd_hardy_fetch": (C.c_int, [_vp, _u32, _u32, _vp, _vp]),
     "pd_hwe_from_counts": (C.c_int, [_vp, _vp, _u32, _u32, _vp]),
     "pd_hwe_lnp_from_counts": (C.c_int, [_vp, _vp, _u32, _u32, _vp]),
     "pd_hwe_xchr_from_counts": (C.c_int, [_vp, _vp, _u32, _u32, _vp]),
     "pd_missing_by_sample": (C.c_int, [_vp, _u32, _u32, _vp]),
     "pd_sample_counts": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),
     "pd_decode_i8": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "pd_decode_start": (C.c_int, [_vp, _u32, _u32, C.POINTER(_vp)]),
+    "pd_decode_fetch": (C.c_int, [_vp, _u32, _u32, _vp]),
     "pd_decode_i8_valid": (C.c_int, [_vp, _u32, _u32, _u32, _vp, _vp]),
     "pd_decode_i8_valid_list": (C.c_int, [_vp, _vp, _u32, _u32, _vp, _vp]),
     "pd_decode_phased": (C.c_int, [_vp, _u32, _u32, _vp]),

@@ -561,7 +561,7 @@ int GroupScore(pd_ctx* c, const uint32_t* vidx, const uint8_t* flip, const doubl
   return rc;
 }
 
-int GroupCountsStart(pd_ctx* c, uint32_t v_begin, uint32_t v_end, pd_job** out) {
+int GroupCountsStart(pd_ctx* c, uint32_t v_begin, uint32_t v_end, bool hardy, uint32_t midp, pd_job** out) {
   std::lock_guard<std::mutex> lock(c->mu);
   if (v_begin > v_end || v_end > c->idx.variant_ct) return c->SetError(PD_ERR_INVALID_ARG, "variant range out of bounds");
   GroupState* g = c->group;
@@ -570,11 +570,13 @@ int GroupCountsStart(pd_ctx* c, uint32_t v_begin, uint32_t v_end, pd_job** out) 
   j->ctx = c;
   j->v_begin = v_begin;
   j->v_end = v_end;
+  j->hardy = hardy;
+  j->midp = midp;
   const std::vector<VRange> r = RangesFor(c, v_begin, v_end, 1);
   for (size_t i = 0; i < g->shards.size(); ++i) {
     if (r[i].v0 >= r[i].v1) continue;
     pd_job* sub = nullptr;
-    const int rc = pd_counts_start(g->shards[i], r[i].v0, r[i].v1, &sub);
+    const int rc = StartScanJob(g->shards[i], r[i].v0, r[i].v1, hardy, midp, &sub);
     if (rc != PD_OK) {
       c->last_error = g->shards[i]->last_error;
       pd_job_free(j);

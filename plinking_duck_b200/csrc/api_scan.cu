@@ -131,17 +131,25 @@ int pd_counts_masked(pd_ctx* c, uint32_t v_begin, uint32_t v_end, const uint64_t
   return rc;
 }
 
-int pd_counts_start(pd_ctx* c, uint32_t v_begin, uint32_t v_end, pd_job** out) {
+}  // extern "C"
+
+// Starts the job thread behind pd_counts_start / pd_hardy_start: the scan runs tile by tile on the context's
+// streams and every finished tile's rows (counts, and exact-test p-values for a hardy job) are published to the
+// job's host arrays, where any number of scan threads fetch their claimed row ranges.
+int pdx::StartScanJob(pd_ctx* c, uint32_t v_begin, uint32_t v_end, bool hardy, uint32_t midp, pd_job** out) {
   if (!c || !out) return PD_ERR_INVALID_ARG;
   *out = nullptr;
-  if (c->group) return GroupCountsStart(c, v_begin, v_end, out);
+  if (c->group) return GroupCountsStart(c, v_begin, v_end, hardy, midp, out);
   if (v_begin > v_end || v_end > c->idx.variant_ct) return c->SetError(PD_ERR_INVALID_ARG, "variant range out of bounds");
   pd_job* j = new (std::nothrow) pd_job();
   if (!j) return PD_ERR_NOMEM;
   j->ctx = c;
   j->v_begin = v_begin;
   j->v_end = v_end;
+  j->hardy = hardy;
+  j->midp = midp;
   j->counts.resize(static_cast<size_t>(v_end - v_begin) * 4);
+  if (hardy) j->pvals.resize(v_end - v_begin);
   j->worker = std::thread([j]() {
     pd_ctx* c = j->ctx;
     std::lock_guard<std::mutex> lock(c->mu);
@@ -155,7 +163,11 @@ int pd_counts_start(pd_ctx* c, uint32_t v_begin, uint32_t v_end, pd_job** out) {
     cudaSetDevice(c->device);
     const uint32_t v0 = (j->v_begin < j->v_end) ? ExtendToBase(c, j->v_begin) : j->v_begin;
     int rc = PD_OK;
-    cudaError_t e = c->d_counts.Reserve(std::max<size_t>(16, static_cast<size_t>(j->v_end - v0) * 16));
+    const size_t nrows_ext = std::max<size_t>(1, j->v_end - v0);
+    cudaError_t e = c->d_counts.Reserve(nrows_ext * 16);
+    if (e == cudaSuccess && j->hardy) e = c->d_pvals.Reserve(nrows_ext * 8);
+    if (e == cudaSuccess && j->hardy) e = c->d_ready.Reserve(nrows_ext * 4);
+    if (e == cudaSuccess && j->hardy) e = c->d_hweq.Reserve((nrows_ext + pdk::kHweQueueWords) * 4);
     if (e != cudaSuccess) rc = CheckCuda(c, e, "counts allocation");
     // Rows are published tile by tile: tile i's rows are copied out while tile i+1 is staged.
     struct Pending { Tile t; cudaEvent_t ev; };
@@ -175,6 +187,11 @@ int pd_counts_start(pd_ctx* c, uint32_t v_begin, uint32_t v_end, pd_job** out) {
         cudaMemcpy(j->counts.data() + static_cast<size_t>(a - j->v_begin) * 4, c->d_counts.as<uint4>() + (a - v0),
                    static_cast<size_t>(b - a) * 16, cudaMemcpyDeviceToHost);
         c->stats.d2h_bytes += static_cast<size_t>(b - a) * 16;
+        if (j->hardy) {
+          cudaMemcpy(j->pvals.data() + (a - j->v_begin), c->d_pvals.as<double>() + (a - v0), static_cast<size_t>(b - a) * 8,
+                     cudaMemcpyDeviceToHost);
+          c->stats.d2h_bytes += static_cast<size_t>(b - a) * 8;
+        }
       }
       {
         std::lock_guard<std::mutex> l2(j->mu);
@@ -186,7 +203,22 @@ int pd_counts_start(pd_ctx* c, uint32_t v_begin, uint32_t v_end, pd_job** out) {
       uint4* out_dev = c->d_counts.as<uint4>();
       rc = RunScan(
           c, j->v_begin, j->v_end, nullptr,
-          [&](const Tile& t, const pdk::RecIndex& ix, cudaStream_t s) { return CountTile(c, c->subset, t, ix, v0, out_dev, s); },
+          [&](const Tile& t, const pdk::RecIndex& ix, cudaStream_t s) {
+            if (!j->hardy) return CountTile(c, c->subset, t, ix, v0, out_dev, s);
+            // plink_hardy: the tile's counts and exact tests (fused K1h for fixed-width records, else K3 + K8)
+            const uint32_t off = t.v0 - v0;
+            double* p_dev = c->d_pvals.as<double>() + off;
+            if (c->idx.fixed && pdk::launch_hardy_fixed(ix, c->subset.Dev(), t.v0, t.v1, out_dev + off, p_dev, j->midp,
+                                                       c->d_hweq.as<uint32_t>(), c->d_ready.as<uint32_t>() + off, s,
+                                                       &c->launch_stats)) {
+              c->stats.scan_launches += 1;
+              return static_cast<int>(PD_OK);
+            }
+            const int r = CountTile(c, c->subset, t, ix, v0, out_dev, s);
+            if (r != PD_OK) return r;
+            pdk::launch_hwe(out_dev + off, t.v1 - t.v0, j->midp, p_dev, c->d_hweq.as<uint32_t>(), s, &c->launch_stats);
+            return static_cast<int>(PD_OK);
+          },
           [&](const Tile& t, cudaEvent_t ev) {
             if (!pending.empty()) {
               // malformed-input detection is only final at the end; rows are provisional until then
@@ -213,15 +245,17 @@ int pd_counts_start(pd_ctx* c, uint32_t v_begin, uint32_t v_end, pd_job** out) {
   return PD_OK;
 }
 
-int pd_counts_fetch(pd_job* j, uint32_t v_begin, uint32_t v_end, uint32_t* out_counts) {
+// Blocks until rows [v_begin, v_end) of the job are final, then copies them out (either output may be NULL).
+static int FetchRows(pd_job* j, uint32_t v_begin, uint32_t v_end, uint32_t* out_counts, double* out_p) {
   if (!j || v_begin > v_end || v_begin < j->v_begin || v_end > j->v_end) return PD_ERR_INVALID_ARG;
   if (v_begin == v_end) return PD_OK;
-  if (!out_counts) return PD_ERR_INVALID_ARG;
+  if (out_p && !j->hardy) return PD_ERR_INVALID_ARG;
   if (!j->subs.empty() || (j->ctx && j->ctx->group)) {
     for (pd_job* sub : j->subs) {
       const uint32_t a = std::max(v_begin, sub->v_begin), b = std::min(v_end, sub->v_end);
       if (a >= b) continue;
-      const int rc = pd_counts_fetch(sub, a, b, out_counts + 4ull * (a - v_begin));
+      const int rc = FetchRows(sub, a, b, out_counts ? out_counts + 4ull * (a - v_begin) : nullptr,
+                               out_p ? out_p + (a - v_begin) : nullptr);
       if (rc != PD_OK) {
         j->ctx->last_error = sub->ctx->last_error;
         return rc;
@@ -234,13 +268,37 @@ int pd_counts_fetch(pd_job* j, uint32_t v_begin, uint32_t v_end, uint32_t* out_c
   j->cv.wait(lock, [&]() { return j->finished || j->rows_ready >= need; });
   if (j->status != PD_OK) return j->status;
   if (j->rows_ready < need) return PD_ERR_READ;
-  memcpy(out_counts, j->counts.data() + static_cast<size_t>(v_begin - j->v_begin) * 4,
-         static_cast<size_t>(v_end - v_begin) * 16);
+  if (out_counts) {
+    memcpy(out_counts, j->counts.data() + static_cast<size_t>(v_begin - j->v_begin) * 4,
+           static_cast<size_t>(v_end - v_begin) * 16);
+  }
+  if (out_p) memcpy(out_p, j->pvals.data() + (v_begin - j->v_begin), static_cast<size_t>(v_end - v_begin) * 8);
   return PD_OK;
+}
+
+extern "C" {
+
+int pd_counts_start(pd_ctx* c, uint32_t v_begin, uint32_t v_end, pd_job** out) {
+  return StartScanJob(c, v_begin, v_end, false, 0, out);
+}
+
+int pd_counts_fetch(pd_job* j, uint32_t v_begin, uint32_t v_end, uint32_t* out_counts) {
+  if (!out_counts && v_end > v_begin) return PD_ERR_INVALID_ARG;
+  return FetchRows(j, v_begin, v_end, out_counts, nullptr);
+}
+
+int pd_hardy_start(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t midp, pd_job** out) {
+  return StartScanJob(c, v_begin, v_end, true, midp, out);
+}
+
+int pd_hardy_fetch(pd_job* j, uint32_t v_begin, uint32_t v_end, uint32_t* out_counts, double* out_p) {
+  if (!out_p && v_end > v_begin) return PD_ERR_INVALID_ARG;
+  return FetchRows(j, v_begin, v_end, out_counts, out_p);
 }
 
 void pd_job_free(pd_job* j) {
   if (!j) return;
+  if (j->decode) FreeDecodeJob(j);
   for (pd_job* sub : j->subs) pd_job_free(sub);
   if (j->worker.joinable()) j->worker.join();
   delete j;

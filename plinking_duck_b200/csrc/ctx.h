@@ -20,6 +20,8 @@ struct pd_job;
 namespace pdx {
 
 struct GroupState;  // group.h
+struct DecodeJob;   // api_async.cu
+void FreeDecodeJob(pd_job* j);
 
 constexpr uint32_t kSlack = 64;  // readable bytes before/after every record buffer (aligned 16 B loads)
 
@@ -167,6 +169,7 @@ int RunRows(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t max_rows,
 int RunRowsList(pd_ctx_impl* c, const uint32_t* vlist, uint32_t n, uint32_t max_rows, const RowFn& fn);
 uint32_t DenseSlotStride(const pd_ctx_impl* c);
 int DownloadRows(pd_ctx_impl* c, const void* dev, size_t bytes, void* host);
+int StartScanJob(pd_ctx* c, uint32_t v_begin, uint32_t v_end, bool hardy, uint32_t midp, pd_job** out);
 
 }  // namespace pdx
 
@@ -177,6 +180,9 @@ struct pd_job {
   pd_ctx* ctx = nullptr;
   uint32_t v_begin = 0, v_end = 0;
   std::vector<uint32_t> counts;  // 4 x rows
+  std::vector<double> pvals;     // rows (hardy jobs)
+  bool hardy = false;            // also runs the exact test per tile
+  uint32_t midp = 0;
   std::mutex mu;
   std::condition_variable cv;
   uint32_t rows_ready = 0;       // rows [0, rows_ready) of counts are final
@@ -185,4 +191,5 @@ struct pd_job {
   bool started = false;          // the worker holds the context
   std::thread worker;
   std::vector<pd_job*> subs;     // multi-GPU context: one job per shard with a non-empty range
+  pdx::DecodeJob* decode = nullptr;  // pd_decode_start jobs
 };

@@ -86,6 +86,6 @@ int GroupMissingBySample(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* 
 int GroupSampleCounts(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint32_t* het, uint32_t* hom_alt, uint32_t* missing);
 int GroupScore(pd_ctx* c, const uint32_t* vidx, const uint8_t* flip, const double* weights, uint32_t n_var, uint32_t K,
                uint32_t mode, double* score_sums, double* dosage_sums, uint32_t* allele_cts);
-int GroupCountsStart(pd_ctx* c, uint32_t v_begin, uint32_t v_end, pd_job** out);
+int GroupCountsStart(pd_ctx* c, uint32_t v_begin, uint32_t v_end, bool hardy, uint32_t midp, pd_job** out);
 
 }  // namespace pdx

@@ -186,6 +186,10 @@ class PgenContext:
         v0, v1 = self._range(v0, v1)
         return CountsJob(self, v0, v1)
 
+    def hardy_async(self, v0=0, v1=None, midp=False) -> "HardyJob":
+        v0, v1 = self._range(v0, v1)
+        return HardyJob(self, v0, v1, midp)
+
     def hardy(self, v0=0, v1=None, midp=False, out_counts=None, out_p=None):
         """out_counts / out_p: optional preallocated (e.g. page-locked) result arrays."""
         v0, v1 = self._range(v0, v1)
@@ -237,6 +241,10 @@ class PgenContext:
         out = np.zeros((max(v1 - v0, 0), self.sample_ct), dtype=np.int8)
         self._check(self._lib.pd_decode_i8(self._h, v0, v1, _p(out)))
         return out
+
+    def decode_async(self, v0=0, v1=None) -> "DecodeJob":
+        v0, v1 = self._range(v0, v1)
+        return DecodeJob(self, v0, v1)
 
     def decode_i8_valid(self, v0=0, v1=None, call_mask=7):
         """Genotype column in DuckDB's child-vector layout: (int8 calls with 0 where invalid, uint64 validity
@@ -312,3 +320,39 @@ class CountsJob:
             self.close()
         except Exception:
             pass
+
+
+class HardyJob(CountsJob):
+    """pd_hardy_start / pd_hardy_fetch: counts + exact-test p-values, fetched in claimed row ranges."""
+
+    def __init__(self, ctx: PgenContext, v0: int, v1: int, midp: bool = False):
+        self._ctx = ctx
+        self._j = C.c_void_p()
+        self.v0, self.v1 = v0, v1
+        ctx._check(ctx._lib.pd_hardy_start(ctx._h, v0, v1, int(bool(midp)), C.byref(self._j)))
+
+    def fetch(self, a: int, b: int):
+        counts = np.zeros((max(b - a, 0), 4), dtype=np.uint32)
+        p = np.zeros(max(b - a, 0), dtype=np.float64)
+        rc = self._ctx._lib.pd_hardy_fetch(self._j, a, b, _p(counts), _p(p))
+        if rc:
+            raise nat.PlinkGpuError(rc, self._ctx._lib.pd_last_error(self._ctx._h).decode(errors="replace"))
+        return counts, p
+
+
+class DecodeJob(CountsJob):
+    """pd_decode_start / pd_decode_fetch: int8 genotype rows decoded ahead of the scan threads that fetch them."""
+
+    def __init__(self, ctx: PgenContext, v0: int, v1: int):
+        self._ctx = ctx
+        self._j = C.c_void_p()
+        self.v0, self.v1 = v0, v1
+        self.n_out = ctx.sample_ct
+        ctx._check(ctx._lib.pd_decode_start(ctx._h, v0, v1, C.byref(self._j)))
+
+    def fetch(self, a: int, b: int) -> np.ndarray:
+        out = np.zeros((max(b - a, 0), self.n_out), dtype=np.int8)
+        rc = self._ctx._lib.pd_decode_fetch(self._j, a, b, _p(out))
+        if rc:
+            raise nat.PlinkGpuError(rc, self._ctx._lib.pd_last_error(self._ctx._h).decode(errors="replace"))
+        return out
