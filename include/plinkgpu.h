@@ -54,7 +54,9 @@ typedef struct pd_open_opts {
                              * loaded at run time (libnccl.so.2) when n_devices > 1. */
   const int32_t* devices;   /* distinct CUDA device ordinals; read during pd_open* only        */
   uint32_t flags;           /* PD_OPEN_* bits                                                   */
-  uint32_t reserved;
+  uint32_t raw_variant_ct;  /* PLINK 1 .bed (mode 0x01) only: the file stores neither count, the caller   */
+  uint32_t raw_sample_ct;   /* supplies them from .bim / .fam as it does to PgfiInitPhase1                 */
+  uint32_t reserved;        /* (src/pfile_reader.cpp:1319); 0 elsewhere                                    */
 } pd_open_opts;
 
 /* pd_open only: map the .pgen writable-shared and page-lock the mapping in place (cudaHostRegister), so that

@@ -32,6 +32,8 @@ def lib():
         vp, u32, u64, i32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int32
         L.ref_open.argtypes = [C.c_char_p, C.POINTER(vp), C.c_char_p, C.c_size_t]
         L.ref_open.restype = C.c_int
+        L.ref_open_counts.argtypes = [C.c_char_p, u32, u32, C.POINTER(vp), C.c_char_p, C.c_size_t]
+        L.ref_open_counts.restype = C.c_int
         L.ref_close.argtypes = [vp]
         L.ref_info.argtypes = [vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]
         L.ref_vrtype.argtypes = [vp, u32]
@@ -72,10 +74,14 @@ def _p(a):
 class RefPgen:
     """One pgenlib reader (PgenFileInfo + PgenReader), as each DuckDB scan thread owns."""
 
-    def __init__(self, path: str):
+    def __init__(self, path: str, raw_counts=None):
+        """raw_counts = (V, N) for PLINK 1 .bed files, which store neither."""
         self._h = C.c_void_p()
         err = C.create_string_buffer(512)
-        rc = lib().ref_open(os.fsencode(path), C.byref(self._h), err, 512)
+        if raw_counts is None:
+            rc = lib().ref_open(os.fsencode(path), C.byref(self._h), err, 512)
+        else:
+            rc = lib().ref_open_counts(os.fsencode(path), int(raw_counts[0]), int(raw_counts[1]), C.byref(self._h), err, 512)
         if rc:
             raise IOError(f"ref_open({path}) failed rc={rc}: {err.value.decode(errors='replace')}")
         self._refresh()

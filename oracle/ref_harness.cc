@@ -63,13 +63,13 @@ struct Reader {
   bool open = false;
 };
 
-int OpenReader(const char* path, Reader* r, char* err, size_t errlen) {
+int OpenReader(const char* path, Reader* r, char* err, size_t errlen, uint32_t raw_v = UINT32_MAX, uint32_t raw_n = UINT32_MAX) {
   PreinitPgfi(&r->pgfi);
   PreinitPgr(&r->pgr);
   char errstr[kPglErrstrBufBlen];
   PgenHeaderCtrl hc;
   uintptr_t c1 = 0;
-  PglErr e = PgfiInitPhase1(path, nullptr, UINT32_MAX, UINT32_MAX, &hc, &r->pgfi, &c1, errstr);
+  PglErr e = PgfiInitPhase1(path, nullptr, raw_v, raw_n, &hc, &r->pgfi, &c1, errstr);
   if (e != kPglRetSuccess) {
     if (err) snprintf(err, errlen, "phase1: %s", errstr);
     PglErr ce = kPglRetSuccess;
@@ -179,6 +179,20 @@ extern "C" {
 int ref_open(const char* path, void** out, char* err, size_t errlen) {
   Reader* r = new Reader();
   int rc = OpenReader(path, r, err, errlen);
+  if (rc) {
+    delete r;
+    *out = nullptr;
+    return rc;
+  }
+  *out = r;
+  return 0;
+}
+
+// Same with the variant / sample counts supplied by the caller (from .bim / .fam): PLINK 1 .bed files carry neither
+// (PgfiInitPhase1's raw_variant_ct / raw_sample_ct arguments, as src/pfile_reader.cpp:1319 passes them).
+int ref_open_counts(const char* path, uint32_t raw_v, uint32_t raw_n, void** out, char* err, size_t errlen) {
+  Reader* r = new Reader();
+  int rc = OpenReader(path, r, err, errlen, raw_v, raw_n);
   if (rc) {
     delete r;
     *out = nullptr;

@@ -23,19 +23,21 @@ ERR_NAMES = {
 
 class OpenOpts(C.Structure):
     _fields_ = [("device", C.c_int32), ("tile_bytes", C.c_uint64), ("n_staging", C.c_uint32), ("n_devices", C.c_uint32),
-                ("devices", C.POINTER(C.c_int32)), ("flags", C.c_uint32), ("reserved", C.c_uint32)]
+                ("devices", C.POINTER(C.c_int32)), ("flags", C.c_uint32), ("raw_variant_ct", C.c_uint32),
+                ("raw_sample_ct", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 PD_OPEN_PIN_FILE = 1
 
 
-def open_opts(device: int = -1, tile_bytes: int = 0, n_staging: int = 0, devices=None, flags: int = 0):
+def open_opts(device: int = -1, tile_bytes: int = 0, n_staging: int = 0, devices=None, flags: int = 0, raw_counts=(0, 0)):
     """pd_open_opts; `devices` (a list of CUDA ordinals) asks for ONE context over several GPUs.  Returns
     (opts, keepalive) -- the device array must outlive the pd_open call."""
     if devices is None:
-        return OpenOpts(device, tile_bytes, n_staging, 0, None, flags, 0), None
+        return OpenOpts(device, tile_bytes, n_staging, 0, None, flags, int(raw_counts[0]), int(raw_counts[1]), 0), None
     arr = (C.c_int32 * len(devices))(*[int(d) for d in devices])
-    return OpenOpts(-1, tile_bytes, n_staging, len(devices), C.cast(arr, C.POINTER(C.c_int32)), flags, 0), arr
+    return OpenOpts(-1, tile_bytes, n_staging, len(devices), C.cast(arr, C.POINTER(C.c_int32)), flags, int(raw_counts[0]),
+                    int(raw_counts[1]), 0), arr
 
 
 class Info(C.Structure):

@@ -146,7 +146,8 @@ int InitDevice(pd_ctx* c, const pd_open_opts* opts) {
 int FinishOpen(pd_ctx* c, const pd_open_opts* opts, pd_ctx** out, char* errbuf, size_t errbuf_len,
                const char* path = nullptr) {
   std::string err;
-  int rc = ParsePgenIndex(c->pgen, c->have_pgi ? &c->pgi : nullptr, &c->idx, &err);
+  int rc = ParsePgenIndex(c->pgen, c->have_pgi ? &c->pgi : nullptr, &c->idx, &err, opts ? opts->raw_variant_ct : 0,
+                          opts ? opts->raw_sample_ct : 0);
   if (rc != PD_OK) {
     CopyErr(errbuf, errbuf_len, err);
     delete c;
@@ -269,6 +270,12 @@ int pd_open_mem(const void* pgen_bytes, uint64_t len, const void* pgi_bytes, uin
     return PD_ERR_INVALID_ARG;
   }
   int rc = FinishOpen(c, opts, out, errbuf, errbuf_len);
+  if (rc == PD_OK && c->dev_image && c->idx.bed) {
+    CopyErr(errbuf, errbuf_len, "a PLINK 1 .bed image in device memory is not supported (its codes are rewritten while staging)");
+    DestroyCtx(c);
+    *out = nullptr;
+    return PD_ERR_NOT_SUPPORTED;
+  }
   if (rc == PD_OK && c->dev_image) {
     if (c->device != attr.device) {
       CopyErr(errbuf, errbuf_len, "device image lives on a different device than the context");
@@ -491,6 +498,7 @@ int pd_load_resident(pd_ctx* c, uint32_t v_begin, uint32_t v_end) {
       ++i;
     }
   }
+  if (ix.bed) pdk::launch_bed_to_pgen(dst, 0, ix.fixed_width, ix.sample_ct, v_end - v0, c->stream, &c->launch_stats);
   e = cudaStreamSynchronize(c->stream);
   if (e != cudaSuccess) return CheckCuda(c, e, "resident copy");
   c->stats.h2d_bytes += len;

@@ -391,6 +391,10 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
       cudaStreamWaitEvent(c->stream, c->ev_copied[b], 0);
       ix.data = c->d_stage[b].as<uint8_t>() + kSlack;
       ix.data_fpos = t.f0;
+      if (ixh.bed) {  // PLINK 1 codes -> .pgen codes before any kernel reads the tile
+        pdk::launch_bed_to_pgen(c->d_stage[b].as<uint8_t>() + kSlack, 0, ixh.fixed_width, ixh.sample_ct, t.v1 - t.v0,
+                                c->stream, &c->launch_stats);
+      }
       cudaEvent_t k0 = PoolEvent(c, 2 * i), k1 = PoolEvent(c, 2 * i + 1);
       cudaEventRecord(k0, c->stream);
       rc = fn(t, ix, c->stream);

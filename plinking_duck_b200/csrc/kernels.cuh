@@ -59,6 +59,13 @@ void launch_cum_popcount(const uint32_t* include_words, uint32_t nwords, uint32_
 void launch_count_fixed(const RecIndex& ix, const SubsetDev& sub, uint32_t v_begin, uint32_t v_end, uint4* out,
                         cudaStream_t s, LaunchStats* st);
 
+// ---- PLINK 1 .bed records (mode 0x01) -> .pgen 2-bit codes, in place in a staged tile / the resident copy:
+// bed 3 / 2 / 0 / 1 = hom-ref / het / hom-alt / missing becomes 0 / 1 / 2 / 3 (what pgenlib does per record in
+// PgrPlink1ToPlink2InplaceUnsafe, and to the counts at pgenlib_read.cc:3709-3719); the pad codes of a record's
+// last byte are cleared.  data + first_off = first byte of record 0 of the range.
+void launch_bed_to_pgen(uint8_t* data, uint64_t first_off, uint32_t width, uint32_t N, uint32_t nrec, cudaStream_t s,
+                        LaunchStats* st);
+
 // ---- K1h: plink_hardy over fixed-width records, counts and exact test in one kernel ----
 // Returns false (nothing launched) when the records are too short for the fused form; the caller
 // then runs launch_count_fixed + launch_hwe.  queue: as launch_hwe (kHweQueueWords + nrec words); ready: device uint32[nrec].

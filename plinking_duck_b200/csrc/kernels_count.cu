@@ -398,6 +398,31 @@ void launch_fixed_t(const RecIndex& ix, const SubsetDev& sub, uint32_t v_begin, 
 
 }  // namespace
 
+namespace {
+__global__ void __launch_bounds__(256) k_bed_to_pgen(uint8_t* __restrict__ data, uint32_t width, uint32_t N, uint64_t total) {
+  const uint32_t tail = N & 3u;
+  for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
+    const uint32_t b = data[i];
+    // per 2-bit code (h, l): h' = ~h, l' = l ^ h
+    uint32_t o = ((~b) & 0xAAu) | ((b ^ (b >> 1)) & 0x55u);
+    if (tail && (i % width) == width - 1) o &= (1u << (2 * tail)) - 1u;
+    data[i] = static_cast<uint8_t>(o);
+  }
+}
+}  // namespace
+
+void launch_bed_to_pgen(uint8_t* data, uint64_t first_off, uint32_t width, uint32_t N, uint32_t nrec, cudaStream_t s,
+                        LaunchStats* st) {
+  if (!nrec) return;
+  const uint64_t total = static_cast<uint64_t>(nrec) * width;
+  uint64_t blocks = (total + 255) / 256;
+  const uint64_t max_blocks = static_cast<uint64_t>(sm_of(st)) * 16;
+  if (blocks > max_blocks) blocks = max_blocks;
+  k_bed_to_pgen<<<static_cast<unsigned>(blocks), 256, 0, s>>>(data + first_off, width, N, total);
+  if (st) st->launches++;
+}
+
 // Enough record bytes per variant that counting, not the exact test, is the long pole.
 bool hardy_fused_applicable(uint32_t N) { return pick_lanes(N) == 32; }
 

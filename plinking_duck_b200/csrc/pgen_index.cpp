@@ -137,7 +137,8 @@ int Fail(std::string* err, int code, const std::string& msg) {
 
 }  // namespace
 
-int ParsePgenIndex(const ByteSource& pgen, const ByteSource* pgi, PgenIndex* out, std::string* err) {
+int ParsePgenIndex(const ByteSource& pgen, const ByteSource* pgi, PgenIndex* out, std::string* err,
+                   uint32_t raw_variant_ct, uint32_t raw_sample_ct) {
   PgenIndex& ix = *out;
   if (pgen.size() < 3) return Fail(err, PD_ERR_MALFORMED, "file is too small to be a valid .pgen file");
   uint8_t magic[3];
@@ -148,9 +149,29 @@ int ParsePgenIndex(const ByteSource& pgen, const ByteSource* pgi, PgenIndex* out
   ix.mode = magic[2];
   if (ix.mode == 0x00) return Fail(err, PD_ERR_NOT_SUPPORTED, "sample-major PLINK 1 .bed files are not supported");
   if (ix.mode == 0x01) {
-    // Needs an externally supplied sample count (pgen_spec.tex:136-138); the extension's PLINK 1
-    // path goes through a .fam that the C ABI does not see yet.
-    return Fail(err, PD_ERR_NOT_SUPPORTED, "PLINK 1 variant-major .bed (mode 0x01) is not supported yet");
+    // PLINK 1 variant-major .bed: three header bytes, then V records of ceil(N/4) bytes; V and N come from the
+    // caller (pgen_spec.tex:136-138; pgenlib_read.cc:744-790: both counts are required and the size must match).
+    if (!raw_variant_ct || !raw_sample_ct) {
+      return Fail(err, PD_ERR_INVALID_ARG, "PLINK 1 .bed file: pd_open_opts.raw_variant_ct / raw_sample_ct must be given");
+    }
+    if (raw_variant_ct > kMaxVariantCt || raw_sample_ct > kMaxSampleCt) return Fail(err, PD_ERR_MALFORMED, "invalid counts for a .bed file");
+    const uint64_t width = (static_cast<uint64_t>(raw_sample_ct) + 3) / 4;
+    if (3 + width * raw_variant_ct != pgen.size()) {
+      char buf[128];
+      snprintf(buf, sizeof(buf), "unexpected PLINK 1 .bed file size (expected %llu bytes)",
+               static_cast<unsigned long long>(3 + width * raw_variant_ct));
+      return Fail(err, PD_ERR_MALFORMED, buf);
+    }
+    ix.variant_ct = raw_variant_ct;
+    ix.sample_ct = raw_sample_ct;
+    ix.fixed = true;
+    ix.bed = true;
+    ix.fixed_width = static_cast<uint32_t>(width);
+    ix.max_width = ix.fixed_width;
+    ix.const_vrtype = 0;
+    ix.data_start = 3;
+    ix.data_bytes = width * raw_variant_ct;
+    return PD_OK;
   }
   if ((ix.mode & 0xfe) == 0x30) return Fail(err, PD_ERR_MALFORMED, "this is a .pgen.pgi index file, not a .pgen file");
 

@@ -57,7 +57,9 @@ struct PgenIndex {
   uint32_t sample_ct = 0;
   uint32_t mode = 0;
   uint32_t header_ctrl = 0;
-  bool fixed = false;          // storage modes 0x02-0x04
+  bool fixed = false;          // storage modes 0x01-0x04
+  bool bed = false;            // mode 0x01: PLINK 1 codes on disk (3 hom-ref, 2 het, 0 hom-alt, 1 missing); staged bytes
+                               // are rewritten to .pgen codes on the device before any kernel sees them
   uint32_t fixed_width = 0;    // bytes per record when fixed
   uint32_t const_vrtype = 0;   // vrtype of every record when fixed
   uint64_t data_start = 0;     // file offset of record 0
@@ -77,6 +79,8 @@ struct PgenIndex {
 };
 
 // Error codes match include/plinkgpu.h PD_ERR_*.
-int ParsePgenIndex(const ByteSource& pgen, const ByteSource* pgi, PgenIndex* out, std::string* err);
+// raw_variant_ct / raw_sample_ct: required for PLINK 1 .bed files (mode 0x01), ignored otherwise.
+int ParsePgenIndex(const ByteSource& pgen, const ByteSource* pgi, PgenIndex* out, std::string* err,
+                   uint32_t raw_variant_ct = 0, uint32_t raw_sample_ct = 0);
 
 }  // namespace pdx

@@ -57,13 +57,15 @@ class PgenContext:
     """Owns a pd_ctx.  All heavy lifting happens in libplinkgpu.so on the GPU."""
 
     def __init__(self, path: Optional[str] = None, *, image: Optional[np.ndarray] = None, pgi: Optional[np.ndarray] = None,
-                 device: int = -1, tile_bytes: int = 0, n_staging: int = 0, devices=None, pin_file: bool = False):
+                 device: int = -1, tile_bytes: int = 0, n_staging: int = 0, devices=None, pin_file: bool = False,
+                 raw_counts=(0, 0)):
         """devices: list of CUDA ordinals for ONE context over several GPUs of this box (pd_open_opts.n_devices):
         variant ranges of equal record bytes per GPU, per-sample sums all-reduced with NCCL inside the library.
+        raw_counts: (variant_ct, sample_ct) for a PLINK 1 .bed file (mode 0x01), which stores neither.
         pin_file: PD_OPEN_PIN_FILE -- page-lock the file's mapping at open so scans DMA straight from the page cache."""
         self._lib = nat.load()
         self._h = C.c_void_p()
-        opts, dev_keep = nat.open_opts(device, tile_bytes, n_staging, devices, nat.PD_OPEN_PIN_FILE if pin_file else 0)
+        opts, dev_keep = nat.open_opts(device, tile_bytes, n_staging, devices, nat.PD_OPEN_PIN_FILE if pin_file else 0, raw_counts)
         self._keep = (image, pgi, dev_keep)
         err = C.create_string_buffer(512)
         if image is not None:

@@ -320,3 +320,18 @@ def genotypes_from_counts(counts: np.ndarray, seed: int) -> np.ndarray:
         rng.shuffle(row)
         g[v] = row
     return g
+
+
+def write_bed(path: str, g: np.ndarray):
+    """PLINK 1 variant-major .bed (mode 0x01): magic 6c 1b 01, then ceil(N/4) bytes per variant with the PLINK 1
+    codes 3 hom-ref, 2 het, 0 hom-alt, 1 missing (pgen_spec.tex:428-432); pad codes are 0."""
+    to_bed = np.array([3, 2, 0, 1], dtype=np.uint8)
+    V, N = g.shape
+    nb = (N + 3) // 4
+    pad = np.zeros((V, nb * 4), dtype=np.uint8)
+    pad[:, :N] = to_bed[g.astype(np.uint8) & 3]
+    q = pad.reshape(V, nb, 4)
+    body = (q[:, :, 0] | (q[:, :, 1] << 2) | (q[:, :, 2] << 4) | (q[:, :, 3] << 6)).astype(np.uint8)
+    with open(path, "wb") as f:
+        f.write(bytes([0x6C, 0x1B, 0x01]))
+        f.write(body.tobytes())
