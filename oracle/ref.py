@@ -62,6 +62,9 @@ def lib():
         L.ref_writer_append_dosage.argtypes = [vp, vp, vp, vp, u32]
         L.ref_writer_append_phased.argtypes = [vp, vp, vp, vp]
         L.ref_decode_phased.argtypes = [vp, u32, u32, vp]
+        L.ref_writer_open_ex.argtypes = [C.c_char_p, u32, u32, u32, vp, C.POINTER(vp)]
+        L.ref_writer_append_multiallelic.argtypes = [vp, vp, vp, vp, u32, vp, vp, u32, u32]
+        L.ref_writer_append_dphase.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, u32, u32]
         L.ref_writer_close.argtypes = [vp]
         _lib = L
     return _lib
@@ -299,3 +302,48 @@ def write_pgen(path: str, genovecs: np.ndarray, N: int, dosage=None, phase=None)
     rc = lib().ref_writer_close(h)
     if rc:
         raise IOError(f"SpgwFinish rc={rc}")
+
+
+class RefWriter:
+    """pgenlib's own writer, record by record (fixtures with multiallelic / dosage-phase tracks).
+    flags: 1 dosage, 2 hardcall phase, 4 dosage phase; allele_cts: per-variant allele counts or None."""
+
+    def __init__(self, path: str, V: int, N: int, flags: int = 0, allele_cts=None):
+        self._h = C.c_void_p()
+        self.N = N
+        ac = None if allele_cts is None else np.ascontiguousarray(allele_cts, dtype=np.uint32)
+        rc = lib().ref_writer_open_ex(os.fsencode(path), V, N, flags, _p(ac), C.byref(self._h))
+        if rc:
+            raise IOError(f"SpgwInitPhase1 rc={rc}")
+
+    def _bits(self, a):
+        return np.ascontiguousarray(a, dtype=np.uint64)
+
+    def append(self, genovec):
+        rc = lib().ref_writer_append(self._h, _p(np.ascontiguousarray(genovec, dtype=np.uint64)))
+        if rc:
+            raise IOError(f"SpgwAppendBiallelicGenovec rc={rc}")
+
+    def append_multiallelic(self, genovec, set01, vals01, set10, vals10, allele_ct):
+        v01 = np.ascontiguousarray(vals01, dtype=np.uint8)
+        v10 = np.ascontiguousarray(vals10, dtype=np.uint8).reshape(-1)
+        rc = lib().ref_writer_append_multiallelic(self._h, _p(np.ascontiguousarray(genovec, dtype=np.uint64)), _p(self._bits(set01)),
+                                                  _p(v01), v01.size, _p(self._bits(set10)), _p(v10), v10.size // 2, int(allele_ct))
+        if rc:
+            raise IOError(f"SpgwAppendMultiallelicSparse rc={rc}")
+
+    def append_dphase(self, genovec, phasepresent, phaseinfo, dosage_present, dphase_present, dosage_main, dphase_delta):
+        dm = np.ascontiguousarray(dosage_main, dtype=np.uint16)
+        dd = np.ascontiguousarray(dphase_delta, dtype=np.int16)
+        rc = lib().ref_writer_append_dphase(self._h, _p(np.ascontiguousarray(genovec, dtype=np.uint64)), _p(self._bits(phasepresent)),
+                                            _p(self._bits(phaseinfo)), _p(self._bits(dosage_present)), _p(self._bits(dphase_present)),
+                                            _p(dm), _p(dd), dm.size, dd.size)
+        if rc:
+            raise IOError(f"SpgwAppendBiallelicGenovecDphase16 rc={rc}")
+
+    def close(self):
+        if self._h:
+            rc = lib().ref_writer_close(self._h)
+            self._h = C.c_void_p()
+            if rc:
+                raise IOError(f"SpgwFinish rc={rc}")

@@ -170,6 +170,7 @@ struct Writer {
   uintptr_t* genovec = nullptr;
   uintptr_t* dosage_present = nullptr;
   uint16_t* dosage_main = nullptr;
+  std::vector<uintptr_t> allele_idx_offsets;  // multiallelic files: cumulative allele counts, V + 1 entries
 };
 
 }  // namespace
@@ -668,6 +669,87 @@ int ref_writer_append_phased(void* h, const uint64_t* genovec, const uint64_t* p
   memcpy(pp.data(), phasepresent, BitCtToWordCt(w->N) * sizeof(uintptr_t));
   memcpy(pi.data(), phaseinfo, BitCtToWordCt(w->N) * sizeof(uintptr_t));
   return static_cast<int>(SpgwAppendBiallelicGenovecHphase(w->genovec, pp.data(), pi.data(), &w->spgw));
+}
+
+// Writer for files with multiallelic variants and / or dosage-phase tracks.  flags: 1 dosage, 2 hardcall phase,
+// 4 dosage phase.  allele_cts: V allele counts (>= 2), or NULL for an all-biallelic file.
+int ref_writer_open_ex(const char* path, uint32_t V, uint32_t N, uint32_t flags, const uint32_t* allele_cts, void** out) {
+  Writer* w = new Writer();
+  PreinitSpgw(&w->spgw);
+  uint32_t max_allele_ct = 2;
+  if (allele_cts) {
+    w->allele_idx_offsets.resize(static_cast<size_t>(V) + 1);
+    uintptr_t cum = 0;
+    for (uint32_t v = 0; v < V; ++v) {
+      w->allele_idx_offsets[v] = cum;
+      cum += allele_cts[v];
+      if (allele_cts[v] > max_allele_ct) max_allele_ct = allele_cts[v];
+    }
+    w->allele_idx_offsets[V] = cum;
+  }
+  uintptr_t alloc_ct = 0;
+  uint32_t max_vrec_len = 0;
+  PgenGlobalFlags gf = kfPgenGlobal0;
+  if (flags & 1) gf |= kfPgenGlobalDosagePresent;
+  if (flags & 2) gf |= kfPgenGlobalHardcallPhasePresent;
+  if (flags & 4) gf |= kfPgenGlobalDosagePresent | kfPgenGlobalDosagePhasePresent | kfPgenGlobalHardcallPhasePresent;
+  PglErr e = SpgwInitPhase1(path, allele_cts ? w->allele_idx_offsets.data() : nullptr, nullptr, V, N, max_allele_ct,
+                            kPgenWriteBackwardSeek, gf, 2, &w->spgw, &alloc_ct, &max_vrec_len);
+  if (e != kPglRetSuccess) {
+    delete w;
+    return static_cast<int>(e);
+  }
+  if (cachealigned_malloc(alloc_ct * kCacheline, &w->alloc)) {
+    delete w;
+    return static_cast<int>(kPglRetNomem);
+  }
+  SpgwInitPhase2(max_vrec_len, &w->spgw, w->alloc);
+  w->N = N;
+  cachealigned_malloc(RoundUpPow2(NypCtToAlignedWordCt(N) * sizeof(uintptr_t) + 64, kCacheline), &w->genovec);
+  cachealigned_malloc(RoundUpPow2(BitCtToAlignedWordCt(N) * sizeof(uintptr_t) + 64, kCacheline), &w->dosage_present);
+  cachealigned_malloc(RoundUpPow2((static_cast<uintptr_t>(N) + 64) * sizeof(uint16_t), kCacheline), &w->dosage_main);
+  *out = w;
+  return 0;
+}
+
+// Multiallelic hardcalls (SpgwAppendMultiallelicSparse): the main track holds 0 = REF/REF, 1 = REF/ALTx,
+// 2 = ALTx/ALTy, 3 = missing; patch_01 names the code-1 samples whose ALT allele is not ALT1 (one allele code
+// each), patch_10 the code-2 samples that are not ALT1/ALT1 (two allele codes each, low <= high).
+int ref_writer_append_multiallelic(void* h, const uint64_t* genovec, const uint64_t* patch_01_set,
+                                   const uint8_t* patch_01_vals, uint32_t patch_01_ct, const uint64_t* patch_10_set,
+                                   const uint8_t* patch_10_vals, uint32_t patch_10_ct, uint32_t allele_ct) {
+  Writer* w = static_cast<Writer*>(h);
+  StageGenovec(w, genovec);
+  const uintptr_t aligned_words = BitCtToAlignedWordCt(w->N);
+  std::vector<uintptr_t> s01(aligned_words + 8, 0), s10(aligned_words + 8, 0);
+  memcpy(s01.data(), patch_01_set, BitCtToWordCt(w->N) * sizeof(uintptr_t));
+  memcpy(s10.data(), patch_10_set, BitCtToWordCt(w->N) * sizeof(uintptr_t));
+  std::vector<AlleleCode> v01(patch_01_ct + 64, 0), v10(2 * static_cast<size_t>(patch_10_ct) + 64, 0);
+  for (uint32_t i = 0; i < patch_01_ct; ++i) v01[i] = patch_01_vals[i];
+  for (uint32_t i = 0; i < 2 * patch_10_ct; ++i) v10[i] = patch_10_vals[i];
+  return static_cast<int>(SpgwAppendMultiallelicSparse(w->genovec, s01.data(), v01.data(), s10.data(), v10.data(), allele_ct,
+                                                       patch_01_ct, patch_10_ct, &w->spgw));
+}
+
+// Dosages with a dosage-phase track (SpgwAppendBiallelicGenovecDphase16; writer opened with flag 4).
+int ref_writer_append_dphase(void* h, const uint64_t* genovec, const uint64_t* phasepresent, const uint64_t* phaseinfo,
+                             const uint64_t* dosage_present, const uint64_t* dphase_present, const uint16_t* dosage_main,
+                             const int16_t* dphase_delta, uint32_t dosage_ct, uint32_t dphase_ct) {
+  Writer* w = static_cast<Writer*>(h);
+  StageGenovec(w, genovec);
+  const uintptr_t aligned_words = BitCtToAlignedWordCt(w->N);
+  const size_t nw = BitCtToWordCt(w->N) * sizeof(uintptr_t);
+  std::vector<uintptr_t> pp(aligned_words + 8, 0), pi(aligned_words + 8, 0), dp(aligned_words + 8, 0), dpp(aligned_words + 8, 0);
+  memcpy(pp.data(), phasepresent, nw);
+  memcpy(pi.data(), phaseinfo, nw);
+  memcpy(dp.data(), dosage_present, nw);
+  memcpy(dpp.data(), dphase_present, nw);
+  std::vector<uint16_t> dm(dosage_ct + 64, 0);
+  std::vector<int16_t> dd(dphase_ct + 64, 0);
+  memcpy(dm.data(), dosage_main, static_cast<size_t>(dosage_ct) * 2);
+  memcpy(dd.data(), dphase_delta, static_cast<size_t>(dphase_ct) * 2);
+  return static_cast<int>(SpgwAppendBiallelicGenovecDphase16(w->genovec, pp.data(), pi.data(), dp.data(), dpp.data(), dm.data(),
+                                                             dd.data(), dosage_ct, dphase_ct, &w->spgw));
 }
 
 int ref_writer_close(void* h) {

@@ -1,0 +1,92 @@
+"""Fixtures for the record tracks beyond biallelic hardcalls, written with pgenlib's own writer
+(oracle/_ref): multiallelic variants (aux1a / aux1b patch sets, pgen_spec.tex:469-564) and dosage-phase tracks
+(:632-676).  The extension reads such files through the biallelic calls (PgrGet, PgrGetCounts, PgrGetMissingness,
+PgrGetD), so parity is defined by what those return.  Test infrastructure."""
+from __future__ import annotations
+
+import numpy as np
+
+import synth
+
+
+def _bits(mask: np.ndarray) -> np.ndarray:
+    n = mask.size
+    w = np.zeros((n + 63) // 64 + 1, dtype=np.uint64)
+    idx = np.nonzero(mask)[0]
+    np.bitwise_or.at(w, idx >> 6, np.uint64(1) << (idx & 63).astype(np.uint64))
+    return w
+
+
+def write_multiallelic(path: str, V: int, N: int, seed: int):
+    """Returns the (V, N) main-track codes that went in (0 REF/REF, 1 REF/ALTx, 2 ALTx/ALTy, 3 missing)."""
+    from oracle import ref
+
+    rng = np.random.default_rng(seed)
+    allele_cts = rng.choice([2, 2, 3, 4, 5, 7, 18, 40], size=V).astype(np.uint32)
+    allele_cts[0] = 2
+    allele_cts[1] = 3
+    w = ref.RefWriter(path, V, N, 0, allele_cts)
+    codes = np.zeros((V, N), dtype=np.int8)
+    for v in range(V):
+        k = int(allele_cts[v])
+        freqs = rng.dirichlet(np.ones(k) * 0.7)
+        freqs[0] += 1.0   # REF-major
+        freqs /= freqs.sum()
+        a = rng.choice(k, size=N, p=freqs)
+        b = rng.choice(k, size=N, p=freqs)
+        lo, hi = np.minimum(a, b), np.maximum(a, b)
+        miss = rng.random(N) < 0.03
+        code = np.where(hi == 0, 0, np.where(lo == 0, 1, 2)).astype(np.int8)
+        code[miss] = 3
+        codes[v] = code
+        gv = synth.to_genovec_words(code[None, :])[0]
+        if k == 2:
+            w.append(gv)
+            continue
+        s01 = (code == 1) & (hi != 1)
+        s10 = (code == 2) & ~((lo == 1) & (hi == 1))
+        vals10 = np.stack([lo[s10], hi[s10]], axis=1)
+        w.append_multiallelic(gv, _bits(s01), hi[s01], _bits(s10), vals10, k)
+    w.close()
+    return codes, allele_cts
+
+
+def write_dphase(path: str, V: int, N: int, seed: int):
+    """Hardcalls + dosages, a third of the variants with an explicit dosage-phase track.  Returns the hardcall
+    codes."""
+    from oracle import ref
+
+    rng = np.random.default_rng(seed)
+    g = synth.gen_hwe_genotypes(V, N, seed=seed, missing=0.03)
+    w = ref.RefWriter(path, V, N, 4, None)
+    for v in range(V):
+        code = g[v]
+        gv = synth.to_genovec_words(code[None, :])[0]
+        kind = v % 3
+        if kind == 0:
+            w.append(gv)
+            continue
+        het = code == 1
+        phasepresent = het & (rng.random(N) < 0.6)
+        phaseinfo = phasepresent & (rng.random(N) < 0.5)
+        dosage_present = (code != 3) & (rng.random(N) < 0.2)
+        base = np.array([0, 16384, 32768, 0], dtype=np.int64)[code]
+        dos = np.clip(base + rng.integers(-5000, 5000, size=N), 0, 32768)
+        dm = dos[dosage_present].astype(np.uint16)
+        if kind == 1:
+            dphase_present = np.zeros(N, dtype=bool)
+            dd = np.zeros(0, dtype=np.int16)
+        else:
+            dphase_present = dosage_present & (rng.random(N) < 0.5)
+            dv = dos[dphase_present]
+            lim = np.minimum(dv, 32768 - dv)      # |delta| <= min(d, 2 - d)
+            dd = (rng.integers(-1, 2, size=dv.size) * (lim // 2)).astype(np.int16)
+            dd[dd == 0] = 1
+            dd = np.where(np.abs(dd) > lim, 0, dd).astype(np.int16)
+            keep = dd != 0
+            idx = np.nonzero(dphase_present)[0]
+            dphase_present[idx[~keep]] = False
+            dd = dd[keep]
+        w.append_dphase(gv, _bits(phasepresent), _bits(phaseinfo), _bits(dosage_present), _bits(dphase_present), dm, dd)
+    w.close()
+    return g
