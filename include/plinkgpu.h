@@ -217,6 +217,19 @@ int pd_decode_i8_valid(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t c
 int pd_decode_i8_valid_list(pd_ctx* ctx, const uint32_t* vidx, uint32_t n_var, uint32_t call_mask, int8_t* out,
                             uint64_t* validity);
 
+/* ---- genotype-orient ("tidy") rows: replaces the load_variant / emit_sample_row double loop of PfileTidyScan
+ *      (src/pfile_reader.cpp:2960-3281) for the columns that come from the genotype path: one row per (variant,
+ *      sample) call -- out_variant[i] = variant index, out_sample[i] = sample index in FILE order (what
+ *      sample_indices[] maps to, :3081-3082: the caller attaches the .psam columns), out_geno[i] = {0, 1, 2, -9}
+ *      (-9: the caller sets the row's genotype NULL, :3163-3167).  emit_mask bit g (0 hom-ref, 1 het, 2 hom-alt,
+ *      3 missing) selects the calls that produce a row: 15 = no genotype_range filter, otherwise
+ *      GenotypeFilter::AllowsCall for bits 0-2 and include_missing for bit 3 (:3043-3075).  Rows are ordered by
+ *      variant, then ascending sample -- the order one scan thread of the reference emits them in.
+ *      *out_rows receives the number of rows; with out_geno == NULL nothing else is written (size query: the count
+ *      follows from the genotype counts).  row_cap = capacity of the three arrays in rows. ---- */
+int pd_tidy_i8(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t emit_mask, uint64_t row_cap, uint32_t* out_variant,
+               uint32_t* out_sample, int8_t* out_geno, uint64_t* out_rows);
+
 /* ---- phased hardcalls : replaces PgrGetP + UnpackPhasedGenotypes (src/plink_common.cpp:1549-1584; call
  *      sites src/pgen_reader.cpp:705-733, src/pfile_reader.cpp:1722-1745, read_pgen / read_pfile with
  *      phased := true).  out: (v_end - v_begin) x n_out x 2 int8 allele pairs in subset order:

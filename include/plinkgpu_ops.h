@@ -103,6 +103,11 @@ typedef struct pd_predecomp_filter {
 int pdop_predecomp_filter(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, const pd_predecomp_filter* filter, uint8_t* skip,
                           uint8_t* all_pass);
 
+/* ---- LIST(TINYINT) genotype columns (genotypes := 'list', src/pgen_reader.cpp:1027-1046): the list_entry_t
+ * {offset, length} pair of each of `rows` consecutive rows whose child values are pd_decode_i8_valid's output:
+ * out[2 r] = base_offset + r * n, out[2 r + 1] = n. ---- */
+void pdop_list_entries(uint64_t base_offset, uint32_t rows, uint32_t n, uint64_t* out);
+
 /* ---- read_pgen / read_pfile genotype column for a range of variants, as the scan emits it
  * (src/pgen_reader.cpp:659-683 filter, :727-733 decode, :1008-1046 fill): counts on the GPU ->
  * CheckPreDecompFilters per variant -> the variants that are not skipped are decoded, in order, into

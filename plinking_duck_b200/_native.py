@@ -92,6 +92,7 @@ SYMBOLS = {
     "pd_decode_fetch": (C.c_int, [_vp, _u32, _u32, _vp]),
     "pd_decode_i8_valid": (C.c_int, [_vp, _u32, _u32, _u32, _vp, _vp]),
     "pd_decode_i8_valid_list": (C.c_int, [_vp, _vp, _u32, _u32, _vp, _vp]),
+    "pd_tidy_i8": (C.c_int, [_vp, _u32, _u32, _u32, _u64, _vp, _vp, _vp, C.POINTER(_u64)]),
     "pd_decode_phased": (C.c_int, [_vp, _u32, _u32, _vp]),
     "pd_dosage_f64": (C.c_int, [_vp, _vp, _u32, _vp]),
     "pd_dosage_counts": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),

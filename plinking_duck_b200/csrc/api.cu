@@ -34,7 +34,7 @@ void DestroyCtx(pd_ctx* c) {
   for (auto e : c->ev_copied) cudaEventDestroy(e);
   for (auto e : c->ev_done) cudaEventDestroy(e);
   for (auto e : c->ev_pool) cudaEventDestroy(e);
-  c->d_counts.Free(); c->d_scratch.Free(); c->d_misc.Free(); c->d_pvals.Free(); c->d_acc.Free(); c->d_ready.Free(); c->d_hweq.Free(); c->d_trim_fpos.Free(); c->d_phase_raw.Free();
+  c->d_counts.Free(); c->d_scratch.Free(); c->d_misc.Free(); c->d_pvals.Free(); c->d_acc.Free(); c->d_ready.Free(); c->d_hweq.Free(); c->d_trim_fpos.Free(); c->d_phase_raw.Free(); c->d_tidy_off.Free();
   c->d_dense.Free(); c->d_rowptrs.Free(); c->d_vlist.Free();
   c->d_loc.Free(); c->d_rank.Free(); c->d_dstats.Free(); c->d_srow.Free(); c->d_weights.Free(); c->d_flip.Free();
   c->d_score.Free(); c->d_dsum.Free(); c->d_act.Free(); c->d_tc.Free();

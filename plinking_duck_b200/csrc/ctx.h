@@ -75,6 +75,7 @@ struct pd_ctx_impl {
   std::vector<uint64_t> trim_fpos;  // [V+1], built on first use
   DevBuf d_trim_fpos;
   DevBuf d_phase_raw;               // pd_decode_phased with a sample subset: unsubsetted pair rows
+  DevBuf d_tidy_off;                // pd_tidy_i8: row offset of every variant of the call
   int trim_state = 0;               // 0 not built, 1 usable, -1 not worth it / not possible
   bool trim_scan = false;           // set by the caller around RunScan
 

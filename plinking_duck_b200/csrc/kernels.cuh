@@ -142,6 +142,15 @@ void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t n, uin
 void launch_subset_indices(const uint32_t* include_words, const uint32_t* cum, uint32_t nwords, uint32_t* out,
                            cudaStream_t s, LaunchStats* st);
 
+// ---- K5t: genotype-orient ("tidy") rows: (variant, sample, call) per emitted call (kernels_tidy.cu) ----
+// emit_mask bit g: calls of category g (0 hom-ref, 1 het, 2 hom-alt, 3 missing) produce a row.
+void launch_tidy_rows(const uint4* counts, uint32_t n, uint32_t emit_mask, unsigned long long* rows_per, cudaStream_t s,
+                      LaunchStats* st);
+// row_off[r] - off0 = first output row of batch row r; variant = vlist ? vlist[r] : variant0 + r.
+void launch_tidy(const DenseRows& rows, const uint32_t* subset_idx, uint32_t n_out, uint32_t emit_mask,
+                 const unsigned long long* row_off, unsigned long long off0, uint32_t variant0, const uint32_t* vlist,
+                 uint32_t* out_variant, uint32_t* out_sample, int8_t* out_geno, cudaStream_t s, LaunchStats* st);
+
 // ---- K6: dosage tracks ----
 struct DosageLoc {            // where a row's dosage tracks are (written by launch_dosage_locate)
   const uint8_t* track3;      // sample-id list (kind 1) or N-bit array (kind 3)

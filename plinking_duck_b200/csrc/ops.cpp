@@ -147,6 +147,14 @@ uint32_t EffectiveSampleCt(const uint32_t* counts) { return counts[0] + counts[1
 
 extern "C" {
 
+void pdop_list_entries(uint64_t base_offset, uint32_t rows, uint32_t n, uint64_t* out) {
+  if (!out) return;
+  for (uint32_t r = 0; r < rows; ++r) {
+    out[2ull * r] = base_offset + static_cast<uint64_t>(r) * n;
+    out[2ull * r + 1] = n;
+  }
+}
+
 int pdop_classify_ploidy(const char* chrom, int32_t pos, const char* build) {
   Par par;
   if (!ResolvePar(build, &par)) return -1;

@@ -38,6 +38,7 @@ _OPS = {
     "pdop_genotype_range": (None, [_vp, _u32, _u32, _vp, _vp]),
     "pdop_predecomp_filter": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),
     "pdop_genotype_column": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp, _vp, _vp]),
+    "pdop_list_entries": (None, [C.c_uint64, _u32, _u32, _vp]),
     "pdop_genotype_stats_variant": (C.c_int, [_vp, _u32, _u32, _vp]),
     "pdop_genotype_stats_sample": (C.c_int, [_vp, _u32, _u32, _vp]),
 }
@@ -194,4 +195,11 @@ def genotype_stats(ctx: PgenContext, v0=0, v1=None, *, orient="variant") -> np.n
         ctx._check(_lib().pdop_genotype_stats_sample(ctx._h, v0, v1, _p(out)))
     else:
         raise ValueError("genotype_stats: orient must be 'variant' or 'sample'")
+    return out
+
+
+def list_entries(base_offset: int, rows: int, n: int) -> np.ndarray:
+    """(rows, 2) uint64 {offset, length} pairs of a LIST(TINYINT) genotype column."""
+    out = np.zeros((rows, 2), dtype=np.uint64)
+    _lib().pdop_list_entries(int(base_offset), int(rows), int(n), _p(out))
     return out

@@ -258,6 +258,20 @@ class PgenContext:
         self._check(self._lib.pd_decode_i8_valid(self._h, v0, v1, call_mask, _p(out), _p(validity)))
         return out, validity
 
+    def tidy(self, v0=0, v1=None, emit_mask=15):
+        """Genotype-orient rows (variant, sample, call) of the calls whose category is in emit_mask."""
+        v0, v1 = self._range(v0, v1)
+        rows = C.c_uint64()
+        self._check(self._lib.pd_tidy_i8(self._h, v0, v1, emit_mask, 0, None, None, None, C.byref(rows)))
+        n = rows.value
+        var = np.zeros(n, dtype=np.uint32)
+        smp = np.zeros(n, dtype=np.uint32)
+        geno = np.zeros(n, dtype=np.int8)
+        if n:
+            self._check(self._lib.pd_tidy_i8(self._h, v0, v1, emit_mask, n, _p(var), _p(smp), _p(geno), C.byref(rows)))
+            assert rows.value == n
+        return var, smp, geno
+
     def decode_phased(self, v0=0, v1=None) -> np.ndarray:
         """(v1 - v0, sample_ct, 2) int8 allele pairs (read_pgen / read_pfile with phased := true)."""
         v0, v1 = self._range(v0, v1)

@@ -347,3 +347,57 @@ def test_c4_compressed_fileset_at_scale(tmp_path):
                 assert np.array_equal(c.counts(lo, hi), exp_counts[lo:hi])
                 counts, p = c.hardy(lo, hi)
                 assert np.array_equal(counts, exp_counts[lo:hi]) and np.all((p >= 0) & (p <= 1))
+
+
+def _tidy_expected(i8, sample_ids, emit_mask, v0=0):
+    """The rows PfileTidyScan emits (src/pfile_reader.cpp:3043-3075 filter): variant-major, ascending sample."""
+    cat = np.where(i8 == -9, 3, i8).astype(np.int64)
+    keep = ((emit_mask >> cat) & 1).astype(bool)
+    vv, ss = np.nonzero(keep)
+    return (vv + v0).astype(np.uint32), np.asarray(sample_ids, dtype=np.uint32)[ss], i8[vv, ss]
+
+
+@pytest.mark.parametrize("name", ["pgen_example", "pca_example", "syn_n1000", "streaming_example", "syn_n70000"])
+def test_tidy_rows_match_reference_emission_order(name, golden):
+    from plinking_duck_b200 import ops
+
+    if name + "/i8" not in golden:
+        pytest.skip("no int8 golden")
+    i8 = golden[name + "/i8"]
+    V, N = i8.shape
+    for kw in (dict(), dict(tile_bytes=2048, n_staging=2), dict(devices=[0])):
+        with _ctx(name, **kw) as c:
+            for mask in (15, 7, 6, 2, 8, 9):
+                var, smp, geno = c.tidy(emit_mask=mask)
+                ev, es, eg = _tidy_expected(i8, np.arange(N), mask)
+                assert np.array_equal(var, ev) and np.array_equal(smp, es) and np.array_equal(geno, eg), (name, mask)
+            a, b = V // 4, V - V // 5
+            var, smp, geno = c.tidy(a, b, emit_mask=14)
+            ev, es, eg = _tidy_expected(i8[a:b], np.arange(N), 14, v0=a)
+            assert np.array_equal(var, ev) and np.array_equal(smp, es) and np.array_equal(geno, eg)
+            if N >= 8:
+                sub = np.arange(1, N, 3)
+                c.set_subset(sub)
+                var, smp, geno = c.tidy(emit_mask=11)
+                ev, es, eg = _tidy_expected(i8[:, sub], sub, 11)   # sample column = FILE index of the subset sample
+                assert np.array_equal(var, ev) and np.array_equal(smp, es) and np.array_equal(geno, eg)
+                c.set_subset(None)
+    le = ops.list_entries(10, 3, 7)
+    assert le.tolist() == [[10, 7], [17, 7], [24, 7]]
+
+
+def test_tidy_many_batches_fixed_width():
+    import synth
+    from plinking_duck_b200.pgen import PgenContext
+
+    V, N = 900, 70_001   # 24 Mi rows per batch -> several batches with mask 15
+    g = synth.gen_hwe_genotypes(V, N, seed=2, missing=0.02)
+    i8 = np.where(g == 3, -9, g).astype(np.int8)
+    with PgenContext(image=synth.fixed_pgen_image(g)) as c:
+        var, smp, geno = c.tidy(emit_mask=15)
+        assert var.size == V * N
+        assert np.array_equal(geno.reshape(V, N), i8)
+        assert np.array_equal(smp.reshape(V, N)[5], np.arange(N)) and np.array_equal(var.reshape(V, N)[:, 3], np.arange(V))
+        var, smp, geno = c.tidy(emit_mask=4 | 8)
+        ev, es, eg = _tidy_expected(i8, np.arange(N), 12)
+        assert np.array_equal(var, ev) and np.array_equal(smp, es) and np.array_equal(geno, eg)
