@@ -260,6 +260,23 @@ int pd_dosage_counts(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t* ou
 int pd_score(pd_ctx* ctx, const uint32_t* vidx, const uint8_t* flip, const double* weights, uint32_t n_var,
              uint32_t K, uint32_t mode, double* score_sums, double* dosage_sums, uint32_t* allele_cts);
 
+/* ---- plink_ld: the sums behind ComputeLdStats (src/plink_ld.cpp:52-86) for a list of variant pairs, as popcount
+ *      contractions of the two packed rows: out_sums[6 i + {0..5}] = n (samples with both calls present), sum gA,
+ *      sum gB, sum gA gB, sum gA^2, sum gB^2 -- exact integers; pdop_ld_stats (plinkgpu_ops.h) turns them into R2 /
+ *      D_PRIME / OBS_CT with the reference's arithmetic.  The caller builds the pair list from its window logic
+ *      (src/plink_ld.cpp:620-690, which needs CHROM / POS).  The variant span of a call is staged into HBM for its
+ *      duration unless it is already resident; the distinct variants of one call must fit one dense batch
+ *      (65 535 rows; 1 GiB of decoded rows for variable-width files). ---- */
+int pd_ld_pairs(pd_ctx* ctx, const uint32_t* va, const uint32_t* vb, uint32_t n_pairs, uint32_t* out_sums);
+
+/* ---- plink_pca / plink_glm: standardised genotype rows, replaces PgrGet + GenoarrToBytesMinus9 +
+ *      NormalizeGenotypes (src/plink_pca.cpp:895-905, src/plink_common.cpp:1521-1543): out[i * n + s] =
+ *      (g - 2 f) / sqrt(2 f (1 - f)) with f the variant's ALT frequency over the (subset) samples
+ *      (src/plink_pca.cpp:403-410), 0 where the call is missing.  Variants without observations or with f in {0, 1}
+ *      (ComputeVariantNorm's skip) yield an all-zero row and out_skip[i] = 1 (out_skip may be NULL).  vidx strictly
+ *      ascending. ---- */
+int pd_standardized_f64(pd_ctx* ctx, const uint32_t* vidx, uint32_t n_var, double* out, uint8_t* out_skip);
+
 /* ---- device-side results for multi-GPU reductions.  After pd_score / pd_missing_by_sample /
  *      pd_sample_counts (whose host output pointers may then be NULL), the accumulators of the last
  *      call stay in HBM; the caller all-reduces them in place over NVLink (NCCL) and reads them back

@@ -103,6 +103,15 @@ typedef struct pd_predecomp_filter {
 int pdop_predecomp_filter(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, const pd_predecomp_filter* filter, uint8_t* skip,
                           uint8_t* all_pass);
 
+/* ---- plink_ld output columns from pd_ld_pairs sums: ComputeLdStats' arithmetic after its sample loop
+ * (src/plink_ld.cpp:88-134), same operation order, so R2 / D_PRIME are bit-identical. ---- */
+typedef struct pd_ld_row {
+  double r2, d_prime;
+  uint32_t obs_ct;
+  uint32_t is_valid;   /* 0: fewer than 2 observations or a monomorphic variant -> R2 / D_PRIME are NULL */
+} pd_ld_row;
+void pdop_ld_stats(const uint32_t* sums, uint32_t n_pairs, pd_ld_row* out);
+
 /* ---- LIST(TINYINT) genotype columns (genotypes := 'list', src/pgen_reader.cpp:1027-1046): the list_entry_t
  * {offset, length} pair of each of `rows` consecutive rows whose child values are pd_decode_i8_valid's output:
  * out[2 r] = base_offset + r * n, out[2 r + 1] = n. ---- */

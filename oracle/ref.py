@@ -62,6 +62,7 @@ def lib():
         L.ref_writer_append_dosage.argtypes = [vp, vp, vp, vp, u32]
         L.ref_writer_append_phased.argtypes = [vp, vp, vp, vp]
         L.ref_decode_phased.argtypes = [vp, u32, u32, vp]
+        L.ref_ld_pair.argtypes = [vp, u32, u32, vp, C.POINTER(u32), C.POINTER(u32)]
         L.ref_writer_open_ex.argtypes = [C.c_char_p, u32, u32, u32, vp, C.POINTER(vp)]
         L.ref_writer_append_multiallelic.argtypes = [vp, vp, vp, vp, u32, vp, vp, u32, u32]
         L.ref_writer_append_dphase.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, u32, u32]
@@ -193,6 +194,15 @@ class RefPgen:
         if rc:
             raise IOError(f"ref_score rc={rc}")
         return s, d, a
+
+    def ld_pair(self, va: int, vb: int):
+        """(r2, d_prime, obs_ct, is_valid) of plink_ld's ComputeLdStats for one variant pair."""
+        out = np.zeros(2, dtype=np.float64)
+        obs, valid = C.c_uint32(), C.c_uint32()
+        rc = lib().ref_ld_pair(self._h, int(va), int(vb), _p(out), C.byref(obs), C.byref(valid))
+        if rc:
+            raise IOError(f"PgrGet rc={rc}")
+        return float(out[0]), float(out[1]), obs.value, valid.value
 
     def sample_counts(self, v0=0, v1=None, sparse=False):
         v0, v1 = self._rng(v0, v1)

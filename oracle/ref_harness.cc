@@ -22,6 +22,7 @@
 //
 // The extension-side arithmetic (score loop, sample-orient accumulation) is restated here
 // because it lives in DuckDB scan callbacks that cannot be built without DuckDB.
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <cmath>
@@ -605,6 +606,65 @@ double ref_bench_score(const char* path, uint32_t threads, const uint32_t* vidx,
   const auto t1 = std::chrono::steady_clock::now();
   for (uint32_t t = 0; t < threads; ++t) CloseReader(&readers[t]);
   return std::chrono::duration<double>(t1 - t0).count();
+}
+
+// ---- plink_ld: ComputeLdStats restated (src/plink_ld.cpp:52-135; a static function of the extension, so it cannot
+// be linked): PgrGet for both variants (ReadGenovec, :564-581), then the per-sample loop and the closed forms.
+// out2 = {r2, d_prime}.
+int ref_ld_pair(void* h, uint32_t va, uint32_t vb, double* out2, uint32_t* obs_ct, uint32_t* is_valid) {
+  Reader* r = static_cast<Reader*>(h);
+  const uint32_t sample_ct = r->sample_ct;
+  const uintptr_t words = NypCtToAlignedWordCt(r->N) + 8;
+  std::vector<uintptr_t> ga(words, 0), gb(words, 0);
+  PglErr e = PgrGet(r->sample_include, r->pssi, sample_ct, va, &r->pgr, ga.data());
+  if (e != kPglRetSuccess) return static_cast<int>(e);
+  e = PgrGet(r->sample_include, r->pssi, sample_ct, vb, &r->pgr, gb.data());
+  if (e != kPglRetSuccess) return static_cast<int>(e);
+  double sum_a = 0, sum_b = 0, sum_ab = 0, sum_a2 = 0, sum_b2 = 0;
+  uint32_t n = 0;
+  const uint32_t word_ct = DivUp(sample_ct, kBitsPerWordD2);
+  for (uint32_t widx = 0; widx < word_ct; widx++) {
+    uintptr_t word_a = ga[widx];
+    uintptr_t word_b = gb[widx];
+    const uint32_t samples_remaining = sample_ct - widx * kBitsPerWordD2;
+    const uint32_t samples_in_word = samples_remaining < kBitsPerWordD2 ? samples_remaining : kBitsPerWordD2;
+    for (uint32_t sidx = 0; sidx < samples_in_word; sidx++) {
+      const uint32_t geno_a = word_a & 3;
+      const uint32_t geno_b = word_b & 3;
+      word_a >>= 2;
+      word_b >>= 2;
+      if (geno_a == 3 || geno_b == 3) continue;
+      const double a = static_cast<double>(geno_a), b = static_cast<double>(geno_b);
+      sum_a += a;
+      sum_b += b;
+      sum_ab += a * b;
+      sum_a2 += a * a;
+      sum_b2 += b * b;
+      n++;
+    }
+  }
+  *obs_ct = n;
+  *is_valid = 0;
+  out2[0] = out2[1] = 0;
+  if (n < 2) return 0;
+  const double dn = static_cast<double>(n);
+  const double mean_a = sum_a / dn, mean_b = sum_b / dn;
+  const double cov_ab = sum_ab / dn - mean_a * mean_b;
+  const double var_a = sum_a2 / dn - mean_a * mean_a;
+  const double var_b = sum_b2 / dn - mean_b * mean_b;
+  if (var_a < 1e-15 || var_b < 1e-15) return 0;
+  *is_valid = 1;
+  out2[0] = (cov_ab * cov_ab) / (var_a * var_b);
+  const double D = cov_ab / 4.0;
+  const double p_a = sum_a / (2.0 * dn), p_b = sum_b / (2.0 * dn);
+  double D_max;
+  if (D >= 0) {
+    D_max = std::min(p_a * (1.0 - p_b), (1.0 - p_a) * p_b);
+  } else {
+    D_max = std::max(-p_a * p_b, -(1.0 - p_a) * (1.0 - p_b));
+  }
+  out2[1] = std::abs(D_max) < 1e-15 ? 0.0 : D / D_max;
+  return 0;
 }
 
 // ---- writer (fixture / synthetic fileset generator; pgenlib picks the record type) ----

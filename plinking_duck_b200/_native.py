@@ -97,6 +97,8 @@ SYMBOLS = {
     "pd_dosage_f64": (C.c_int, [_vp, _vp, _u32, _vp]),
     "pd_dosage_counts": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),
     "pd_score": (C.c_int, [_vp, _vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
+    "pd_ld_pairs": (C.c_int, [_vp, _vp, _vp, _u32, _vp]),
+    "pd_standardized_f64": (C.c_int, [_vp, _vp, _u32, _vp, _vp]),
     "pd_device_result": (C.c_int, [_vp, _u32, C.POINTER(_vp), C.POINTER(_u64)]),
     "pd_get_stats": (C.c_int, [_vp, C.POINTER(Stats)]),
     "pd_reset_stats": (C.c_int, [_vp]),

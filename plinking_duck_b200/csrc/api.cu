@@ -34,7 +34,7 @@ void DestroyCtx(pd_ctx* c) {
   for (auto e : c->ev_copied) cudaEventDestroy(e);
   for (auto e : c->ev_done) cudaEventDestroy(e);
   for (auto e : c->ev_pool) cudaEventDestroy(e);
-  c->d_counts.Free(); c->d_scratch.Free(); c->d_misc.Free(); c->d_pvals.Free(); c->d_acc.Free(); c->d_ready.Free(); c->d_hweq.Free(); c->d_trim_fpos.Free(); c->d_phase_raw.Free(); c->d_tidy_off.Free();
+  c->d_counts.Free(); c->d_scratch.Free(); c->d_misc.Free(); c->d_pvals.Free(); c->d_acc.Free(); c->d_ready.Free(); c->d_hweq.Free(); c->d_trim_fpos.Free(); c->d_phase_raw.Free(); c->d_tidy_off.Free(); c->d_span.Free(); c->d_pairs.Free();
   c->d_dense.Free(); c->d_rowptrs.Free(); c->d_vlist.Free();
   c->d_loc.Free(); c->d_rank.Free(); c->d_dstats.Free(); c->d_srow.Free(); c->d_weights.Free(); c->d_flip.Free();
   c->d_score.Free(); c->d_dsum.Free(); c->d_act.Free(); c->d_tc.Free();
@@ -459,6 +459,14 @@ int pd_load_resident(pd_ctx* c, uint32_t v_begin, uint32_t v_end) {
   if (c->group) return GroupLoadResident(c, v_begin, v_end);
   std::lock_guard<std::mutex> lock(c->mu);
   cudaSetDevice(c->device);
+  return LoadRange(c, v_begin, v_end, &c->d_resident);
+}
+
+}  // extern "C"
+
+// Stages the records of [v_begin, v_end) (extended back to an LD base) into *buf and makes them the context's
+// resident range.  Caller holds c->mu.
+int pdx::LoadRange(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, DevBuf* buf) {
   const PgenIndex& ix = c->idx;
   if (v_begin >= v_end || v_end > ix.variant_ct) return c->SetError(PD_ERR_INVALID_ARG, "variant range out of bounds");
   const uint32_t v0 = ExtendToBase(c, v_begin);
@@ -467,13 +475,13 @@ int pd_load_resident(pd_ctx* c, uint32_t v_begin, uint32_t v_end) {
   const uint64_t len = f1 - f0;
   if (c->dev_image) return PD_OK;  // already in HBM
   c->resident = false;
-  cudaError_t e = c->d_resident.Reserve(len + 2 * kSlack);
+  cudaError_t e = buf->Reserve(len + 2 * kSlack);
   if (e != cudaSuccess) {
     cudaGetLastError();
     return c->SetError(PD_ERR_NOMEM, std::string("cannot hold the requested range in HBM: ") + cudaGetErrorString(e));
   }
-  uint8_t* dst = c->d_resident.as<uint8_t>() + kSlack;
-  cudaMemsetAsync(c->d_resident.p, 0, kSlack, c->stream);
+  uint8_t* dst = buf->as<uint8_t>() + kSlack;
+  cudaMemsetAsync(buf->p, 0, kSlack, c->stream);
   cudaMemsetAsync(dst + len, 0, kSlack, c->stream);
   if (c->src_pinned) {
     e = CopyFromPinnedSource(c, dst, f0, len, c->stream);
@@ -510,6 +518,8 @@ int pd_load_resident(pd_ctx* c, uint32_t v_begin, uint32_t v_end) {
   c->res_f1 = f1;
   return PD_OK;
 }
+
+extern "C" {
 
 int pd_unload(pd_ctx* c) {
   if (!c) return PD_ERR_INVALID_ARG;

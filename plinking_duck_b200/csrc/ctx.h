@@ -76,6 +76,8 @@ struct pd_ctx_impl {
   DevBuf d_trim_fpos;
   DevBuf d_phase_raw;               // pd_decode_phased with a sample subset: unsubsetted pair rows
   DevBuf d_tidy_off;                // pd_tidy_i8: row offset of every variant of the call
+  DevBuf d_pairs;                   // pd_ld_pairs: row positions of the pairs; pd_standardized_f64: per-row norms
+  DevBuf d_span;                    // pd_ld_pairs: the variant span of a call, held in HBM for its duration
   int trim_state = 0;               // 0 not built, 1 usable, -1 not worth it / not possible
   bool trim_scan = false;           // set by the caller around RunScan
 
@@ -170,6 +172,7 @@ int RunRows(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t max_rows,
 int RunRowsList(pd_ctx_impl* c, const uint32_t* vlist, uint32_t n, uint32_t max_rows, const RowFn& fn);
 uint32_t DenseSlotStride(const pd_ctx_impl* c);
 int DownloadRows(pd_ctx_impl* c, const void* dev, size_t bytes, void* host);
+int LoadRange(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, DevBuf* buf);
 int StartScanJob(pd_ctx* c, uint32_t v_begin, uint32_t v_end, bool hardy, uint32_t midp, pd_job** out);
 
 }  // namespace pdx

@@ -151,6 +151,15 @@ void launch_tidy(const DenseRows& rows, const uint32_t* subset_idx, uint32_t n_o
                  const unsigned long long* row_off, unsigned long long off0, uint32_t variant0, const uint32_t* vlist,
                  uint32_t* out_variant, uint32_t* out_sample, int8_t* out_geno, cudaStream_t s, LaunchStats* st);
 
+// ---- plink_ld / plink_pca / plink_glm consumers of the dense rows (kernels_ld.cu) ----
+// out[6 i + {0..5}] = n, sum gA, sum gB, sum gA gB, sum gA^2, sum gB^2 over the samples where both calls of pair i
+// (rows ra[i], rb[i]) are present (and, with include_words, selected).
+void launch_ld_pairs(const DenseRows& rows, const uint32_t* ra, const uint32_t* rb, uint32_t n_pairs,
+                     const uint32_t* include_words, uint32_t* out, cudaStream_t s, LaunchStats* st);
+// out[r * n_out + j] = (g - norm[r].x) * norm[r].y, 0 where the call is missing.
+void launch_standardize(const DenseRows& rows, const uint32_t* subset_idx, uint32_t n_out, const double2* norm, double* out,
+                        cudaStream_t s, LaunchStats* st);
+
 // ---- K6: dosage tracks ----
 struct DosageLoc {            // where a row's dosage tracks are (written by launch_dosage_locate)
   const uint8_t* track3;      // sample-id list (kind 1) or N-bit array (kind 3)

@@ -147,6 +147,43 @@ uint32_t EffectiveSampleCt(const uint32_t* counts) { return counts[0] + counts[1
 
 extern "C" {
 
+void pdop_ld_stats(const uint32_t* sums, uint32_t n_pairs, pd_ld_row* out) {
+  if (!sums || !out) return;
+  for (uint32_t i = 0; i < n_pairs; ++i) {
+    const uint32_t* s = sums + 6ull * i;
+    const uint32_t n = s[0];
+    const double sum_a = s[1], sum_b = s[2], sum_ab = s[3], sum_a2 = s[4], sum_b2 = s[5];
+    pd_ld_row r;
+    r.obs_ct = n;
+    r.is_valid = 0;
+    r.r2 = 0;
+    r.d_prime = 0;
+    if (n >= 2) {
+      const double dn = static_cast<double>(n);
+      const double mean_a = sum_a / dn;
+      const double mean_b = sum_b / dn;
+      const double cov_ab = sum_ab / dn - mean_a * mean_b;
+      const double var_a = sum_a2 / dn - mean_a * mean_a;
+      const double var_b = sum_b2 / dn - mean_b * mean_b;
+      if (!(var_a < 1e-15 || var_b < 1e-15)) {
+        r.is_valid = 1;
+        r.r2 = (cov_ab * cov_ab) / (var_a * var_b);
+        const double D = cov_ab / 4.0;
+        const double p_a = sum_a / (2.0 * dn);
+        const double p_b = sum_b / (2.0 * dn);
+        double D_max;
+        if (D >= 0) {
+          D_max = std::min(p_a * (1.0 - p_b), (1.0 - p_a) * p_b);
+        } else {
+          D_max = std::max(-p_a * p_b, -(1.0 - p_a) * (1.0 - p_b));
+        }
+        r.d_prime = std::abs(D_max) < 1e-15 ? 0.0 : D / D_max;
+      }
+    }
+    out[i] = r;
+  }
+}
+
 void pdop_list_entries(uint64_t base_offset, uint32_t rows, uint32_t n, uint64_t* out) {
   if (!out) return;
   for (uint32_t r = 0; r < rows; ++r) {

@@ -38,6 +38,7 @@ _OPS = {
     "pdop_genotype_range": (None, [_vp, _u32, _u32, _vp, _vp]),
     "pdop_predecomp_filter": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),
     "pdop_genotype_column": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp, _vp, _vp]),
+    "pdop_ld_stats": (None, [_vp, _u32, _vp]),
     "pdop_list_entries": (None, [C.c_uint64, _u32, _u32, _vp]),
     "pdop_genotype_stats_variant": (C.c_int, [_vp, _u32, _u32, _vp]),
     "pdop_genotype_stats_sample": (C.c_int, [_vp, _u32, _u32, _vp]),
@@ -202,4 +203,15 @@ def list_entries(base_offset: int, rows: int, n: int) -> np.ndarray:
     """(rows, 2) uint64 {offset, length} pairs of a LIST(TINYINT) genotype column."""
     out = np.zeros((rows, 2), dtype=np.uint64)
     _lib().pdop_list_entries(int(base_offset), int(rows), int(n), _p(out))
+    return out
+
+
+LD_DTYPE = np.dtype([("R2", "<f8"), ("D_PRIME", "<f8"), ("OBS_CT", "<u4"), ("is_valid", "<u4")], align=True)
+
+
+def plink_ld(ctx: PgenContext, va, vb) -> np.ndarray:
+    """R2 / D_PRIME / OBS_CT rows of plink_ld for the given variant pairs (pd_ld_pairs + pdop_ld_stats)."""
+    sums = ctx.ld_pairs(va, vb)
+    out = np.zeros(sums.shape[0], dtype=LD_DTYPE)
+    _lib().pdop_ld_stats(_p(sums), sums.shape[0], _p(out))
     return out

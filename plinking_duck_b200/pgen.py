@@ -285,6 +285,22 @@ class PgenContext:
         self._check(self._lib.pd_dosage_f64(self._h, _p(vidx), vidx.size, _p(out)))
         return out
 
+    def ld_pairs(self, va, vb) -> np.ndarray:
+        """(n, 6) uint32 sums of plink_ld's estimator for the variant pairs (va[i], vb[i])."""
+        va = np.ascontiguousarray(va, dtype=np.uint32)
+        vb = np.ascontiguousarray(vb, dtype=np.uint32)
+        out = np.zeros((va.size, 6), dtype=np.uint32)
+        self._check(self._lib.pd_ld_pairs(self._h, _p(va), _p(vb), va.size, _p(out)))
+        return out
+
+    def standardized(self, vidx):
+        """(rows (n, sample_ct) float64, skip (n,) uint8): NormalizeGenotypes of the listed variants."""
+        vidx = np.ascontiguousarray(vidx, dtype=np.uint32)
+        out = np.zeros((vidx.size, self.sample_ct), dtype=np.float64)
+        skip = np.zeros(vidx.size, dtype=np.uint8)
+        self._check(self._lib.pd_standardized_f64(self._h, _p(vidx), vidx.size, _p(out), _p(skip)))
+        return out, skip
+
     def dosage_counts(self, v0=0, v1=None):
         v0, v1 = self._range(v0, v1)
         n = max(v1 - v0, 0)
