@@ -74,16 +74,17 @@ int CheckCuda(pd_ctx_impl* c, cudaError_t e, const char* what) {
 }
 
 cudaError_t CopyFromPinnedSource(pd_ctx_impl* c, void* dst, uint64_t off, uint64_t len, cudaStream_t s) {
-  const uint8_t* src = c->pgen.mem();
-  if (!c->pgen.pinned()) return cudaMemcpyAsync(dst, src + off, len, cudaMemcpyHostToDevice, s);
+  // A page-locked file mapping is registered in pieces and one DMA may not span two registrations.  The shards of a
+  // multi-GPU context see that mapping as a plain memory image, so the piece grid is looked up by address.
+  const uint8_t* src = c->pgen.mem() + off;
   uint8_t* d = static_cast<uint8_t*>(dst);
   while (len) {
-    const uint64_t room = ByteSource::kPinPiece - (off % ByteSource::kPinPiece);
+    const uint64_t room = ByteSource::PieceRoom(src);
     const uint64_t n = len < room ? len : room;
-    const cudaError_t e = cudaMemcpyAsync(d, src + off, n, cudaMemcpyHostToDevice, s);
+    const cudaError_t e = cudaMemcpyAsync(d, src, n, cudaMemcpyHostToDevice, s);
     if (e != cudaSuccess) return e;
     d += n;
-    off += n;
+    src += n;
     len -= n;
   }
   return cudaSuccess;

@@ -12,23 +12,60 @@
 #include <atomic>
 #include <cerrno>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <thread>
 
 #include "../../include/plinkgpu.h"
 
 namespace pdx {
 
+namespace {
+
+struct PinnedRegion {
+  const uint8_t* base;
+  uint64_t size, piece;
+};
+std::mutex g_pin_mu;
+std::vector<PinnedRegion> g_pinned;
+
+uint64_t PinPieceBytes() {
+  const char* e = getenv("PD_PIN_PIECE_MB");
+  const long mb = e ? atol(e) : 0;
+  return mb >= 2 ? static_cast<uint64_t>(mb) << 20 : 1ull << 30;
+}
+
+}  // namespace
+
 ByteSource::~ByteSource() {
+  if (!pinned_pieces_.empty()) {
+    std::lock_guard<std::mutex> lk(g_pin_mu);
+    for (size_t i = 0; i < g_pinned.size(); ++i) {
+      if (g_pinned[i].base == map_) {
+        g_pinned.erase(g_pinned.begin() + static_cast<long>(i));
+        break;
+      }
+    }
+  }
   for (auto& pc : pinned_pieces_) cudaHostUnregister(pc.first);
   if (map_) munmap(const_cast<uint8_t*>(map_), size_);
   if (fd_ >= 0) close(fd_);
 }
 
+uint64_t ByteSource::PieceRoom(const void* p) {
+  const uint8_t* q = static_cast<const uint8_t*>(p);
+  std::lock_guard<std::mutex> lk(g_pin_mu);
+  for (const PinnedRegion& r : g_pinned) {
+    if (q >= r.base && q < r.base + r.size) return r.piece - static_cast<uint64_t>(q - r.base) % r.piece;
+  }
+  return UINT64_MAX;
+}
+
 bool ByteSource::PinMapping() {
   if (!map_ || !map_writable_ || !size_) return false;
   // 1 GiB pieces on 2 MiB boundaries, registered from a few threads at once (the driver pins ~6.6 GiB/s per call)
-  const uint64_t kPiece = kPinPiece;
+  const uint64_t kPiece = PinPieceBytes();
   uint8_t* base = const_cast<uint8_t*>(map_);
   std::vector<std::pair<uint8_t*, uint64_t>> pieces;
   for (uint64_t off = 0; off < size_; off += kPiece) pieces.emplace_back(base + off, std::min(kPiece, size_ - off));
@@ -59,6 +96,10 @@ bool ByteSource::PinMapping() {
     return false;
   }
   pinned_pieces_ = pieces;
+  {
+    std::lock_guard<std::mutex> lk(g_pin_mu);
+    g_pinned.push_back({map_, size_, kPiece});
+  }
   mem_ = map_;  // from here on: a page-locked memory image
   return true;
 }

@@ -27,8 +27,11 @@ class ByteSource {
   // like a page-locked memory image (mem() == the mapping).  False (nothing left registered) on any failure.
   bool PinMapping();
   bool pinned() const { return !pinned_pieces_.empty(); }
-  // Page-locked pieces are separate registrations: one DMA must not span two of them.
-  static constexpr uint64_t kPinPiece = 1ull << 30;
+  // Page-locked pieces are separate registrations and one DMA must not span two of them.  PieceRoom(p): how many
+  // bytes from host address p stay inside one registration of a mapping pinned by ANY ByteSource of this process
+  // (the shards of a multi-GPU context read the parent's mapping as a plain memory image); UINT64_MAX when p is
+  // not inside such a mapping.  Piece size: 1 GiB (PD_PIN_PIECE_MB overrides it so tests cross pieces with small files).
+  static uint64_t PieceRoom(const void* p);
   void OpenMem(const void* p, uint64_t len);
   // A .pgen image that already lives in device memory (reads go through cudaMemcpy).
   void OpenDevice(const void* p, uint64_t len);

@@ -169,6 +169,38 @@ def test_group_over_pinned_file(k, tmp_path, golden):
             assert np.array_equal(c.missing_by_sample(), golden[name + "/missing_by_sample"])
 
 
+@pytest.mark.parametrize("k", K)
+def test_group_over_pinned_file_crossing_registration_pieces(k, tmp_path, monkeypatch):
+    """The page-locked mapping is registered in pieces and one DMA may not span two of them: with 2 MiB pieces
+    (PD_PIN_PIECE_MB) a 9 MB file is five registrations, tiles of 1.5 MiB straddle them, and the shards -- which
+    see the parent's mapping as a plain memory image -- must cut their copies at the same grid (the N = 2 bench
+    failed with 'invalid argument' before they did)."""
+    import os
+    import tempfile
+
+    import synth
+    from plinking_duck_b200.pgen import PgenContext
+
+    shm = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+    if shm is None:
+        pytest.skip("needs a tmpfs to page-lock a file mapping")
+    monkeypatch.setenv("PD_PIN_PIECE_MB", "2")
+    g = synth.gen_hwe_genotypes(3000, 12011, seed=77)
+    exp = synth.counts_numpy(g)
+    with tempfile.TemporaryDirectory(dir=shm) as d:
+        path = os.path.join(d, "pieces.pgen")
+        synth.write_fixed_pgen(path, g)
+        for devices in (None, _devices(k)):
+            with PgenContext(path, devices=devices, pin_file=True, tile_bytes=3 << 19) as c:
+                assert c.info().pinned_file == 1
+                assert np.array_equal(c.counts(), exp)
+                counts, p = c.hardy()
+                assert np.array_equal(counts, exp)
+                assert np.array_equal(c.missing_by_sample(), (g == 3).sum(0).astype(np.uint32))
+                c.load_resident()
+                assert np.array_equal(c.counts(), exp)
+
+
 def test_group_rejects_bad_device_lists():
     from plinking_duck_b200 import _native as nat
     from plinking_duck_b200.pgen import PgenContext
