@@ -401,6 +401,11 @@ __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
   return v;
 }
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
 __device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
@@ -498,10 +503,27 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
     for (uint32_t j = grp; j < nsteps; j += kGroups) {
       mbar_wait_addr(p_full0 + pst * 8u, pphase);
       const uint32_t mis = lds32(pk_mis + pst * (kSlabK * 4u));
-      const uint32_t src = pk_row + pst * (kSlabK * kPRow) + (mis & ~3u);  // first wanted byte, rounded down to a word
+      // the 16 wanted bytes start `mis` bytes into this thread's two aligned chunks.  Two 128-bit loads: a quarter
+      // warp reads one chunk of 8 consecutive rows, and with the 80-byte row pitch those sit in 8 different bank
+      // groups (5 r mod 8) -- conflict-free, where word loads at a 20-word pitch were 4-way conflicts and the shared
+      // memory data pipe is what bounds this kernel (profiles/r02_ncu_k_score_mma_*: LSU + tensor wavefronts = cycles)
+      const uint32_t src = pk_row + pst * (kSlabK * kPRow);
+      uint4 c0 = make_uint4(0u, 0u, 0u, 0u), c1 = c0;
+      if (in_row) {
+        c0 = lds128(src);
+        c1 = lds128(src + 16u);
+      }
       uint32_t w[5];
-#pragma unroll
-      for (int u = 0; u < 5; ++u) w[u] = in_row ? lds32(src + 4u * u) : 0u;
+      {
+        const bool q2 = (mis & 8u) != 0u, q1 = (mis & 4u) != 0u;
+        const uint32_t x0 = q2 ? c0.z : c0.x, x1 = q2 ? c0.w : c0.y, x2 = q2 ? c1.x : c0.z, x3 = q2 ? c1.y : c0.w,
+                       x4 = q2 ? c1.z : c1.x, x5 = q2 ? c1.w : c1.y;
+        w[0] = q1 ? x1 : x0;
+        w[1] = q1 ? x2 : x1;
+        w[2] = q1 ? x3 : x2;
+        w[3] = q1 ? x4 : x3;
+        w[4] = q1 ? x5 : x4;
+      }
       const uint32_t sh = (mis & 3u) * 8u;
 #pragma unroll
       for (int u = 0; u < 4; ++u) w[u] = __funnelshift_r(w[u], w[u + 1], sh);
