@@ -16,14 +16,23 @@
 // (bit-reproducible across sample tiles, k splits and launches); its error is the quantisation
 // max|x| 2^-55 per term, i.e. tighter than the fp64 FMA loop it replaces.
 //
-// GEMM shape per CTA:  D[128 x 256] (int32, 256 TMEM columns) += A[128 x 32] * B[32 x 256]  per slab
+// GEMM shape per CTA:  two accumulators D_h[128 x 256] (int32, all 512 TMEM columns) += A[128 x 32] * B_h[32 x 256]
 //   A (M side) = weight limbs: row r = column c * 7 + limb l, K-major, prepared once per batch in
 //                global memory in the canonical no-swizzle shared-memory order (one 4 KB bulk copy);
-//   B (N side) = 256 samples x 32 k-rows of unpacked genotypes, N-major (samples contiguous -- the
-//                order the .pgen record already has), written to shared memory by 128 unpack threads
+//   B (N side) = 2 x 256 samples x 32 k-rows of unpacked genotypes, N-major (samples contiguous -- the
+//                order the .pgen record already has), written to shared memory by 256 unpack threads
 //                from the packed 2-bit rows (PRMT table look-up on nibble-spread codes).
-// One tcgen05.mma (M=128, N=256, K=32, kind::i8) per slab, issued by one thread; stages are handed
-// over with mbarriers (producers -> MMA) and tcgen05.commit (MMA -> producers).
+// Two tcgen05.mma (M=128, N=256, K=32, kind::i8) per k-slab, issued by one thread; the second takes A from the
+// tensor core's collector buffer (collector::a::fill / lastuse).  Stages are handed over with mbarriers
+// (producers -> MMA) and tcgen05.commit (MMA -> producers).
+//
+// What bounds it is the shared-memory data pipe: one 128-byte wavefront per cycle shared by the LSU (st.shared of
+// the unpacked bytes, ld.shared / cp.async of the packed ones) and the tensor core's operand reads -- ncu: LSU +
+// tensor wavefronts = elapsed cycles.  Per MMA: 64 wavefronts of B written + 64 read are inherent to int8 operands
+// in shared memory; everything else is overhead this layout keeps small: the 512-sample tile halves the A reads
+// per MMA (32 -> 16) and the cache lines touched per staged byte (a row window is 144 B instead of 80 B: 2.1
+// instead of 1.6 lines per row, for twice the samples), and the converters read the staged rows with
+// conflict-free 128-bit loads.
 //
 // The unit of producer work is a STEP = 32 variants.  Variants with missing calls come first in the batch's
 // k-row list ("pair" steps): their packed bytes are fetched and aligned ONCE and unpacked twice, into the G slab
@@ -36,20 +45,26 @@ namespace pdk {
 
 namespace {
 
-constexpr uint32_t kTileN = 256;    // samples per CTA tile (MMA N)
+constexpr uint32_t kMmaN = 256;     // samples per MMA (N)
+constexpr uint32_t kHalves = 2;     // MMAs per k-slab: the CTA's tile is two N = 256 halves that share the A slab
+constexpr uint32_t kTileN = kMmaN * kHalves;  // samples per CTA tile
 constexpr uint32_t kSlabK = 32;     // k-rows per MMA (K of kind::i8)
 constexpr uint32_t kRowsM = 128;    // MMA M: weight-limb rows
 constexpr uint32_t kLimbs = 7;
-constexpr uint32_t kStages = 6;     // B slabs (8 KB each) between the unpackers and the MMA
+constexpr uint32_t kStages = 6;     // B stages (one k-slab of both halves, 16 KB each) between the unpackers and the MMA
 constexpr uint32_t kAStages = 2 * kStages;  // A slabs (4 KB bulk copies from L2): their latency under load is ~2 us, so they run further ahead than the B slabs
-constexpr uint32_t kBBytes = kTileN * kSlabK;  // 8 KB
+constexpr uint32_t kBHalfBytes = kMmaN * kSlabK;      // 8 KB
+constexpr uint32_t kBBytes = kHalves * kBHalfBytes;   // 16 KB
 constexpr uint32_t kABytes = kRowsM * kSlabK;  // 4 KB
-constexpr uint32_t kProducers = 128;  // threads that unpack one slab
-constexpr uint32_t kGroups = 2;       // producer groups; group g unpacks slabs g, g + kGroups, ... of the CTA
+constexpr uint32_t kProducers = 256;  // threads that unpack one step: 32 rows x 8 chunks of 64 samples
+constexpr uint32_t kGroups = 2;       // producer groups; group g unpacks steps g, g + kGroups, ... of the CTA
 constexpr uint32_t kProdWarps = kGroups * kProducers / 32;
 constexpr uint32_t kMmaThreads = kGroups * kProducers + 64 + 32 * kGroups;  // + MMA issue / TMEM warp, A-copy warp, one packed-row loader warp per group
-constexpr uint32_t kPStages = 6;    // steps of packed rows in flight between the loader warp and the converters
-constexpr uint32_t kPRow = 80;      // bytes staged per row and step: the 64 wanted ones at any 16-byte misalignment
+constexpr uint32_t kPStages = 6;    // steps of packed rows in flight between the loader warps and the converters
+constexpr uint32_t kRowWin = kTileN / 4;  // 128 wanted bytes of a row and step
+constexpr uint32_t kPRow = kRowWin + 16;  // staged per row: the wanted bytes at any 16-byte misalignment; 9 chunks -- an ODD
+                                          // count, so a quarter warp's 128-bit loads (8 rows, one chunk) never share a bank
+constexpr uint32_t kPChunks = kPRow / 16;
 constexpr uint32_t kPlaneM = 0x80000000u;
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -149,6 +164,30 @@ __device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t a_desc, uint64
       "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// The same with the A operand kept in the tensor core's collector buffer for the next MMA (fill) / taken from it
+// for the last time (lastuse): the two halves of a tile multiply the same A slab, so it leaves shared memory once.
+__device__ __forceinline__ void umma_i8_a_fill(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                               uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::i8.collector::a::fill [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_i8_a_lastuse(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                                  uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::i8.collector::a::lastuse [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // Arrives on the mbarrier once every tcgen05.mma issued so far by this thread has completed.
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
@@ -177,7 +216,7 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes,
 
 // Instruction descriptor (cute::UMMA::InstrDescriptor): c = S32 (2 << 4), a = b = signed int8
 // (1 << 7, 1 << 10), A K-major (bit 15 = 0), B MN-major (bit 16 = 1), N >> 3 at [17,23), M >> 4 at [24,29).
-constexpr uint32_t kIdesc = (2u << 4) | (1u << 7) | (1u << 10) | (1u << 16) | ((kTileN >> 3) << 17) | ((kRowsM >> 4) << 24);
+constexpr uint32_t kIdesc = (2u << 4) | (1u << 7) | (1u << 10) | (1u << 16) | ((kMmaN >> 3) << 17) | ((kRowsM >> 4) << 24);
 
 // Byte offset of element (row r, k) of an A slab: canonical K-major no-swizzle order -- core matrix =
 // 8 rows x 16 bytes of K (row stride 16 B); the two K halves 128 B apart (LBO), 8-row groups 256 B apart (SBO).
@@ -351,10 +390,10 @@ k_tc_quant(DenseRows rows, const ScoreRow* __restrict__ srow, const double* __re
 }
 
 // ---------------------------------------------------------------------------------------------
-// k_score_mma: grid = (sample tiles, k splits).  Warps 0-3 unpack, warp 4 issues the MMAs and owns
-// the TMEM allocation, warp 5 copies the A slabs; after the last slab warps 0-3 drain the
-// accumulators (TMEM lane = limb row, column = sample) into acc32[sample][row] with integer
-// reductions, which is what makes k splits order-independent.
+// k_score_mma: grid = (512-sample tiles, k splits), one CTA per SM.  Warps 0-15 unpack (two groups of 8 taking
+// alternate steps), warp 16 issues the MMAs and owns the TMEM allocation, warp 17 copies the A slabs, warps 18-19
+// stage the packed rows; after the last slab warps 0-15 drain the accumulators (TMEM lane = limb row, column =
+// sample) into acc32[sample][row] with integer reductions, which is what makes k splits order-independent.
 // ---------------------------------------------------------------------------------------------
 struct MmaSmem {
   alignas(128) uint8_t b[kStages][kBBytes];
@@ -441,7 +480,7 @@ __device__ __forceinline__ StepRange step_range(const uint32_t* __restrict__ met
   return r;
 }
 
-__global__ void __launch_bounds__(kMmaThreads, 2)
+__global__ void __launch_bounds__(kMmaThreads, 1)
 k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, const int8_t* __restrict__ a_tiles,
             const uint32_t* __restrict__ meta, uint32_t ksplit, int32_t* __restrict__ acc32, uint32_t n_samples,
             uint32_t acc_stride) {
@@ -480,19 +519,20 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
 
   if (warp < kProdWarps) {
     // ================= producers: packed 2-bit rows -> int8 B slabs =================
-    const uint32_t grp = warp >> 2, wq = warp & 3u;
-    const uint32_t kk = wq * 8 + (lane & 7u);     // variant within the step = k-row within its slab(s)
-    const uint32_t gq = lane >> 3;                // which 64 samples of the 256
+    const uint32_t grp = warp >> 3, wq = warp & 7u;
+    const uint32_t kk = (wq & 3u) * 8 + (lane & 7u);   // variant within the step = k-row within its slab(s)
+    const uint32_t ch = (wq >> 2) * 4 + (lane >> 3);   // which 64 samples of the 512: half = ch >> 2, quarter = ch & 3
     const uint32_t row_bytes = (n_raw + 3) >> 2;
-    const uint32_t off = tile * (kTileN / 4) + gq * 16;  // byte offset of this quarter inside a row
+    const uint32_t off = tile * kRowWin + ch * 16;     // byte offset of this chunk inside a row
     // The packed rows of a step arrive through the loader warp (cp.async into sm.pk, below): these warps never
     // have a global load in flight, so the proxy fence in front of every slab hand-over (a MEMBAR that waits for
     // all of the thread's outstanding memory operations) costs shared-memory latency, not HBM latency -- with the
     // loads prefetched by the unpacking threads themselves every fence waited for them and a step took ~2500
     // cycles (profiles/r02_ncu_k_score_mma_*).  Step i of group grp is the CTA's step j = grp + i * kGroups.
-    const uint32_t b_thread = smem_u32(sm.b[0]) + (kk & 7u) * 16u + (kk >> 3) * kBLbo + (gq * 4u) * kBSbo;
-    const bool in_row = off < row_bytes;  // quarters past the end of the row: zeros
-    const uint32_t pk_row = smem_u32(&sm.pk[0][kk][0]) + gq * 16u;
+    const uint32_t b_thread = smem_u32(sm.b[0]) + (ch >> 2) * kBHalfBytes + (kk & 7u) * 16u + (kk >> 3) * kBLbo +
+                              ((ch & 3u) * 4u) * kBSbo;
+    const bool in_row = off < row_bytes;  // chunks past the end of the row: zeros
+    const uint32_t pk_row = smem_u32(&sm.pk[0][kk][0]) + ch * 16u;
     const uint32_t pk_mis = smem_u32(&sm.pk_mis[0][kk]);
     const uint32_t p_full0 = smem_u32(&sm.p_full[0]), p_empty0 = smem_u32(&sm.p_empty[0]);
     const uint32_t full0 = smem_u32(&sm.full[0]), empty0 = smem_u32(&sm.empty[0]);
@@ -562,10 +602,14 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
     // ================= epilogue: TMEM -> acc32 =================
     mbar_wait(&sm.acc_ready, 0);
     tc_fence_after();
-    const uint32_t r = wq * 32 + lane;  // limb row = TMEM lane (a warp reaches lanes 32 * (warp % 4) ..)
-    for (uint32_t c0 = grp * 16; c0 < kTileN; c0 += 16 * kGroups) {
+    // 16 warps: TMEM lane quarter = warp % 4 (the only lanes a warp can reach), 128 of the 512 columns each
+    const uint32_t lq = warp & 3u;
+    const uint32_t r = lq * 32 + lane;  // limb row = TMEM lane
+    const uint32_t cbeg = (warp >> 2) * (kTileN / 4);
+    for (uint32_t c0 = cbeg; c0 < cbeg + kTileN / 4; c0 += 16) {
+      if (tile * kTileN + c0 >= n_samples) break;  // whole groups past the last sample (their half may never have been multiplied)
       uint32_t v[16];
-      tmem_ld16(tmem + ((wq * 32u) << 16) + c0, v);
+      tmem_ld16(tmem + ((lq * 32u) << 16) + c0, v);
 #pragma unroll
       for (int u = 0; u < 16; ++u) {
         const uint32_t s = tile * kTileN + c0 + group_perm(u);
@@ -582,6 +626,7 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
     // MMA, one commit.  (A leaner loop matters: with ~65 dependent instructions per slab in one thread the issuer,
     // not the tensor pipe, set the pace -- profiles/r02_ncu_k_score_mma_*.)
     const uint32_t nslabs = sr.slabs();
+    const bool two_halves = tile * kTileN + kMmaN < n_samples;  // a ragged last tile may end inside its first half
     const uint64_t a_desc0 = smem_desc(smem_u32(sm.a[0]), kALbo, kASbo);
     const uint64_t b_desc0 = smem_desc(smem_u32(sm.b[0]), kBLbo, kBSbo);
     const uint32_t full0 = smem_u32(&sm.full[0]), empty0 = smem_u32(&sm.empty[0]);
@@ -598,8 +643,15 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
           mbar_wait_addr(full0 + bst * 8u, bphase);
           tc_fence_after();
           if (elect_one()) {
-            umma_i8(tmem, a_desc0 + ((st * kABytes) >> 4), b_desc0 + ((bst * kBBytes) >> 4), kIdesc, base + st ? 1u : 0u);
-            umma_commit_addr(empty0 + bst * 8u);    // frees the stages once the MMA has read them
+            const uint64_t ad = a_desc0 + ((st * kABytes) >> 4), bd = b_desc0 + ((bst * kBBytes) >> 4);
+            const uint32_t accumulate = base + st ? 1u : 0u;
+            if (two_halves) {
+              umma_i8_a_fill(tmem, ad, bd, kIdesc, accumulate);
+              umma_i8_a_lastuse(tmem + kMmaN, ad, bd + (kBHalfBytes >> 4), kIdesc, accumulate);
+            } else {
+              umma_i8(tmem, ad, bd, kIdesc, accumulate);
+            }
+            umma_commit_addr(empty0 + bst * 8u);    // frees the stages once the MMAs have read them
             umma_commit_addr(a_empty0 + st * 8u);
           }
           __syncwarp();
@@ -612,18 +664,18 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
   } else if (warp >= kProdWarps + 2) {
     // ================= loaders: packed rows of every step, global -> shared with cp.async =================
     // One loader warp per converter group (steps j = g, g + kGroups, ...).  Lane l owns row l of the step (its
-    // pointer, its misalignment); the 32 x 5 aligned 16-byte chunks of a step are then copied by consecutive lanes
-    // (5 lanes per row: contiguous global reads).  Row pointers are requested two of the warp's steps ahead.
+    // pointer, its misalignment); the 32 x 9 aligned 16-byte chunks of a step are then copied by consecutive lanes
+    // (9 lanes per row: contiguous global reads).  Row pointers are requested two of the warp's steps ahead.
     const uint32_t g = warp - (kProdWarps + 2);
     const uint32_t row_bytes = (n_raw + 3) >> 2;
-    const uint32_t tile_off = tile * (kTileN / 4);
-    const uint32_t len = min(kTileN / 4, row_bytes - tile_off);  // wanted bytes of a row (the last tile is ragged)
-    uint32_t row_q[5], ch16_q[5], dst_q[5];
+    const uint32_t tile_off = tile * kRowWin;
+    const uint32_t len = min(kRowWin, row_bytes - tile_off);  // wanted bytes of a row (the last tile is ragged)
+    uint32_t row_q[kPChunks], ch16_q[kPChunks], dst_q[kPChunks];
 #pragma unroll
-    for (uint32_t q = 0; q < 5; ++q) {
+    for (uint32_t q = 0; q < kPChunks; ++q) {
       const uint32_t idx = q * 32u + lane;
-      row_q[q] = idx / 5u;
-      ch16_q[q] = (idx - row_q[q] * 5u) * 16u;
+      row_q[q] = idx / kPChunks;
+      ch16_q[q] = (idx - row_q[q] * kPChunks) * 16u;
       dst_q[q] = smem_u32(&sm.pk[0][row_q[q]][0]) + ch16_q[q];
     }
     auto ptr_of = [&](uint32_t j) { return j < nsteps ? __ldg(krow_ptr + sr.slot0(j) + lane) : 0ull; };
@@ -643,7 +695,7 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
       __syncwarp();
       const uint32_t pk_off = pst * (kSlabK * kPRow);
 #pragma unroll
-      for (uint32_t q = 0; q < 5; ++q) {
+      for (uint32_t q = 0; q < kPChunks; ++q) {
         const unsigned long long rb = __shfl_sync(0xffffffffu, base, row_q[q]);
         const uint32_t rmis = __shfl_sync(0xffffffffu, mis, row_q[q]);
         const uint32_t nb = ch16_q[q] < rmis + len ? 16u : 0u;  // chunks past the wanted bytes: zero-filled, not read
@@ -784,9 +836,9 @@ void launch_score_tc(const DenseRows& rows, const uint4* counts, const ScoreRow*
                                                                           w.krow_ptr);
   const uint32_t tiles = (n_samples + kTileN - 1) / kTileN;
   const int sms = sm_of(st);
-  // k splits: the smallest count that fills whole waves of 2 CTAs per SM to >= 90 % (each split pays one
+  // k splits: the smallest count that fills whole waves of one CTA per SM to >= 90 % (each split pays one
   // accumulator drain per tile), keeping at least 32 slabs per CTA.
-  const uint32_t slots = static_cast<uint32_t>(sms) * 2;
+  const uint32_t slots = static_cast<uint32_t>(sms);
   const uint32_t max_split = nk_batch / kSlabK / 32u > 1u ? nk_batch / kSlabK / 32u : 1u;
   uint32_t ksplit = 1;
   double best = 0.0;
