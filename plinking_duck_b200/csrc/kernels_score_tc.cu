@@ -38,6 +38,8 @@
 // k-row list ("pair" steps): their packed bytes are fetched and aligned ONCE and unpacked twice, into the G slab
 // and the M slab of the same 32 variants (two MMAs per step); variants without missing calls follow ("single"
 // steps, G slab only).  The order of k-rows inside a batch is free: the int32 sums are exact.
+#include <algorithm>
+
 #include "device_common.cuh"
 #include "kernels.cuh"
 
@@ -229,7 +231,7 @@ constexpr uint32_t kALbo = 128, kASbo = 256;
 constexpr uint32_t kBSbo = 128, kBLbo = 2048;
 
 // ---------------------------------------------------------------------------------------------
-// k_tc_plan: K + 3 CTAs per batch (one per column, one for the k-row list).  Lists the k-rows (a G row per active variant, an M row when it
+// k_tc_plan: (K + 2) x 32 + 1 CTAs per batch (32 row parts per column, one CTA for the k-row list).  Lists the k-rows (a G row per active variant, an M row when it
 // has missing calls), and per column the fixed-point scale (a power of two >= max|x| 2^-54, so
 // x / scale is exact up to the final rint) and the constant term sum_v w T0 (fixed reduction order).
 // Columns: c < K score columns, c = K the dosage-sum column (weight 1), c = K + 1 counts the
@@ -245,78 +247,136 @@ __device__ __forceinline__ double col_weight(const double* __restrict__ weights,
   return 0.0;
 }
 
+// Exclusive prefix sum of one value per thread over the block's 1024 threads (s_warp: 33 words); total = the sum.
+__device__ __forceinline__ uint32_t plan_block_scan(uint32_t v, uint32_t* s_warp, uint32_t& total) {
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+  uint32_t inc = v;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const uint32_t n = __shfl_up_sync(0xffffffffu, inc, off);
+    if (lane >= static_cast<uint32_t>(off)) inc += n;
+  }
+  if (lane == 31) s_warp[wid] = inc;
+  __syncthreads();
+  if (wid == 0) {
+    const uint32_t x = s_warp[lane];
+    uint32_t xi = x;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const uint32_t n = __shfl_up_sync(0xffffffffu, xi, off);
+      if (lane >= static_cast<uint32_t>(off)) xi += n;
+    }
+    s_warp[lane] = xi - x;
+    if (lane == 31) s_warp[32] = xi;
+  }
+  __syncthreads();
+  total = s_warp[32];
+  const uint32_t r = s_warp[wid] + inc - v;
+  __syncthreads();
+  return r;
+}
+
+constexpr uint32_t kPlanParts = 32;   // row parts per column in k_tc_plan
+constexpr uint32_t kPlanChunks = 64;  // 1024-row chunks of a batch (<= 65 535 rows)
+
 __global__ void __launch_bounds__(kPlanThreads)
 k_tc_plan(const uint4* __restrict__ counts, const ScoreRow* __restrict__ srow, const double* __restrict__ weights,
           uint32_t nrows, uint32_t K, uint32_t mode, uint32_t* __restrict__ krow, double* __restrict__ col_scale,
-          double* __restrict__ col_const, uint32_t* __restrict__ meta) {
-  __shared__ uint32_t s_scan[kPlanThreads];
+          double* __restrict__ col_const, uint32_t* __restrict__ meta, double* __restrict__ part, uint32_t* __restrict__ part_ctr) {
+  __shared__ uint32_t s_scan[40];
   __shared__ double s_red[kPlanThreads];
+  __shared__ uint32_t s_cnt[2][kPlanChunks * 32];  // [list][chunk * 32 + warp]: entries of the warp in the chunk, then their offsets
   const uint32_t t = threadIdx.x;
   const uint32_t ncols = K + 2;
-  if (blockIdx.x == ncols) {
-    // ---- block K+2: the k-row list: active variants with missing calls (pair steps), then those without ----
-    uint32_t region_base = 0, n_real[2] = {0, 0}, n_steps[2] = {0, 0};
-    uint32_t nact_total = 0;
+  if (blockIdx.x == ncols * kPlanParts) {
+    // ---- last block: the k-row list: active variants with missing calls (pair steps), then those without, each
+    // in row order.  Chunk i = rows [1024 i, 1024 i + 1024); every load is issued before the first barrier, the
+    // offsets come from ONE scan over the (chunk, warp) counts. ----
     const uint32_t lane = t & 31u, wid = t >> 5;
-    uint32_t* warp_tot = s_scan;  // [32] per-warp totals of the current chunk
-    // which of this thread's rows (t, t + 1024, ...; at most 64 for a batch of 65 535) go to which list: all
-    // loads are issued before the first barrier
-    unsigned long long want[2] = {0ull, 0ull};
-    for (uint32_t r0 = 0, i = 0; r0 < nrows; r0 += kPlanThreads, ++i) {
-      const uint32_t r = r0 + t;
-      if (r < nrows && (srow[r].flags & kScoreActive)) want[counts[r].w != 0 ? 0 : 1] |= 1ull << i;
-    }
-    for (uint32_t pass = 0; pass < 2; ++pass) {
-      uint32_t base = 0;  // entries of this pass so far (same value in every thread)
-      for (uint32_t r0 = 0, i = 0; r0 < nrows; r0 += kPlanThreads, ++i) {
-        const uint32_t r = r0 + t;
-        const bool take = (want[pass] >> i) & 1ull;
-        const uint32_t bal = __ballot_sync(0xffffffffu, take);
-        if (lane == 0) warp_tot[wid] = __popc(bal);
-        __syncthreads();
-        uint32_t before = 0, total = 0;
-#pragma unroll 4
-        for (uint32_t w = 0; w < kPlanThreads / 32; ++w) {
-          const uint32_t c = warp_tot[w];
-          before += w < wid ? c : 0u;
-          total += c;
+    unsigned long long want0 = 0ull, want1 = 0ull;  // rows of this thread for the pair list / the single list
+#pragma unroll 8
+    for (uint32_t i = 0; i < kPlanChunks; ++i) {
+      const uint32_t r = i * kPlanThreads + t;
+      if (r < nrows) {
+        const uint32_t fl = srow[r].flags, mis = counts[r].w;
+        if (fl & kScoreActive) {
+          if (mis != 0) {
+            want0 |= 1ull << i;
+          } else {
+            want1 |= 1ull << i;
+          }
         }
-        if (take) krow[region_base + base + before + __popc(bal & ((1u << lane) - 1u))] = r;
-        base += total;
-        __syncthreads();
       }
-      const uint32_t n = base;
-      const uint32_t n_pad = (n + kSlabK - 1) / kSlabK * kSlabK;
-      for (uint32_t i = n + t; i < n_pad; i += kPlanThreads) krow[region_base + i] = 0;  // zero weights; any valid row will do
-      n_real[pass] = n;
+    }
+    for (uint32_t i = 0; i < kPlanChunks; ++i) {
+#pragma unroll
+      for (uint32_t pass = 0; pass < 2; ++pass) {
+        const uint32_t bal = __ballot_sync(0xffffffffu, ((pass ? want1 : want0) >> i) & 1ull);
+        if (lane == 0) s_cnt[pass][i * 32 + wid] = __popc(bal);
+      }
+    }
+    __syncthreads();
+    uint32_t n_real[2], n_steps[2], region[2];
+    uint32_t region_base = 0;
+#pragma unroll
+    for (uint32_t pass = 0; pass < 2; ++pass) {
+      const uint32_t a = s_cnt[pass][2 * t], b = s_cnt[pass][2 * t + 1];
+      uint32_t total;
+      const uint32_t ex = plan_block_scan(a + b, s_scan, total);
+      s_cnt[pass][2 * t] = ex;
+      s_cnt[pass][2 * t + 1] = ex + a;
+      const uint32_t n_pad = (total + kSlabK - 1) / kSlabK * kSlabK;
+      for (uint32_t i = total + t; i < n_pad; i += kPlanThreads) krow[region_base + i] = 0;  // zero weights; any valid row will do
+      n_real[pass] = total;
       n_steps[pass] = n_pad / kSlabK;
-      nact_total += n;
+      region[pass] = region_base;
       region_base += n_pad;
     }
+    __syncthreads();
+    for (uint32_t i = 0; i < kPlanChunks; ++i) {
+#pragma unroll
+      for (uint32_t pass = 0; pass < 2; ++pass) {
+        const bool take = ((pass ? want1 : want0) >> i) & 1ull;
+        const uint32_t bal = __ballot_sync(0xffffffffu, take);
+        if (take) krow[region[pass] + s_cnt[pass][i * 32 + wid] + __popc(bal & ((1u << lane) - 1u))] = i * kPlanThreads + t;
+      }
+    }
     if (t == 0) {
-      meta[0] = n_steps[0];   // pair steps (two slabs each)
-      meta[1] = nact_total;   // active variants
-      meta[2] = n_steps[1];   // single steps
+      meta[0] = n_steps[0];            // pair steps (two slabs each)
+      meta[1] = n_real[0] + n_real[1]; // active variants
+      meta[2] = n_steps[1];            // single steps
       meta[3] = n_real[0];
       meta[4] = n_real[1];
     }
     return;
   }
-  // ---- block c: max |x| over both planes of column c, and its constant term ----
-  const uint32_t c = blockIdx.x;
+  // ---- block (c, part): max |x| over both planes of column c and its constant term over one part of the rows;
+  // the last block of a column to finish combines the parts in index order (a fixed reduction order whatever the
+  // block schedule).  One block per column walked 64 rows per thread at one L2 round trip each: 190 us. ----
+  const uint32_t c = blockIdx.x / kPlanParts, pt = blockIdx.x % kPlanParts;
+  const uint32_t per = (nrows + kPlanParts - 1) / kPlanParts;
+  const uint32_t r_end = min(nrows, (pt + 1) * per);
   double mx = 0.0, cs = 0.0;
-  for (uint32_t r = t; r < nrows; r += kPlanThreads) {
-    const ScoreRow& R = srow[r];
-    if (!(R.flags & kScoreActive)) continue;
-    if (c == K + 1) {
-      if (mode != 0) mx = 1.0;
-      continue;
+  if (c == K + 1) {
+    if (mode != 0) {
+      for (uint32_t r = pt * per + t; r < r_end; r += kPlanThreads) {
+        if (srow[r].flags & kScoreActive) mx = 1.0;
+      }
     }
-    const double w = col_weight(weights, K, mode, r, c);
-    const double xg = w * (0.5 * (R.T[2] - R.T[0]));
-    const double xm = w * (R.T[3] - R.T[0]);
-    mx = fmax(mx, fmax(fabs(xg), fabs(xm)));
-    cs += w * R.T[0];
+  } else {
+#pragma unroll 2
+    for (uint32_t r = pt * per + t; r < r_end; r += kPlanThreads) {
+      const ScoreRow& R = srow[r];
+      const uint32_t fl = R.flags;
+      const double t0 = R.T[0], t2 = R.T[2], t3 = R.T[3];
+      const double w = col_weight(weights, K, mode, r, c);
+      const double xg = w * (0.5 * (t2 - t0));
+      const double xm = w * (t3 - t0);
+      if (fl & kScoreActive) {
+        mx = fmax(mx, fmax(fabs(xg), fabs(xm)));
+        cs += w * t0;
+      }
+    }
   }
   s_red[t] = mx;
   __syncthreads();
@@ -324,7 +384,7 @@ k_tc_plan(const uint4* __restrict__ counts, const ScoreRow* __restrict__ srow, c
     if (t < off) s_red[t] = fmax(s_red[t], s_red[t + off]);
     __syncthreads();
   }
-  const double colmax = s_red[0];
+  const double partmax = s_red[0];
   __syncthreads();
   s_red[t] = cs;
   __syncthreads();
@@ -333,14 +393,27 @@ k_tc_plan(const uint4* __restrict__ counts, const ScoreRow* __restrict__ srow, c
     __syncthreads();
   }
   if (t == 0) {
-    int e = 0;
-    double scale = 1.0;
-    if (c <= K && colmax > 0.0) {
-      frexp(colmax, &e);          // colmax < 2^e
-      scale = ldexp(1.0, e - 54);  // |x / scale| < 2^54
+    double* pm = part + static_cast<size_t>(c) * 2 * kPlanParts;  // [max x kPlanParts][sum x kPlanParts]
+    pm[pt] = partmax;
+    pm[kPlanParts + pt] = s_red[0];
+    __threadfence();
+    if (atomicAdd(part_ctr + c, 1u) == kPlanParts - 1) {
+      __threadfence();
+      double colmax = 0.0, sum = 0.0;
+      for (uint32_t i = 0; i < kPlanParts; ++i) {
+        colmax = fmax(colmax, __ldcg(pm + i));
+        sum += __ldcg(pm + kPlanParts + i);
+      }
+      int e = 0;
+      double scale = 1.0;
+      if (c <= K && colmax > 0.0) {
+        frexp(colmax, &e);          // colmax < 2^e
+        scale = ldexp(1.0, e - 54);  // |x / scale| < 2^54
+      }
+      col_scale[c] = scale;
+      col_const[c] = sum;
+      part_ctr[c] = 0;  // ready for the next batch
     }
-    col_scale[c] = scale;
-    col_const[c] = s_red[0];
   }
 }
 
@@ -663,6 +736,8 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
     __syncwarp();
   } else if (warp >= kProdWarps + 2) {
     // ================= loaders: packed rows of every step, global -> shared with cp.async =================
+    // (Loading through registers instead -- 9 x LDG.128 per lane, then 128-bit st.shared, six loader warps -- was
+    // measured 4 % slower: the LDG return path costs the same pipe more than LDGSTS's sector-wise writes save.)
     // One loader warp per converter group (steps j = g, g + kGroups, ...).  Lane l owns row l of the step (its
     // pointer, its misalignment); the 32 x 9 aligned 16-byte chunks of a step are then copied by consecutive lanes
     // (9 lanes per row: contiguous global reads).  Row pointers are requested two of the warp's steps ahead.
@@ -736,7 +811,7 @@ k_score_mma(const unsigned long long* __restrict__ krow_ptr, uint32_t n_raw, con
 }
 
 // ---------------------------------------------------------------------------------------------
-// k_tc_finish: thread per (sample, column).  Recombines the seven limb sums exactly
+// k_tc_finish: warp per sample, lane per column.  Recombines the seven limb sums exactly
 // (value = hi * 2^24 + lo with |hi|, |lo| < 2^53), applies the column scale, adds the constant
 // term, accumulates into the fp64 results and clears acc32 for the next batch.
 // ---------------------------------------------------------------------------------------------
@@ -744,30 +819,49 @@ __global__ void __launch_bounds__(256)
 k_tc_finish(int32_t* __restrict__ acc32, const double* __restrict__ col_scale, const double* __restrict__ col_const,
             const uint32_t* __restrict__ meta, uint32_t n_samples, uint32_t K, uint32_t mode, double* __restrict__ score,
             double* __restrict__ dosage_sums, uint32_t* __restrict__ allele_cts) {
-  const uint32_t ncols = K + 2;
-  const uint64_t tid = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const uint32_t s = static_cast<uint32_t>(tid / ncols);
-  const uint32_t c = static_cast<uint32_t>(tid % ncols);
-  if (s >= n_samples) return;
-  int32_t* a = acc32 + static_cast<uint64_t>(s) * kRowsM + c * kLimbs;
-  long long limb[kLimbs];
+  // A warp per sample, walking the samples with the grid's stride (a few resident blocks per SM): its 128 limb sums
+  // are one 512-byte row -- a 128-bit load and a 128-bit clearing store per lane; the row is turned through shared
+  // memory so that lane c gets the 7 limbs of column c (word pitch 7: no bank conflicts).  The old outputs are
+  // requested BEFORE the clearing store: with the store directly behind the row load, and one short-lived block per
+  // 8 samples, the same pass took 80-210 us instead of 20 (scripts/finish_probe.cu, profiles/r02_finish_probe.json).
+  __shared__ __align__(16) int32_t s_row[8][kRowsM];
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+  const uint32_t nwarps = gridDim.x * 8u;
+  const uint32_t c = lane;
+  const uint32_t n_active = meta[1];
+  const double scale = c <= K ? col_scale[c] : 0.0, cst = c <= K ? col_const[c] : 0.0;
+  for (uint32_t s = blockIdx.x * 8u + wid; s < n_samples; s += nwarps) {
+    int4* row = reinterpret_cast<int4*>(acc32 + static_cast<uint64_t>(s) * kRowsM);
+    const int4 v = row[lane];
+    double old = 0.0;
+    uint32_t old_ct = 0;
+    if (c < K) {
+      old = score[static_cast<uint64_t>(s) * K + c];
+    } else if (c == K) {
+      if (mode != 2) old = dosage_sums[s];
+    } else if (c == K + 1) {
+      old_ct = allele_cts[s];
+    }
+    row[lane] = make_int4(0, 0, 0, 0);
+    __syncwarp();  // the previous sample's limbs have been read
+    reinterpret_cast<int4*>(s_row[wid])[lane] = v;
+    __syncwarp();
+    if (c >= K + 2) continue;
+    long long limb[kLimbs];
 #pragma unroll
-  for (uint32_t l = 0; l < kLimbs; ++l) {
-    limb[l] = a[l];
-    a[l] = 0;
-  }
-  if (c == K + 1) {
-    const uint32_t n_active = meta[1];
-    if (n_active) allele_cts[s] += 2u * (n_active - static_cast<uint32_t>(limb[0]));
-    return;
-  }
-  const long long lo = limb[0] + (limb[1] << 8) + (limb[2] << 16);
-  const long long hi = limb[3] + (limb[4] << 8) + (limb[5] << 16) + (limb[6] << 24);
-  const double val = fma(static_cast<double>(hi), 16777216.0, static_cast<double>(lo)) * col_scale[c] + col_const[c];
-  if (c < K) {
-    score[static_cast<uint64_t>(s) * K + c] += val;
-  } else if (mode != 2) {
-    dosage_sums[s] += val;
+    for (uint32_t l = 0; l < kLimbs; ++l) limb[l] = s_row[wid][c * kLimbs + l];
+    if (c == K + 1) {
+      if (n_active) allele_cts[s] = old_ct + 2u * (n_active - static_cast<uint32_t>(limb[0]));
+      continue;
+    }
+    const long long lo = limb[0] + (limb[1] << 8) + (limb[2] << 16);
+    const long long hi = limb[3] + (limb[4] << 8) + (limb[5] << 16) + (limb[6] << 24);
+    const double val = fma(static_cast<double>(hi), 16777216.0, static_cast<double>(lo)) * scale + cst;
+    if (c < K) {
+      score[static_cast<uint64_t>(s) * K + c] = old + val;
+    } else if (mode != 2) {
+      dosage_sums[s] = old + val;
+    }
   }
 }
 
@@ -781,6 +875,8 @@ struct TcWorkspace {
   double* col_scale;
   double* col_const;
   uint32_t* meta;
+  double* plan_part;     // [kMaxCols][2][kPlanParts] partial column maxima / constant terms
+  uint32_t* plan_ctr;    // [kMaxCols] finished parts per column (zero between launches)
   int32_t* acc32;
   uint32_t acc_stride;  // samples per limb row of acc32, padded
   size_t bytes;
@@ -806,6 +902,8 @@ TcWorkspace carve(void* base, uint32_t max_rows, uint32_t n_samples) {
   w.col_scale = reinterpret_cast<double*>(take(kMaxCols * 8));
   w.col_const = reinterpret_cast<double*>(take(kMaxCols * 8));
   w.meta = reinterpret_cast<uint32_t*>(take(32));
+  w.plan_part = reinterpret_cast<double*>(take(static_cast<size_t>(kMaxCols) * 2 * kPlanParts * 8));
+  w.plan_ctr = reinterpret_cast<uint32_t*>(take(kMaxCols * 4));
   w.acc_stride = (n_samples + 63u) & ~63u;
   w.acc32 = reinterpret_cast<int32_t*>(take(static_cast<size_t>(w.acc_stride) * kRowsM * 4));
   w.bytes = off;
@@ -824,12 +922,15 @@ void launch_score_tc(const DenseRows& rows, const uint4* counts, const ScoreRow*
                      double* score, double* dosage_sums, uint32_t* allele_cts, cudaStream_t s, LaunchStats* st) {
   if (!rows.nrows || !n_samples) return;
   const TcWorkspace w = carve(workspace, max_rows, n_samples);
-  if (first_batch) cudaMemsetAsync(w.acc32, 0, static_cast<size_t>(w.acc_stride) * kRowsM * 4, s);
+  if (first_batch) {
+    cudaMemsetAsync(w.acc32, 0, static_cast<size_t>(w.acc_stride) * kRowsM * 4, s);
+    cudaMemsetAsync(w.plan_ctr, 0, kMaxCols * 4, s);
+  }
   const uint32_t slot_cap = static_cast<uint32_t>(slot_cap_of(rows.nrows));
   const uint32_t nk_batch = 2u * slot_cap;  // upper bound of the batch's k-rows (every variant a pair)
   cudaMemsetAsync(w.a_tiles, 0, slab_cap_of(rows.nrows) * kABytes, s);
-  k_tc_plan<<<K + 3, kPlanThreads, 0, s>>>(counts, srow, weights, rows.nrows, K, mode, w.krow, w.col_scale, w.col_const,
-                                       w.meta);
+  k_tc_plan<<<(K + 2) * kPlanParts + 1, kPlanThreads, 0, s>>>(counts, srow, weights, rows.nrows, K, mode, w.krow,
+                                                          w.col_scale, w.col_const, w.meta, w.plan_part, w.plan_ctr);
   const uint64_t qthreads = static_cast<uint64_t>(slot_cap) * (K + 2);
   k_tc_quant<<<static_cast<unsigned>((qthreads + 255) / 256), 256, 0, s>>>(rows, srow, weights, K, mode, w.krow,
                                                                           w.col_scale, w.meta, slot_cap, w.a_tiles,
@@ -854,8 +955,7 @@ void launch_score_tc(const DenseRows& rows, const uint4* counts, const ScoreRow*
   }
   k_score_mma<<<dim3(tiles, ksplit), kMmaThreads, sizeof(MmaSmem) + 128, s>>>(w.krow_ptr, rows.N, w.a_tiles, w.meta,
                                                                             ksplit, w.acc32, n_samples, w.acc_stride);
-  const uint64_t fthreads = static_cast<uint64_t>(n_samples) * (K + 2);
-  k_tc_finish<<<static_cast<unsigned>((fthreads + 255) / 256), 256, 0, s>>>(w.acc32, w.col_scale, w.col_const, w.meta,
+  k_tc_finish<<<std::min<uint32_t>((n_samples + 7) / 8, static_cast<uint32_t>(sms) * 8u), 256, 0, s>>>(w.acc32, w.col_scale, w.col_const, w.meta,
                                                                            n_samples, K, mode, score, dosage_sums,
                                                                            allele_cts);
   if (st) st->launches += 4;
