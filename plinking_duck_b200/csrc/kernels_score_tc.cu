@@ -294,16 +294,23 @@ k_tc_plan(const uint4* __restrict__ counts, const ScoreRow* __restrict__ srow, c
     // offsets come from ONE scan over the (chunk, warp) counts. ----
     const uint32_t lane = t & 31u, wid = t >> 5;
     unsigned long long want0 = 0ull, want1 = 0ull;  // rows of this thread for the pair list / the single list
-#pragma unroll 8
-    for (uint32_t i = 0; i < kPlanChunks; ++i) {
-      const uint32_t r = i * kPlanThreads + t;
-      if (r < nrows) {
-        const uint32_t fl = srow[r].flags, mis = counts[r].w;
-        if (fl & kScoreActive) {
-          if (mis != 0) {
-            want0 |= 1ull << i;
+    for (uint32_t i0 = 0; i0 < kPlanChunks && i0 * kPlanThreads < nrows; i0 += 8) {
+      // eight rows' loads in flight together (clamped, unconditional: behind a bounds branch they serialise)
+      uint32_t fl[8], mis[8];
+#pragma unroll
+      for (uint32_t k = 0; k < 8; ++k) {
+        const uint32_t r = min((i0 + k) * kPlanThreads + t, nrows - 1u);
+        fl[k] = srow[r].flags;
+        mis[k] = counts[r].w;
+      }
+#pragma unroll
+      for (uint32_t k = 0; k < 8; ++k) {
+        const uint32_t r = (i0 + k) * kPlanThreads + t;
+        if (r < nrows && (fl[k] & kScoreActive)) {
+          if (mis[k] != 0) {
+            want0 |= 1ull << (i0 + k);
           } else {
-            want1 |= 1ull << i;
+            want1 |= 1ull << (i0 + k);
           }
         }
       }
@@ -418,48 +425,61 @@ k_tc_plan(const uint4* __restrict__ counts, const ScoreRow* __restrict__ srow, c
 }
 
 // ---------------------------------------------------------------------------------------------
-// k_tc_quant: thread per (k-row, column): fixed-point value -> 7 signed int8 limbs, written straight
-// into the shared-memory order of the A slabs (a_offset).  Slabs are zeroed beforehand.
+// k_tc_quant: CTA per step, thread per (k-row, column): fixed-point value -> 7 signed int8 limbs, assembled in
+// the shared-memory order of the A slabs (a_offset) and stored as whole slabs.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 k_tc_quant(DenseRows rows, const ScoreRow* __restrict__ srow, const double* __restrict__ weights, uint32_t K,
            uint32_t mode, const uint32_t* __restrict__ krow, const double* __restrict__ col_scale,
-           const uint32_t* __restrict__ meta, uint32_t slot_cap, int8_t* __restrict__ a_tiles,
-           unsigned long long* __restrict__ krow_ptr) {
+           const uint32_t* __restrict__ meta, int8_t* __restrict__ a_tiles, unsigned long long* __restrict__ krow_ptr) {
+  // one CTA per step: its one (single step) or two (pair step: G plane, M plane) slabs are built in shared memory
+  // -- padding slots and unused limb rows stay zero -- and leave as whole 4 KB images
+  __shared__ __align__(16) int8_t s_slab[2][kABytes];
   const uint32_t ncols = K + 2;
-  const uint64_t tid = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const uint32_t i = static_cast<uint32_t>(tid / ncols);  // slot in the k-row list
-  const uint32_t c = static_cast<uint32_t>(tid % ncols);
-  const uint32_t pair_slots = meta[0] * kSlabK, single_slots = meta[2] * kSlabK;
-  if (i >= slot_cap || i >= pair_slots + single_slots) return;
-  const uint32_t r = krow[i];
-  if (c == 0) {  // where the variant's packed genotypes start
+  const uint32_t t = threadIdx.x;
+  const uint32_t P = meta[0], S = meta[2];
+  const uint32_t st = blockIdx.x;
+  if (st >= P + S) return;
+  const bool pair = st < P;
+  const uint32_t planes = pair ? 2u : 1u;
+  const uint32_t slot0 = st * kSlabK;                                  // first slot of the step in the k-row list
+  const uint32_t j0 = (pair ? st : st - P) * kSlabK;                   // ... inside its region
+  const uint32_t n_real = pair ? meta[3] : meta[4];
+  const uint32_t slab_g = pair ? 2u * st : 2u * P + (st - P);
+  for (uint32_t i = t; i < planes * kABytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(&s_slab[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
+  if (t < kSlabK) {  // where the variant's packed genotypes start
+    const uint32_t r = krow[slot0 + t];
     const uint8_t* row = rows.ptrs ? rows.ptrs[r] : rows.base + static_cast<uint64_t>(r) * rows.stride;
-    krow_ptr[i] = reinterpret_cast<unsigned long long>(row);
+    krow_ptr[slot0 + t] = reinterpret_cast<unsigned long long>(row);
   }
-  const bool pair = i < pair_slots;
-  const uint32_t j = pair ? i : i - pair_slots;                 // slot inside its region
-  if (j >= (pair ? meta[3] : meta[4])) return;                  // padding slots keep their zero limbs
-  const uint32_t slab_g = pair ? 2u * (j / kSlabK) : 2u * meta[0] + j / kSlabK;
-  const uint32_t k = j % kSlabK;
-  const ScoreRow& R = srow[r];
-  for (uint32_t plane = 0; plane < (pair ? 2u : 1u); ++plane) {
-    long long q;
-    if (c == K + 1) {
-      q = (plane && mode != 0) ? 1 : 0;
-    } else {
-      const double w = col_weight(weights, K, mode, r, c);
-      const double x = plane ? w * (R.T[3] - R.T[0]) : w * (0.5 * (R.T[2] - R.T[0]));
-      q = __double2ll_rn(x / col_scale[c]);  // scale is a power of two: the division is exact
-    }
-    int8_t* slab = a_tiles + static_cast<uint64_t>(slab_g + plane) * kABytes;
+  __syncthreads();
+  for (uint32_t item = t; item < kSlabK * ncols; item += blockDim.x) {
+    const uint32_t k = item / ncols, c = item - k * ncols;
+    if (j0 + k >= n_real) continue;  // padding slots keep their zero limbs
+    const uint32_t r = krow[slot0 + k];
+    const ScoreRow& R = srow[r];
+    const double t0 = R.T[0], t2 = R.T[2], t3 = R.T[3];
+    const double w = c <= K ? col_weight(weights, K, mode, r, c) : 0.0;
+    const double scale = c <= K ? col_scale[c] : 1.0;
+    for (uint32_t plane = 0; plane < planes; ++plane) {
+      long long q;
+      if (c == K + 1) {
+        q = (plane && mode != 0) ? 1 : 0;
+      } else {
+        const double x = plane ? w * (t3 - t0) : w * (0.5 * (t2 - t0));
+        q = __double2ll_rn(x / scale);  // scale is a power of two: the division is exact
+      }
 #pragma unroll
-    for (uint32_t l = 0; l < kLimbs; ++l) {
-      const long long b = static_cast<long long>(static_cast<int8_t>(q & 0xff));
-      slab[a_offset(c * kLimbs + l, k)] = static_cast<int8_t>(b);
-      q = (q - b) >> 8;
+      for (uint32_t l = 0; l < kLimbs; ++l) {
+        const long long b = static_cast<long long>(static_cast<int8_t>(q & 0xff));
+        s_slab[plane][a_offset(c * kLimbs + l, k)] = static_cast<int8_t>(b);
+        q = (q - b) >> 8;
+      }
     }
   }
+  __syncthreads();
+  uint4* dst = reinterpret_cast<uint4*>(a_tiles + static_cast<uint64_t>(slab_g) * kABytes);
+  for (uint32_t i = t; i < planes * kABytes / 16; i += blockDim.x) dst[i] = reinterpret_cast<const uint4*>(&s_slab[0][0])[i];
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -928,13 +948,10 @@ void launch_score_tc(const DenseRows& rows, const uint4* counts, const ScoreRow*
   }
   const uint32_t slot_cap = static_cast<uint32_t>(slot_cap_of(rows.nrows));
   const uint32_t nk_batch = 2u * slot_cap;  // upper bound of the batch's k-rows (every variant a pair)
-  cudaMemsetAsync(w.a_tiles, 0, slab_cap_of(rows.nrows) * kABytes, s);
   k_tc_plan<<<(K + 2) * kPlanParts + 1, kPlanThreads, 0, s>>>(counts, srow, weights, rows.nrows, K, mode, w.krow,
                                                           w.col_scale, w.col_const, w.meta, w.plan_part, w.plan_ctr);
-  const uint64_t qthreads = static_cast<uint64_t>(slot_cap) * (K + 2);
-  k_tc_quant<<<static_cast<unsigned>((qthreads + 255) / 256), 256, 0, s>>>(rows, srow, weights, K, mode, w.krow,
-                                                                          w.col_scale, w.meta, slot_cap, w.a_tiles,
-                                                                          w.krow_ptr);
+  k_tc_quant<<<slot_cap / kSlabK, 256, 0, s>>>(rows, srow, weights, K, mode, w.krow, w.col_scale, w.meta, w.a_tiles,
+                                               w.krow_ptr);
   const uint32_t tiles = (n_samples + kTileN - 1) / kTileN;
   const int sms = sm_of(st);
   // k splits: the smallest count that fills whole waves of one CTA per SM to >= 90 % (each split pays one
