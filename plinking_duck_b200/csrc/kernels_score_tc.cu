@@ -284,7 +284,7 @@ k_tc_plan(const uint4* __restrict__ counts, const ScoreRow* __restrict__ srow, c
           uint32_t nrows, uint32_t K, uint32_t mode, uint32_t* __restrict__ krow, double* __restrict__ col_scale,
           double* __restrict__ col_const, uint32_t* __restrict__ meta, double* __restrict__ part, uint32_t* __restrict__ part_ctr) {
   __shared__ uint32_t s_scan[40];
-  __shared__ double s_red[kPlanThreads];
+  __shared__ double s_red[64];
   __shared__ uint32_t s_cnt[2][kPlanChunks * 32];  // [list][chunk * 32 + warp]: entries of the warp in the chunk, then their offsets
   const uint32_t t = threadIdx.x;
   const uint32_t ncols = K + 2;
@@ -385,24 +385,28 @@ k_tc_plan(const uint4* __restrict__ counts, const ScoreRow* __restrict__ srow, c
       }
     }
   }
-  s_red[t] = mx;
-  __syncthreads();
-  for (uint32_t off = kPlanThreads / 2; off > 0; off >>= 1) {
-    if (t < off) s_red[t] = fmax(s_red[t], s_red[t + off]);
-    __syncthreads();
+  // block reduction in a fixed order: butterflies inside a warp, then the 32 warp results in warp order
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+    cs += __shfl_xor_sync(0xffffffffu, cs, off);
   }
-  const double partmax = s_red[0];
+  if ((t & 31u) == 0) {
+    s_red[t >> 5] = mx;
+    s_red[32 + (t >> 5)] = cs;
+  }
   __syncthreads();
-  s_red[t] = cs;
-  __syncthreads();
-  for (uint32_t off = kPlanThreads / 2; off > 0; off >>= 1) {
-    if (t < off) s_red[t] += s_red[t + off];
-    __syncthreads();
+  double partmax = 0.0, partsum = 0.0;
+  if (t == 0) {
+    for (uint32_t i = 0; i < kPlanThreads / 32; ++i) {
+      partmax = fmax(partmax, s_red[i]);
+      partsum += s_red[32 + i];
+    }
   }
   if (t == 0) {
     double* pm = part + static_cast<size_t>(c) * 2 * kPlanParts;  // [max x kPlanParts][sum x kPlanParts]
     pm[pt] = partmax;
-    pm[kPlanParts + pt] = s_red[0];
+    pm[kPlanParts + pt] = partsum;
     __threadfence();
     if (atomicAdd(part_ctr + c, 1u) == kPlanParts - 1) {
       __threadfence();
