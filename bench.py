@@ -302,7 +302,9 @@ def parity_at_bench_size(path, V_total, N, out_counts, out_p):
     assert np.all(out_counts[:V_total].sum(axis=1, dtype=np.uint64) == N), "counts do not add up to N"
     p = out_p[:V_total]
     assert np.all(np.isfinite(p)) and float(p.min()) >= 0.0 and float(p.max()) <= 1.0
-    n_sample = max(64, V_total // 100)
+    # >= 1 % of the variants up to 2M (N <= 2); beyond that 20 000 variants stratified over the whole range (the
+    # numpy tally of the sample runs on rank 0 while every GPU of the box is held)
+    n_sample = max(64, min(V_total // 100, 20_000))
     rng = np.random.default_rng(SEED)
     strata = np.linspace(0, V_total, n_sample + 1).astype(np.int64)
     idx = np.unique(np.minimum(strata[:-1] + rng.integers(0, np.maximum(1, np.diff(strata))), V_total - 1))
