@@ -176,6 +176,24 @@ int pd_hwe_from_counts(pd_ctx* ctx, const uint32_t* counts, uint32_t n, uint32_t
  * without observations. */
 int pd_hwe_lnp_from_counts(pd_ctx* ctx, const uint32_t* counts, uint32_t n, uint32_t midp, double* out_lnp);
 
+/* ---- Allocation-free form of the two calls above.  It has NO counterpart in the reference: it was added
+ *      for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ *      tight serving loops, harnesses that forbid it).  No context: d_counts (n x 4 uint32, 16-byte aligned) and
+ *      d_out (n doubles) are DEVICE buffers of the CURRENT device, owned by the caller; the kernels are enqueued
+ *      on `stream` (a cudaStream_t, NULL = the default stream) and the call returns without synchronising.
+ *      want_lnp = 0: p as pd_hwe_from_counts, != 0: ln p as pd_hwe_lnp_from_counts (bit-identical results).
+ *      The kernels' scratch (work-queue counters + the list of tables that need the scaled walk) is a static
+ *      device array of 16 + 4 * PD_NOALLOC_HWE_MAX_VARIANTS bytes (4 MiB) that every GPU using the library holds
+ *      until exit; n beyond the limit returns PD_ERR_INVALID_ARG with a message in errbuf (split the call).
+ *      The call allocates and frees nothing (no cudaMalloc / cudaFree / cudaHostAlloc, no library that does).
+ *      Every call on a GPU shares that array: calls that overlap on the GPU (other streams, other threads) RACE
+ *      and must be serialised by the caller; back-to-back calls on one stream are fine (each clears what must
+ *      start at zero).  errbuf may be NULL. ---- */
+#define PD_NOALLOC_HWE_MAX_VARIANTS (1u << 20)
+uint32_t pd_hwe_noalloc_max_variants(void);
+int pd_hwe_from_counts_noalloc(const uint32_t* d_counts, uint32_t n, uint32_t midp, uint32_t want_lnp, double* d_out,
+                               void* stream, char* errbuf, size_t errbuf_len);
+
 /* chrX non-PAR exact test on the device: replaces HweExactTestXchr -> plink2::HweXchrLnP
  * (src/plink_hardy.cpp:83-95).  c5[5*i + {0..4}] = female hom_ref, female het, female hom_alt,
  * male REF-hemizygous, male ALT-hemizygous. */

@@ -85,6 +85,8 @@ SYMBOLS = {
     "pd_hwe_from_counts": (C.c_int, [_vp, _vp, _u32, _u32, _vp]),
     "pd_hwe_lnp_from_counts": (C.c_int, [_vp, _vp, _u32, _u32, _vp]),
     "pd_hwe_xchr_from_counts": (C.c_int, [_vp, _vp, _u32, _u32, _vp]),
+    "pd_hwe_noalloc_max_variants": (_u32, []),
+    "pd_hwe_from_counts_noalloc": (C.c_int, [_vp, _u32, _u32, _u32, _vp, _vp, C.c_char_p, C.c_size_t]),
     "pd_missing_by_sample": (C.c_int, [_vp, _u32, _u32, _vp]),
     "pd_sample_counts": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),
     "pd_decode_i8": (C.c_int, [_vp, _u32, _u32, _vp]),
