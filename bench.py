@@ -28,6 +28,8 @@ ranks only join the rendezvous.  Inputs are larger than L2 (25 GB vs 126 MB), so
 needed between steps.
 """
 import argparse
+import contextlib
+import io
 import concurrent.futures as cf
 import datetime
 import json
@@ -637,10 +639,26 @@ def run_reference(args):
 
 def main():
     args = parse_args()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_ours(args)
+    # stdout carries exactly ONE line, the JSON result: libraries that write to file descriptor 1 (NCCL prints its
+    # version there) are sent to stderr for the length of the run
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    buf = io.StringIO()
+    try:
+        with contextlib.redirect_stdout(buf):
+            if args.impl == "reference":
+                run_reference(args)
+            else:
+                run_ours(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+        out = buf.getvalue()
+        if out:
+            sys.stdout.write(out)
+            sys.stdout.flush()
 
 
 if __name__ == "__main__":

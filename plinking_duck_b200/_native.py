@@ -119,7 +119,8 @@ def load():
                 f"{LIB_PATH} not found: the CUDA extension is required (no CPU fallback). "
                 "Build it with `make -C plinking_duck_b200/csrc`."
             )
-        lib = C.CDLL(LIB_PATH)
+        # PLINKGPU_LIB: a differently built copy of the same library (A/B runs of development scripts only)
+        lib = C.CDLL(os.environ.get("PLINKGPU_LIB") or LIB_PATH)
         for name, (res, args) in SYMBOLS.items():
             fn = getattr(lib, name)  # AttributeError if the library does not export it
             fn.restype = res

@@ -304,8 +304,8 @@ __device__ __forceinline__ bool parse_difflist(const uint8_t*& p, const uint8_t*
 // the stored group byte lengths, which is what makes the varint stream parallel at group
 // granularity.  Returns false (on all lanes) if any lane saw malformed input.
 template <class F>
-__device__ __forceinline__ bool difflist_walk(const Difflist& d, uint32_t N, int lane, F f,
-                                              const uint8_t** track_end = nullptr) {
+__device__ __forceinline__ bool difflist_walk_lanes(const Difflist& d, uint32_t N, int lane, F f,
+                                                    const uint8_t** track_end = nullptr) {
   bool ok = true;
   uint64_t batch_off = 0;
   const uint8_t* my_end = d.deltas;  // meaningful on the lane that walked the last group
@@ -387,6 +387,157 @@ __device__ __forceinline__ uint32_t load_bits32(const uint8_t* row, uint64_t bit
 // Word k (16 genotypes) of a packed 2-bit row at any byte alignment.
 __device__ __forceinline__ uint32_t row_word(const uint8_t* row, uint32_t k) {
   return load_bits32(row, static_cast<uint64_t>(k) << 5);
+}
+
+// The same walk with the WHOLE WARP on one 64-entry group at a time (bit-parallel varint decode): lane l takes bytes
+// 4 l .. 4 l + 3 of the group's delta stream.  A byte with its high bit clear ends a varint; byte i of a varint
+// contributes (b & 127) << 7 i, so the id behind the j-th terminator is first_id + (the sum of the contributions of
+// all bytes up to it) -- two warp prefix sums (contributions, terminators) replace the 63 serial steps, and the
+// position of a byte inside its varint needs only the run of continuation bytes in front of it (from the lanes
+// before: two shuffles).  ~130 warp instructions per group against ~340 for lane-per-group on 20-group records
+// (profiles/r01f_sparse_walk_experiment.txt).  Same callback, same error behaviour as difflist_walk.
+template <class F>
+__device__ __forceinline__ bool difflist_walk_swar(const Difflist& d, uint32_t N, int lane, F f,
+                                                   const uint8_t** track_end = nullptr) {
+  bool ok = true;
+  uint64_t batch_off = 0;
+  const uint8_t* list_end = d.deltas;
+  const uint64_t avail = static_cast<uint64_t>(d.end - d.deltas);
+  for (uint32_t g0 = 0; g0 < d.ngroups; g0 += 32) {
+    const uint32_t gl = g0 + lane;
+    uint32_t sz = 0;
+    if (gl + 1 < d.ngroups) sz = static_cast<uint32_t>(d.group_sizes[gl]) + 63u;
+    uint32_t incl = sz;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= off) incl += t;
+    }
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    const uint32_t my_first = gl < d.ngroups ? load_le(d.first_ids + static_cast<uint64_t>(gl) * d.idbytes, d.idbytes) : 0u;
+    const uint32_t nb = min(32u, d.ngroups - g0);
+#pragma unroll 1
+    for (uint32_t k = 0; k < nb; ++k) {
+      const uint32_t g = g0 + k;
+      const uint64_t start = batch_off + (__shfl_sync(0xffffffffu, incl, k) - __shfl_sync(0xffffffffu, sz, k));
+      const uint32_t gsz = __shfl_sync(0xffffffffu, sz, k);
+      const uint32_t first_id = __shfl_sync(0xffffffffu, my_first, k);
+      const bool last = g + 1 == d.ngroups;
+      const uint32_t need = min(64u, d.len - (g << 6)) - 1u;  // varints of this group
+      const uint32_t e0 = g << 6;
+      if (start > avail) {
+        ok = false;
+        break;
+      }
+      const uint8_t* ptr = d.deltas + start;
+      const uint64_t room = (!last && start + gsz <= avail) ? gsz : avail - start;  // bytes this group may use
+      if (lane == 0) {
+        if (first_id >= N) {
+          ok = false;
+        } else {
+          f(first_id, d.raregeno ? (static_cast<uint32_t>(d.raregeno[e0 >> 2]) & 3u) : 0u, e0);
+        }
+      }
+      uint32_t c_sum = 0, c_terms = 0, c_run = 0;
+      const uint8_t* my_end = ptr;  // (last group) byte behind the terminator that completes the list
+      bool found_end = need == 0;
+#pragma unroll 1
+      for (uint64_t c = 0; c_terms < need; c += 128) {
+        if (c >= room) {
+          ok = false;  // the stream ends before the group's entries do
+          break;
+        }
+        const uint64_t a = c + 4u * static_cast<uint32_t>(lane);
+        const uint32_t nvalid = a < room ? static_cast<uint32_t>(room - a < 4 ? room - a : 4) : 0u;
+        uint32_t w = 0;
+        if (nvalid) w = load_bits32(ptr + a, 0);
+        if (nvalid < 4) w &= (1u << (8u * nvalid)) - 1u;
+        const uint32_t vm = nvalid >= 4 ? 0x80808080u : (0x80808080u & ((1u << (8u * nvalid)) - 1u));
+        const uint32_t term = ~w & vm;
+        const uint32_t c0 = (w >> 7) & 1u, c1 = (w >> 15) & 1u, c2 = (w >> 23) & 1u, c3 = w >> 31;
+        const uint32_t tr = c3 ? (c2 ? (c1 ? (c0 ? 4u : 3u) : 2u) : 1u) : 0u;
+        uint32_t p1 = __shfl_up_sync(0xffffffffu, tr, 1), p2 = __shfl_up_sync(0xffffffffu, tr, 2);
+        if (lane == 0) {
+          p1 = c_run;
+          p2 = 0;
+        } else if (lane == 1) {
+          p2 = c_run;
+        }
+        const uint32_t run_in = (lane >= 1 && p1 == 4u) ? p1 + p2 : p1;
+        const uint32_t k0 = run_in, k1 = c0 ? k0 + 1u : 0u, k2 = c1 ? k1 + 1u : 0u, k3 = c2 ? k2 + 1u : 0u;
+        const uint32_t run_out = c3 ? k3 + 1u : 0u;
+        const uint32_t b0 = w & 0xffu, b1 = (w >> 8) & 0xffu, b2 = (w >> 16) & 0xffu, b3 = w >> 24;
+        // GetVint31: at most 5 bytes, the fifth may carry 3 value bits
+        const uint32_t bad = ((k0 > 4u) | (k0 == 4u && (b0 & 0xf8u))) | (((k1 > 4u) | (k1 == 4u && (b1 & 0xf8u))) << 1) |
+                             (((k2 > 4u) | (k2 == 4u && (b2 & 0xf8u))) << 2) | (((k3 > 4u) | (k3 == 4u && (b3 & 0xf8u))) << 3);
+        const uint32_t s0 = (b0 & 127u) << (7u * min(k0, 4u));
+        const uint32_t s1 = s0 + ((b1 & 127u) << (7u * min(k1, 4u)));
+        const uint32_t s2 = s1 + ((b2 & 127u) << (7u * min(k2, 4u)));
+        const uint32_t s3 = s2 + ((b3 & 127u) << (7u * min(k3, 4u)));
+        const uint32_t tcount = __popc(term);
+        uint32_t isum = s3, icnt = tcount;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+          const uint32_t ts = __shfl_up_sync(0xffffffffu, isum, off);
+          const uint32_t tc = __shfl_up_sync(0xffffffffu, icnt, off);
+          if (lane >= off) {
+            isum += ts;
+            icnt += tc;
+          }
+        }
+        const uint32_t sbase = c_sum + isum - s3, cbase = c_terms + icnt - tcount;
+        const uint32_t sums[4] = {s0, s1, s2, s3};
+#pragma unroll
+        for (uint32_t i = 0; i < 4; ++i) {
+          const uint32_t before = cbase + __popc(term & ((1u << (8u * i)) - 1u));  // varints completed before byte i
+          if (i < nvalid && before < need) {
+            if ((bad >> i) & 1u) ok = false;
+            if ((term >> (8u * i + 7u)) & 1u) {
+              const uint32_t ord = before + 1u;
+              const uint32_t id = first_id + sbase + sums[i];
+              if (id >= N || id < first_id) {
+                ok = false;
+              } else {
+                const uint32_t e = e0 + ord;
+                f(id, d.raregeno ? ((static_cast<uint32_t>(d.raregeno[e >> 2]) >> (2u * (e & 3u))) & 3u) : 0u, e);
+              }
+              if (ord == need) {
+                my_end = ptr + a + i + 1u;
+                found_end = true;
+              }
+            }
+          }
+        }
+        c_sum += __shfl_sync(0xffffffffu, isum, 31);
+        c_terms += __shfl_sync(0xffffffffu, icnt, 31);
+        c_run = __shfl_sync(0xffffffffu, run_out, 31);
+      }
+      if (last) {
+        const uint32_t who = __ballot_sync(0xffffffffu, found_end && (need == 0 ? lane == 0 : true));
+        if (who) {
+          const unsigned long long e = __shfl_sync(
+              0xffffffffu, static_cast<unsigned long long>(reinterpret_cast<uintptr_t>(my_end)), __ffs(who) - 1);
+          list_end = reinterpret_cast<const uint8_t*>(static_cast<uintptr_t>(e));
+        }
+      }
+      if (!__all_sync(0xffffffffu, ok)) break;
+    }
+    batch_off += total;
+    if (!__all_sync(0xffffffffu, ok)) break;
+  }
+  if (track_end) *track_end = list_end;
+  return __all_sync(0xffffffffu, ok);
+}
+
+// The walker every kernel calls.  PD_WALK_LANES (compile-time) selects the round-1 lane-per-group walk for A/B runs.
+template <class F>
+__device__ __forceinline__ bool difflist_walk(const Difflist& d, uint32_t N, int lane, F f,
+                                              const uint8_t** track_end = nullptr) {
+#ifdef PD_WALK_LANES
+  return difflist_walk_lanes(d, N, lane, f, track_end);
+#else
+  return difflist_walk_swar(d, N, lane, f, track_end);
+#endif
 }
 
 // Same through L2 only (rows that other lanes patched with atomics moments ago).
