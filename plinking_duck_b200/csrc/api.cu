@@ -27,7 +27,7 @@ void DestroyCtx(pd_ctx* c) {
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
   if (c->d2h_stream) cudaStreamSynchronize(c->d2h_stream);
-  c->d_fpos.Free(); c->d_vrtypes.Free(); c->d_ldbase.Free(); c->d_base_slot.Free(); c->d_slot_vidx.Free();
+  c->d_fpos.Free(); c->d_vrtypes.Free(); c->d_ldbase.Free(); c->d_base_slot.Free(); c->d_slot_vidx.Free(); c->d_allele_cts.Free();
   c->d_resident.Free();
   for (auto& b : c->h_stage) b.Free();
   for (auto& b : c->d_stage) b.Free();
@@ -137,6 +137,12 @@ int InitDevice(pd_ctx* c, const pd_open_opts* opts) {
       cudaMemcpyAsync(c->d_slot_vidx.p, c->slot_vidx.data(), c->slot_vidx.size() * 4, cudaMemcpyHostToDevice, c->stream);
     }
     c->stats.h2d_bytes += (static_cast<size_t>(V) + 1) * 8 + vt.size() + static_cast<size_t>(V) * 8;
+    if (!ix.allele_cts.empty()) {
+      e = c->d_allele_cts.Reserve(V);
+      if (e != cudaSuccess) return CheckCuda(c, e, "index allocation");
+      cudaMemcpyAsync(c->d_allele_cts.p, ix.allele_cts.data(), V, cudaMemcpyHostToDevice, c->stream);
+      c->stats.h2d_bytes += V;
+    }
   }
   e = cudaStreamSynchronize(c->stream);
   if (e != cudaSuccess) return CheckCuda(c, e, "index upload");

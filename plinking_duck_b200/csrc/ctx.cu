@@ -304,6 +304,7 @@ int RunScan(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t* v_ext, c
   ix.fixed_width = ixh.fixed_width;
   ix.const_vrtype = ixh.const_vrtype;
   ix.N = ixh.sample_ct;
+  ix.allele_cts = c->d_allele_cts.p ? c->d_allele_cts.as<uint8_t>() : nullptr;
   c->stats.record_bytes = ixh.RecOff(v_end - 1) + (ixh.fixed ? ixh.fixed_width : ixh.fpos[v_end] - ixh.fpos[v_end - 1]) -
                           ixh.RecOff(v_begin);
 

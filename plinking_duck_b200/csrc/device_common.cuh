@@ -396,13 +396,28 @@ __device__ __forceinline__ uint32_t row_word(const uint8_t* row, uint32_t k) {
 // position of a byte inside its varint needs only the run of continuation bytes in front of it (from the lanes
 // before: two shuffles).  ~130 warp instructions per group against ~340 for lane-per-group on 20-group records
 // (profiles/r01f_sparse_walk_experiment.txt).  Same callback, same error behaviour as difflist_walk.
+// First 128 stream bytes of a group as one 32-bit word per lane (bytes 4 l .. 4 l + 3 from `ptr`; lanes past `room`
+// read nothing and get 0), plus -- lanes 0-3 -- the four 32-bit words of the group's 64 two-bit raregeno codes.
+struct SwarChunk {
+  uint32_t w;   // stream bytes of this lane, bytes past the group's room cleared
+  uint32_t rg;  // raregeno word `lane` of the group (lanes 0-3), else 0
+};
+__device__ __forceinline__ uint32_t swar_load(const uint8_t* ptr, uint32_t a, uint32_t room) {
+  uint32_t w = 0;
+  if (a < room) {
+    w = load_bits32(ptr + a, 0);
+    if (room - a < 4u) w &= (1u << (8u * (room - a))) - 1u;
+  }
+  return w;
+}
+
 template <class F>
 __device__ __forceinline__ bool difflist_walk_swar(const Difflist& d, uint32_t N, int lane, F f,
                                                    const uint8_t** track_end = nullptr) {
   bool ok = true;
-  uint64_t batch_off = 0;
+  uint32_t batch_off = 0;  // a record is far below 4 GiB: 32-bit offsets into its delta stream
   const uint8_t* list_end = d.deltas;
-  const uint64_t avail = static_cast<uint64_t>(d.end - d.deltas);
+  const uint32_t avail = static_cast<uint32_t>(d.end - d.deltas);
   for (uint32_t g0 = 0; g0 < d.ngroups; g0 += 32) {
     const uint32_t gl = g0 + lane;
     uint32_t sz = 0;
@@ -416,11 +431,32 @@ __device__ __forceinline__ bool difflist_walk_swar(const Difflist& d, uint32_t N
     const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
     const uint32_t my_first = gl < d.ngroups ? load_le(d.first_ids + static_cast<uint64_t>(gl) * d.idbytes, d.idbytes) : 0u;
     const uint32_t nb = min(32u, d.ngroups - g0);
+    // where group k of the batch starts and how many bytes it may use (warp-uniform)
+    auto start_of = [&](uint32_t k) { return batch_off + (__shfl_sync(0xffffffffu, incl, k) - __shfl_sync(0xffffffffu, sz, k)); };
+    auto room_of = [&](uint32_t k, uint32_t start) -> uint32_t {
+      const uint32_t gsz = __shfl_sync(0xffffffffu, sz, k);
+      if (start > avail) return 0u;
+      return (g0 + k + 1 != d.ngroups && start + gsz <= avail) ? gsz : avail - start;
+    };
+    auto load_group = [&](uint32_t k, uint32_t start, uint32_t room) {
+      SwarChunk c;
+      c.w = swar_load(d.deltas + start, 4u * static_cast<uint32_t>(lane), room);
+      c.rg = 0;
+      if (d.raregeno && lane < 4) {
+        // 16 raregeno bytes per full group, fewer at the end of the list (what is read past them lies inside the
+        // record or its slack and is never looked at)
+        const uint32_t e0 = (g0 + k) << 6;
+        const uint32_t nbytes = (min(64u, d.len - e0) + 3u) >> 2;
+        if (4u * lane < nbytes) c.rg = load_bits32(d.raregeno + (e0 >> 2) + 4u * lane, 0);
+      }
+      return c;
+    };
+    uint32_t start = start_of(0);
+    uint32_t room = room_of(0, start);
+    SwarChunk cur = load_group(0, start, room);
 #pragma unroll 1
     for (uint32_t k = 0; k < nb; ++k) {
       const uint32_t g = g0 + k;
-      const uint64_t start = batch_off + (__shfl_sync(0xffffffffu, incl, k) - __shfl_sync(0xffffffffu, sz, k));
-      const uint32_t gsz = __shfl_sync(0xffffffffu, sz, k);
       const uint32_t first_id = __shfl_sync(0xffffffffu, my_first, k);
       const bool last = g + 1 == d.ngroups;
       const uint32_t need = min(64u, d.len - (g << 6)) - 1u;  // varints of this group
@@ -430,28 +466,35 @@ __device__ __forceinline__ bool difflist_walk_swar(const Difflist& d, uint32_t N
         break;
       }
       const uint8_t* ptr = d.deltas + start;
-      const uint64_t room = (!last && start + gsz <= avail) ? gsz : avail - start;  // bytes this group may use
+      const uint32_t cur_room = room;
+      // the next group's bytes are requested before this group's arithmetic starts
+      SwarChunk nxt{0u, 0u};
+      uint32_t nstart = 0, nroom = 0;
+      if (k + 1 < nb) {
+        nstart = start_of(k + 1);
+        nroom = room_of(k + 1, nstart);
+        nxt = load_group(k + 1, nstart, nroom);
+      }
       if (lane == 0) {
         if (first_id >= N) {
           ok = false;
         } else {
-          f(first_id, d.raregeno ? (static_cast<uint32_t>(d.raregeno[e0 >> 2]) & 3u) : 0u, e0);
+          f(first_id, cur.rg & 3u, e0);
         }
       }
       uint32_t c_sum = 0, c_terms = 0, c_run = 0;
       const uint8_t* my_end = ptr;  // (last group) byte behind the terminator that completes the list
       bool found_end = need == 0;
+      uint32_t w = cur.w;
 #pragma unroll 1
-      for (uint64_t c = 0; c_terms < need; c += 128) {
-        if (c >= room) {
+      for (uint32_t c = 0; c_terms < need; c += 128) {
+        if (c >= cur_room) {
           ok = false;  // the stream ends before the group's entries do
           break;
         }
-        const uint64_t a = c + 4u * static_cast<uint32_t>(lane);
-        const uint32_t nvalid = a < room ? static_cast<uint32_t>(room - a < 4 ? room - a : 4) : 0u;
-        uint32_t w = 0;
-        if (nvalid) w = load_bits32(ptr + a, 0);
-        if (nvalid < 4) w &= (1u << (8u * nvalid)) - 1u;
+        const uint32_t a = c + 4u * static_cast<uint32_t>(lane);
+        if (c) w = swar_load(ptr, a, cur_room);
+        const uint32_t nvalid = a < cur_room ? min(cur_room - a, 4u) : 0u;
         const uint32_t vm = nvalid >= 4 ? 0x80808080u : (0x80808080u & ((1u << (8u * nvalid)) - 1u));
         const uint32_t term = ~w & vm;
         const uint32_t c0 = (w >> 7) & 1u, c1 = (w >> 15) & 1u, c2 = (w >> 23) & 1u, c3 = w >> 31;
@@ -466,14 +509,25 @@ __device__ __forceinline__ bool difflist_walk_swar(const Difflist& d, uint32_t N
         const uint32_t run_in = (lane >= 1 && p1 == 4u) ? p1 + p2 : p1;
         const uint32_t k0 = run_in, k1 = c0 ? k0 + 1u : 0u, k2 = c1 ? k1 + 1u : 0u, k3 = c2 ? k2 + 1u : 0u;
         const uint32_t run_out = c3 ? k3 + 1u : 0u;
-        const uint32_t b0 = w & 0xffu, b1 = (w >> 8) & 0xffu, b2 = (w >> 16) & 0xffu, b3 = w >> 24;
-        // GetVint31: at most 5 bytes, the fifth may carry 3 value bits
-        const uint32_t bad = ((k0 > 4u) | (k0 == 4u && (b0 & 0xf8u))) | (((k1 > 4u) | (k1 == 4u && (b1 & 0xf8u))) << 1) |
-                             (((k2 > 4u) | (k2 == 4u && (b2 & 0xf8u))) << 2) | (((k3 > 4u) | (k3 == 4u && (b3 & 0xf8u))) << 3);
-        const uint32_t s0 = (b0 & 127u) << (7u * min(k0, 4u));
-        const uint32_t s1 = s0 + ((b1 & 127u) << (7u * min(k1, 4u)));
-        const uint32_t s2 = s1 + ((b2 & 127u) << (7u * min(k2, 4u)));
-        const uint32_t s3 = s2 + ((b3 & 127u) << (7u * min(k3, 4u)));
+        const uint32_t b0 = w & 0x7fu, b1 = (w >> 8) & 0x7fu, b2 = (w >> 16) & 0x7fu, b3 = (w >> 24) & 0x7fu;
+        // GetVint31: at most 5 bytes, the fifth may carry 3 value bits.  Fifth bytes are rare: the test is one
+        // comparison per lane unless one shows up.
+        uint32_t bad = 0;
+        uint32_t s0, s1, s2, s3;
+        if (max(max(k0, k1), max(k2, k3)) < 4u) {
+          s0 = b0 << (7u * k0);
+          s1 = s0 + (b1 << (7u * k1));
+          s2 = s1 + (b2 << (7u * k2));
+          s3 = s2 + (b3 << (7u * k3));
+        } else {
+          bad = ((k0 > 4u) | (k0 == 4u && ((w & 0xf8u) != 0u))) | (((k1 > 4u) | (k1 == 4u && ((w & 0xf800u) != 0u))) << 1) |
+                (((k2 > 4u) | (k2 == 4u && ((w & 0xf80000u) != 0u))) << 2) |
+                (((k3 > 4u) | (k3 == 4u && ((w & 0xf8000000u) != 0u))) << 3);
+          s0 = b0 << (7u * min(k0, 4u));
+          s1 = s0 + (b1 << (7u * min(k1, 4u)));
+          s2 = s1 + (b2 << (7u * min(k2, 4u)));
+          s3 = s2 + (b3 << (7u * min(k3, 4u)));
+        }
         const uint32_t tcount = __popc(term);
         uint32_t isum = s3, icnt = tcount;
 #pragma unroll
@@ -485,21 +539,22 @@ __device__ __forceinline__ bool difflist_walk_swar(const Difflist& d, uint32_t N
             icnt += tc;
           }
         }
-        const uint32_t sbase = c_sum + isum - s3, cbase = c_terms + icnt - tcount;
+        const uint32_t sbase = first_id + c_sum + isum - s3, cbase = c_terms + icnt - tcount;
         const uint32_t sums[4] = {s0, s1, s2, s3};
 #pragma unroll
         for (uint32_t i = 0; i < 4; ++i) {
           const uint32_t before = cbase + __popc(term & ((1u << (8u * i)) - 1u));  // varints completed before byte i
+          const uint32_t ord = before + 1u;
+          // the entry's 2-bit code: word ord >> 4 of the group's raregeno sits in lane ord >> 4 (every lane shuffles)
+          const uint32_t rgw = __shfl_sync(0xffffffffu, cur.rg, (ord >> 4) & 3u);
           if (i < nvalid && before < need) {
             if ((bad >> i) & 1u) ok = false;
             if ((term >> (8u * i + 7u)) & 1u) {
-              const uint32_t ord = before + 1u;
-              const uint32_t id = first_id + sbase + sums[i];
+              const uint32_t id = sbase + sums[i];
               if (id >= N || id < first_id) {
                 ok = false;
               } else {
-                const uint32_t e = e0 + ord;
-                f(id, d.raregeno ? ((static_cast<uint32_t>(d.raregeno[e >> 2]) >> (2u * (e & 3u))) & 3u) : 0u, e);
+                f(id, (rgw >> (2u * (ord & 15u))) & 3u, e0 + ord);
               }
               if (ord == need) {
                 my_end = ptr + a + i + 1u;
@@ -512,7 +567,7 @@ __device__ __forceinline__ bool difflist_walk_swar(const Difflist& d, uint32_t N
         c_terms += __shfl_sync(0xffffffffu, icnt, 31);
         c_run = __shfl_sync(0xffffffffu, run_out, 31);
       }
-      if (last) {
+      if (last && track_end) {
         const uint32_t who = __ballot_sync(0xffffffffu, found_end && (need == 0 ? lane == 0 : true));
         if (who) {
           const unsigned long long e = __shfl_sync(
@@ -521,6 +576,9 @@ __device__ __forceinline__ bool difflist_walk_swar(const Difflist& d, uint32_t N
         }
       }
       if (!__all_sync(0xffffffffu, ok)) break;
+      cur = nxt;
+      start = nstart;
+      room = nroom;
     }
     batch_off += total;
     if (!__all_sync(0xffffffffu, ok)) break;

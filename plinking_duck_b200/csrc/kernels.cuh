@@ -17,6 +17,7 @@ struct RecIndex {
   uint32_t fixed_width;
   uint32_t const_vrtype;
   uint32_t N;               // raw sample count
+  const uint8_t* allele_cts;// [V] allele count per variant, nullptr when the file stores none (all biallelic)
 };
 
 // Sample subset (and strata) in the layouts the kernels consume.
@@ -200,6 +201,15 @@ struct ScoreRow {
   uint32_t cmask;       // bit g set: hardcall g counts towards ALLELE_CT (0 for skipped rows)
   uint32_t pad;
 };
+// out[(r * n_out + j) * 2 + {0,1}] = allele codes of sample subset_idx[j] (or j) -- PgrGetM +
+// PglMultiallelicSparseToDenseMiss: 0,0 / 0,1 / 1,1 / 255,255 from the main track, patched by the aux1a / aux1b sets of
+// multiallelic records.  raw_scratch: nrows x ((N + 7) & ~7) x 2 bytes, only used with a subset.
+void launch_expand_alleles(const RecIndex& ix, const DenseRows& rows, const uint32_t* vlist, uint32_t v0,
+                           const uint32_t* subset_idx, uint32_t n_out, uint8_t* raw_scratch, uint8_t* out, int* err,
+                           cudaStream_t s, LaunchStats* st);
+// out[r, j] = raw[r, idx[j]] as 16-bit pairs (sample subset of a row of pairs).
+void launch_gather_pairs(const uint16_t* raw, uint32_t raw_stride, const uint32_t* idx, uint32_t n_out, uint32_t nrows,
+                         uint16_t* out, cudaStream_t s, LaunchStats* st);
 // counts: (subset) hardcall counts per row; stats: dosage sums per row or nullptr; flip: per row or nullptr.
 void launch_score_prep(const uint4* counts, const DosageStats* stats, const uint8_t* flip, uint32_t nrows, uint32_t mode,
                        ScoreRow* out, cudaStream_t s, LaunchStats* st);

@@ -45,7 +45,11 @@ __device__ __forceinline__ bool sparse_accumulate(uint32_t common, bool all_comm
   if (!parse_difflist(q, end, N, true, d)) return false;
   if (!d.len) return true;
   const uint32_t kinds = sa.kinds;
-  return difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g, uint32_t) {
+  // lane-per-group walk on purpose: this path is bound by the L2 reductions it issues (one per listed sample and
+  // plane: 121 M per 200k rare-variant records = the measured 1.9 ms at ~64 G/s), and the warp-per-group walker,
+  // which wins wherever the walk itself is the cost (counts, dense decode), was measured 60 % slower here
+  // (profiles/r02n_compressed_walk_ab.txt)
+  return difflist_walk_lanes(d, N, lane, [&](uint32_t id, uint32_t g, uint32_t) {
     const uint32_t ge = g & 1u, go = g >> 1, gb = ge & go;
     if ((kinds & 1u) && ge != ce) atomicAdd(sa.acc_e + id, ge - ce);
     if ((kinds & 2u) && go != co) atomicAdd(sa.acc_o + id, go - co);
@@ -60,7 +64,7 @@ __device__ __forceinline__ bool sparse_accumulate(uint32_t common, bool all_comm
 // are independent of each other and of batch boundaries.
 // ---------------------------------------------------------------------------------------------
 template <bool SPARSE>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 3)
 k_densify(RecIndex ix, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t nrows, uint8_t* __restrict__ scratch,
           uint32_t slot_stride, const uint8_t** __restrict__ ptrs, uint32_t* __restrict__ work_counter,
           int* __restrict__ err, SparseAcc sa) {

@@ -615,12 +615,19 @@ void launch_expand_phased(const RecIndex& ix, const DenseRows& rows, const uint3
   // subset: expand all raw samples, then gather the kept pairs (phase is a per-sample property)
   const uint32_t raw_stride = (ix.N + 7) & ~7u;  // keeps every scratch row 16-byte aligned
   k_expand_phased<<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, rows, vlist, v0, raw_stride, raw_scratch, err);
-  const uint64_t total = static_cast<uint64_t>(rows.nrows) * n_out;
+  launch_gather_pairs(reinterpret_cast<const uint16_t*>(raw_scratch), raw_stride, subset_idx, n_out, rows.nrows,
+                      reinterpret_cast<uint16_t*>(out), s, st);
+  if (st) st->launches++;
+}
+
+void launch_gather_pairs(const uint16_t* raw, uint32_t raw_stride, const uint32_t* idx, uint32_t n_out, uint32_t nrows,
+                         uint16_t* out, cudaStream_t s, LaunchStats* st) {
+  const uint64_t total = static_cast<uint64_t>(nrows) * n_out;
+  if (!total) return;
   uint64_t gb = (total + 255) / 256;
   if (gb > 148ull * 32) gb = 148ull * 32;
-  k_gather_pairs<<<static_cast<unsigned>(gb), 256, 0, s>>>(reinterpret_cast<const uint16_t*>(raw_scratch), raw_stride,
-                                                        subset_idx, n_out, total, reinterpret_cast<uint16_t*>(out));
-  if (st) st->launches += 2;
+  k_gather_pairs<<<static_cast<unsigned>(gb), 256, 0, s>>>(raw, raw_stride, idx, n_out, total, out);
+  if (st) st->launches++;
 }
 
 }  // namespace pdk

@@ -400,7 +400,11 @@ int ParsePgenIndex(const ByteSource& pgen, const ByteSource* pgi, PgenIndex* out
       else if (main == 1 || main >= 4) ix.has_difflist = true;
     }
     pos += total;
-    if (allele_ct_bytes) pos += static_cast<uint64_t>(n) * allele_ct_bytes;
+    if (allele_ct_bytes) {  // one byte per variant (pgenlib_read.cc:1436-1471)
+      if (ix.allele_cts.empty()) ix.allele_cts.assign(V, 2);
+      if (!hdr->ReadAt(pos, ix.allele_cts.data() + v0, n)) return Fail(err, PD_ERR_READ, "header read failure (allele counts)");
+      pos += static_cast<uint64_t>(n) * allele_ct_bytes;
+    }
     if (nonref_storage == 3) pos += (n + 7) / 8;
   }
   ix.fpos[V] = fpos;

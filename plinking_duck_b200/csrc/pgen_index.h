@@ -73,12 +73,16 @@ struct PgenIndex {
   // ldbase[v] = index of the last variant <= v whose main track is not LD-compressed
   // (semantics of GetLdbaseVidx, pgenlib_read.cc:1846-1894); ldbase[v] == v for non-LD records.
   std::vector<uint32_t> ldbase;   // [V]
+  // allele count of every variant (header_ctrl bits 4-5 = 1: one byte each); empty when the file stores none
+  // (every variant biallelic as far as the reader is concerned)
+  std::vector<uint8_t> allele_cts;  // [V]
   bool has_ld = false, has_difflist = false, has_dosage = false, has_phase = false, has_multiallelic = false;
   uint32_t max_width = 0;
 
   uint64_t RecOff(uint32_t v) const { return fixed ? data_start + static_cast<uint64_t>(v) * fixed_width : fpos[v]; }
   uint32_t Vrtype(uint32_t v) const { return fixed ? const_vrtype : vrtypes[v]; }
   uint32_t Ldbase(uint32_t v) const { return fixed ? v : ldbase[v]; }
+  uint32_t AlleleCt(uint32_t v) const { return allele_cts.empty() ? 2u : allele_cts[v]; }
 };
 
 // Error codes match include/plinkgpu.h PD_ERR_*.
