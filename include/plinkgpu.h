@@ -256,6 +256,18 @@ int pd_tidy_i8(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t emit_mask
  *      reference).  Variants without a phase track decode every het as 0,1.  Multiallelic records with a
  *      phase track return PD_ERR_NOT_SUPPORTED. ---- */
 int pd_decode_phased(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, int8_t* out);
+/* Multiallelic hardcalls: replaces PgrGetM + PglMultiallelicSparseToDenseMiss (pgenlib_read.cc:6668-6681,
+ * pgenlib_misc.cc:3552-3578; the aux1a / aux1b patch sets of pgen_spec.tex:469-564).  out[(row * n + s) * 2 + {0,1}] =
+ * the two allele codes of sample s (0 = REF, 1 = ALT1, ...; first <= second), 255,255 for a missing call.  Biallelic
+ * records give 0,0 / 0,1 / 1,1.  The extension itself reads multiallelic files through the biallelic calls (pd_counts,
+ * pd_decode_i8, ...: the main track); this entry point completes the codec. */
+int pd_decode_alleles(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint8_t* out);
+/* Allele count of every variant (n = variant count, each 2..255), as a caller derives them from the .pvar: the
+ * drop-in for PgenFileInfo.allele_idx_offsets, which pgenlib expects preloaded the same way (pgenlib_read.cc:695-697,
+ * 1113-1121; plink2's own writer does not store them in the .pgen).  Needed by pd_decode_alleles for records with a
+ * patch track; files that do store counts in their header (header_ctrl bits 4-5) are read without this call.
+ * NULL clears the table. */
+int pd_set_allele_counts(pd_ctx* ctx, const uint32_t* allele_cts, uint32_t n);
 
 /* ---- dosage decode: replaces PgrGetD + Dosage16ToDoublesMinus9 (src/plink_score.cpp:587-596,
  *      src/pgen_reader.cpp:694-703).  out is n_var x effective sample_ct double, -9.0 = missing. ---- */

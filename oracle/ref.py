@@ -34,6 +34,10 @@ def lib():
         L.ref_open.restype = C.c_int
         L.ref_open_counts.argtypes = [C.c_char_p, u32, u32, C.POINTER(vp), C.c_char_p, C.c_size_t]
         L.ref_open_counts.restype = C.c_int
+        L.ref_open_alleles.argtypes = [C.c_char_p, vp, C.POINTER(vp), C.c_char_p, C.c_size_t]
+        L.ref_open_alleles.restype = C.c_int
+        L.ref_decode_alleles.argtypes = [vp, u32, u32, vp]
+        L.ref_decode_alleles.restype = C.c_int
         L.ref_close.argtypes = [vp]
         L.ref_info.argtypes = [vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]
         L.ref_vrtype.argtypes = [vp, u32]
@@ -78,11 +82,15 @@ def _p(a):
 class RefPgen:
     """One pgenlib reader (PgenFileInfo + PgenReader), as each DuckDB scan thread owns."""
 
-    def __init__(self, path: str, raw_counts=None):
-        """raw_counts = (V, N) for PLINK 1 .bed files, which store neither."""
+    def __init__(self, path: str, raw_counts=None, allele_cts=None):
+        """raw_counts = (V, N) for PLINK 1 .bed files, which store neither.  allele_cts = per-variant allele counts
+        (from the .pvar) for the multiallelic view (decode_alleles)."""
         self._h = C.c_void_p()
         err = C.create_string_buffer(512)
-        if raw_counts is None:
+        if allele_cts is not None:
+            ac = np.ascontiguousarray(allele_cts, dtype=np.uint32)
+            rc = lib().ref_open_alleles(os.fsencode(path), _p(ac), C.byref(self._h), err, 512)
+        elif raw_counts is None:
             rc = lib().ref_open(os.fsencode(path), C.byref(self._h), err, 512)
         else:
             rc = lib().ref_open_counts(os.fsencode(path), int(raw_counts[0]), int(raw_counts[1]), C.byref(self._h), err, 512)
@@ -94,6 +102,15 @@ class RefPgen:
         V, N, S = C.c_uint32(), C.c_uint32(), C.c_uint32()
         lib().ref_info(self._h, C.byref(V), C.byref(N), C.byref(S))
         self.V, self.N, self.sample_ct = V.value, N.value, S.value
+
+    def decode_alleles(self, v0=0, v1=None) -> np.ndarray:
+        """PgrGetM + PglMultiallelicSparseToDenseMiss: (rows, sample_ct, 2) uint8 allele codes, 255 = missing."""
+        v1 = self.V if v1 is None else v1
+        out = np.zeros((v1 - v0, self.sample_ct, 2), dtype=np.uint8)
+        rc = lib().ref_decode_alleles(self._h, v0, v1, _p(out))
+        if rc:
+            raise IOError(f"ref_decode_alleles failed rc={rc}")
+        return out
 
     def close(self):
         if self._h:

@@ -61,10 +61,13 @@ struct Reader {
   uint16_t* dosage_main = nullptr;
   uintptr_t* raregeno = nullptr;
   uint32_t* difflist_ids = nullptr;
+  // multiallelic view (ref_open_alleles): what a caller derives from the .pvar and hands to pgenlib
+  std::vector<uintptr_t> allele_idx_offsets;
   bool open = false;
 };
 
-int OpenReader(const char* path, Reader* r, char* err, size_t errlen, uint32_t raw_v = UINT32_MAX, uint32_t raw_n = UINT32_MAX) {
+int OpenReader(const char* path, Reader* r, char* err, size_t errlen, uint32_t raw_v = UINT32_MAX, uint32_t raw_n = UINT32_MAX,
+               const uint32_t* allele_cts = nullptr) {
   PreinitPgfi(&r->pgfi);
   PreinitPgr(&r->pgr);
   char errstr[kPglErrstrBufBlen];
@@ -82,7 +85,23 @@ int OpenReader(const char* path, Reader* r, char* err, size_t errlen, uint32_t r
   }
   uint32_t maxw = 0;
   uintptr_t c2 = 0;
-  e = PgfiInitPhase2(hc, 0, 0, 0, 0, r->pgfi.raw_variant_ct, &maxw, &r->pgfi, r->pgfi_alloc, &c2, errstr);
+  if (allele_cts) {
+    // allele counts preloaded by the caller (they live in the .pvar, not in the .pgen): pgfi.allele_idx_offsets +
+    // max_allele_ct before phase 2, allele_cts_already_loaded = 1 (pgenlib_read.cc:695-697,1113-1121)
+    const uint32_t V = r->pgfi.raw_variant_ct;
+    r->allele_idx_offsets.resize(static_cast<size_t>(V) + 1);
+    uintptr_t cum = 0;
+    uint32_t mx = 2;
+    for (uint32_t v = 0; v < V; ++v) {
+      r->allele_idx_offsets[v] = cum;
+      cum += allele_cts[v];
+      if (allele_cts[v] > mx) mx = allele_cts[v];
+    }
+    r->allele_idx_offsets[V] = cum;
+    r->pgfi.allele_idx_offsets = r->allele_idx_offsets.data();
+    r->pgfi.max_allele_ct = mx;
+  }
+  e = PgfiInitPhase2(hc, allele_cts ? 1 : 0, 0, 0, 0, r->pgfi.raw_variant_ct, &maxw, &r->pgfi, r->pgfi_alloc, &c2, errstr);
   if (e != kPglRetSuccess) {
     if (err) snprintf(err, errlen, "phase2: %s", errstr);
     PglErr ce = kPglRetSuccess;
@@ -202,6 +221,59 @@ int ref_open_counts(const char* path, uint32_t raw_v, uint32_t raw_n, void** out
   }
   *out = r;
   return 0;
+}
+
+// Reader with the caller's allele counts (V entries), for ref_decode_alleles.
+int ref_open_alleles(const char* path, const uint32_t* allele_cts, void** out, char* err, size_t errlen) {
+  Reader* r = new Reader();
+  int rc = OpenReader(path, r, err, errlen, UINT32_MAX, UINT32_MAX, allele_cts);
+  if (rc) {
+    delete r;
+    *out = nullptr;
+    return rc;
+  }
+  *out = r;
+  return 0;
+}
+
+// PgrGetM + PglMultiallelicSparseToDenseMiss for variants [v0, v1) under the reader's sample subset:
+// out[(row * sample_ct + s) * 2 + {0, 1}] = allele codes, 255 = missing (pgenlib_read.cc:6668-6681,
+// pgenlib_misc.cc:3552-3578).
+int ref_decode_alleles(void* h, uint32_t v0, uint32_t v1, uint8_t* out) {
+  Reader* r = static_cast<Reader*>(h);
+  if (!r->pgfi.allele_idx_offsets) return static_cast<int>(kPglRetImproperFunctionCall);
+  const uint32_t n = r->sample_ct;
+  const uintptr_t bit_bytes = BitCtToAlignedWordCt(r->N) * sizeof(uintptr_t) + 64;
+  PgenVariant pgv;
+  memset(&pgv, 0, sizeof(pgv));
+  unsigned char *s01 = nullptr, *s10 = nullptr, *v01 = nullptr, *v10 = nullptr, *wide = nullptr;
+  cachealigned_malloc(RoundUpPow2(bit_bytes, kCacheline), &s01);
+  cachealigned_malloc(RoundUpPow2(bit_bytes, kCacheline), &s10);
+  cachealigned_malloc(RoundUpPow2(r->N + 64, kCacheline), &v01);
+  cachealigned_malloc(RoundUpPow2(2 * static_cast<uintptr_t>(r->N) + 64, kCacheline), &v10);
+  cachealigned_malloc(RoundUpPow2(2 * static_cast<uintptr_t>(r->N) + 256, kCacheline), &wide);
+  pgv.genovec = r->genovec;
+  pgv.patch_01_set = reinterpret_cast<uintptr_t*>(s01);
+  pgv.patch_10_set = reinterpret_cast<uintptr_t*>(s10);
+  pgv.patch_01_vals = reinterpret_cast<AlleleCode*>(v01);
+  pgv.patch_10_vals = reinterpret_cast<AlleleCode*>(v10);
+  int rc = 0;
+  for (uint32_t v = v0; v < v1 && !rc; ++v) {
+    PglErr e = PgrGetM(r->sample_include, r->pssi, n, v, &r->pgr, &pgv);
+    if (e != kPglRetSuccess) {
+      rc = static_cast<int>(e);
+      break;
+    }
+    ZeroTrailingNyps(n, pgv.genovec);
+    PglMultiallelicSparseToDenseMiss(&pgv, n, reinterpret_cast<AlleleCode*>(wide));
+    memcpy(out + static_cast<size_t>(v - v0) * n * 2, wide, static_cast<size_t>(n) * 2);
+  }
+  aligned_free(s01);
+  aligned_free(s10);
+  aligned_free(v01);
+  aligned_free(v10);
+  aligned_free(wide);
+  return rc;
 }
 
 void ref_close(void* h) {

@@ -90,6 +90,8 @@ SYMBOLS = {
     "pd_missing_by_sample": (C.c_int, [_vp, _u32, _u32, _vp]),
     "pd_sample_counts": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),
     "pd_decode_i8": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "pd_decode_alleles": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "pd_set_allele_counts": (C.c_int, [_vp, _vp, _u32]),
     "pd_decode_start": (C.c_int, [_vp, _u32, _u32, C.POINTER(_vp)]),
     "pd_decode_fetch": (C.c_int, [_vp, _u32, _u32, _vp]),
     "pd_decode_i8_valid": (C.c_int, [_vp, _u32, _u32, _u32, _vp, _vp]),

@@ -460,6 +460,40 @@ int pd_set_sample_subset(pd_ctx* c, const uint64_t* sample_include, uint32_t sub
   return PD_OK;
 }
 
+int pd_set_allele_counts(pd_ctx* c, const uint32_t* allele_cts, uint32_t n) {
+  if (!c) return PD_ERR_INVALID_ARG;
+  if (allele_cts) {
+    if (n != c->idx.variant_ct) return c->SetError(PD_ERR_INVALID_ARG, "pd_set_allele_counts: one count per variant is required");
+    for (uint32_t v = 0; v < n; ++v) {
+      if (allele_cts[v] < 2 || allele_cts[v] > 255) {
+        return c->SetError(PD_ERR_NOT_SUPPORTED, "pd_set_allele_counts: allele counts must lie in 2..255 (pgenlib's own limit)");
+      }
+    }
+  }
+  if (c->group) {
+    for (pd_ctx* s : c->group->shards) {
+      const int rc = pd_set_allele_counts(s, allele_cts, n);
+      if (rc != PD_OK) return c->SetError(rc, s->last_error);
+    }
+    return PD_OK;
+  }
+  std::lock_guard<std::mutex> lock(c->mu);
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);  // no kernel may be reading the old table
+  if (!allele_cts) {
+    c->idx.allele_cts.clear();
+    c->d_allele_cts.Free();
+    return PD_OK;
+  }
+  c->idx.allele_cts.resize(n);
+  for (uint32_t v = 0; v < n; ++v) c->idx.allele_cts[v] = static_cast<uint8_t>(allele_cts[v]);
+  if (!n) return PD_OK;
+  cudaError_t e = c->d_allele_cts.Reserve(n);
+  if (e == cudaSuccess) e = cudaMemcpy(c->d_allele_cts.p, c->idx.allele_cts.data(), n, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) return CheckCuda(c, e, "allele count upload");
+  return PD_OK;
+}
+
 int pd_load_resident(pd_ctx* c, uint32_t v_begin, uint32_t v_end) {
   if (!c) return PD_ERR_INVALID_ARG;
   if (c->group) return GroupLoadResident(c, v_begin, v_end);

@@ -326,6 +326,62 @@ int pd_decode_phased(pd_ctx* c, uint32_t v_begin, uint32_t v_end, int8_t* out) {
   return rc != PD_OK ? rc : rc2;
 }
 
+int pd_decode_alleles(pd_ctx* c, uint32_t v_begin, uint32_t v_end, uint8_t* out) {
+  if (!c || (!out && v_end > v_begin)) return PD_ERR_INVALID_ARG;
+  if (c->group) {
+    const size_t n = EffectiveSamples(c);
+    return GroupRunRanges(c, v_begin, v_end, 1, [&](pd_ctx* s, uint32_t a, uint32_t b, uint32_t row) {
+      return pd_decode_alleles(s, a, b, out + 2 * row * n);
+    });
+  }
+  std::lock_guard<std::mutex> lock(c->mu);
+  cudaSetDevice(c->device);
+  const uint32_t N = c->idx.sample_ct;
+  const uint32_t n_out = c->subset.active ? c->subset.count : N;
+  if (v_begin >= v_end || !n_out) {
+    if (v_begin > v_end || v_end > c->idx.variant_ct) return c->SetError(PD_ERR_INVALID_ARG, "variant range out of bounds");
+    return PD_OK;
+  }
+  if (c->idx.has_multiallelic && c->idx.allele_cts.empty()) {
+    return c->SetError(PD_ERR_INVALID_ARG,
+                       "pd_decode_alleles: the file has multiallelic records but stores no allele counts: "
+                       "call pd_set_allele_counts (counts from the .pvar) first");
+  }
+  // rows per batch: 128 MiB of code pairs per buffer
+  const uint64_t kOutBytes = 128ull << 20;
+  const uint64_t row_bytes = 2ull * n_out;
+  const uint32_t max_rows = static_cast<uint32_t>(std::max<uint64_t>(1, std::min<uint64_t>(65535, kOutBytes / row_bytes)));
+  OutPipe pipe;
+  int rc = pipe.Init(c, out, static_cast<size_t>(max_rows) * row_bytes);
+  if (rc != PD_OK) return rc;
+  const uint32_t* idx = c->subset.active ? c->subset.d_idx.as<uint32_t>() : nullptr;
+  if (idx) {
+    const cudaError_t e = c->d_phase_raw.Reserve(static_cast<size_t>(max_rows) * ((N + 7) & ~7u) * 2 + 64);
+    if (e != cudaSuccess) return CheckCuda(c, e, "allele scratch allocation");
+  }
+  cudaEventRecord(c->ev_c0, c->stream);
+  rc = RunRows(c, v_begin, v_end, max_rows, 0, [&](const RowBatch& b, const pdk::RecIndex& ix, cudaStream_t s) {
+    void* dev = nullptr;
+    int slot = 0;
+    int r = pipe.Acquire(&dev, &slot);
+    if (r != PD_OK) return r;
+    pdk::launch_expand_alleles(ix, b.rows, b.d_vlist, b.v_first, idx, n_out, c->d_phase_raw.as<uint8_t>(),
+                               static_cast<uint8_t*>(dev), DevErr(c), s, &c->launch_stats);
+    c->stats.scan_launches += 1;
+    return pipe.Send(slot, s, out + static_cast<size_t>(b.row0) * row_bytes, static_cast<size_t>(b.n) * row_bytes);
+  });
+  const int rc2 = pipe.Finish();
+  cudaEventRecord(c->ev_c1, c->stream);
+  cudaEventSynchronize(c->ev_c1);
+  if (rc == PD_OK && rc2 == PD_OK) {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev_c0, c->ev_c1);
+    c->stats.call_ms = ms;
+    c->stats.kernel_ms = pipe.produce_ms;
+  }
+  return rc != PD_OK ? rc : rc2;
+}
+
 int pd_device_result(pd_ctx* c, uint32_t which, void** dev_ptr, uint64_t* bytes) {
   if (!c || !dev_ptr || !bytes) return PD_ERR_INVALID_ARG;
   if (c->group) {  // after the all-reduce every device holds the totals: hand out the first device's copy

@@ -215,6 +215,22 @@ class PgenContext:
         self._check(self._lib.pd_hwe_lnp_from_counts(self._h, _p(counts), counts.shape[0], int(bool(midp)), _p(out)))
         return out
 
+    def set_allele_counts(self, allele_cts) -> None:
+        """Per-variant allele counts from the .pvar (None clears them); needed by decode_alleles."""
+        if allele_cts is None:
+            self._check(self._lib.pd_set_allele_counts(self._h, None, 0))
+            return
+        a = np.ascontiguousarray(allele_cts, dtype=np.uint32)
+        self._check(self._lib.pd_set_allele_counts(self._h, _p(a), a.size))
+
+    def decode_alleles(self, v0=0, v1=None) -> np.ndarray:
+        """(rows, n_out, 2) uint8 allele codes (PgrGetM + PglMultiallelicSparseToDenseMiss), 255 = missing."""
+        info = self.info()
+        v1 = info.variant_ct if v1 is None else v1
+        out = np.zeros((max(v1 - v0, 0), info.effective_sample_ct, 2), dtype=np.uint8)
+        self._check(self._lib.pd_decode_alleles(self._h, v0, v1, _p(out)))
+        return out
+
     def hwe_xchr_from_counts(self, c5, midp=False) -> np.ndarray:
         """c5: (n, 5) female hom_ref / het / hom_alt, male ref / alt."""
         c5 = np.ascontiguousarray(c5, dtype=np.uint32).reshape(-1, 5)

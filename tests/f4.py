@@ -17,8 +17,10 @@ def _bits(mask: np.ndarray) -> np.ndarray:
     return w
 
 
-def write_multiallelic(path: str, V: int, N: int, seed: int):
-    """Returns the (V, N) main-track codes that went in (0 REF/REF, 1 REF/ALTx, 2 ALTx/ALTy, 3 missing)."""
+def write_multiallelic(path: str, V: int, N: int, seed: int, rare_every: int = 0):
+    """Returns the (V, N) main-track codes that went in (0 REF/REF, 1 REF/ALTx, 2 ALTx/ALTy, 3 missing).
+    rare_every = k > 0: every k-th variant has rare ALT2+ alleles, so that pgenlib's writer stores its patch sets as
+    sample-id lists (aux1 mode 1) instead of bit arrays (mode 0)."""
     from oracle import ref
 
     rng = np.random.default_rng(seed)
@@ -31,6 +33,9 @@ def write_multiallelic(path: str, V: int, N: int, seed: int):
         k = int(allele_cts[v])
         freqs = rng.dirichlet(np.ones(k) * 0.7)
         freqs[0] += 1.0   # REF-major
+        if rare_every and v % rare_every == 0 and k > 2:
+            freqs[1] += 1.0
+            freqs[2:] *= 0.01  # a handful of ALT2+ carriers among many REF/ALT1 and ALT1/ALT1 calls
         freqs /= freqs.sum()
         a = rng.choice(k, size=N, p=freqs)
         b = rng.choice(k, size=N, p=freqs)

@@ -55,6 +55,78 @@ def test_multiallelic_records_read_as_pgenlib_reads_them(tmp_path, refmod_gpu, k
         assert isinstance(nat.PD_ERR_NOT_SUPPORTED, int)
 
 
+def _aux1_modes(path, vrtypes, fpos, N):
+    """(aux1a mode, aux1b mode) of every multiallelic record whose main track is a plain 2-bit array (its patch track
+    then starts ceil(N / 4) bytes into the record; pgen_spec.tex:469-479)."""
+    raw = np.fromfile(path, dtype=np.uint8)
+    out = []
+    for v in np.nonzero(((vrtypes & 8) != 0) & ((vrtypes & 7) == 0))[0]:
+        b = int(raw[int(fpos[v]) + (N + 3) // 4])
+        out.append((b & 15, b >> 4))
+    return out
+
+
+@pytest.mark.parametrize("kw", [dict(), dict(tile_bytes=4096, n_staging=2), dict(devices=[0])])
+@pytest.mark.parametrize("N", [37, 1501, 20011])
+def test_decode_alleles_matches_pgrgetm(tmp_path, refmod_gpu, kw, N):
+    """pd_decode_alleles = PgrGetM + PglMultiallelicSparseToDenseMiss (pgenlib_read.cc:6668-6681,
+    pgenlib_misc.cc:3552-3578): allele counts 2..40 (every aux1a / aux1b value width), patch sets stored as bit arrays
+    and as sample-id lists, every main-track type the writer picks, streamed / tiny tiles / resident / a group context,
+    sub-ranges and a sample subset."""
+    from plinking_duck_b200 import _native as nat
+    from plinking_duck_b200.pgen import PgenContext
+
+    ref = refmod_gpu
+    V = 240 if N < 20000 else 90
+    path = str(tmp_path / "ma.pgen")
+    codes, allele_cts = f4.write_multiallelic(path, V, N, seed=21 + N, rare_every=2)
+    with ref.RefPgen(path, allele_cts=allele_cts) as r:
+        exp = r.decode_alleles()
+        sub = np.arange(1, N, 3, dtype=np.uint32)
+        r.set_subset(sub)
+        exp_sub = r.decode_alleles()
+    # the biallelic view of the codes is the main track that went in
+    lo, hi = exp[..., 0].astype(int), exp[..., 1].astype(int)
+    assert np.array_equal(np.where(lo == 255, 3, np.where(hi == 0, 0, np.where(lo == 0, 1, 2))), codes)
+    with PgenContext(path, **kw) as c:
+        vt, fpos = c.index()
+        if N >= 1501:
+            modes = _aux1_modes(path, vt, fpos, N)
+            assert any(a == 0 for a, _ in modes) and any(b == 0 for _, b in modes), "no bit-array patch set in the fixture"
+            assert any(a == 1 for a, _ in modes) and any(b == 1 for _, b in modes), "no id-list patch set in the fixture"
+        with pytest.raises(nat.PlinkGpuError) as ei:
+            c.decode_alleles()
+        assert "pd_set_allele_counts" in str(ei.value)
+        c.set_allele_counts(allele_cts)
+        for resident in (False, True):
+            if resident:
+                c.load_resident()
+            got = c.decode_alleles()
+            bad = np.nonzero((got != exp).any(axis=(1, 2)))[0]
+            assert bad.size == 0, f"variants {bad[:8]} differ (allele counts {allele_cts[bad[:8]]}, vrtypes {vt[bad[:8]]})"
+            assert np.array_equal(c.decode_alleles(V // 3, V // 3 + 17), exp[V // 3:V // 3 + 17])
+        c.set_subset(sub)
+        assert np.array_equal(c.decode_alleles(), exp_sub)
+        c.set_subset(None)
+        # the biallelic entry points are unaffected by the table
+        assert np.array_equal(c.decode_i8(), np.where(codes == 3, -9, codes).astype(np.int8))
+        with pytest.raises(nat.PlinkGpuError):
+            c.set_allele_counts(allele_cts[:-1])
+
+
+def test_decode_alleles_on_biallelic_files(golden):
+    """Files without patch tracks need no allele counts: 0,0 / 0,1 / 1,1 / 255,255 from the main track."""
+    from conftest import fixture_path
+    from plinking_duck_b200.pgen import PgenContext
+
+    for name in ("pgen_example", "streaming_example", "syn_n1000"):
+        with PgenContext(fixture_path(name)) as c:
+            got = c.decode_alleles()
+        g = golden[name + "/i8"].astype(int)
+        exp = np.stack([np.where(g == -9, 255, np.where(g == 2, 1, 0)), np.where(g == -9, 255, np.where(g >= 1, 1, 0))], axis=-1)
+        assert np.array_equal(got, exp.astype(np.uint8)), name
+
+
 def test_dosage_phase_tracks_are_skipped_like_pgenlib(tmp_path, refmod_gpu):
     """vrtype bit 7: PgrGetD / PgrGetDCounts ignore the dphase values behind the dosage track; the hardcall phase
     track in front of it is read by PgrGetP."""
