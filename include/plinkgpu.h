@@ -253,8 +253,10 @@ int pd_tidy_i8(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, uint32_t emit_mask
  *      phased := true).  out: (v_end - v_begin) x n_out x 2 int8 allele pairs in subset order:
  *      hom-ref 0,0; hom-alt 1,1; missing -9,-9; het 1,0 when the record's hardcall-phase track marks the
  *      sample phased with the ALT allele first, else 0,1 (phased REF|ALT and unphased hets alike, as the
- *      reference).  Variants without a phase track decode every het as 0,1.  Multiallelic records with a
- *      phase track return PD_ERR_NOT_SUPPORTED. ---- */
+ *      reference).  Variants without a phase track decode every het as 0,1.  Records with BOTH a multiallelic
+ *      patch track and a phase track are read once pd_set_allele_counts supplied the allele counts (the phase
+ *      track counts the ALTx/ALTy calls of the patch set among its hets: pgenlib_read.cc:6874-6962; pgenlib needs
+ *      allele_idx_offsets for the same reason) and return PD_ERR_NOT_SUPPORTED without them. ---- */
 int pd_decode_phased(pd_ctx* ctx, uint32_t v_begin, uint32_t v_end, int8_t* out);
 /* Multiallelic hardcalls: replaces PgrGetM + PglMultiallelicSparseToDenseMiss (pgenlib_read.cc:6668-6681,
  * pgenlib_misc.cc:3552-3578; the aux1a / aux1b patch sets of pgen_spec.tex:469-564).  out[(row * n + s) * 2 + {0,1}] =

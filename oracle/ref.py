@@ -69,6 +69,8 @@ def lib():
         L.ref_ld_pair.argtypes = [vp, u32, u32, vp, C.POINTER(u32), C.POINTER(u32)]
         L.ref_writer_open_ex.argtypes = [C.c_char_p, u32, u32, u32, vp, C.POINTER(vp)]
         L.ref_writer_append_multiallelic.argtypes = [vp, vp, vp, vp, u32, vp, vp, u32, u32]
+        L.ref_writer_append_multiallelic_hphase.argtypes = [vp, vp, vp, vp, u32, vp, vp, u32, vp, vp, u32]
+        L.ref_writer_append_multiallelic_hphase.restype = C.c_int
         L.ref_writer_append_dphase.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, u32, u32]
         L.ref_writer_close.argtypes = [vp]
         _lib = L
@@ -351,6 +353,12 @@ class RefWriter:
         if rc:
             raise IOError(f"SpgwAppendBiallelicGenovec rc={rc}")
 
+    def append_hphase(self, genovec, phasepresent, phaseinfo):
+        rc = lib().ref_writer_append_phased(self._h, _p(np.ascontiguousarray(genovec, dtype=np.uint64)), _p(self._bits(phasepresent)),
+                                            _p(self._bits(phaseinfo)))
+        if rc:
+            raise IOError(f"SpgwAppendBiallelicGenovecHphase rc={rc}")
+
     def append_multiallelic(self, genovec, set01, vals01, set10, vals10, allele_ct):
         v01 = np.ascontiguousarray(vals01, dtype=np.uint8)
         v10 = np.ascontiguousarray(vals10, dtype=np.uint8).reshape(-1)
@@ -358,6 +366,15 @@ class RefWriter:
                                                   _p(v01), v01.size, _p(self._bits(set10)), _p(v10), v10.size // 2, int(allele_ct))
         if rc:
             raise IOError(f"SpgwAppendMultiallelicSparse rc={rc}")
+
+    def append_multiallelic_hphase(self, genovec, set01, vals01, set10, vals10, phasepresent, phaseinfo, allele_ct):
+        v01 = np.ascontiguousarray(vals01, dtype=np.uint8)
+        v10 = np.ascontiguousarray(vals10, dtype=np.uint8).reshape(-1)
+        rc = lib().ref_writer_append_multiallelic_hphase(
+            self._h, _p(np.ascontiguousarray(genovec, dtype=np.uint64)), _p(self._bits(set01)), _p(v01), v01.size,
+            _p(self._bits(set10)), _p(v10), v10.size // 2, _p(self._bits(phasepresent)), _p(self._bits(phaseinfo)), int(allele_ct))
+        if rc:
+            raise IOError(f"SpgwAppendMultiallelicGenovecHphase rc={rc}")
 
     def append_dphase(self, genovec, phasepresent, phaseinfo, dosage_present, dphase_present, dosage_main, dphase_delta):
         dm = np.ascontiguousarray(dosage_main, dtype=np.uint16)

@@ -863,6 +863,28 @@ int ref_writer_append_multiallelic(void* h, const uint64_t* genovec, const uint6
                                                        patch_01_ct, patch_10_ct, &w->spgw));
 }
 
+// Multiallelic hardcalls with a hardcall-phase track (SpgwAppendMultiallelicGenovecHphase; writer opened with flag 2
+// and allele counts).  phasepresent may only be set at hets of the full genotype (01 calls and ALTx/ALTy, x != y).
+int ref_writer_append_multiallelic_hphase(void* h, const uint64_t* genovec, const uint64_t* patch_01_set,
+                                          const uint8_t* patch_01_vals, uint32_t patch_01_ct, const uint64_t* patch_10_set,
+                                          const uint8_t* patch_10_vals, uint32_t patch_10_ct, const uint64_t* phasepresent,
+                                          const uint64_t* phaseinfo, uint32_t allele_ct) {
+  Writer* w = static_cast<Writer*>(h);
+  StageGenovec(w, genovec);
+  const uintptr_t aligned_words = BitCtToAlignedWordCt(w->N);
+  const size_t nw = BitCtToWordCt(w->N) * sizeof(uintptr_t);
+  std::vector<uintptr_t> s01(aligned_words + 8, 0), s10(aligned_words + 8, 0), pp(aligned_words + 8, 0), pi(aligned_words + 8, 0);
+  memcpy(s01.data(), patch_01_set, nw);
+  memcpy(s10.data(), patch_10_set, nw);
+  memcpy(pp.data(), phasepresent, nw);
+  memcpy(pi.data(), phaseinfo, nw);
+  std::vector<AlleleCode> v01(patch_01_ct + 64, 0), v10(2 * static_cast<size_t>(patch_10_ct) + 64, 0);
+  for (uint32_t i = 0; i < patch_01_ct; ++i) v01[i] = patch_01_vals[i];
+  for (uint32_t i = 0; i < 2 * patch_10_ct; ++i) v10[i] = patch_10_vals[i];
+  return static_cast<int>(SpgwAppendMultiallelicGenovecHphase(w->genovec, s01.data(), v01.data(), s10.data(), v10.data(), pp.data(),
+                                                              pi.data(), allele_ct, patch_01_ct, patch_10_ct, &w->spgw));
+}
+
 // Dosages with a dosage-phase track (SpgwAppendBiallelicGenovecDphase16; writer opened with flag 4).
 int ref_writer_append_dphase(void* h, const uint64_t* genovec, const uint64_t* phasepresent, const uint64_t* phaseinfo,
                              const uint64_t* dosage_present, const uint64_t* dphase_present, const uint16_t* dosage_main,

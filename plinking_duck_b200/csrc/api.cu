@@ -27,7 +27,7 @@ void DestroyCtx(pd_ctx* c) {
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
   if (c->d2h_stream) cudaStreamSynchronize(c->d2h_stream);
-  c->d_fpos.Free(); c->d_vrtypes.Free(); c->d_ldbase.Free(); c->d_base_slot.Free(); c->d_slot_vidx.Free(); c->d_allele_cts.Free();
+  c->d_fpos.Free(); c->d_vrtypes.Free(); c->d_ldbase.Free(); c->d_base_slot.Free(); c->d_slot_vidx.Free(); c->d_allele_cts.Free(); c->d_mhet.Free();
   c->d_resident.Free();
   for (auto& b : c->h_stage) b.Free();
   for (auto& b : c->d_stage) b.Free();

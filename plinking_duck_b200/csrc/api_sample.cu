@@ -303,6 +303,14 @@ int pd_decode_phased(pd_ctx* c, uint32_t v_begin, uint32_t v_end, int8_t* out) {
     const cudaError_t e = c->d_phase_raw.Reserve(static_cast<size_t>(max_rows) * ((N + 7) & ~7u) * 2 + 64);
     if (e != cudaSuccess) return CheckCuda(c, e, "phase scratch allocation");
   }
+  // records with a multiallelic patch track AND a phase track need the allele counts (pd_set_allele_counts) and a
+  // bit array per CTA; without the counts they report PD_ERR_NOT_SUPPORTED
+  uint32_t* mhet = nullptr;
+  if (c->idx.has_multiallelic && c->idx.has_phase && !c->idx.allele_cts.empty()) {
+    const cudaError_t e = c->d_mhet.Reserve(pdk::phased_mhet_scratch_bytes(N));
+    if (e != cudaSuccess) return CheckCuda(c, e, "phase scratch allocation");
+    mhet = c->d_mhet.as<uint32_t>();
+  }
   cudaEventRecord(c->ev_c0, c->stream);
   rc = RunRows(c, v_begin, v_end, max_rows, 0, [&](const RowBatch& b, const pdk::RecIndex& ix, cudaStream_t s) {
     void* dev = nullptr;
@@ -310,7 +318,7 @@ int pd_decode_phased(pd_ctx* c, uint32_t v_begin, uint32_t v_end, int8_t* out) {
     int r = pipe.Acquire(&dev, &slot);
     if (r != PD_OK) return r;
     pdk::launch_expand_phased(ix, b.rows, b.d_vlist, b.v_first, idx, n_out, c->d_phase_raw.as<int8_t>(),
-                              static_cast<int8_t*>(dev), DevErr(c), s, &c->launch_stats);
+                              static_cast<int8_t*>(dev), DevErr(c), s, &c->launch_stats, mhet);
     c->stats.scan_launches += 1;
     return pipe.Send(slot, s, out + static_cast<size_t>(b.row0) * row_bytes, static_cast<size_t>(b.n) * row_bytes);
   });

@@ -89,6 +89,7 @@ struct pd_ctx_impl {
   // device copies of the index (variable-width files)
   DevBuf d_fpos, d_vrtypes, d_ldbase, d_base_slot, d_slot_vidx;
   DevBuf d_allele_cts;  // [V] bytes, only for files that store allele counts
+  DevBuf d_mhet;        // K5p: per-CTA bit arrays of ALTx/ALTy calls (multiallelic + phased records)
   std::vector<uint32_t> base_slot;  // [V]: scratch slot of the LD base (non-type-0 bases), else ~0u
   std::vector<uint32_t> slot_vidx;  // slot -> base variant
 

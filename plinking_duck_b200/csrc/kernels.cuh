@@ -122,7 +122,13 @@ void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint
 // UnpackPhasedGenotypes.  raw_scratch: nrows x roundup8(N) x 2 bytes, only used with a subset.
 void launch_expand_phased(const RecIndex& ix, const DenseRows& rows, const uint32_t* vlist, uint32_t v0,
                           const uint32_t* subset_idx, uint32_t n_out, int8_t* raw_scratch, int8_t* out, int* err,
-                          cudaStream_t s, LaunchStats* st);
+                          cudaStream_t s, LaunchStats* st, uint32_t* mhet_scratch = nullptr);
+// mhet_scratch: phased_mhet_scratch_bytes(N) of device memory, needed only for records that carry BOTH a multiallelic
+// patch track and a phase track (one bit array of N bits per CTA of the launch); nullptr -> such records report
+// PD_ERR_NOT_SUPPORTED.
+constexpr uint32_t kPhasedMaxBlocks = 148u * 16u;
+inline uint32_t phased_mhet_stride_words(uint32_t N) { return ((N + 31u) >> 5) + 2u; }
+size_t phased_mhet_scratch_bytes(uint32_t N);
 // K5v: int8 calls (0 where invalid) + validity bits in DuckDB's child-vector layout; vbits must be zero-filled
 // except for bits below bitbase in its first word (the previous batch's calls).
 void launch_expand_i8_valid(const DenseRows& rows, const uint32_t* subset_idx, uint32_t n_out, uint32_t call_mask,

@@ -7,6 +7,7 @@
 // [aux7/8 dosage phase, bit 7].  The dosage track can only be found by walking what precedes it:
 // the main track's difflist ends where its last varint group ends, and the phase track's length
 // depends on the number of heterozygous hardcalls (SkipAux2, pgenlib_read.cc:6844-6865).
+#include "aux1_device.cuh"
 #include "device_common.cuh"
 #include "kernels.cuh"
 
@@ -38,7 +39,7 @@ __device__ __forceinline__ bool difflist_end(const uint8_t* q, const uint8_t* en
     *out_end = q;
     return true;
   }
-  return difflist_walk(d, N, lane, [](uint32_t, uint32_t, uint32_t) {}, out_end);
+  return difflist_walk_lanes(d, N, lane, [](uint32_t, uint32_t, uint32_t) {}, out_end);  // end-finding only: the small walker keeps K5p at 50 registers
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -387,14 +388,20 @@ __device__ __forceinline__ uint32_t warp_excl_scan(uint32_t x, int lane, uint32_
   return incl - x;
 }
 
+// MULTI: compiled with the multiallelic + phased pre-pass (only launched for files that need it: it costs registers).
+template <bool MULTI>
 __global__ void __launch_bounds__(kThreads)
 k_expand_phased(RecIndex ix, DenseRows rows, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t out_stride_pairs,
-                int8_t* __restrict__ out, int* __restrict__ err) {
+                int8_t* __restrict__ out, int* __restrict__ err, uint32_t* __restrict__ mhet_scratch,
+                uint32_t mhet_stride_words) {
   // One CTA (8 warps) per row: the row is cut into 8 contiguous parts of whole 512-sample steps; a warp
   // first counts the hets of its part, the counts are exchanged through shared memory, and the flag
   // offset of a part is a popcount over the aux2 bits before it -- so the parts expand independently.
   constexpr int kWarps = kThreads / 32;
   __shared__ uint32_t sm_het[kWarps];
+  __shared__ uint32_t sm_c10[kWarps];
+  __shared__ PatchSet sm_setb;
+  __shared__ uint32_t sm_wb;
   __shared__ const uint8_t* sm_q;
   __shared__ int sm_bad;
   const int lane = threadIdx.x & 31;
@@ -423,11 +430,109 @@ k_expand_phased(RecIndex ix, DenseRows rows, const uint32_t* __restrict__ vlist,
       if (valid < 16) x &= (1u << (2 * valid)) - 1u;
       return x;
     };
+    // ---- multiallelic record with a phase track: the phase track counts the ALTx/ALTy (x != y) calls of the patch
+    // set aux1b among its hets (PgrDetectGenoarrHetsMultiallelic / GetAux1bHets, pgenlib_read.cc:5270-5409,6874-6962),
+    // although the biallelic view returns them as hom-alt and their phase bits are dropped.  They are marked in a
+    // per-CTA bit array (halfword w = samples 16 w .. 16 w + 15) before the hets are counted. ----
+    const bool mp = MULTI && (vrtype & 0x18u) == 0x18u && mhet_scratch != nullptr && ix.allele_cts != nullptr;
+    uint16_t* mh = reinterpret_cast<uint16_t*>(mhet_scratch + static_cast<uint64_t>(blockIdx.x) * mhet_stride_words);
+    if (mp) {  // uniform for the CTA
+      uint32_t my01 = 0, my10 = 0;
+      for (uint32_t w = wbeg + lane; w < wend; w += 32) {
+        const uint32_t x = word_at(w);
+        my01 += __popc(x & ~(x >> 1) & kM5);
+        my10 += __popc((x >> 1) & ~x & kM5);
+        mh[w] = 0;
+      }
+      my01 = group_sum<32>(my01);
+      my10 = group_sum<32>(my10);
+      if (lane == 0) {
+        sm_het[wid] = my01;
+        sm_c10[wid] = my10;
+      }
+      __syncthreads();
+      uint32_t tot01 = 0, tot10 = 0, base10 = 0;
+#pragma unroll
+      for (int j = 0; j < kWarps; ++j) {
+        tot01 += sm_het[j];
+        tot10 += sm_c10[j];
+        if (j < wid) base10 += sm_c10[j];
+      }
+      if (wid == 0) {
+        int bad = 0;
+        PatchSet a, b;
+        b.mode = 15;
+        b.count = 0;
+        b.fset = b.vals = p;
+        const uint32_t allele_ct = ix.allele_cts[v];
+        const uint8_t* q = nullptr;
+        if (allele_ct < 3) {
+          bad = kErrMalformed;
+        } else if (!main_track_end(vrtype & 7u, p, end, N, lane, &q) || q >= end) {
+          bad = kErrMalformed;
+        } else {
+          const uint32_t modes = *q++;
+          if (!parse_patch_set(modes & 15u, q, end, N, tot01, aux1a_width(allele_ct), lane, a) ||
+              !parse_patch_set(modes >> 4, q, end, N, tot10, aux1b_width(allele_ct), lane, b)) {
+            bad = kErrMalformed;
+          }
+        }
+        if (bad) {
+          b.mode = 15;
+          q = nullptr;
+        }
+        if (lane == 0) {
+          sm_setb = b;
+          sm_wb = aux1b_width(max(allele_ct, 3u));
+          sm_q = q;  // start of aux2
+          sm_bad = bad;
+        }
+      }
+      __syncthreads();
+      const PatchSet B = sm_setb;
+      const uint32_t wb = sm_wb;
+      if (B.mode == 0) {
+        uint32_t flag = group_sum<32>(popcount_bits<32>(B.fset, base10, nullptr, 0, lane));
+        for (uint32_t w0 = wbeg; w0 < wend; w0 += 32) {
+          const uint32_t w = w0 + lane;
+          const uint32_t x = w < wend ? word_at(w) : 0u;
+          const uint32_t m10 = (x >> 1) & ~x & kM5;
+          const uint32_t c10 = __popc(m10);
+          uint32_t t10 = 0, tf = 0;
+          const uint32_t h10 = base10 + warp_excl_scan(c10, lane, &t10);
+          const uint32_t bits = c10 ? (load_bits32(B.fset, h10) & ((1u << c10) - 1u)) : 0u;
+          uint32_t off = flag + warp_excl_scan(__popc(bits), lane, &tf);
+          uint32_t marks = 0, n10 = 0;
+          for (uint32_t m = m10; m; m &= m - 1u, ++n10) {
+            if ((bits >> n10) & 1u) {
+              const uint32_t pair = aux1b_pair(B.vals, wb, off++);
+              if ((pair & 0xffu) != (pair >> 8)) marks |= 1u << ((__ffs(m) - 1) >> 1);
+            }
+          }
+          if (w < wend && marks) mh[w] = static_cast<uint16_t>(marks);
+          base10 += t10;
+          flag += tf;
+        }
+      } else if (B.mode == 1 && wid == 0 && B.count) {
+        uint32_t* words = mhet_scratch + static_cast<uint64_t>(blockIdx.x) * mhet_stride_words;
+        difflist_walk(B.list, N, lane, [&](uint32_t id, uint32_t, uint32_t k) {
+          const uint32_t pair = aux1b_pair(B.vals, wb, k);
+          if ((pair & 0xffu) != (pair >> 8)) atomicOr(words + (id >> 5), 1u << (id & 31u));
+        });
+      }
+      __syncthreads();
+    }
+    // all hets of word w: the 01 calls plus (multiallelic + phased records) the marked ALTx/ALTy calls
+    auto hets_of = [&](uint32_t w, uint32_t x) -> uint32_t {
+      uint32_t h = x & ~(x >> 1) & kM5;
+      if (mp) h |= spread16(__ldcg(reinterpret_cast<const unsigned short*>(mh) + w));
+      return h;
+    };
     // ---- hets of my part; warp 0 also finds the end of the main track ----
     uint32_t my_het = 0;
     for (uint32_t w = wbeg + lane; w < wend; w += 32) {
       const uint32_t x = word_at(w);
-      my_het += __popc(x & ~(x >> 1) & kM5);
+      my_het += __popc(hets_of(w, x));
     }
     my_het = group_sum<32>(my_het);
     if (lane == 0) sm_het[wid] = my_het;
@@ -436,7 +541,14 @@ k_expand_phased(RecIndex ix, DenseRows rows, const uint32_t* __restrict__ vlist,
       const uint8_t* q = nullptr;
       if (vrtype & 0x10u) {
         if (vrtype & 0x08u) {
-          bad = kErrNotSupported;  // multiallelic patch sets precede aux2; "next" row f4
+          // the patch sets precede aux2: found above when the caller supplied allele counts (pd_set_allele_counts);
+          // without them the track cannot be measured (pgenlib needs allele_idx_offsets for the same reason)
+          if (mp) {
+            q = sm_q;
+            bad = sm_bad;
+          } else {
+            bad = kErrNotSupported;
+          }
         } else {
           const uint32_t main = vrtype & 7u;
           q = p;
@@ -499,7 +611,7 @@ k_expand_phased(RecIndex ix, DenseRows rows, const uint32_t* __restrict__ vlist,
     for (uint32_t w0 = wbeg; w0 < wend; w0 += 32) {
       const uint32_t w = w0 + lane;
       const uint32_t x = w < wend ? word_at(w) : 0u;
-      const uint32_t hm = x & ~(x >> 1) & kM5;  // hets, one bit per sample at even positions
+      const uint32_t hm = w < wend ? hets_of(w, x) : 0u;  // hets, one bit per sample at even positions
       const uint32_t cnt = __popc(hm);
       uint32_t tot_h = 0, tot_f = 0;
       const uint32_t hoff = het_base + warp_excl_scan(cnt, lane, &tot_h);
@@ -532,8 +644,10 @@ k_expand_phased(RecIndex ix, DenseRows rows, const uint32_t* __restrict__ vlist,
           for (int h = 0; h < 2; ++h) {
             const uint32_t g = (x >> (4 * i + 2 * h)) & 3u;
             uint32_t pair = g == 0 ? 0x0000u : (g == 2 ? 0x0101u : (g == 3 ? 0xF7F7u : 0x0100u));
-            if (g == 1) {
-              if ((info >> hj) & 1u) pair = 0x0001u;
+            // a het of the phase track (with MULTI also the marked ALTx/ALTy calls); only 01 calls show their phase
+            const bool track_het = MULTI ? (((hm >> (4 * i + 2 * h)) & 1u) != 0u) : (g == 1);
+            if (track_het) {
+              if (g == 1 && ((info >> hj) & 1u)) pair = 0x0001u;
               ++hj;
             }
             word |= pair << (16 * h);
@@ -603,22 +717,36 @@ void launch_dosage_stats(const DenseRows& rows, const DosageLoc* loc, const uint
 
 void launch_expand_phased(const RecIndex& ix, const DenseRows& rows, const uint32_t* vlist, uint32_t v0,
                           const uint32_t* subset_idx, uint32_t n_out, int8_t* raw_scratch, int8_t* out, int* err,
-                          cudaStream_t s, LaunchStats* st) {
+                          cudaStream_t s, LaunchStats* st, uint32_t* mhet_scratch) {
   if (!rows.nrows || !n_out) return;
   uint64_t blocks = rows.nrows;  // one CTA per row
-  if (blocks > 148ull * 16) blocks = 148ull * 16;
+  if (blocks > kPhasedMaxBlocks) blocks = kPhasedMaxBlocks;
+  const uint32_t mstride = phased_mhet_stride_words(ix.N);
   if (!subset_idx) {
-    k_expand_phased<<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, rows, vlist, v0, ix.N, out, err);
+    if (mhet_scratch) {
+      k_expand_phased<true><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, rows, vlist, v0, ix.N, out, err,
+                                                                               mhet_scratch, mstride);
+    } else {
+      k_expand_phased<false><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, rows, vlist, v0, ix.N, out, err, nullptr, 0);
+    }
     if (st) st->launches++;
     return;
   }
   // subset: expand all raw samples, then gather the kept pairs (phase is a per-sample property)
   const uint32_t raw_stride = (ix.N + 7) & ~7u;  // keeps every scratch row 16-byte aligned
-  k_expand_phased<<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, rows, vlist, v0, raw_stride, raw_scratch, err);
+  if (mhet_scratch) {
+    k_expand_phased<true><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, rows, vlist, v0, raw_stride, raw_scratch,
+                                                                             err, mhet_scratch, mstride);
+  } else {
+    k_expand_phased<false><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, rows, vlist, v0, raw_stride, raw_scratch,
+                                                                              err, nullptr, 0);
+  }
   launch_gather_pairs(reinterpret_cast<const uint16_t*>(raw_scratch), raw_stride, subset_idx, n_out, rows.nrows,
                       reinterpret_cast<uint16_t*>(out), s, st);
   if (st) st->launches++;
 }
+
+size_t phased_mhet_scratch_bytes(uint32_t N) { return static_cast<size_t>(kPhasedMaxBlocks) * phased_mhet_stride_words(N) * 4; }
 
 void launch_gather_pairs(const uint16_t* raw, uint32_t raw_stride, const uint32_t* idx, uint32_t n_out, uint32_t nrows,
                          uint16_t* out, cudaStream_t s, LaunchStats* st) {

@@ -56,6 +56,63 @@ def write_multiallelic(path: str, V: int, N: int, seed: int, rare_every: int = 0
     return codes, allele_cts
 
 
+def write_multiallelic_phased(path: str, V: int, N: int, seed: int):
+    """Multiallelic AND biallelic variants, most of them with a hardcall-phase track (vrtype bits 3 + 4 together): the
+    phase track counts the ALTx/ALTy (x != y) calls among its hets.  Returns (allele pairs (V, N, 2) with 255 = missing
+    in file order lo <= hi, phasepresent, phaseinfo, allele counts)."""
+    from oracle import ref
+
+    rng = np.random.default_rng(seed)
+    allele_cts = rng.choice([2, 3, 3, 4, 5, 7, 18, 40], size=V).astype(np.uint32)
+    allele_cts[0] = 2
+    allele_cts[1] = 3
+    w = ref.RefWriter(path, V, N, 2, allele_cts)
+    pairs = np.zeros((V, N, 2), dtype=np.uint8)
+    pps = np.zeros((V, N), dtype=bool)
+    pis = np.zeros((V, N), dtype=bool)
+    for v in range(V):
+        k = int(allele_cts[v])
+        freqs = rng.dirichlet(np.ones(k) * 0.7)
+        freqs[0] += 0.6
+        if v % 3 == 0 and k > 2:
+            freqs[1] += 1.0
+            freqs[2:] *= 0.02   # patch sets as id lists
+        freqs /= freqs.sum()
+        a = rng.choice(k, size=N, p=freqs)
+        b = rng.choice(k, size=N, p=freqs)
+        lo, hi = np.minimum(a, b), np.maximum(a, b)
+        miss = rng.random(N) < 0.03
+        code = np.where(hi == 0, 0, np.where(lo == 0, 1, 2)).astype(np.int8)
+        code[miss] = 3
+        pairs[v, :, 0] = np.where(miss, 255, lo)
+        pairs[v, :, 1] = np.where(miss, 255, hi)
+        het = ~miss & (lo != hi)
+        mode = v % 4
+        if mode == 0:      # no phase track at all
+            pp = np.zeros(N, dtype=bool)
+        elif mode == 1:    # every het phased (aux2 without an explicit phasepresent array)
+            pp = het.copy()
+        else:
+            pp = het & (rng.random(N) < 0.6)
+        pi = pp & (rng.random(N) < 0.5)
+        pps[v], pis[v] = pp, pi
+        gv = synth.to_genovec_words(code[None, :])[0]
+        s01 = (code == 1) & (hi != 1)
+        s10 = (code == 2) & ~((lo == 1) & (hi == 1))
+        vals10 = np.stack([lo[s10], hi[s10]], axis=1)
+        if k == 2:
+            if pp.any():
+                w.append_hphase(gv, _bits(pp), _bits(pi))
+            else:
+                w.append(gv)
+        elif pp.any():
+            w.append_multiallelic_hphase(gv, _bits(s01), hi[s01], _bits(s10), vals10, _bits(pp), _bits(pi), k)
+        else:
+            w.append_multiallelic(gv, _bits(s01), hi[s01], _bits(s10), vals10, k)
+    w.close()
+    return pairs, pps, pis, allele_cts
+
+
 def write_dphase(path: str, V: int, N: int, seed: int):
     """Hardcalls + dosages, a third of the variants with an explicit dosage-phase track.  Returns the hardcall
     codes."""

@@ -114,6 +114,46 @@ def test_decode_alleles_matches_pgrgetm(tmp_path, refmod_gpu, kw, N):
             c.set_allele_counts(allele_cts[:-1])
 
 
+@pytest.mark.parametrize("kw", [dict(), dict(tile_bytes=4096, n_staging=2), dict(devices=[0])])
+@pytest.mark.parametrize("N", [37, 1501, 20011])
+def test_phased_decode_of_multiallelic_records(tmp_path, refmod_gpu, kw, N):
+    """Records with BOTH a multiallelic patch track and a hardcall-phase track: aux2 sits behind aux1 and counts the
+    ALTx/ALTy (x != y) calls of aux1b among its hets (ReadGenovecHphaseSubsetUnsafe, pgenlib_read.cc:6874-6962).
+    pd_decode_phased must return what PgrGetP + UnpackPhasedGenotypes return once pgenlib knows the allele counts --
+    and, like pgenlib, cannot read such records without them."""
+    from plinking_duck_b200 import _native as nat
+    from plinking_duck_b200.pgen import PgenContext
+
+    ref = refmod_gpu
+    V = 240 if N < 20000 else 90
+    path = str(tmp_path / "map.pgen")
+    pairs, pps, pis, allele_cts = f4.write_multiallelic_phased(path, V, N, seed=3 + N)
+    with ref.RefPgen(path, allele_cts=allele_cts) as r:
+        vt = r.vrtypes()
+        exp = r.decode_phased()
+        exp_al = r.decode_alleles()
+        sub = np.arange(1, N, 3, dtype=np.uint32)
+        r.set_subset(sub)
+        exp_sub = r.decode_phased()
+    assert ((vt & 0x18) == 0x18).any() and ((vt & 0x18) == 0x10).any() and ((vt & 0x18) == 0x08).any()
+    assert np.array_equal(exp_al, pairs)
+    with PgenContext(path, **kw) as c:
+        with pytest.raises(nat.PlinkGpuError) as ei:
+            c.decode_phased()
+        assert ei.value.code == nat.PD_ERR_NOT_SUPPORTED
+        c.set_allele_counts(allele_cts)
+        for resident in (False, True):
+            if resident:
+                c.load_resident()
+            got = c.decode_phased()
+            bad = np.nonzero((got != exp).any(axis=(1, 2)))[0]
+            assert bad.size == 0, f"variants {bad[:8]} differ (allele counts {allele_cts[bad[:8]]}, vrtypes {vt[bad[:8]]})"
+            assert np.array_equal(c.decode_phased(V // 3, V // 3 + 17), exp[V // 3:V // 3 + 17])
+            assert np.array_equal(c.decode_alleles(), pairs)
+        c.set_subset(sub)
+        assert np.array_equal(c.decode_phased(), exp_sub)
+
+
 def test_decode_alleles_on_biallelic_files(golden):
     """Files without patch tracks need no allele counts: 0,0 / 0,1 / 1,1 / 255,255 from the main track."""
     from conftest import fixture_path
