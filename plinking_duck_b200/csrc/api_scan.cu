@@ -34,6 +34,7 @@ int CountTile(pd_ctx_impl* c, const SubsetState& sub, const Tile& t, const pdk::
   if (slot_lo != 0xffffffffu) {
     scratch.stride = ((c->idx.sample_ct + 3) / 4 + 15) / 16 * 16 + 16;
     scratch.slot_lo = slot_lo;
+    scratch.slot_ct = slot_hi - slot_lo + 1;
     const size_t need = static_cast<size_t>(slot_hi - slot_lo + 1) * scratch.stride;
     if (need > c->d_scratch.cap) {
       // growing frees the old buffer: make sure no earlier tile still reads it

@@ -472,6 +472,35 @@ struct TileBytesGuard {
 
 }  // namespace
 
+// Dense copies of the LD bases that the rows of [v_lo, v_hi) refer to (those that are not plain 2-bit records, which
+// are read in place), decoded once per batch by a CTA each; k_densify's LD rows copy them.  Without this every LD row
+// decoded its base again, alone in its warp: with one-bit bases (a 12 k-entry difflist at 100k samples) that was most
+// of the time of k_densify on LD-compressed files.  Leaves *out empty when the range has no such base.
+int PrepareBases(pd_ctx_impl* c, const pdk::RecIndex& ix, uint32_t v_lo, uint32_t v_hi, cudaStream_t s,
+                 pdk::LdScratch* out) {
+  *out = pdk::LdScratch{};
+  if (!c->idx.has_ld || c->slot_vidx.empty() || v_lo >= v_hi) return PD_OK;
+  // bases of rows in [v_lo, v_hi) lie in [Ldbase(v_lo), v_hi); the slots of that range are contiguous
+  const uint32_t b_lo = c->idx.Ldbase(v_lo);
+  auto lo = std::lower_bound(c->slot_vidx.begin(), c->slot_vidx.end(), b_lo);
+  auto hi = std::lower_bound(c->slot_vidx.begin(), c->slot_vidx.end(), v_hi);
+  if (lo == hi) return PD_OK;
+  const uint32_t slot_lo = static_cast<uint32_t>(lo - c->slot_vidx.begin());
+  const uint32_t slot_ct = static_cast<uint32_t>(hi - lo);
+  out->stride = ((c->idx.sample_ct + 3) / 4 + 15) / 16 * 16 + 16;
+  out->slot_lo = slot_lo;
+  const size_t need = static_cast<size_t>(slot_ct) * out->stride;
+  if (need > c->d_scratch.cap) {
+    cudaStreamSynchronize(s);  // growing frees the old buffer: no earlier batch may still read it
+    const cudaError_t e = c->d_scratch.Reserve(need + (need >> 2));
+    if (e != cudaSuccess) return CheckCuda(c, e, "LD scratch allocation");
+  }
+  out->dense = c->d_scratch.as<uint8_t>();
+  out->slot_ct = slot_ct;
+  pdk::launch_decode_bases(ix, c->d_slot_vidx.as<uint32_t>(), *out, slot_lo + slot_ct - 1, DevErr(c), s, &c->launch_stats);
+  return PD_OK;
+}
+
 int RunRows(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t max_rows, uint64_t min_tile_bytes,
             const RowFn& fn) {
   // never reserve scratch for more rows than the range holds (a 1 GiB batch for a 100-variant file)
@@ -507,9 +536,12 @@ int RunRows(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t max_rows,
         b.rows.base = ix.data + (ix.fixed_start + static_cast<uint64_t>(v) * ix.fixed_width - ix.data_fpos);
         b.rows.stride = ix.fixed_width;
       } else {
+        pdk::LdScratch bases;
+        const int pr = PrepareBases(c, ix, v, v + b.n, s, &bases);
+        if (pr != PD_OK) return pr;
         pdk::launch_densify(ix, nullptr, v, b.n, c->d_dense.as<uint8_t>(), slot_stride,
                             c->d_rowptrs.as<const uint8_t*>(), DevWorkCounter(c), DevErr(c), s, &c->launch_stats,
-                            sparse);
+                            sparse, &bases);
         b.rows.ptrs = c->d_rowptrs.as<const uint8_t*>();
         if (sparse) {
           b.rows.nrows = std::min(b.n, cap);
@@ -565,8 +597,16 @@ int RunRowsList(pd_ctx_impl* c, const uint32_t* vlist, uint32_t n, uint32_t max_
         b.d_vlist = c->d_vlist.as<uint32_t>() + j;
         b.rows.nrows = b.n;
         b.rows.N = ix.N;
+        // lists: pre-decode the bases only when the list is dense in its range (else most would not be used)
+        pdk::LdScratch bases;
+        const uint32_t span = vlist[j + b.n - 1] + 1 - vlist[j];
+        if (span <= 4 * b.n) {
+          const int pr = PrepareBases(c, ix, vlist[j], vlist[j + b.n - 1] + 1, s, &bases);
+          if (pr != PD_OK) return pr;
+        }
         pdk::launch_densify(ix, b.d_vlist, 0, b.n, c->d_dense.as<uint8_t>(), slot_stride,
-                            c->d_rowptrs.as<const uint8_t*>(), DevWorkCounter(c), DevErr(c), s, &c->launch_stats);
+                            c->d_rowptrs.as<const uint8_t*>(), DevWorkCounter(c), DevErr(c), s, &c->launch_stats,
+                            nullptr, &bases);
         b.rows.ptrs = c->d_rowptrs.as<const uint8_t*>();
         const int r = fn(b, ix, s);
         if (r != PD_OK) return r;

@@ -411,9 +411,12 @@ __device__ __forceinline__ uint32_t swar_load(const uint8_t* ptr, uint32_t a, ui
   return w;
 }
 
+// team_rank / team_size: the warps of a CTA share one (long) list -- warp r takes groups r, r + size, ... of every
+// 32-group batch (size must divide 32; track_end is only meaningful with size 1).
 template <class F>
 __device__ __forceinline__ bool difflist_walk_swar(const Difflist& d, uint32_t N, int lane, F f,
-                                                   const uint8_t** track_end = nullptr) {
+                                                   const uint8_t** track_end = nullptr, uint32_t team_rank = 0,
+                                                   uint32_t team_size = 1) {
   bool ok = true;
   uint32_t batch_off = 0;  // a record is far below 4 GiB: 32-bit offsets into its delta stream
   const uint8_t* list_end = d.deltas;
@@ -451,11 +454,15 @@ __device__ __forceinline__ bool difflist_walk_swar(const Difflist& d, uint32_t N
       }
       return c;
     };
-    uint32_t start = start_of(0);
-    uint32_t room = room_of(0, start);
-    SwarChunk cur = load_group(0, start, room);
+    if (team_rank >= nb) {  // nothing of this batch is mine (warp-uniform)
+      batch_off += total;
+      continue;
+    }
+    uint32_t start = start_of(team_rank);
+    uint32_t room = room_of(team_rank, start);
+    SwarChunk cur = load_group(team_rank, start, room);
 #pragma unroll 1
-    for (uint32_t k = 0; k < nb; ++k) {
+    for (uint32_t k = team_rank; k < nb; k += team_size) {
       const uint32_t g = g0 + k;
       const uint32_t first_id = __shfl_sync(0xffffffffu, my_first, k);
       const bool last = g + 1 == d.ngroups;
@@ -470,10 +477,10 @@ __device__ __forceinline__ bool difflist_walk_swar(const Difflist& d, uint32_t N
       // the next group's bytes are requested before this group's arithmetic starts
       SwarChunk nxt{0u, 0u};
       uint32_t nstart = 0, nroom = 0;
-      if (k + 1 < nb) {
-        nstart = start_of(k + 1);
-        nroom = room_of(k + 1, nstart);
-        nxt = load_group(k + 1, nstart, nroom);
+      if (k + team_size < nb) {
+        nstart = start_of(k + team_size);
+        nroom = room_of(k + team_size, nstart);
+        nxt = load_group(k + team_size, nstart, nroom);
       }
       if (lane == 0) {
         if (first_id >= N) {
@@ -616,19 +623,32 @@ __device__ __forceinline__ uint32_t spread16(uint32_t x) {
   return x;
 }
 
-__device__ __forceinline__ bool decode_nonld_dense(uint32_t main, const uint8_t* p, const uint8_t* end, uint32_t N,
-                                                   uint32_t* dst, int lane) {
+// CTA = false: one warp decodes the record.  CTA = true: the `size` warps of a CTA decode it together (every thread of
+// the CTA must call, with rank = its warp): the fill is strided over the warps and a long difflist is split by
+// groups -- a one-bit record with a 12 k-entry list is ~200 us of serial latency for a single warp.
+template <bool CTA>
+__device__ __forceinline__ bool decode_nonld_dense_team(uint32_t main, const uint8_t* p, const uint8_t* end, uint32_t N,
+                                                        uint32_t* dst, int lane, uint32_t rank, uint32_t size) {
   const uint32_t nwords = (N + 15) >> 4;
   const uint32_t geno_bytes = (N + 3) >> 2;
+  const uint32_t first = CTA ? rank * 32u + static_cast<uint32_t>(lane) : static_cast<uint32_t>(lane);
+  const uint32_t step = CTA ? size * 32u : 32u;
+  auto sync = [] {
+    if (CTA) {
+      __syncthreads();
+    } else {
+      __syncwarp();
+    }
+  };
   if (main == 0) {
     if (static_cast<uint64_t>(end - p) < geno_bytes) return false;
-    for (uint32_t w = lane; w < nwords; w += 32) dst[w] = row_word(p, w);
-    __syncwarp();
+    for (uint32_t w = first; w < nwords; w += step) dst[w] = row_word(p, w);
+    sync();
     return true;
   }
   if (main == 5) {
-    for (uint32_t w = lane; w < nwords; w += 32) dst[w] = 0u;
-    __syncwarp();
+    for (uint32_t w = first; w < nwords; w += step) dst[w] = 0u;
+    sync();
     return true;
   }
   if (main == 1) {
@@ -639,41 +659,48 @@ __device__ __forceinline__ bool decode_nonld_dense(uint32_t main, const uint8_t*
     const uint32_t delta = common2 & 3u;
     if (low + delta > 3u) return false;
     const uint8_t* bits = p + 1;
-    for (uint32_t w = lane; w < nwords; w += 32) {
+    for (uint32_t w = first; w < nwords; w += step) {
       const uint32_t b16 = load_bits32(bits, static_cast<uint64_t>(w) << 4) & 0xffffu;
       dst[w] = low * kM5 + spread16(b16) * delta;
     }
-    __syncwarp();
+    sync();
     const uint8_t* q = bits + bit_bytes;
     Difflist d;
     if (!parse_difflist(q, end, N, true, d)) return false;
     bool ok = true;
     if (d.len) {
-      ok = difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g, uint32_t) {
+      auto patch = [&](uint32_t id, uint32_t g, uint32_t) {
         const uint32_t orig = low + (bit_at(bits, id) ? delta : 0u);
         atomicXor(&dst[id >> 4], (orig ^ g) << (2 * (id & 15)));
-      });
+      };
+      ok = CTA ? difflist_walk_swar(d, N, lane, patch, nullptr, rank, size) : difflist_walk(d, N, lane, patch);
     }
-    __syncwarp();
+    sync();
     return ok;
   }
   if (main == 4 || main == 6 || main == 7) {
     const uint32_t common = main & 3u;
-    for (uint32_t w = lane; w < nwords; w += 32) dst[w] = common * kM5;
-    __syncwarp();
+    for (uint32_t w = first; w < nwords; w += step) dst[w] = common * kM5;
+    sync();
     const uint8_t* q = p;
     Difflist d;
     if (!parse_difflist(q, end, N, true, d)) return false;
     bool ok = true;
     if (d.len) {
-      ok = difflist_walk(d, N, lane, [&](uint32_t id, uint32_t g, uint32_t) {
+      auto patch = [&](uint32_t id, uint32_t g, uint32_t) {
         atomicXor(&dst[id >> 4], (common ^ g) << (2 * (id & 15)));
-      });
+      };
+      ok = CTA ? difflist_walk_swar(d, N, lane, patch, nullptr, rank, size) : difflist_walk(d, N, lane, patch);
     }
-    __syncwarp();
+    sync();
     return ok;
   }
   return false;
+}
+
+__device__ __forceinline__ bool decode_nonld_dense(uint32_t main, const uint8_t* p, const uint8_t* end, uint32_t N,
+                                                   uint32_t* dst, int lane) {
+  return decode_nonld_dense_team<false>(main, p, end, N, dst, lane, 0, 1);
 }
 
 // LD-compressed record (type 2 / 3) on top of an already decoded copy of its base in dst:

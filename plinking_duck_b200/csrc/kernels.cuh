@@ -37,6 +37,7 @@ struct LdScratch {
   uint8_t* dense;          // slot s at dense + (s - slot_lo) * stride
   uint32_t stride;         // bytes per slot, multiple of 16
   uint32_t slot_lo;
+  uint32_t slot_ct;        // slots decoded (k_densify checks it; 0 = no scratch)
 };
 
 // Per-context launch state: every launch wrapper receives the owning context's copy, so one process can
@@ -113,11 +114,13 @@ struct SparseAcc {
   uint32_t* dense_count; // [1] rows appended to ptrs by this launch (zeroed by launch_densify)
 };
 
+// bases: dense copies of the LD bases of the batch (launch_decode_bases); LD rows then copy their base instead of
+// decoding it again.
 // Row r = variant vlist[r] (vlist != nullptr) or v0 + r.  Type-0 records are pointed at in place,
 // everything else (difflist, 1-bit, LD with its base resolved) is decoded into scratch slot r.
 void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint32_t nrows, uint8_t* scratch,
                     uint32_t slot_stride, const uint8_t** ptrs, uint32_t* work_counter, int* err, cudaStream_t s,
-                    LaunchStats* st, const SparseAcc* sparse = nullptr);
+                    LaunchStats* st, const SparseAcc* sparse = nullptr, const LdScratch* bases = nullptr);
 // out[(r * n_out + j) * 2 + {0,1}] = allele pair of sample subset_idx[j] (or j) -- PgrGetP +
 // UnpackPhasedGenotypes.  raw_scratch: nrows x roundup8(N) x 2 bytes, only used with a subset.
 void launch_expand_phased(const RecIndex& ix, const DenseRows& rows, const uint32_t* vlist, uint32_t v0,

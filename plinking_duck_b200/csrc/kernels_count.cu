@@ -298,19 +298,22 @@ __global__ void k_ld_fixup(RecIndex ix, uint32_t v_begin, uint32_t v_end, uint4*
 
 namespace {
 
-// One warp per scratch slot: dense copy of a non-type-0 record that LD records refer to.
+// One CTA per scratch slot: dense copy of a non-type-0 record that LD records refer to.  The warps of the CTA share
+// the record (decode_nonld_dense_team): bases are often common variants stored as one-bit records with difflists of
+// thousands of entries, which one warp walks in ~200 us (profiles/r02p_*: this kernel was 80 % of pd_counts on the
+// LD-compressed fileset with a warp per slot).
 __global__ void __launch_bounds__(kThreads)
 k_decode_bases(RecIndex ix, const uint32_t* __restrict__ slot_vidx, LdScratch scratch, uint32_t slot_hi,
                int* __restrict__ err) {
-  const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint32_t w = blockIdx.x;
   const int lane = threadIdx.x & 31;
   const uint32_t slot = scratch.slot_lo + w;
-  if (slot > slot_hi) return;
+  if (slot > slot_hi) return;  // uniform for the CTA
   const uint32_t v = slot_vidx[slot];
   const uint8_t* p = ix.data + (ix.fpos[v] - ix.data_fpos);
   const uint8_t* end = ix.data + (ix.fpos[v + 1] - ix.data_fpos);
   uint32_t* dst = reinterpret_cast<uint32_t*>(scratch.dense + static_cast<uint64_t>(w) * scratch.stride);
-  const bool ok = decode_nonld_dense(ix.vrtypes[v] & 7u, p, end, ix.N, dst, lane);
+  const bool ok = decode_nonld_dense_team<true>(ix.vrtypes[v] & 7u, p, end, ix.N, dst, lane, threadIdx.x >> 5, kThreads / 32);
   if (!ok && lane == 0) report_error(err, kErrMalformed, v);
 }
 
@@ -482,8 +485,7 @@ void launch_decode_bases(const RecIndex& ix, const uint32_t* slot_vidx, const Ld
                          int* err, cudaStream_t s, LaunchStats* st) {
   if (slot_hi < scratch.slot_lo) return;
   const uint32_t nslots = slot_hi - scratch.slot_lo + 1;
-  const uint32_t blocks = (nslots * 32 + kThreads - 1) / kThreads;
-  k_decode_bases<<<blocks, kThreads, 0, s>>>(ix, slot_vidx, scratch, slot_hi, err);
+  k_decode_bases<<<nslots, kThreads, 0, s>>>(ix, slot_vidx, scratch, slot_hi, err);
   if (st) st->launches++;
 }
 

@@ -67,7 +67,7 @@ template <bool SPARSE>
 __global__ void __launch_bounds__(kThreads, 3)
 k_densify(RecIndex ix, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t nrows, uint8_t* __restrict__ scratch,
           uint32_t slot_stride, const uint8_t** __restrict__ ptrs, uint32_t* __restrict__ work_counter,
-          int* __restrict__ err, SparseAcc sa) {
+          int* __restrict__ err, SparseAcc sa, LdScratch bases) {
   const int lane = threadIdx.x & 31;
   const uint32_t N = ix.N;
   const bool sparse = SPARSE && sa.dense_count != nullptr;
@@ -105,7 +105,18 @@ k_densify(RecIndex ix, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t
       const uint32_t bmain = ix.vrtypes[b] & 7u;
       const uint8_t* bp = ix.data + (ix.fpos[b] - ix.data_fpos);
       const uint8_t* bend = ix.data + (ix.fpos[b + 1] - ix.data_fpos);
-      ok = (b < v) && bmain != 2 && bmain != 3 && decode_nonld_dense(bmain, bp, bend, N, slot, lane);
+      ok = (b < v) && bmain != 2 && bmain != 3;
+      const uint32_t bs = ok && bases.slot_ct ? ix.base_slot[v] - bases.slot_lo : 0xffffffffu;
+      if (ok && bs < bases.slot_ct) {
+        // the base was decoded once for the whole batch (k_decode_bases): copy it
+        const uint4* src = reinterpret_cast<const uint4*>(bases.dense + static_cast<uint64_t>(bs) * bases.stride);
+        uint4* dst4 = reinterpret_cast<uint4*>(slot);
+        const uint32_t n16 = (((N + 3) >> 2) + 15) >> 4;
+        for (uint32_t i = lane; i < n16; i += 32) dst4[i] = src[i];
+        __syncwarp();
+      } else if (ok) {
+        ok = decode_nonld_dense(bmain, bp, bend, N, slot, lane);
+      }
       if (ok) ok = apply_ld_record(main, p, end, N, slot, lane);
     } else {
       ok = decode_nonld_dense(main, p, end, N, slot, lane);
@@ -589,7 +600,8 @@ k_count_rows(DenseRows rows, SubsetDev sub, uint4* __restrict__ out) {
 
 void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint32_t nrows, uint8_t* scratch,
                     uint32_t slot_stride, const uint8_t** ptrs, uint32_t* work_counter, int* err, cudaStream_t s,
-                    LaunchStats* st, const SparseAcc* sparse) {
+                    LaunchStats* st, const SparseAcc* sparse, const LdScratch* bases) {
+  const LdScratch bs = bases ? *bases : LdScratch{};
   if (sparse) cudaMemsetAsync(sparse->dense_count, 0, sizeof(uint32_t), s);
   if (!nrows) return;
   cudaMemsetAsync(work_counter, 0, sizeof(uint32_t), s);
@@ -598,10 +610,10 @@ void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint
   if (blocks > max_blocks) blocks = max_blocks;
   if (sparse) {
     k_densify<true><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, vlist, v0, nrows, scratch, slot_stride, ptrs,
-                                                                      work_counter, err, *sparse);
+                                                                      work_counter, err, *sparse, bs);
   } else {
     k_densify<false><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, vlist, v0, nrows, scratch, slot_stride,
-                                                                       ptrs, work_counter, err, SparseAcc{});
+                                                                       ptrs, work_counter, err, SparseAcc{}, bs);
   }
   if (st) st->launches++;
 }
