@@ -328,6 +328,32 @@ int pd_reset_stats(pd_ctx* ctx);
 /* Library / build identification: "plinkgpu <version> sm_100a". */
 const char* pd_version(void);
 
+/* ---- Multi-file filesets: variant-sharded, row-concatenated sources that share one sample set -- read_pfile's file
+ *      lists (src/pfile_reader.cpp:325-400 sources, :1003-1012 the sample-count check, :2133-2151 scan batches that
+ *      never span a file boundary).  One context per file (each may span GPUs through opts->n_devices); global variant
+ *      index g = variant g - offsets[f] of file f.  Ranged per-variant calls return the concatenation over the files a
+ *      range touches; per-sample calls return the sums over them (added in file order).  Every other entry point is
+ *      reached per file through pd_fileset_ctx.  A fileset is used by one thread at a time. ---- */
+typedef struct pd_fileset pd_fileset;
+int pd_fileset_open(const char* const* pgen_paths, uint32_t n_files, const pd_open_opts* opts, pd_fileset** out,
+                    char* errbuf, size_t errbuf_len);
+void pd_fileset_close(pd_fileset* fs);
+const char* pd_fileset_last_error(const pd_fileset* fs);
+uint32_t pd_fileset_file_count(const pd_fileset* fs);
+uint32_t pd_fileset_variant_ct(const pd_fileset* fs);   /* total over the files */
+uint32_t pd_fileset_sample_ct(const pd_fileset* fs);
+int pd_fileset_offsets(const pd_fileset* fs, uint32_t* out /* file_count + 1 */);
+pd_ctx* pd_fileset_ctx(pd_fileset* fs, uint32_t file);
+int pd_fileset_set_sample_subset(pd_fileset* fs, const uint64_t* sample_include, uint32_t subset_sample_ct);
+int pd_fileset_counts(pd_fileset* fs, uint32_t g_begin, uint32_t g_end, uint32_t* out_counts);
+int pd_fileset_hardy(pd_fileset* fs, uint32_t g_begin, uint32_t g_end, uint32_t midp, uint32_t* out_counts, double* out_p);
+int pd_fileset_decode_i8(pd_fileset* fs, uint32_t g_begin, uint32_t g_end, int8_t* out);
+int pd_fileset_missing_by_sample(pd_fileset* fs, uint32_t g_begin, uint32_t g_end, uint32_t* out_missing);
+int pd_fileset_sample_counts(pd_fileset* fs, uint32_t g_begin, uint32_t g_end, uint32_t* out_het, uint32_t* out_hom_alt,
+                             uint32_t* out_missing);
+int pd_fileset_score(pd_fileset* fs, const uint32_t* g_vidx, const uint8_t* flip, const double* weights, uint32_t n_var,
+                     uint32_t K, uint32_t mode, double* score_sums, double* dosage_sums, uint32_t* allele_cts);
+
 #ifdef __cplusplus
 }
 #endif

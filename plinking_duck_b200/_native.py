@@ -104,6 +104,21 @@ SYMBOLS = {
     "pd_ld_pairs": (C.c_int, [_vp, _vp, _vp, _u32, _vp]),
     "pd_standardized_f64": (C.c_int, [_vp, _vp, _u32, _vp, _vp]),
     "pd_device_result": (C.c_int, [_vp, _u32, C.POINTER(_vp), C.POINTER(_u64)]),
+    "pd_fileset_open": (C.c_int, [C.POINTER(C.c_char_p), _u32, C.POINTER(OpenOpts), C.POINTER(_vp), C.c_char_p, C.c_size_t]),
+    "pd_fileset_close": (None, [_vp]),
+    "pd_fileset_last_error": (C.c_char_p, [_vp]),
+    "pd_fileset_file_count": (_u32, [_vp]),
+    "pd_fileset_variant_ct": (_u32, [_vp]),
+    "pd_fileset_sample_ct": (_u32, [_vp]),
+    "pd_fileset_offsets": (C.c_int, [_vp, _vp]),
+    "pd_fileset_ctx": (_vp, [_vp, _u32]),
+    "pd_fileset_set_sample_subset": (C.c_int, [_vp, _vp, _u32]),
+    "pd_fileset_counts": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "pd_fileset_hardy": (C.c_int, [_vp, _u32, _u32, _u32, _vp, _vp]),
+    "pd_fileset_decode_i8": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "pd_fileset_missing_by_sample": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "pd_fileset_sample_counts": (C.c_int, [_vp, _u32, _u32, _vp, _vp, _vp]),
+    "pd_fileset_score": (C.c_int, [_vp, _vp, _vp, _vp, _u32, _u32, _u32, _vp, _vp, _vp]),
     "pd_get_stats": (C.c_int, [_vp, C.POINTER(Stats)]),
     "pd_reset_stats": (C.c_int, [_vp]),
     "pd_version": (C.c_char_p, []),

@@ -299,6 +299,16 @@ __device__ __forceinline__ bool parse_difflist(const uint8_t*& p, const uint8_t*
   return true;
 }
 
+// 4 bytes at any alignment (the two aligned words that cover them; up to 7 bytes past the window are touched, every
+// record buffer carries >= 16 B of slack).
+__device__ __forceinline__ uint32_t ldu32(const uint8_t* p) {
+  const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~static_cast<uintptr_t>(3));
+  const uint32_t sh = static_cast<uint32_t>(a & 3) << 3;
+  const uint32_t lo = __ldg(w);
+  return sh ? __funnelshift_r(lo, __ldg(w + 1), sh) : lo;
+}
+
 // Warp-cooperative walk: lane g of each batch of 32 groups decodes group g serially and calls
 // f(sample_id, geno2bit, entry_ordinal) for every entry.  Group start offsets come from a warp prefix sum of
 // the stored group byte lengths, which is what makes the varint stream parallel at group
@@ -331,24 +341,74 @@ __device__ __forceinline__ bool difflist_walk_lanes(const Difflist& d, uint32_t 
         if (g + 1 < d.ngroups && start + sz <= avail) gend = ptr + sz;
         uint32_t id = load_le(d.first_ids + static_cast<uint64_t>(g) * d.idbytes, d.idbytes);
         const uint32_t cnt = min(64u, d.len - (g << 6));
-        uint32_t gb = 0;
+        // Buffered reader: up to 8 bytes of the group's deltas sit in a register and are refilled a word at a time,
+        // the following word already requested -- with a byte load per varint byte the dependent load latency was
+        // the largest stall of the sparse per-sample kernel (profiles/r02p_ncu_k_densify_sparse.txt: 29 % of samples
+        // on the instruction behind that load).
+        uint64_t buf = 0;
+        uint32_t have = 0, consumed = 0;
+        uint32_t remaining = static_cast<uint32_t>(gend - ptr);  // bytes of the group not yet in buf
+        const uint8_t* rp = ptr;
+        uint32_t nextw = remaining ? ldu32(rp) : 0u;
+        // the group's 2-bit codes (16 bytes for a full group), requested up front as well
+        uint32_t rg0 = 0, rg1 = 0, rg2 = 0, rg3 = 0;
+        if (d.raregeno) {
+          const uint8_t* rgp = d.raregeno + (g << 4);
+          const uint32_t nbytes = (cnt + 3u) >> 2;
+          rg0 = ldu32(rgp);
+          if (nbytes > 4u) rg1 = ldu32(rgp + 4);
+          if (nbytes > 8u) rg2 = ldu32(rgp + 8);
+          if (nbytes > 12u) rg3 = ldu32(rgp + 12);
+        }
 #pragma unroll 1
         for (uint32_t k = 0; k < cnt; ++k) {
           if (id >= N) {
             ok = false;
             break;
           }
-          if (d.raregeno && !(k & 3)) gb = d.raregeno[(g << 4) + (k >> 2)];
-          f(id, (gb >> (2 * (k & 3))) & 3u, (g << 6) + k);
+          const uint32_t wsel = k >> 4;
+          const uint32_t rw = wsel == 0 ? rg0 : (wsel == 1 ? rg1 : (wsel == 2 ? rg2 : rg3));
+          f(id, (rw >> (2 * (k & 15))) & 3u, (g << 6) + k);
           if (k + 1 < cnt) {
-            uint32_t delta;
-            if (!get_vint31(ptr, gend, delta)) {
+            while (have < 5u && remaining) {  // a whole varint (<= 5 bytes) or the rest of the stream
+              const uint32_t take = min(4u, remaining);
+              const uint32_t w = take < 4u ? (nextw & ((1u << (8u * take)) - 1u)) : nextw;
+              buf |= static_cast<uint64_t>(w) << (8u * have);
+              have += take;
+              rp += take;
+              remaining -= take;
+              nextw = remaining ? ldu32(rp) : 0u;
+            }
+            const uint32_t lo = static_cast<uint32_t>(buf);
+            uint32_t delta = lo & 127u, used = 1;
+            if (lo & 128u) {  // GetVint31: up to 5 bytes, the fifth may carry 3 value bits
+              bool done = false;
+#pragma unroll
+              for (uint32_t i = 1; i < 5; ++i) {
+                if (!done) {
+                  const uint32_t b = static_cast<uint32_t>(buf >> (8u * i)) & 0xffu;
+                  if (i == 4 && (b & 0xf8u)) break;
+                  delta |= (b & 127u) << (7u * i);
+                  used = i + 1;
+                  done = !(b & 128u);
+                }
+              }
+              if (!done) {
+                ok = false;
+                break;
+              }
+            }
+            if (used > have) {  // the stream ended inside the varint
               ok = false;
               break;
             }
+            buf >>= 8u * used;
+            have -= used;
+            consumed += used;
             id += delta;
           }
         }
+        ptr += consumed;
         my_end = ptr;
       }
     }
