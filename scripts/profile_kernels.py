@@ -25,6 +25,9 @@ def main():
     ap.add_argument("--ops", default="counts,counts_subset,hardy,missing_by_sample,sample_counts,decode_i8,decode_i8_valid,decode_phased,score1,score16")
     ap.add_argument("--score-variants", type=int, default=20_000)
     ap.add_argument("--decode-variants", type=int, default=20_000)
+    ap.add_argument("--cpu-variants", type=int, default=0,
+                    help="also time the reference's CPU loops (oracle/_ref, all host threads) for counts / hardy / "
+                         "missingness / decode on the first this-many variants of the same data (tmpfs file)")
     args = ap.parse_args()
 
     import torch
@@ -124,6 +127,27 @@ def main():
             report(f"score_K{K}", lambda: ctx.score(vid, fl, Wt, 0), Vs * W, Vs * N,
                    {"flops": 2.0 * Vs * N * K, "note": "TFLOP/s = flops / kernel_ms"})
     ctx.close()
+    if args.cpu_variants:
+        # the reference's loops beside the kernels: pgenlib readers, one per host thread,
+        # 128-variant claims (oracle/ref_harness.cc: ref_bench_scan)
+        from oracle import ref
+
+        if ref.available():
+            Vc = min(V, args.cpu_variants)
+            d = "/dev/shm" if os.path.isdir("/dev/shm") else "/tmp"
+            path = os.path.join(d, f"plinkgpu_table_{Vc}x{N}.pgen")
+            host = img[: 12 + Vc * W].cpu().numpy().copy()
+            host[3:7] = np.frombuffer(np.uint32(Vc).tobytes(), dtype=np.uint8)  # variant count of the slice
+            host.tofile(path)
+            threads = os.cpu_count() or 1
+            try:
+                for kind, name in ((0, "counts"), (1, "hardy"), (3, "missing_by_sample"), (4, "decode_i8")):
+                    ref.bench_scan(path, threads, 0, min(Vc, 2048), kind)
+                    t = min(ref.bench_scan(path, threads, 0, Vc, kind)[0] for _ in range(3))
+                    print(json.dumps({"op": name, "cpu_reference": "pgenlib, %d threads, %d variants on tmpfs" % (threads, Vc),
+                                      "s": t, "Tcalls_per_s": Vc * N / t / 1e12}), flush=True)
+            finally:
+                os.unlink(path)
 
 
 if __name__ == "__main__":
