@@ -536,7 +536,7 @@ int RunRows(pd_ctx_impl* c, uint32_t v_begin, uint32_t v_end, uint32_t max_rows,
         b.rows.base = ix.data + (ix.fixed_start + static_cast<uint64_t>(v) * ix.fixed_width - ix.data_fpos);
         b.rows.stride = ix.fixed_width;
       } else {
-        pdk::LdScratch bases;
+        pdk::LdScratch bases{};
         const int pr = PrepareBases(c, ix, v, v + b.n, s, &bases);
         if (pr != PD_OK) return pr;
         pdk::launch_densify(ix, nullptr, v, b.n, c->d_dense.as<uint8_t>(), slot_stride,
@@ -598,7 +598,7 @@ int RunRowsList(pd_ctx_impl* c, const uint32_t* vlist, uint32_t n, uint32_t max_
         b.rows.nrows = b.n;
         b.rows.N = ix.N;
         // lists: pre-decode the bases only when the list is dense in its range (else most would not be used)
-        pdk::LdScratch bases;
+        pdk::LdScratch bases{};
         const uint32_t span = vlist[j + b.n - 1] + 1 - vlist[j];
         if (span <= 4 * b.n) {
           const int pr = PrepareBases(c, ix, vlist[j], vlist[j + b.n - 1] + 1, s, &bases);

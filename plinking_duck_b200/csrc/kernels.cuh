@@ -34,10 +34,10 @@ struct SubsetDev {
 
 // Scratch for dense copies of non-type-0 LD bases.
 struct LdScratch {
-  uint8_t* dense;          // slot s at dense + (s - slot_lo) * stride
-  uint32_t stride;         // bytes per slot, multiple of 16
-  uint32_t slot_lo;
-  uint32_t slot_ct;        // slots decoded (k_densify checks it; 0 = no scratch)
+  uint8_t* dense = nullptr;  // slot s at dense + (s - slot_lo) * stride
+  uint32_t stride = 0;       // bytes per slot, multiple of 16
+  uint32_t slot_lo = 0;
+  uint32_t slot_ct = 0;           // slots decoded (k_densify checks it; 0 = no scratch)
 };
 
 // Per-context launch state: every launch wrapper receives the owning context's copy, so one process can

@@ -66,3 +66,13 @@ def refmod(built):
     if not ref.available():
         pytest.skip("oracle/_ref/libpgenref.so not available")
     return ref
+
+
+def need_devices(kw):
+    """Skips a GPU test whose context options ask for more devices than the box has (devices=[0, 1] on one GPU)."""
+    devs = (kw or {}).get("devices")
+    if devs:
+        import torch
+
+        if torch.cuda.device_count() <= max(devs):
+            pytest.skip(f"needs {max(devs) + 1} GPUs")

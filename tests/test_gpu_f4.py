@@ -18,8 +18,11 @@ def refmod_gpu():
     return ref
 
 
-@pytest.mark.parametrize("kw", [dict(), dict(tile_bytes=2048, n_staging=2), dict(devices=[0])])
+@pytest.mark.parametrize("kw", [dict(), dict(tile_bytes=2048, n_staging=2), dict(devices=[0]), dict(devices=[0, 1])])
 def test_multiallelic_records_read_as_pgenlib_reads_them(tmp_path, refmod_gpu, kw):
+    from conftest import need_devices
+
+    need_devices(kw)
     from plinking_duck_b200 import _native as nat
     from plinking_duck_b200.pgen import PgenContext
 
@@ -66,13 +69,16 @@ def _aux1_modes(path, vrtypes, fpos, N):
     return out
 
 
-@pytest.mark.parametrize("kw", [dict(), dict(tile_bytes=4096, n_staging=2), dict(devices=[0])])
+@pytest.mark.parametrize("kw", [dict(), dict(tile_bytes=4096, n_staging=2), dict(devices=[0]), dict(devices=[0, 1])])
 @pytest.mark.parametrize("N", [37, 1501, 20011])
 def test_decode_alleles_matches_pgrgetm(tmp_path, refmod_gpu, kw, N):
     """pd_decode_alleles = PgrGetM + PglMultiallelicSparseToDenseMiss (pgenlib_read.cc:6668-6681,
     pgenlib_misc.cc:3552-3578): allele counts 2..40 (every aux1a / aux1b value width), patch sets stored as bit arrays
     and as sample-id lists, every main-track type the writer picks, streamed / tiny tiles / resident / a group context,
     sub-ranges and a sample subset."""
+    from conftest import need_devices
+
+    need_devices(kw)
     from plinking_duck_b200 import _native as nat
     from plinking_duck_b200.pgen import PgenContext
 
@@ -114,13 +120,16 @@ def test_decode_alleles_matches_pgrgetm(tmp_path, refmod_gpu, kw, N):
             c.set_allele_counts(allele_cts[:-1])
 
 
-@pytest.mark.parametrize("kw", [dict(), dict(tile_bytes=4096, n_staging=2), dict(devices=[0])])
+@pytest.mark.parametrize("kw", [dict(), dict(tile_bytes=4096, n_staging=2), dict(devices=[0]), dict(devices=[0, 1])])
 @pytest.mark.parametrize("N", [37, 1501, 20011])
 def test_phased_decode_of_multiallelic_records(tmp_path, refmod_gpu, kw, N):
     """Records with BOTH a multiallelic patch track and a hardcall-phase track: aux2 sits behind aux1 and counts the
     ALTx/ALTy (x != y) calls of aux1b among its hets (ReadGenovecHphaseSubsetUnsafe, pgenlib_read.cc:6874-6962).
     pd_decode_phased must return what PgrGetP + UnpackPhasedGenotypes return once pgenlib knows the allele counts --
     and, like pgenlib, cannot read such records without them."""
+    from conftest import need_devices
+
+    need_devices(kw)
     from plinking_duck_b200 import _native as nat
     from plinking_duck_b200.pgen import PgenContext
 

@@ -29,8 +29,11 @@ def _p(a):
     return a.ctypes.data_as(C.c_void_p)
 
 
-@pytest.mark.parametrize("kw", [dict(), dict(tile_bytes=1 << 16, n_staging=2), dict(devices=[0])])
+@pytest.mark.parametrize("kw", [dict(), dict(tile_bytes=1 << 16, n_staging=2), dict(devices=[0]), dict(devices=[0, 1])])
 def test_fileset_equals_the_unsplit_file(tmp_path, kw):
+    from conftest import need_devices
+
+    need_devices(kw)
     from plinking_duck_b200.pgen import PgenContext
 
     V, N, K = 5000, 4099, 3
