@@ -50,6 +50,37 @@ def test_no_cpu_fallback(built):
     assert "no CPU fallback" in str(e.value)
 
 
+def test_fileset_and_noalloc_entry_points_fail_loudly_without_a_gpu(built):
+    """The layers added on top of pd_open keep its contract: no device, no result -- and argument errors that need
+    no device are still reported as such."""
+    import ctypes as C
+    import os
+
+    import torch
+
+    from plinking_duck_b200 import _native as nat
+
+    lib = nat.load()
+    err = C.create_string_buffer(256)
+    # sizes beyond the static scratch are rejected before any device is touched
+    limit = lib.pd_hwe_noalloc_max_variants()
+    assert limit == 1 << 20
+    rc = lib.pd_hwe_from_counts_noalloc(None, limit + 1, 0, 0, None, None, err, len(err))
+    assert rc == nat.PD_ERR_INVALID_ARG and b"PD_NOALLOC_HWE_MAX_VARIANTS" in err.value
+    assert lib.pd_hwe_from_counts_noalloc(None, 0, 0, 0, None, None, None, 0) == nat.PD_OK
+    if torch.cuda.is_available():
+        return
+    path = os.fsencode(fixture_path("pgen_example"))
+    arr = (C.c_char_p * 2)(path, path)
+    fs = C.c_void_p()
+    rc = lib.pd_fileset_open(arr, 2, None, C.byref(fs), err, len(err))
+    assert rc == nat.PD_ERR_CUDA and not fs and b"no CPU fallback" in err.value
+    host = (C.c_uint32 * 16)()
+    out = (C.c_double * 4)()
+    rc = lib.pd_hwe_from_counts_noalloc(host, 4, 0, 0, out, None, err, len(err))
+    assert rc != nat.PD_OK and err.value
+
+
 @pytest.mark.parametrize("name", fixture_names())
 def test_probe_index_matches_pgenlib(name, golden, built, fixture_meta):
     from plinking_duck_b200.pgen import probe
