@@ -301,15 +301,10 @@ __device__ __forceinline__ bool parse_difflist(const uint8_t*& p, const uint8_t*
 
 // 4 bytes at any alignment (the two aligned words that cover them; up to 7 bytes past the window are touched, every
 // record buffer carries >= 16 B of slack).
-template <bool PLAIN = false>  // PLAIN: ordinary loads (the bytes may sit in shared memory; __ldg is for global memory only)
 __device__ __forceinline__ uint32_t ldu32(const uint8_t* p) {
   const uintptr_t a = reinterpret_cast<uintptr_t>(p);
   const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~static_cast<uintptr_t>(3));
   const uint32_t sh = static_cast<uint32_t>(a & 3) << 3;
-  if (PLAIN) {
-    const uint32_t lo = w[0];
-    return sh ? __funnelshift_r(lo, w[1], sh) : lo;
-  }
   const uint32_t lo = __ldg(w);
   return sh ? __funnelshift_r(lo, __ldg(w + 1), sh) : lo;
 }
@@ -318,8 +313,7 @@ __device__ __forceinline__ uint32_t ldu32(const uint8_t* p) {
 // f(sample_id, geno2bit, entry_ordinal) for every entry.  Group start offsets come from a warp prefix sum of
 // the stored group byte lengths, which is what makes the varint stream parallel at group
 // granularity.  Returns false (on all lanes) if any lane saw malformed input.
-// SMEM: the record was copied to shared memory first (sparse per-sample path): plain loads, ~30-cycle latency.
-template <class F, bool SMEM = false>
+template <class F>
 __device__ __forceinline__ bool difflist_walk_lanes(const Difflist& d, uint32_t N, int lane, F f,
                                                     const uint8_t** track_end = nullptr) {
   bool ok = true;
@@ -355,16 +349,16 @@ __device__ __forceinline__ bool difflist_walk_lanes(const Difflist& d, uint32_t 
         uint32_t have = 0, consumed = 0;
         uint32_t remaining = static_cast<uint32_t>(gend - ptr);  // bytes of the group not yet in buf
         const uint8_t* rp = ptr;
-        uint32_t nextw = remaining ? ldu32<SMEM>(rp) : 0u;
+        uint32_t nextw = remaining ? ldu32(rp) : 0u;
         // the group's 2-bit codes (16 bytes for a full group), requested up front as well
         uint32_t rg0 = 0, rg1 = 0, rg2 = 0, rg3 = 0;
         if (d.raregeno) {
           const uint8_t* rgp = d.raregeno + (g << 4);
           const uint32_t nbytes = (cnt + 3u) >> 2;
-          rg0 = ldu32<SMEM>(rgp);
-          if (nbytes > 4u) rg1 = ldu32<SMEM>(rgp + 4);
-          if (nbytes > 8u) rg2 = ldu32<SMEM>(rgp + 8);
-          if (nbytes > 12u) rg3 = ldu32<SMEM>(rgp + 12);
+          rg0 = ldu32(rgp);
+          if (nbytes > 4u) rg1 = ldu32(rgp + 4);
+          if (nbytes > 8u) rg2 = ldu32(rgp + 8);
+          if (nbytes > 12u) rg3 = ldu32(rgp + 12);
         }
 #pragma unroll 1
         for (uint32_t k = 0; k < cnt; ++k) {
@@ -383,7 +377,7 @@ __device__ __forceinline__ bool difflist_walk_lanes(const Difflist& d, uint32_t 
               have += take;
               rp += take;
               remaining -= take;
-              nextw = remaining ? ldu32<SMEM>(rp) : 0u;
+              nextw = remaining ? ldu32(rp) : 0u;
             }
             const uint32_t lo = static_cast<uint32_t>(buf);
             uint32_t delta = lo & 127u, used = 1;

@@ -31,10 +31,8 @@ __device__ __forceinline__ const uint8_t* row_ptr(const DenseRows& rows, uint32_
 // without expanding it: every listed sample gets planes(entry) - planes(common), the common planes
 // go to base[] once.  Unsigned wrap-around makes the negative deltas exact: the final per-sample
 // value base + acc is a true count >= 0.
-constexpr uint32_t kSparseCap = 4096;  // record bytes staged in shared memory per warp (a 100k-sample difflist record: ~2.5 KB)
-
 __device__ __forceinline__ bool sparse_accumulate(uint32_t common, bool all_common, const uint8_t* p, const uint8_t* end,
-                                                  uint32_t N, int lane, const SparseAcc& sa, uint8_t* stage) {
+                                                  uint32_t N, int lane, const SparseAcc& sa) {
   const uint32_t ce = common & 1u, co = common >> 1, cb = ce & co;
   if (lane == 0) {
     if ((sa.kinds & 1u) && ce) atomicAdd(sa.base + 0, 1u);
@@ -42,40 +40,21 @@ __device__ __forceinline__ bool sparse_accumulate(uint32_t common, bool all_comm
     if ((sa.kinds & 4u) && cb) atomicAdd(sa.base + 2, 1u);
   }
   if (all_common) return true;
-  const uint32_t kinds = sa.kinds;
-  auto add = [&](uint32_t id, uint32_t g, uint32_t) {
-    const uint32_t ge = g & 1u, go = g >> 1, gb = ge & go;
-    if ((kinds & 1u) && ge != ce) atomicAdd(sa.acc_e + id, ge - ce);
-    if ((kinds & 2u) && go != co) atomicAdd(sa.acc_o + id, go - co);
-    if ((kinds & 4u) && gb != cb) atomicAdd(sa.acc_b + id, gb - cb);
-  };
-  // The record is copied to shared memory with a few coalesced 16-byte loads per lane and walked there: the walk is a
-  // serial chain per lane (64 entries), and with the bytes in global memory every refill of that chain waited for
-  // L2 (profiles/r02p_ncu_k_densify_sparse.txt: half of all stall samples were long-scoreboard waits on those loads).
-  const uintptr_t a0 = reinterpret_cast<uintptr_t>(p) & ~static_cast<uintptr_t>(15);
-  const uint32_t lead = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(p) - a0);
-  const uint32_t len = static_cast<uint32_t>(end - p);
-  if (stage && lead + len <= kSparseCap) {
-    const uint32_t n16 = (lead + len + 15u) >> 4;
-    const uint4* src = reinterpret_cast<const uint4*>(a0);
-    uint4* dst = reinterpret_cast<uint4*>(stage);
-    for (uint32_t i = lane; i < n16; i += 32) dst[i] = ldg_stream(src + i);
-    __syncwarp();
-    const uint8_t* q = stage + lead;
-    const uint8_t* qend = q + len;
-    Difflist d;
-    bool ok = parse_difflist(q, qend, N, true, d);
-    if (ok && d.len) ok = difflist_walk_lanes<decltype(add), true>(d, N, lane, add);
-    __syncwarp();  // the buffer is reused for the warp's next record
-    return ok;
-  }
-  // lane-per-group walk on purpose (measured 60 % faster here than the warp-per-group walker: this path issues one L2
-  // reduction per listed sample and plane, profiles/r02n_compressed_walk_ab.txt)
   const uint8_t* q = p;
   Difflist d;
   if (!parse_difflist(q, end, N, true, d)) return false;
   if (!d.len) return true;
-  return difflist_walk_lanes(d, N, lane, add);
+  const uint32_t kinds = sa.kinds;
+  // Lane-per-group walk on purpose: every alternative measured this round was slower or equal here -- the
+  // warp-per-group walker (+28 % time), a buffered stream reader (-2 %), the record staged in shared memory (+3 %),
+  // per-CTA shared-memory counters for the missing plane (+15 %) -- while more resident warps helped (-10 %):
+  // profiles/r02n_compressed_walk_ab.txt has the numbers and what they rule out.
+  return difflist_walk_lanes(d, N, lane, [&](uint32_t id, uint32_t g, uint32_t) {
+    const uint32_t ge = g & 1u, go = g >> 1, gb = ge & go;
+    if ((kinds & 1u) && ge != ce) atomicAdd(sa.acc_e + id, ge - ce);
+    if ((kinds & 2u) && go != co) atomicAdd(sa.acc_o + id, go - co);
+    if ((kinds & 4u) && gb != cb) atomicAdd(sa.acc_b + id, gb - cb);
+  });
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -92,7 +71,6 @@ __global__ void __launch_bounds__(kThreads, 4)
 k_densify(RecIndex ix, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t nrows, uint8_t* __restrict__ scratch,
           uint32_t slot_stride, const uint8_t** __restrict__ ptrs, uint32_t* __restrict__ work_counter,
           int* __restrict__ err, SparseAcc sa, LdScratch bases) {
-  __shared__ __align__(16) uint8_t s_stage[SPARSE ? kThreads / 32 : 1][SPARSE ? kSparseCap + 32 : 16];
   const int lane = threadIdx.x & 31;
   const uint32_t N = ix.N;
   const bool sparse = SPARSE && sa.dense_count != nullptr;
@@ -110,7 +88,7 @@ k_densify(RecIndex ix, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t
     const uint8_t* p = ix.data + (ix.fpos[v] - ix.data_fpos);
     const uint8_t* end = ix.data + (ix.fpos[v + 1] - ix.data_fpos);
     if (SPARSE && sparse && main >= 4) {
-      const bool ok = sparse_accumulate(main == 5 ? 0u : (main & 3u), main == 5, p, end, N, lane, sa, s_stage[threadIdx.x >> 5]);
+      const bool ok = sparse_accumulate(main == 5 ? 0u : (main & 3u), main == 5, p, end, N, lane, sa);
       if (!ok && lane == 0) report_error(err, kErrMalformed, v);
       continue;
     }

@@ -23,11 +23,12 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
-def make_file(path, V, N, seed, device):
-    """The C4 fileset of tests/c4.py: rare-variant MAF model + LD blocks + ALT-major + one-bit rows."""
+def make_file(path, V, N, seed, device, plain=False):
+    """The C4 fileset of tests/c4.py: rare-variant MAF model + LD blocks + ALT-major + one-bit rows (plain: the MAF
+    model alone = the round-1 rare-variant fileset)."""
     import c4
 
-    c4.make_c4_file(path, V, N, seed, device)
+    c4.make_c4_file(path, V, N, seed, device, plain=plain)
 
 
 def main():
@@ -35,6 +36,7 @@ def main():
     ap.add_argument("--variants", type=int, default=30_000)
     ap.add_argument("--samples", type=int, default=100_000)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--plain", action="store_true", help="rare-variant MAF model only (vrtypes 0 / 1 / 4), as in round 1")
     args = ap.parse_args()
 
     import torch
@@ -49,7 +51,7 @@ def main():
     d = "/dev/shm" if os.path.isdir("/dev/shm") else "/tmp"
     path = os.path.join(d, f"plinkgpu_rare_{V}x{N}.pgen")
     t0 = time.time()
-    make_file(path, V, N, 777, dev)
+    make_file(path, V, N, 777, dev, plain=args.plain)
     size = os.path.getsize(path)
     threads = os.cpu_count() or 1
     try:

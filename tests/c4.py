@@ -9,8 +9,9 @@ from __future__ import annotations
 import numpy as np
 
 
-def make_c4_file(path: str, V: int, N: int, seed: int, device) -> np.ndarray:
-    """Writes the file; returns the genovec words (V, ceil(N/32)) uint64 that went in."""
+def make_c4_file(path: str, V: int, N: int, seed: int, device, plain: bool = False) -> np.ndarray:
+    """Writes the file; returns the genovec words (V, ceil(N/32)) uint64 that went in.  plain = True: the MAF model
+    alone (no LD runs, ALT-major or two-category rows): the round-1 rare-variant fileset, vrtypes 0 / 1 / 4."""
     import torch
 
     from oracle import ref
@@ -35,14 +36,14 @@ def make_c4_file(path: str, V: int, N: int, seed: int, device) -> np.ndarray:
         r = torch.arange(vt, device=device)
         # common variants in LD blocks: rows 16k+1 .. 16k+4 copy their predecessor with ~N/1500 calls changed;
         # row 16k+4 additionally swaps the alleles (0 <-> 2), which pgenlib stores as an inverted LD record (type 3)
-        base = r[(r % 16 == 0)]
+        base = r[(r % 16 == 0)] if not plain else r[:0]
         if base.numel():
             pb = 0.2 + 0.3 * torch.rand((base.numel(), 1), device=device, generator=gen)
             xb = torch.rand((base.numel(), W64 * 32), device=device, generator=gen)
             cb = (xb < pb * pb).to(torch.int64) * 2 + ((xb >= pb * pb) & (xb < pb * pb + 2 * pb * (1 - pb))).to(torch.int64)
             code[base] = torch.where(miss[base], torch.full_like(cb, 3), cb)
         for k in (1, 2, 3, 4):
-            idx = r[(r % 16 == k)]
+            idx = r[(r % 16 == k)] if not plain else r[:0]
             if not idx.numel():
                 continue
             prev = code[idx - 1]
@@ -52,12 +53,12 @@ def make_c4_file(path: str, V: int, N: int, seed: int, device) -> np.ndarray:
             newv = torch.randint(0, 4, prev.shape, device=device, generator=gen)
             code[idx] = torch.where(flip, newv, prev)
         # ALT-major rare variants (difflist against all hom-alt, type 6)
-        idx = r[(r % 16 == 9)]
+        idx = r[(r % 16 == 9)] if not plain else r[:0]
         if idx.numel():
             c9 = code[idx]
             code[idx] = torch.where(c9 == 3, c9, 2 - c9)
         # two dominant categories (one-bit records, type 1)
-        idx = r[(r % 16 == 12)]
+        idx = r[(r % 16 == 12)] if not plain else r[:0]
         if idx.numel():
             two = (torch.rand((idx.numel(), W64 * 32), device=device, generator=gen) < 0.4).to(torch.int64)
             code[idx] = torch.where(miss[idx], torch.full_like(two, 3), two)
