@@ -133,6 +133,94 @@ k_densify(RecIndex ix, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t
 }
 
 // ---------------------------------------------------------------------------------------------
+// k_densify_team: one CTA (8 warps) per row, the row built in SHARED memory and written out once.
+// k_densify patches a row in global memory with one atomicXor per difflist entry (~1.4 k per 100k-sample rare-variant
+// record: the atomics, not the walk, set its pace -- profiles/r02n_compressed_walk_ab.txt).  Here the warps of a CTA
+// fill the row in shared memory (common value / expanded bit array / the LD base copied from the batch's base
+// scratch), split the difflist by groups (difflist_walk_swar with team_rank / team_size) and patch with shared-memory
+// atomics; the finished row leaves with coalesced 128-bit stores.  Used for dense decode (no SparseAcc) when a row
+// fits the default dynamic shared memory.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t kTeamMaxSmem = 48u << 10;
+
+__global__ void __launch_bounds__(kThreads)
+k_densify_team(RecIndex ix, const uint32_t* __restrict__ vlist, uint32_t v0, uint32_t nrows, uint8_t* __restrict__ scratch,
+               uint32_t slot_stride, const uint8_t** __restrict__ ptrs, int* __restrict__ err, LdScratch bases) {
+  extern __shared__ __align__(16) uint32_t s_row[];
+  const int lane = threadIdx.x & 31;
+  const uint32_t wid = threadIdx.x >> 5;
+  constexpr uint32_t kTeam = kThreads / 32;
+  const uint32_t N = ix.N;
+  const uint32_t nwords = (N + 15) >> 4;
+  const uint32_t n16 = (((N + 3) >> 2) + 15) >> 4;  // 16-byte chunks of a row
+  const uint32_t r = blockIdx.x;
+  if (r >= nrows) return;
+  const uint32_t v = vlist ? vlist[r] : v0 + r;
+  const uint32_t main = ix.vrtypes[v] & 7u;
+  const uint8_t* p = ix.data + (ix.fpos[v] - ix.data_fpos);
+  const uint8_t* end = ix.data + (ix.fpos[v + 1] - ix.data_fpos);
+  if (main == 0) {  // used in place
+    if (threadIdx.x == 0) {
+      if (static_cast<uint64_t>(end - p) < ((N + 3) >> 2)) report_error(err, kErrMalformed, v);
+      ptrs[r] = p;
+    }
+    return;
+  }
+  for (uint32_t w = nwords + threadIdx.x; w < n16 * 4; w += kThreads) s_row[w] = 0u;  // the padding of the last chunk
+  bool ok = true;
+  if (main == 2 || main == 3) {
+    const uint32_t b = ix.ldbase[v];
+    const uint32_t bmain = ix.vrtypes[b] & 7u;
+    ok = (b < v) && bmain != 2 && bmain != 3;  // uniform for the CTA
+    if (ok) {
+      const uint32_t bs = bases.slot_ct ? ix.base_slot[v] - bases.slot_lo : 0xffffffffu;
+      if (bs < bases.slot_ct) {
+        const uint4* src = reinterpret_cast<const uint4*>(bases.dense + static_cast<uint64_t>(bs) * bases.stride);
+        uint4* dst4 = reinterpret_cast<uint4*>(s_row);
+        for (uint32_t i = threadIdx.x; i < n16; i += kThreads) dst4[i] = __ldcs(src + i);
+        __syncthreads();
+      } else {
+        const uint8_t* bp = ix.data + (ix.fpos[b] - ix.data_fpos);
+        const uint8_t* bend = ix.data + (ix.fpos[b + 1] - ix.data_fpos);
+        ok = decode_nonld_dense_team<true>(bmain, bp, bend, N, s_row, lane, wid, kTeam);
+        ok = __syncthreads_and(ok) != 0;  // a warp's walk may fail alone: every barrier below needs a uniform branch
+      }
+    }
+    if (ok) {
+      const uint8_t* q = p;
+      Difflist d;
+      ok = parse_difflist(q, end, N, true, d);
+      if (ok && d.len) {
+        ok = difflist_walk_swar(d, N, lane, [&](uint32_t id, uint32_t g, uint32_t) {
+          const uint32_t old = (reinterpret_cast<volatile uint32_t*>(s_row)[id >> 4] >> (2 * (id & 15))) & 3u;
+          atomicXor(&s_row[id >> 4], (old ^ g) << (2 * (id & 15)));  // each sample id occurs once per difflist
+        }, nullptr, wid, kTeam);
+      }
+      ok = __syncthreads_and(ok) != 0;
+      if (ok && main == 3) {  // GenovecInvertUnsafe: 0 <-> 2
+        for (uint32_t w = threadIdx.x; w < nwords; w += kThreads) {
+          const uint32_t x = s_row[w];
+          s_row[w] = x ^ ((~x & 0x55555555u) << 1);
+        }
+      }
+    }
+  } else {
+    ok = decode_nonld_dense_team<true>(main, p, end, N, s_row, lane, wid, kTeam);
+  }
+  ok = __syncthreads_and(ok) != 0;
+  uint8_t* slot = scratch + static_cast<uint64_t>(r) * slot_stride;
+  if (ok) {
+    uint4* out4 = reinterpret_cast<uint4*>(slot);
+    const uint4* row4 = reinterpret_cast<const uint4*>(s_row);
+    for (uint32_t i = threadIdx.x; i < n16; i += kThreads) out4[i] = row4[i];
+  }
+  if (threadIdx.x == 0) {
+    if (!ok) report_error(err, kErrMalformed, v);
+    ptrs[r] = slot;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // k_expand_i8: blockIdx.y = row (no division), threads of a CTA stride over the row's 16-byte output
 // chunks (one 128-bit streaming store each; consecutive lanes = consecutive chunks).  The output is a
 // flat (nrows x n_out) byte matrix, so a row starts at any byte: its first chunk boundary is found
@@ -616,8 +704,13 @@ void launch_densify(const RecIndex& ix, const uint32_t* vlist, uint32_t v0, uint
     k_densify<true><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, vlist, v0, nrows, scratch, slot_stride, ptrs,
                                                                       work_counter, err, *sparse, bs);
   } else {
-    k_densify<false><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, vlist, v0, nrows, scratch, slot_stride,
-                                                                       ptrs, work_counter, err, SparseAcc{}, bs);
+    const uint32_t row_smem = (((ix.N + 3u) >> 2) + 15u) / 16u * 16u;
+    if (ix.fpos && ix.N >= 200u && row_smem <= kTeamMaxSmem && row_smem <= slot_stride) {
+      k_densify_team<<<nrows, kThreads, row_smem, s>>>(ix, vlist, v0, nrows, scratch, slot_stride, ptrs, err, bs);
+    } else {
+      k_densify<false><<<static_cast<unsigned>(blocks), kThreads, 0, s>>>(ix, vlist, v0, nrows, scratch, slot_stride,
+                                                                         ptrs, work_counter, err, SparseAcc{}, bs);
+    }
   }
   if (st) st->launches++;
 }
